@@ -1,0 +1,260 @@
+// Implicit-GEMM convolution (fprop and stride-1 dgrad) on the 5th-gen tensor cores, TF32 inputs / fp32 accumulate.
+//
+//   GEMM view:  D[M = N*Ho*Wo pixels, 128] = A[M, K = R*S*Cin] * B[K, 128]
+//   A is never materialised: one TMA *im2col* load per (filter tap, 32-channel chunk) gathers the 128 shifted
+//   pixel rows of the NHWC activation straight into a 128B-swizzled smem tile (zero fill at the borders).
+//   B (weights [Cout][kh][kw][Cin]) is a plain 2-D TMA tile: K-major for fprop, MN-major for dgrad, so the same
+//   weight memory serves both directions without a transpose pass.
+//   One elected thread issues tcgen05.mma (M128 N128 K8, kind::tf32) into a 128-column TMEM accumulator;
+//   4 epilogue warps read it back with tcgen05.ld and fuse bias / timestep-embedding / residual adds.
+//
+// CTA = 192 threads: warp 0 TMA producer, warp 1 TMEM owner + MMA issuer, warps 2-5 epilogue.
+// 3-stage smem ring (32 KB per stage) so two CTAs are co-resident per SM (one's epilogue overlaps the other's MMAs).
+#include "host_common.h"
+#include "ptx.cuh"
+
+#include "../../include/b200ddpm.h"
+
+namespace b200 {
+
+constexpr int kStages = 3;
+constexpr int kTileBytes = 16384;                 // 128 rows x 128 B
+constexpr int kStageBytes = 2 * kTileBytes;       // A + B
+constexpr int kConvSmem = kStages * kStageBytes + 1024 /*align slack*/ + 256 /*barriers*/;
+
+struct ConvK {
+  float* out;
+  const float* bias;
+  const float* emb;
+  const float* residual;
+  int M_total, HoWo, Wo;
+  int stride, pad_eff;
+  int R, S;
+  int chunks1, chunks;  // 32-channel chunks of source 1 / of both sources
+  int mode;
+  int w_rowlen_tap;     // columns per tap in the weight matrix (= Cin of the weight tensor)
+  int n_off;
+  int out_ld, emb_ld, res_ld;
+};
+
+__global__ void __launch_bounds__(192)
+conv_igemm_tf32_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmA2,
+                       const __grid_constant__ CUtensorMap tmB, const ConvK a) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint64_t* full = reinterpret_cast<uint64_t*>(smem + kStages * kStageBytes);
+  uint64_t* empty = full + kStages;
+  uint64_t* tmem_full = empty + kStages;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_full + 1);
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+
+  if (threadIdx.x == 0) {
+    tma_prefetch_desc(&tmA);
+    tma_prefetch_desc(&tmA2);
+    tma_prefetch_desc(&tmB);
+    for (int s = 0; s < kStages; ++s) {
+      mbar_init(&full[s], 1);
+      mbar_init(&empty[s], 1);
+    }
+    mbar_init(tmem_full, 1);
+    fence_mbar_init();
+  }
+  if (warp == 1) {
+    tmem_alloc(tmem_slot, 128);
+    tmem_relinquish();
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  const int m0 = blockIdx.x * 128;
+  const int num_it = a.R * a.S * a.chunks;
+
+  if (warp == 0) {
+    if (lane == 0) {
+      // ---------------- TMA producer
+      const int n = m0 / a.HoWo;
+      const int rem = m0 - n * a.HoWo;
+      const int p = rem / a.Wo;
+      const int q = rem - p * a.Wo;
+      const int w_base = q * a.stride - a.pad_eff;
+      const int h_base = p * a.stride - a.pad_eff;
+      int tap = 0, ch = 0;
+      for (int it = 0; it < num_it; ++it) {
+        const int s = it % kStages;
+        const uint32_t ph = (it / kStages) & 1;
+        mbar_wait(&empty[s], ph ^ 1);
+        mbar_expect_tx(&full[s], kStageBytes);
+        const int kh = tap / a.S, kw = tap - kh * a.S;
+        uint8_t* sA = smem + s * kStageBytes;
+        uint8_t* sB = sA + kTileBytes;
+        if (ch < a.chunks1)
+          tma_load_im2col_4d(sA, &tmA, &full[s], ch * 32, w_base, h_base, n, (uint16_t)kw, (uint16_t)kh);
+        else
+          tma_load_im2col_4d(sA, &tmA2, &full[s], (ch - a.chunks1) * 32, w_base, h_base, n, (uint16_t)kw,
+                             (uint16_t)kh);
+        if (a.mode == 0) {
+          tma_load_2d(sB, &tmB, &full[s], tap * a.w_rowlen_tap + ch * 32, 0);
+        } else {
+          const int wtap = (a.R - 1 - kh) * a.S + (a.S - 1 - kw);
+#pragma unroll
+          for (int j = 0; j < 4; ++j)
+            tma_load_2d(sB + j * 4096, &tmB, &full[s], wtap * a.w_rowlen_tap + a.n_off + j * 32, ch * 32);
+        }
+        if (++ch == a.chunks) {
+          ch = 0;
+          ++tap;
+        }
+      }
+    }
+  } else if (warp == 1) {
+    if (lane == 0) {
+      // ---------------- MMA issuer
+      const uint32_t idesc = make_idesc(2u, 128u, 128u, 0u, a.mode == 0 ? 0u : 1u);
+      for (int it = 0; it < num_it; ++it) {
+        const int s = it % kStages;
+        const uint32_t ph = (it / kStages) & 1;
+        mbar_wait(&full[s], ph);
+        tc_fence_after();
+        const uint32_t a_base = smem_u32(smem + s * kStageBytes);
+        const uint32_t b_base = a_base + kTileBytes;
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+          const uint64_t adesc = make_smem_desc_sw128(a_base + k * 32, 16, 1024);
+          const uint64_t bdesc = (a.mode == 0) ? make_smem_desc_sw128(b_base + k * 32, 16, 1024)
+                                               : make_smem_desc_sw128(b_base + k * 1024, 4096, 512, 1);
+          mma_tf32_ss(tmem_base, adesc, bdesc, idesc, (it | k) != 0 ? 1u : 0u);
+        }
+        tc_commit(&empty[s]);
+      }
+      tc_commit(tmem_full);
+    }
+  } else {
+    // ---------------- epilogue: TMEM -> registers -> (+bias +emb +residual) -> global
+    const int quarter = warp & 3;  // TMEM lane quarter this warp may read
+    const int row = quarter * 32 + lane;
+    const int m = m0 + row;
+    mbar_wait(tmem_full, 0);
+    tc_fence_after();
+    const bool valid = m < a.M_total;
+    const int n = valid ? m / a.HoWo : 0;
+    float* orow = a.out + static_cast<size_t>(m) * a.out_ld;
+    const float* rrow = a.residual ? a.residual + static_cast<size_t>(m) * a.res_ld : nullptr;
+    const float* erow = a.emb ? a.emb + static_cast<size_t>(n) * a.emb_ld : nullptr;
+#pragma unroll 1
+    for (int cc = 0; cc < 4; ++cc) {
+      uint32_t r[32];
+      tmem_ld_32x32(tmem_base + (static_cast<uint32_t>(quarter * 32) << 16) + cc * 32, r);
+      tmem_ld_wait();
+      if (valid) {
+#pragma unroll
+        for (int j = 0; j < 32; j += 4) {
+          float4 v = make_float4(__uint_as_float(r[j]), __uint_as_float(r[j + 1]), __uint_as_float(r[j + 2]),
+                                 __uint_as_float(r[j + 3]));
+          const int c = cc * 32 + j;
+          if (a.bias) {
+            const float4 b = *reinterpret_cast<const float4*>(a.bias + c);
+            v.x += b.x; v.y += b.y; v.z += b.z; v.w += b.w;
+          }
+          if (erow) {
+            const float4 e = *reinterpret_cast<const float4*>(erow + c);
+            v.x += e.x; v.y += e.y; v.z += e.z; v.w += e.w;
+          }
+          if (rrow) {
+            const float4 e = *reinterpret_cast<const float4*>(rrow + c);
+            v.x += e.x; v.y += e.y; v.z += e.z; v.w += e.w;
+          }
+          *reinterpret_cast<float4*>(orow + c) = v;
+        }
+      }
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    tc_fence_after();
+    tmem_dealloc(tmem_base, 128);
+  }
+}
+
+}  // namespace b200
+
+using namespace b200;
+
+extern "C" int b200_conv_igemm(const b200_conv_args* a, void* ws, size_t ws_bytes, void* stream) {
+  (void)ws;
+  (void)ws_bytes;
+  if (!a || !a->x || !a->w || !a->out) return fail_arg("conv_igemm: null pointer");
+  if (a->C1 <= 0 || a->C1 % 32 || a->C2 < 0 || a->C2 % 32) return fail_arg("conv_igemm: C1/C2 must be multiples of 32");
+  if (a->C2 > 0 && !a->x2) return fail_arg("conv_igemm: C2 > 0 needs x2");
+  if (a->R != a->S || (a->R != 1 && a->R != 3)) return fail_arg("conv_igemm: only 1x1 and 3x3 filters");
+  if (a->mode != 0 && a->mode != 1) return fail_arg("conv_igemm: mode must be 0 (fprop) or 1 (dgrad)");
+  if (a->out_ld % 4 || (a->residual && a->res_ld % 4) || (a->emb && a->emb_ld % 4))
+    return fail_arg("conv_igemm: leading dimensions must be multiples of 4 floats");
+  const int Cin = a->C1 + a->C2;
+  int lower, upper, pad_eff;
+  if (a->mode == 0) {
+    if (a->w_cout != 128 || a->w_cin != Cin) return fail_arg("conv_igemm fprop: weight must be [128][R*S*(C1+C2)]");
+    if (a->stride != 1 && a->stride != 2) return fail_arg("conv_igemm: stride must be 1 or 2");
+    pad_eff = a->pad;
+    lower = -a->pad;
+    upper = a->pad - (a->R - 1);
+    const int ho = (a->H + 2 * a->pad - a->R) / a->stride + 1, wo = (a->W + 2 * a->pad - a->S) / a->stride + 1;
+    if (ho != a->Ho || wo != a->Wo) return fail_arg("conv_igemm fprop: Ho/Wo do not match the geometry");
+  } else {
+    if (a->stride != 1) return fail_arg("conv_igemm dgrad: stride must be 1 (zero-stuff dY for strided layers)");
+    if (a->C2 != 0 || a->C1 != a->w_cout) return fail_arg("conv_igemm dgrad: x is dY with w_cout channels");
+    if (a->n_off < 0 || a->n_off + 128 > a->w_cin || a->n_off % 32) return fail_arg("conv_igemm dgrad: bad n_off");
+    if (a->Ho != a->H || a->Wo != a->W) return fail_arg("conv_igemm dgrad: output size must equal dY size");
+    if (a->bias || a->emb) return fail_arg("conv_igemm dgrad: bias/emb not applicable");
+    pad_eff = a->R - 1 - a->pad;
+    lower = -pad_eff;
+    upper = -a->pad;
+  }
+  CUtensorMap tmA, tmA2, tmB;
+  int r = get_tmap_im2col(a->x, a->N, a->H, a->W, a->C1, lower, upper, a->stride, 32, 128, 4, 0, &tmA);
+  if (r) return r;
+  if (a->C2 > 0) {
+    r = get_tmap_im2col(a->x2, a->N, a->H, a->W, a->C2, lower, upper, a->stride, 32, 128, 4, 0, &tmA2);
+    if (r) return r;
+  } else {
+    tmA2 = tmA;
+  }
+  const uint64_t wcols = static_cast<uint64_t>(a->R) * a->S * a->w_cin;
+  r = get_tmap_2d(a->w, a->w_cout, wcols, wcols, 32, a->mode == 0 ? 128 : 32, 4, a->mode == 0 ? 0 : 1, &tmB);
+  if (r) return r;
+
+  ConvK k;
+  k.out = a->out;
+  k.bias = a->bias;
+  k.emb = a->emb;
+  k.residual = a->residual;
+  k.M_total = a->N * a->Ho * a->Wo;
+  k.HoWo = a->Ho * a->Wo;
+  k.Wo = a->Wo;
+  k.stride = a->stride;
+  k.pad_eff = pad_eff;
+  k.R = a->R;
+  k.S = a->S;
+  k.chunks1 = a->C1 / 32;
+  k.chunks = Cin / 32;
+  k.mode = a->mode;
+  k.w_rowlen_tap = a->w_cin;
+  k.n_off = a->n_off;
+  k.out_ld = a->out_ld;
+  k.emb_ld = a->emb_ld;
+  k.res_ld = a->res_ld;
+
+  static bool attr_set = false;
+  if (!attr_set) {
+    cudaError_t e = cudaFuncSetAttribute(conv_igemm_tf32_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kConvSmem);
+    if (e != cudaSuccess) return check_cuda(e, "cudaFuncSetAttribute(conv_igemm)");
+    attr_set = true;
+  }
+  const int grid = (k.M_total + 127) / 128;
+  conv_igemm_tf32_kernel<<<grid, 192, kConvSmem, static_cast<cudaStream_t>(stream)>>>(tmA, tmA2, tmB, k);
+  return after_launch("conv_igemm_tf32_kernel");
+}

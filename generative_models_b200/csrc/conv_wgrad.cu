@@ -1,0 +1,205 @@
+// Convolution weight gradient on tcgen05, TF32 inputs / fp32 accumulate, split over the pixel reduction.
+//
+//   dW[co, tap, ci] = sum_pixels dY[pixel, co] * X[pixel shifted by tap, ci]
+//   GEMM view per (tap, 128-wide ci block):  D[128 co, 128 ci] = A^T[K = pixels, 128 co] * B[K = pixels, 128 ci]
+//   Both operands are "MN-major" (the reduction index — pixels — is the slow dimension of the NHWC rows), which
+//   tcgen05 takes directly from 128B-swizzled smem tiles: dY rows come from a 2-D TMA tile, shifted X rows from
+//   the same im2col TMA map the forward uses (border pixels arrive as zeros).
+//   grid = (pixel slices, taps * ci blocks); every CTA reduces its slice in TMEM and adds the 128x128 fp32 tile
+//   into dW with red.global.add.f32 (dW is zeroed once per step by the caller).
+#include "host_common.h"
+#include "ptx.cuh"
+
+#include "../../include/b200ddpm.h"
+
+namespace b200 {
+
+constexpr int kWgStages = 3;
+constexpr int kWgTileBytes = 16384;  // 4 boxes of (32 pixels x 128 B)
+constexpr int kWgStageBytes = 2 * kWgTileBytes;
+constexpr int kWgSmem = kWgStages * kWgStageBytes + 1024 + 256;
+constexpr int kWgPix = 32;  // pixels (reduction elements) per pipeline stage
+
+struct WgradK {
+  float* dw;
+  int M_total, HoWo, Wo;
+  int stride, pad;
+  int S;
+  int C1, Cin;
+  int steps_total, steps_per_slice;
+};
+
+__global__ void __launch_bounds__(192)
+conv_wgrad_tf32_kernel(const __grid_constant__ CUtensorMap tmDY, const __grid_constant__ CUtensorMap tmX,
+                       const __grid_constant__ CUtensorMap tmX2, const WgradK a) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint64_t* full = reinterpret_cast<uint64_t*>(smem + kWgStages * kWgStageBytes);
+  uint64_t* empty = full + kWgStages;
+  uint64_t* tmem_full = empty + kWgStages;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_full + 1);
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+
+  const int step_begin = blockIdx.x * a.steps_per_slice;
+  const int step_end = min(step_begin + a.steps_per_slice, a.steps_total);
+  const int num_it = step_end - step_begin;
+  if (num_it <= 0) return;  // uniform for the whole CTA
+
+  const int ci_blocks = a.Cin / 128;
+  const int tap = blockIdx.y / ci_blocks;
+  const int cib = blockIdx.y - tap * ci_blocks;
+  const int kh = tap / a.S, kw = tap - kh * a.S;
+
+  if (threadIdx.x == 0) {
+    tma_prefetch_desc(&tmDY);
+    tma_prefetch_desc(&tmX);
+    tma_prefetch_desc(&tmX2);
+    for (int s = 0; s < kWgStages; ++s) {
+      mbar_init(&full[s], 1);
+      mbar_init(&empty[s], 1);
+    }
+    mbar_init(tmem_full, 1);
+    fence_mbar_init();
+  }
+  if (warp == 1) {
+    tmem_alloc(tmem_slot, 128);
+    tmem_relinquish();
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp == 0) {
+    if (lane == 0) {
+      const int c_glob = cib * 128;
+      const CUtensorMap* xm = (c_glob < a.C1) ? &tmX : &tmX2;
+      const int c_src = (c_glob < a.C1) ? c_glob : c_glob - a.C1;
+      for (int it = 0; it < num_it; ++it) {
+        const int s = it % kWgStages;
+        const uint32_t ph = (it / kWgStages) & 1;
+        mbar_wait(&empty[s], ph ^ 1);
+        mbar_expect_tx(&full[s], kWgStageBytes);
+        const int pix0 = (step_begin + it) * kWgPix;
+        const int n = pix0 / a.HoWo;
+        const int rem = pix0 - n * a.HoWo;
+        const int p = rem / a.Wo;
+        const int q = rem - p * a.Wo;
+        uint8_t* sA = smem + s * kWgStageBytes;
+        uint8_t* sB = sA + kWgTileBytes;
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          tma_load_2d(sA + j * 4096, &tmDY, &full[s], j * 32, pix0);
+          tma_load_im2col_4d(sB + j * 4096, xm, &full[s], c_src + j * 32, q * a.stride - a.pad, p * a.stride - a.pad, n,
+                             (uint16_t)kw, (uint16_t)kh);
+        }
+      }
+    }
+  } else if (warp == 1) {
+    if (lane == 0) {
+      const uint32_t idesc = make_idesc(2u, 128u, 128u, 1u, 1u);
+      for (int it = 0; it < num_it; ++it) {
+        const int s = it % kWgStages;
+        const uint32_t ph = (it / kWgStages) & 1;
+        mbar_wait(&full[s], ph);
+        tc_fence_after();
+        const uint32_t a_base = smem_u32(smem + s * kWgStageBytes);
+        const uint32_t b_base = a_base + kWgTileBytes;
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+          const uint64_t adesc = make_smem_desc_sw128(a_base + k * 1024, 4096, 512, 1);
+          const uint64_t bdesc = make_smem_desc_sw128(b_base + k * 1024, 4096, 512, 1);
+          mma_tf32_ss(tmem_base, adesc, bdesc, idesc, (it | k) != 0 ? 1u : 0u);
+        }
+        tc_commit(&empty[s]);
+      }
+      tc_commit(tmem_full);
+    }
+  } else {
+    const int quarter = warp & 3;
+    const int co = quarter * 32 + lane;
+    mbar_wait(tmem_full, 0);
+    tc_fence_after();
+    const int row_len = a.S * a.S * a.Cin;
+    float* drow = a.dw + static_cast<size_t>(co) * row_len + tap * a.Cin + cib * 128;
+#pragma unroll 1
+    for (int cc = 0; cc < 4; ++cc) {
+      uint32_t r[32];
+      tmem_ld_32x32(tmem_base + (static_cast<uint32_t>(quarter * 32) << 16) + cc * 32, r);
+      tmem_ld_wait();
+#pragma unroll
+      for (int j = 0; j < 32; ++j) atomicAdd(drow + cc * 32 + j, __uint_as_float(r[j]));
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    tc_fence_after();
+    tmem_dealloc(tmem_base, 128);
+  }
+}
+
+}  // namespace b200
+
+using namespace b200;
+
+extern "C" int b200_conv_wgrad(const b200_wgrad_args* a, void* ws, size_t ws_bytes, void* stream) {
+  (void)ws;
+  (void)ws_bytes;
+  if (!a || !a->x || !a->dy || !a->dw) return fail_arg("conv_wgrad: null pointer");
+  if (a->C1 <= 0 || a->C1 % 128 || a->C2 < 0 || a->C2 % 128) return fail_arg("conv_wgrad: C1/C2 must be multiples of 128");
+  if (a->C2 > 0 && !a->x2) return fail_arg("conv_wgrad: C2 > 0 needs x2");
+  if (a->R != a->S || (a->R != 1 && a->R != 3)) return fail_arg("conv_wgrad: only 1x1 and 3x3 filters");
+  if (a->stride != 1 && a->stride != 2) return fail_arg("conv_wgrad: stride must be 1 or 2");
+  const int ho = (a->H + 2 * a->pad - a->R) / a->stride + 1, wo = (a->W + 2 * a->pad - a->S) / a->stride + 1;
+  if (ho != a->Ho || wo != a->Wo) return fail_arg("conv_wgrad: Ho/Wo do not match the geometry");
+  const int Cin = a->C1 + a->C2;
+  const int M_total = a->N * a->Ho * a->Wo;
+  const int lower = -a->pad, upper = a->pad - (a->R - 1);
+
+  CUtensorMap tmDY, tmX, tmX2;
+  int r = get_tmap_2d(a->dy, M_total, 128, 128, 32, kWgPix, 4, 1, &tmDY);
+  if (r) return r;
+  r = get_tmap_im2col(a->x, a->N, a->H, a->W, a->C1, lower, upper, a->stride, 32, kWgPix, 4, 1, &tmX);
+  if (r) return r;
+  if (a->C2 > 0) {
+    r = get_tmap_im2col(a->x2, a->N, a->H, a->W, a->C2, lower, upper, a->stride, 32, kWgPix, 4, 1, &tmX2);
+    if (r) return r;
+  } else {
+    tmX2 = tmX;
+  }
+
+  const int tiles = a->R * a->S * (Cin / 128);
+  WgradK k;
+  k.dw = a->dw;
+  k.M_total = M_total;
+  k.HoWo = a->Ho * a->Wo;
+  k.Wo = a->Wo;
+  k.stride = a->stride;
+  k.pad = a->pad;
+  k.S = a->S;
+  k.C1 = a->C1;
+  k.Cin = Cin;
+  k.steps_total = (M_total + kWgPix - 1) / kWgPix;
+  int slices = a->k_slices;
+  if (slices <= 0) {
+    slices = (148 * 4 + tiles - 1) / tiles;
+    const int max_slices = (k.steps_total + 7) / 8;  // at least 8 pipeline steps per CTA
+    if (slices > max_slices) slices = max_slices;
+    if (slices < 1) slices = 1;
+  }
+  k.steps_per_slice = (k.steps_total + slices - 1) / slices;
+  slices = (k.steps_total + k.steps_per_slice - 1) / k.steps_per_slice;
+
+  static bool attr_set = false;
+  if (!attr_set) {
+    cudaError_t e = cudaFuncSetAttribute(conv_wgrad_tf32_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kWgSmem);
+    if (e != cudaSuccess) return check_cuda(e, "cudaFuncSetAttribute(conv_wgrad)");
+    attr_set = true;
+  }
+  dim3 grid(slices, tiles);
+  conv_wgrad_tf32_kernel<<<grid, 192, kWgSmem, static_cast<cudaStream_t>(stream)>>>(tmDY, tmX, tmX2, k);
+  return after_launch("conv_wgrad_tf32_kernel");
+}

@@ -1,0 +1,132 @@
+// Library-wide state of libb200ddpm.so: ABI version, error string, launch counter, TMA descriptor encoding.
+#include "host_common.h"
+
+#include "../../include/b200ddpm.h"
+
+namespace b200 {
+
+thread_local char g_last_error[512] = {0};
+std::atomic<unsigned long long> g_launches{0};
+
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                  const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+typedef CUresult (*EncodeIm2colFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                   const cuuint64_t*, const int*, const int*, cuuint32_t, cuuint32_t,
+                                   const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                   CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+static EncodeTiledFn g_encode_tiled = nullptr;
+static EncodeIm2colFn g_encode_im2col = nullptr;
+static std::mutex g_mu;
+static std::unordered_map<TmapKey, CUtensorMap, TmapKeyHash> g_cache;
+
+// The driver entry points are fetched through the runtime so the library does not link libcuda directly.
+static int load_driver_fns() {
+  if (g_encode_tiled && g_encode_im2col) return 0;
+  void* fn = nullptr;
+  cudaDriverEntryPointQueryResult qres;
+  cudaError_t e = cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &qres);
+  if (e != cudaSuccess || qres != cudaDriverEntryPointSuccess || !fn)
+    return fail_arg("cudaGetDriverEntryPoint(cuTensorMapEncodeTiled) failed");
+  g_encode_tiled = reinterpret_cast<EncodeTiledFn>(fn);
+  fn = nullptr;
+  e = cudaGetDriverEntryPoint("cuTensorMapEncodeIm2col", &fn, cudaEnableDefault, &qres);
+  if (e != cudaSuccess || qres != cudaDriverEntryPointSuccess || !fn)
+    return fail_arg("cudaGetDriverEntryPoint(cuTensorMapEncodeIm2col) failed");
+  g_encode_im2col = reinterpret_cast<EncodeIm2colFn>(fn);
+  return 0;
+}
+
+static CUtensorMapDataType dtype_of(int elem_bytes) {
+  return elem_bytes == 4 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT32 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16;
+}
+
+int get_tmap_2d(const void* base, uint64_t rows, uint64_t cols, uint64_t ld_elems, uint32_t box_cols,
+                uint32_t box_rows, int elem_bytes, int swizzle32, CUtensorMap* out) {
+  TmapKey k = {{reinterpret_cast<uint64_t>(base), rows, cols, ld_elems,
+                (static_cast<uint64_t>(box_cols) << 32) | box_rows, static_cast<uint64_t>(elem_bytes), 2, static_cast<uint64_t>(swizzle32)}};
+  std::lock_guard<std::mutex> lock(g_mu);
+  auto it = g_cache.find(k);
+  if (it != g_cache.end()) {
+    *out = it->second;
+    return 0;
+  }
+  if (int r = load_driver_fns()) return r;
+  cuuint64_t dims[2] = {cols, rows};
+  cuuint64_t strides[1] = {ld_elems * static_cast<uint64_t>(elem_bytes)};
+  cuuint32_t box[2] = {box_cols, box_rows};
+  cuuint32_t estr[2] = {1, 1};
+  CUtensorMap m;
+  CUresult r = g_encode_tiled(&m, dtype_of(elem_bytes), 2, const_cast<void*>(base), dims, strides, box, estr,
+                              CU_TENSOR_MAP_INTERLEAVE_NONE,
+                              swizzle32 ? CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B : CU_TENSOR_MAP_SWIZZLE_128B,
+                              CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) {
+    snprintf(g_last_error, sizeof(g_last_error), "cuTensorMapEncodeTiled failed (CUresult %d) rows=%llu cols=%llu",
+             static_cast<int>(r), (unsigned long long)rows, (unsigned long long)cols);
+    return -2;
+  }
+  g_cache.emplace(k, m);
+  *out = m;
+  return 0;
+}
+
+int get_tmap_im2col(const void* base, int N, int H, int W, int C, int lower, int upper, int stride, uint32_t box_c,
+                    uint32_t box_pix, int elem_bytes, int swizzle32, CUtensorMap* out) {
+  TmapKey k = {{reinterpret_cast<uint64_t>(base),
+                (static_cast<uint64_t>(N) << 32) | static_cast<uint32_t>(C),
+                (static_cast<uint64_t>(H) << 32) | static_cast<uint32_t>(W),
+                (static_cast<uint64_t>(static_cast<uint32_t>(lower)) << 32) | static_cast<uint32_t>(upper),
+                static_cast<uint64_t>(stride), (static_cast<uint64_t>(box_c) << 32) | box_pix,
+                static_cast<uint64_t>(elem_bytes) | (static_cast<uint64_t>(swizzle32) << 8), 4}};
+  std::lock_guard<std::mutex> lock(g_mu);
+  auto it = g_cache.find(k);
+  if (it != g_cache.end()) {
+    *out = it->second;
+    return 0;
+  }
+  if (int r = load_driver_fns()) return r;
+  const uint64_t eb = static_cast<uint64_t>(elem_bytes);
+  cuuint64_t dims[4] = {(cuuint64_t)C, (cuuint64_t)W, (cuuint64_t)H, (cuuint64_t)N};
+  cuuint64_t strides[3] = {C * eb, (uint64_t)W * C * eb, (uint64_t)H * W * C * eb};
+  int lo[2] = {lower, lower};
+  int hi[2] = {upper, upper};
+  cuuint32_t estr[4] = {1, (cuuint32_t)stride, (cuuint32_t)stride, 1};
+  CUtensorMap m;
+  CUresult r = g_encode_im2col(&m, dtype_of(elem_bytes), 4, const_cast<void*>(base), dims, strides, lo, hi, box_c,
+                               box_pix, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                              swizzle32 ? CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B : CU_TENSOR_MAP_SWIZZLE_128B,
+                               CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) {
+    snprintf(g_last_error, sizeof(g_last_error),
+             "cuTensorMapEncodeIm2col failed (CUresult %d) N=%d H=%d W=%d C=%d lo=%d hi=%d stride=%d", static_cast<int>(r),
+             N, H, W, C, lower, upper, stride);
+    return -2;
+  }
+  g_cache.emplace(k, m);
+  *out = m;
+  return 0;
+}
+
+}  // namespace b200
+
+extern "C" {
+
+int b200_abi_version(void) { return B200_ABI_VERSION; }
+
+int b200_init(int device) {
+  cudaError_t e = cudaSetDevice(device);
+  if (e != cudaSuccess) return b200::check_cuda(e, "cudaSetDevice");
+  cudaDeviceProp prop;
+  e = cudaGetDeviceProperties(&prop, device);
+  if (e != cudaSuccess) return b200::check_cuda(e, "cudaGetDeviceProperties");
+  if (prop.major != 10) return b200::fail_arg("libb200ddpm.so requires a compute-capability 10.x (Blackwell) device");
+  return 0;
+}
+
+const char* b200_last_error(void) { return b200::g_last_error; }
+
+unsigned long long b200_launch_count(void) { return b200::g_launches.load(); }
+
+}  // extern "C"
