@@ -215,10 +215,10 @@ extern "C" int b200_conv_igemm(const b200_conv_args* a, void* ws, size_t ws_byte
     upper = -a->pad;
   }
   CUtensorMap tmA, tmA2, tmB;
-  int r = get_tmap_im2col(a->x, a->N, a->H, a->W, a->C1, lower, upper, a->stride, 32, 128, 4, 0, &tmA);
+  int r = get_tmap_im2col(a->x, a->N, a->H, a->W, a->C1, a->x_ld ? a->x_ld : a->C1, lower, upper, a->stride, 32, 128, 4, 0, &tmA);
   if (r) return r;
   if (a->C2 > 0) {
-    r = get_tmap_im2col(a->x2, a->N, a->H, a->W, a->C2, lower, upper, a->stride, 32, 128, 4, 0, &tmA2);
+    r = get_tmap_im2col(a->x2, a->N, a->H, a->W, a->C2, a->x2_ld ? a->x2_ld : a->C2, lower, upper, a->stride, 32, 128, 4, 0, &tmA2);
     if (r) return r;
   } else {
     tmA2 = tmA;

@@ -160,12 +160,12 @@ extern "C" int b200_conv_wgrad(const b200_wgrad_args* a, void* ws, size_t ws_byt
   const int lower = -a->pad, upper = a->pad - (a->R - 1);
 
   CUtensorMap tmDY, tmX, tmX2;
-  int r = get_tmap_2d(a->dy, M_total, 128, 128, 32, kWgPix, 4, 1, &tmDY);
+  int r = get_tmap_2d(a->dy, M_total, 128, a->dy_ld ? a->dy_ld : 128, 32, kWgPix, 4, 1, &tmDY);
   if (r) return r;
-  r = get_tmap_im2col(a->x, a->N, a->H, a->W, a->C1, lower, upper, a->stride, 32, kWgPix, 4, 1, &tmX);
+  r = get_tmap_im2col(a->x, a->N, a->H, a->W, a->C1, a->x_ld ? a->x_ld : a->C1, lower, upper, a->stride, 32, kWgPix, 4, 1, &tmX);
   if (r) return r;
   if (a->C2 > 0) {
-    r = get_tmap_im2col(a->x2, a->N, a->H, a->W, a->C2, lower, upper, a->stride, 32, kWgPix, 4, 1, &tmX2);
+    r = get_tmap_im2col(a->x2, a->N, a->H, a->W, a->C2, a->x2_ld ? a->x2_ld : a->C2, lower, upper, a->stride, 32, kWgPix, 4, 1, &tmX2);
     if (r) return r;
   } else {
     tmX2 = tmX;

@@ -1,0 +1,261 @@
+// Per-pixel diffusion math around the UNet: q_sample, the clipped x/eps loss (forward + gradient w.r.t. the net
+// output) and the fused sampler update (x/eps reconstruction, classifier-free guidance, ancestral or DDIM step).
+// One HBM pass each.  Arithmetic mirrors the reference's evaluation order with explicitly rounded mul/add
+// (__fmul_rn/__fadd_rn are never contracted into FMAs), because the x<->eps conversions are ill-conditioned at
+// |logsnr| ~ 20 and parity has to survive that.
+// Reference: gms/diffusion/diffusion_utils.py:34-105, gms/diffusion/gaussian_diffusion.py:45-79,81-100,156-243.
+#include "host_common.h"
+
+#include "../../include/b200ddpm.h"
+
+namespace b200 {
+
+__device__ __forceinline__ float mulr(float a, float b) { return __fmul_rn(a, b); }
+__device__ __forceinline__ float addr(float a, float b) { return __fadd_rn(a, b); }
+__device__ __forceinline__ float subr(float a, float b) { return __fsub_rn(a, b); }
+__device__ __forceinline__ float sigmoid_t(float x) { return 1.0f / (1.0f + expf(-x)); }  // torch CUDA sigmoid
+__device__ __forceinline__ float clip1(float v) { return fminf(fmaxf(v, -1.0f), 1.0f); }
+
+// Per-sample coefficients of diffusion_utils.py:76-105 for a given logsnr l.
+struct Coef {
+  float A;      // sqrt(1 + exp(-l))       predict_x_from_eps outer
+  float Bc;     // rsqrt(1 + exp(l))       predict_x_from_eps inner
+  float Ce;     // sqrt(1 + exp(l))        predict_eps_from_x outer
+  float De;     // rsqrt(1 + exp(-l))      predict_eps_from_x inner
+  float alpha;  // sqrt(sigmoid(l))
+  float sigma;  // sqrt(sigmoid(-l))
+};
+__device__ __forceinline__ Coef make_coef(float l) {
+  Coef c;
+  const float en = expf(-l), ep = expf(l);
+  c.A = sqrtf(1.0f + en);
+  c.Bc = rsqrtf(1.0f + ep);
+  c.Ce = sqrtf(1.0f + ep);
+  c.De = rsqrtf(1.0f + en);
+  c.alpha = sqrtf(sigmoid_t(l));
+  c.sigma = sqrtf(sigmoid_t(-l));
+  return c;
+}
+// raw net output -> unclipped x prediction (gaussian_diffusion.py:55-63)
+__device__ __forceinline__ float xhat_from_out(const Coef& c, int mean_type, float z, float out) {
+  if (mean_type == 0) return mulr(c.A, subr(z, mulr(out, c.Bc)));
+  if (mean_type == 1) return out;
+  return subr(mulr(c.alpha, z), mulr(c.sigma, out));
+}
+__device__ __forceinline__ float eps_from_x(const Coef& c, float z, float x) {
+  return mulr(c.Ce, subr(z, mulr(x, c.De)));
+}
+
+// ------------------------------------------------------------------------------------------------ q_sample
+// z = x * sqrt(sigmoid(l)) + sqrt(sigmoid(-l)) * eps      (12 B/px)
+__global__ void __launch_bounds__(256)
+q_sample_kernel(const float* __restrict__ x, const float* __restrict__ eps, const float* __restrict__ logsnr,
+                float* __restrict__ z, int B, int D4) {
+  const size_t total = static_cast<size_t>(B) * D4;
+  for (size_t i = blockIdx.x * static_cast<size_t>(blockDim.x) + threadIdx.x; i < total;
+       i += static_cast<size_t>(gridDim.x) * blockDim.x) {
+    const int b = static_cast<int>(i / D4);
+    const float l = logsnr[b];
+    const float a = sqrtf(sigmoid_t(l)), s = sqrtf(sigmoid_t(-l));
+    const float4 xv = reinterpret_cast<const float4*>(x)[i];
+    const float4 ev = reinterpret_cast<const float4*>(eps)[i];
+    float4 o;
+    o.x = addr(mulr(xv.x, a), mulr(s, ev.x));
+    o.y = addr(mulr(xv.y, a), mulr(s, ev.y));
+    o.z = addr(mulr(xv.z, a), mulr(s, ev.z));
+    o.w = addr(mulr(xv.w, a), mulr(s, ev.w));
+    reinterpret_cast<float4*>(z)[i] = o;
+  }
+}
+
+// ------------------------------------------------------------------------------------------------ loss
+__device__ __forceinline__ float block_sum(float v, float* sh) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  const int w = threadIdx.x >> 5, l = threadIdx.x & 31;
+  __syncthreads();
+  if (l == 0) sh[w] = v;
+  __syncthreads();
+  float t = (threadIdx.x < (blockDim.x >> 5)) ? sh[threadIdx.x] : 0.f;
+  if (w == 0) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) t += __shfl_xor_sync(0xffffffffu, t, o);
+    if (l == 0) sh[0] = t;
+  }
+  __syncthreads();
+  return sh[0];
+}
+
+// One CTA per sample.  loss_b = max(mean (xc-x)^2, mean (ec-eps)^2); dout = d(grad_scale * loss_b)/d(out).
+__global__ void __launch_bounds__(256)
+loss_kernel(const float* __restrict__ out, const float* __restrict__ z, const float* __restrict__ x,
+            const float* __restrict__ eps, const float* __restrict__ logsnr, float* __restrict__ loss_b,
+            float* __restrict__ mse2, float* __restrict__ dout, int D, int mean_type, float grad_scale) {
+  __shared__ float sh[32];
+  const int b = blockIdx.x;
+  const Coef c = make_coef(logsnr[b]);
+  const size_t base = static_cast<size_t>(b) * D;
+  float sx = 0.f, se = 0.f;
+  for (int i = threadIdx.x; i < D; i += blockDim.x) {
+    const float zv = z[base + i];
+    const float xc = clip1(xhat_from_out(c, mean_type, zv, out[base + i]));
+    const float ec = eps_from_x(c, zv, xc);
+    const float dx = xc - x[base + i], de = ec - eps[base + i];
+    sx += dx * dx;
+    se += de * de;
+  }
+  const float x_mse = block_sum(sx, sh) / static_cast<float>(D);
+  const float e_mse = block_sum(se, sh) / static_cast<float>(D);
+  if (threadIdx.x == 0) {
+    loss_b[b] = fmaxf(x_mse, e_mse);
+    if (mse2) {
+      mse2[2 * b] = x_mse;
+      mse2[2 * b + 1] = e_mse;
+    }
+  }
+  if (!dout) return;
+  // torch.maximum backward: the larger branch gets the gradient, exact ties split it in half.
+  const float gx = (x_mse > e_mse) ? 1.f : ((x_mse == e_mse) ? 0.5f : 0.f);
+  const float ge = 1.f - gx;
+  const float k = 2.0f * grad_scale / static_cast<float>(D);
+  const float dxc_de = -(c.Ce * c.De);
+  const float dxh_dout = (mean_type == 0) ? -(c.A * c.Bc) : ((mean_type == 1) ? 1.f : -c.sigma);
+  for (int i = threadIdx.x; i < D; i += blockDim.x) {
+    const float zv = z[base + i];
+    const float xh = xhat_from_out(c, mean_type, zv, out[base + i]);
+    const float xc = clip1(xh);
+    const float ec = eps_from_x(c, zv, xc);
+    float g = k * (gx * (xc - x[base + i]) + ge * (ec - eps[base + i]) * dxc_de);
+    if (xh < -1.0f || xh > 1.0f) g = 0.f;  // clip backward is inclusive at +-1
+    dout[base + i] = g * dxh_dout;
+  }
+}
+
+// mean over B values, one block, fixed order (deterministic).
+__global__ void __launch_bounds__(256) mean_kernel(const float* __restrict__ v, float* __restrict__ out, int B) {
+  __shared__ float sh[32];
+  float s = 0.f;
+  for (int i = threadIdx.x; i < B; i += blockDim.x) s += v[i];
+  const float t = block_sum(s, sh);
+  if (threadIdx.x == 0) out[0] = t / static_cast<float>(B);
+}
+
+// ------------------------------------------------------------------------------------------------ sampler update
+struct SampK {
+  const float* z;
+  const float* out_c;
+  const float* out_u;   // NULL: no guidance
+  const float* cond_w;  // [n]
+  const float* noise;   // noisy sampler
+  const float* sched;   // [T][2] = (logsnr_t, logsnr_s) per loop index i
+  const int* step_dev;  // device loop index (graph replay) or NULL
+  float* z_next;
+  float* x_hist;  // optional [n*D]
+  float* e_hist;
+  int n, D, step, mean_type, sampler;
+};
+
+__global__ void __launch_bounds__(256) sampler_step_kernel(SampK a) {
+  const int step = a.step_dev ? *a.step_dev : a.step;
+  const float lt = a.sched[2 * step], ls = a.sched[2 * step + 1];
+  const Coef c = make_coef(lt);
+  // diffusion_reverse (diffusion_utils.py:34-51) / ddim (gaussian_diffusion.py:210-212) coefficients
+  const float alpha_st = sqrtf((1.0f + expf(-lt)) / (1.0f + expf(-ls)));
+  const float alpha_s = sqrtf(sigmoid_t(ls));
+  const float sigma_s = sqrtf(sigmoid_t(-ls));
+  const float r = expf(lt - ls);
+  const float omr = -expm1f(lt - ls);
+  const float k_z = mulr(r, alpha_st);
+  const float k_x = mulr(omr, alpha_s);
+  const float stdv = sqrtf(mulr(omr, sigmoid_t(-lt)));
+  const bool last = (step == 0);
+  const size_t total = static_cast<size_t>(a.n) * a.D;
+  for (size_t i = blockIdx.x * static_cast<size_t>(blockDim.x) + threadIdx.x; i < total;
+       i += static_cast<size_t>(gridDim.x) * blockDim.x) {
+    const float zv = a.z[i];
+    float xc = clip1(xhat_from_out(c, a.mean_type, zv, a.out_c[i]));
+    float ec = eps_from_x(c, zv, xc);
+    if (a.out_u) {  // _cf_guidance, gaussian_diffusion.py:174-187
+      const float xu = clip1(xhat_from_out(c, a.mean_type, zv, a.out_u[i]));
+      const float eu = eps_from_x(c, zv, xu);
+      const float w = a.cond_w[i / a.D];
+      const float e = addr(mulr(addr(1.0f, w), ec), mulr(-w, eu));
+      xc = clip1(mulr(c.A, subr(zv, mulr(e, c.Bc))));
+      ec = eps_from_x(c, zv, xc);
+    }
+    float zs;
+    if (a.sampler == 1) {
+      const float mean = addr(mulr(k_z, zv), mulr(k_x, xc));
+      zs = addr(mean, mulr(stdv, a.noise[i]));
+    } else {
+      zs = addr(mulr(alpha_s, xc), mulr(sigma_s, ec));
+    }
+    a.z_next[i] = last ? xc : zs;
+    if (a.x_hist) a.x_hist[i] = xc;
+    if (a.e_hist) a.e_hist[i] = ec;
+  }
+}
+
+// (logsnr_t broadcast to n) for the embedding kernel + decrement of the device loop index: one tiny launch that
+// closes a captured sampler step.
+__global__ void step_advance_kernel(int* step_dev) {
+  if (threadIdx.x == 0 && blockIdx.x == 0) *step_dev -= 1;
+}
+
+static int ew_grid1(size_t total) {
+  size_t blocks = (total + 255) / 256;
+  const size_t cap = 148 * 8;
+  return static_cast<int>(blocks < cap ? (blocks ? blocks : 1) : cap);
+}
+
+}  // namespace b200
+
+using namespace b200;
+
+extern "C" int b200_q_sample(const b200_q_sample_args* a, void* ws, size_t ws_bytes, void* stream) {
+  (void)ws; (void)ws_bytes;
+  if (!a || !a->x || !a->eps || !a->logsnr || !a->z) return fail_arg("q_sample: null pointer");
+  if (a->D % 4) return fail_arg("q_sample: D must be a multiple of 4");
+  const size_t total = static_cast<size_t>(a->B) * (a->D / 4);
+  q_sample_kernel<<<ew_grid1(total), 256, 0, static_cast<cudaStream_t>(stream)>>>(a->x, a->eps, a->logsnr, a->z, a->B,
+                                                                                  a->D / 4);
+  return after_launch("q_sample_kernel");
+}
+
+extern "C" int b200_loss(const b200_loss_args* a, void* ws, size_t ws_bytes, void* stream) {
+  (void)ws; (void)ws_bytes;
+  if (!a || !a->out || !a->z || !a->x || !a->eps || !a->logsnr || !a->loss_b) return fail_arg("loss: null pointer");
+  if (a->mean_type < 0 || a->mean_type > 2) return fail_arg("loss: mean_type must be 0 (eps), 1 (x) or 2 (v)");
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  loss_kernel<<<a->B, 256, 0, st>>>(a->out, a->z, a->x, a->eps, a->logsnr, a->loss_b, a->mse2, a->dout, a->D,
+                                    a->mean_type, a->grad_scale);
+  if (int r = after_launch("loss_kernel")) return r;
+  if (a->loss_mean) {
+    mean_kernel<<<1, 256, 0, st>>>(a->loss_b, a->loss_mean, a->B);
+    return after_launch("mean_kernel");
+  }
+  return 0;
+}
+
+extern "C" int b200_sampler_step(const b200_sampler_step_args* a, void* ws, size_t ws_bytes, void* stream) {
+  (void)ws; (void)ws_bytes;
+  if (!a || !a->z || !a->out_c || !a->sched || !a->z_next) return fail_arg("sampler_step: null pointer");
+  if (a->out_u && !a->cond_w) return fail_arg("sampler_step: guidance needs cond_w");
+  if (a->sampler == 1 && !a->noise) return fail_arg("sampler_step: the noisy sampler needs noise");
+  if (a->sampler != 0 && a->sampler != 1) return fail_arg("sampler_step: sampler must be 0 (ddim) or 1 (noisy)");
+  if (a->mean_type < 0 || a->mean_type > 2) return fail_arg("sampler_step: bad mean_type");
+  SampK k;
+  k.z = a->z; k.out_c = a->out_c; k.out_u = a->out_u; k.cond_w = a->cond_w; k.noise = a->noise; k.sched = a->sched;
+  k.step_dev = a->step_dev; k.z_next = a->z_next; k.x_hist = a->x_hist; k.e_hist = a->e_hist;
+  k.n = a->n; k.D = a->D; k.step = a->step; k.mean_type = a->mean_type; k.sampler = a->sampler;
+  const size_t total = static_cast<size_t>(a->n) * a->D;
+  sampler_step_kernel<<<ew_grid1(total), 256, 0, static_cast<cudaStream_t>(stream)>>>(k);
+  return after_launch("sampler_step_kernel");
+}
+
+extern "C" int b200_step_advance(const b200_step_advance_args* a, void* ws, size_t ws_bytes, void* stream) {
+  (void)ws; (void)ws_bytes;
+  if (!a || !a->step_dev) return fail_arg("step_advance: null pointer");
+  step_advance_kernel<<<1, 32, 0, static_cast<cudaStream_t>(stream)>>>(a->step_dev);
+  return after_launch("step_advance_kernel");
+}

@@ -1,0 +1,249 @@
+// The two convolutions that are not tensor-core shaped: the 1->128 input conv (K = 9) and the 128->1 output conv
+// (N = 1).  Both are bandwidth-bound on the 128-channel side, so they are written as coalesced float4 kernels with
+// warp-shuffle / shared-memory reductions.  Forward, weight/bias gradients and (for the output conv) data gradient.
+// Reference: simple_unet.py:92-94 (Downsample(1, C, 1) = Conv2d(1, C, 3, padding=1)) and :41 (Conv2d(C, 1, 3, padding=1)).
+#include "host_common.h"
+
+#include "../../include/b200ddpm.h"
+
+namespace b200 {
+
+// ------------------------------------------------------------------------------------------------ conv_in forward
+// out[n,y,x,c] = b[c] + sum_{kh,kw} x[n,y+kh-1,x+kw-1] * w[c][kh][kw];  one thread = one pixel x 4 channels.
+__global__ void __launch_bounds__(256)
+conv_in_fwd_kernel(const float* __restrict__ x, const float* __restrict__ w, const float* __restrict__ bias,
+                   float* __restrict__ out, int N, int H, int W) {
+  __shared__ float sw[9][128];
+  __shared__ float sb[128];
+  for (int i = threadIdx.x; i < 9 * 128; i += blockDim.x) sw[i % 9][i / 9] = w[i];  // w is [c][tap]
+  if (threadIdx.x < 128) sb[threadIdx.x] = bias[threadIdx.x];
+  __syncthreads();
+  const size_t total = static_cast<size_t>(N) * H * W * 32;
+  for (size_t i = blockIdx.x * static_cast<size_t>(blockDim.x) + threadIdx.x; i < total;
+       i += static_cast<size_t>(gridDim.x) * blockDim.x) {
+    const size_t pix = i >> 5;
+    const int c = static_cast<int>(i & 31) * 4;
+    const int n = static_cast<int>(pix / (H * W));
+    const int rem = static_cast<int>(pix - static_cast<size_t>(n) * H * W);
+    const int y = rem / W, xx = rem - y * W;
+    float4 acc = make_float4(sb[c], sb[c + 1], sb[c + 2], sb[c + 3]);
+    const float* img = x + static_cast<size_t>(n) * H * W;
+#pragma unroll
+    for (int kh = 0; kh < 3; ++kh) {
+      const int yy = y + kh - 1;
+      if (yy < 0 || yy >= H) continue;
+#pragma unroll
+      for (int kw = 0; kw < 3; ++kw) {
+        const int xw = xx + kw - 1;
+        if (xw < 0 || xw >= W) continue;
+        const float v = img[yy * W + xw];
+        const float4 wv = *reinterpret_cast<const float4*>(&sw[kh * 3 + kw][c]);
+        acc.x += v * wv.x; acc.y += v * wv.y; acc.z += v * wv.z; acc.w += v * wv.w;
+      }
+    }
+    *reinterpret_cast<float4*>(out + pix * 128 + c) = acc;
+  }
+}
+
+// ------------------------------------------------------------------------------------------------ conv_in backward
+// dw[c][tap] += sum_pix dy[pix][c] * x[pix + tap];  db[c] += sum_pix dy[pix][c].  grid (chunks, N), block 256:
+// thread = (pixel row r = tid/32, channel quad tid%32); 40 register accumulators, smem reduce over the 8 pixel rows.
+__global__ void __launch_bounds__(256)
+conv_in_bwd_kernel(const float* __restrict__ x, const float* __restrict__ dy, float* __restrict__ dw,
+                   float* __restrict__ db, int H, int W, int pix_per_chunk) {
+  __shared__ float sh[8][32][41];
+  const int n = blockIdx.y;
+  const int q = threadIdx.x & 31, r = threadIdx.x >> 5;
+  const int HW = H * W;
+  const float* img = x + static_cast<size_t>(n) * HW;
+  float acc[10][4];
+#pragma unroll
+  for (int t = 0; t < 10; ++t)
+#pragma unroll
+    for (int j = 0; j < 4; ++j) acc[t][j] = 0.f;
+  const int p0 = blockIdx.x * pix_per_chunk, p1 = min(p0 + pix_per_chunk, HW);
+  for (int p = p0 + r; p < p1; p += 8) {
+    const float4 d = *reinterpret_cast<const float4*>(dy + (static_cast<size_t>(n) * HW + p) * 128 + q * 4);
+    const int y = p / W, xx = p - y * W;
+#pragma unroll
+    for (int kh = 0; kh < 3; ++kh)
+#pragma unroll
+      for (int kw = 0; kw < 3; ++kw) {
+        const int yy = y + kh - 1, xw = xx + kw - 1;
+        const float v = (yy >= 0 && yy < H && xw >= 0 && xw < W) ? img[yy * W + xw] : 0.f;
+        acc[kh * 3 + kw][0] += d.x * v; acc[kh * 3 + kw][1] += d.y * v;
+        acc[kh * 3 + kw][2] += d.z * v; acc[kh * 3 + kw][3] += d.w * v;
+      }
+    acc[9][0] += d.x; acc[9][1] += d.y; acc[9][2] += d.z; acc[9][3] += d.w;
+  }
+#pragma unroll
+  for (int t = 0; t < 10; ++t)
+#pragma unroll
+    for (int j = 0; j < 4; ++j) sh[r][q][t * 4 + j] = acc[t][j];
+  __syncthreads();
+  // 128 channels x 10 values, summed over the 8 pixel rows
+  for (int i = threadIdx.x; i < 1280; i += 256) {
+    const int c = i / 10, t = i - c * 10;
+    float s = 0.f;
+#pragma unroll
+    for (int rr = 0; rr < 8; ++rr) s += sh[rr][c >> 2][t * 4 + (c & 3)];
+    if (t < 9) atomicAdd(&dw[c * 9 + t], s);
+    else atomicAdd(&db[c], s);
+  }
+}
+
+// ------------------------------------------------------------------------------------------------ conv_out forward
+// out[pix] = b + sum_{tap,c} h[pix+tap][c] * w[tap][c].  One CTA per image (HW <= 1024): every input row is read
+// once, its 9 per-tap dot products are parked in smem, then each output pixel gathers its 9 partials.
+__global__ void __launch_bounds__(256)
+conv_out_fwd_kernel(const float* __restrict__ h, const float* __restrict__ w, const float* __restrict__ bias,
+                    float* __restrict__ out, int H, int W) {
+  extern __shared__ float part[];  // [HW][9]
+  const int n = blockIdx.x;
+  const int HW = H * W;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  float4 wv[9];
+#pragma unroll
+  for (int t = 0; t < 9; ++t) wv[t] = *reinterpret_cast<const float4*>(w + t * 128 + lane * 4);
+  for (int p = warp; p < HW; p += 8) {
+    const float4 v = *reinterpret_cast<const float4*>(h + (static_cast<size_t>(n) * HW + p) * 128 + lane * 4);
+    float d[9];
+#pragma unroll
+    for (int t = 0; t < 9; ++t) d[t] = v.x * wv[t].x + v.y * wv[t].y + v.z * wv[t].z + v.w * wv[t].w;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1)
+#pragma unroll
+      for (int t = 0; t < 9; ++t) d[t] += __shfl_xor_sync(0xffffffffu, d[t], o);
+    if (lane < 9) {
+      float sel = d[0];
+#pragma unroll
+      for (int t = 1; t < 9; ++t) sel = (lane == t) ? d[t] : sel;
+      part[p * 9 + lane] = sel;
+    }
+  }
+  __syncthreads();
+  const float b = bias[0];
+  for (int p = threadIdx.x; p < HW; p += blockDim.x) {
+    const int y = p / W, xx = p - y * W;
+    float s = b;
+#pragma unroll
+    for (int kh = 0; kh < 3; ++kh)
+#pragma unroll
+      for (int kw = 0; kw < 3; ++kw) {
+        const int yy = y + kh - 1, xw = xx + kw - 1;
+        if (yy >= 0 && yy < H && xw >= 0 && xw < W) s += part[(yy * W + xw) * 9 + kh * 3 + kw];
+      }
+    out[static_cast<size_t>(n) * HW + p] = s;
+  }
+}
+
+// ------------------------------------------------------------------------------------------------ conv_out backward
+// dh[pix][c] = sum_tap dout[pix - tap + 1] * w[tap][c];  dw[tap][c] += sum_pix h[pix][c] * dout[pix - tap + 1];
+// db += sum dout.  One CTA per image; dout of the image lives in smem.
+__global__ void __launch_bounds__(256)
+conv_out_bwd_kernel(const float* __restrict__ h, const float* __restrict__ w, const float* __restrict__ dout,
+                    float* __restrict__ dh, float* __restrict__ dw, float* __restrict__ db, int H, int W) {
+  extern __shared__ float sm[];  // [HW] dout, then [8][9][128] dw partials
+  const int n = blockIdx.x;
+  const int HW = H * W;
+  float* sd = sm;
+  float* sdw = sm + ((HW + 3) & ~3);
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  float bsum = 0.f;
+  for (int p = threadIdx.x; p < HW; p += blockDim.x) {
+    const float v = dout[static_cast<size_t>(n) * HW + p];
+    sd[p] = v;
+    bsum += v;
+  }
+  __syncthreads();
+  float4 wv[9], aw[9];
+#pragma unroll
+  for (int t = 0; t < 9; ++t) {
+    wv[t] = *reinterpret_cast<const float4*>(w + t * 128 + lane * 4);
+    aw[t] = make_float4(0.f, 0.f, 0.f, 0.f);
+  }
+  for (int p = warp; p < HW; p += 8) {
+    const size_t off = (static_cast<size_t>(n) * HW + p) * 128 + lane * 4;
+    const float4 v = *reinterpret_cast<const float4*>(h + off);
+    const int y = p / W, xx = p - y * W;
+    float4 g = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+    for (int kh = 0; kh < 3; ++kh)
+#pragma unroll
+      for (int kw = 0; kw < 3; ++kw) {
+        const int yy = y - kh + 1, xw = xx - kw + 1;
+        const float d = (yy >= 0 && yy < H && xw >= 0 && xw < W) ? sd[yy * W + xw] : 0.f;
+        const int t = kh * 3 + kw;
+        g.x += d * wv[t].x; g.y += d * wv[t].y; g.z += d * wv[t].z; g.w += d * wv[t].w;
+        aw[t].x += d * v.x; aw[t].y += d * v.y; aw[t].z += d * v.z; aw[t].w += d * v.w;
+      }
+    *reinterpret_cast<float4*>(dh + off) = g;
+  }
+#pragma unroll
+  for (int t = 0; t < 9; ++t) *reinterpret_cast<float4*>(sdw + (warp * 9 + t) * 128 + lane * 4) = aw[t];
+  __syncthreads();
+  for (int i = threadIdx.x; i < 9 * 128; i += blockDim.x) {
+    float s = 0.f;
+#pragma unroll
+    for (int ww = 0; ww < 8; ++ww) s += sdw[ww * 9 * 128 + i];
+    atomicAdd(&dw[i], s);
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) bsum += __shfl_xor_sync(0xffffffffu, bsum, o);
+  if (lane == 0) atomicAdd(db, bsum);
+}
+
+}  // namespace b200
+
+using namespace b200;
+
+extern "C" int b200_conv_in_fwd(const b200_conv_in_args* a, void* ws, size_t ws_bytes, void* stream) {
+  (void)ws; (void)ws_bytes;
+  if (!a || !a->x || !a->w || !a->bias || !a->out) return fail_arg("conv_in_fwd: null pointer");
+  const size_t total = static_cast<size_t>(a->N) * a->H * a->W * 32;
+  size_t blocks = (total + 255) / 256;
+  if (blocks > 148 * 8) blocks = 148 * 8;
+  conv_in_fwd_kernel<<<static_cast<int>(blocks), 256, 0, static_cast<cudaStream_t>(stream)>>>(a->x, a->w, a->bias, a->out,
+                                                                                              a->N, a->H, a->W);
+  return after_launch("conv_in_fwd_kernel");
+}
+
+extern "C" int b200_conv_in_bwd(const b200_conv_in_args* a, void* ws, size_t ws_bytes, void* stream) {
+  (void)ws; (void)ws_bytes;
+  if (!a || !a->x || !a->dy || !a->dw || !a->db) return fail_arg("conv_in_bwd: null pointer");
+  const int HW = a->H * a->W;
+  int chunks = (592 + a->N - 1) / a->N;
+  if (chunks > (HW + 63) / 64) chunks = (HW + 63) / 64;
+  if (chunks < 1) chunks = 1;
+  const int ppc = (HW + chunks - 1) / chunks;
+  conv_in_bwd_kernel<<<dim3(chunks, a->N), 256, 0, static_cast<cudaStream_t>(stream)>>>(a->x, a->dy, a->dw, a->db, a->H,
+                                                                                        a->W, ppc);
+  return after_launch("conv_in_bwd_kernel");
+}
+
+extern "C" int b200_conv_out_fwd(const b200_conv_out_args* a, void* ws, size_t ws_bytes, void* stream) {
+  (void)ws; (void)ws_bytes;
+  if (!a || !a->h || !a->w || !a->bias || !a->out) return fail_arg("conv_out_fwd: null pointer");
+  const int HW = a->H * a->W;
+  if (HW > 1024) return fail_arg("conv_out_fwd: H*W must be <= 1024");
+  const size_t smem = static_cast<size_t>(HW) * 9 * sizeof(float);
+  conv_out_fwd_kernel<<<a->N, 256, smem, static_cast<cudaStream_t>(stream)>>>(a->h, a->w, a->bias, a->out, a->H, a->W);
+  return after_launch("conv_out_fwd_kernel");
+}
+
+extern "C" int b200_conv_out_bwd(const b200_conv_out_args* a, void* ws, size_t ws_bytes, void* stream) {
+  (void)ws; (void)ws_bytes;
+  if (!a || !a->h || !a->w || !a->dout || !a->dh || !a->dw || !a->db) return fail_arg("conv_out_bwd: null pointer");
+  const int HW = a->H * a->W;
+  if (HW > 1024) return fail_arg("conv_out_bwd: H*W must be <= 1024");
+  const size_t smem = (static_cast<size_t>((HW + 3) & ~3) + 8 * 9 * 128) * sizeof(float);
+  static bool attr_set = false;
+  if (!attr_set) {
+    cudaError_t e = cudaFuncSetAttribute(conv_out_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 48 * 1024);
+    if (e != cudaSuccess) return check_cuda(e, "cudaFuncSetAttribute(conv_out_bwd)");
+    attr_set = true;
+  }
+  conv_out_bwd_kernel<<<a->N, 256, smem, static_cast<cudaStream_t>(stream)>>>(a->h, a->w, a->dout, a->dh, a->dw, a->db,
+                                                                              a->H, a->W);
+  return after_launch("conv_out_bwd_kernel");
+}

@@ -72,13 +72,13 @@ int get_tmap_2d(const void* base, uint64_t rows, uint64_t cols, uint64_t ld_elem
   return 0;
 }
 
-int get_tmap_im2col(const void* base, int N, int H, int W, int C, int lower, int upper, int stride, uint32_t box_c,
+int get_tmap_im2col(const void* base, int N, int H, int W, int C, int ld, int lower, int upper, int stride, uint32_t box_c,
                     uint32_t box_pix, int elem_bytes, int swizzle32, CUtensorMap* out) {
   TmapKey k = {{reinterpret_cast<uint64_t>(base),
                 (static_cast<uint64_t>(N) << 32) | static_cast<uint32_t>(C),
                 (static_cast<uint64_t>(H) << 32) | static_cast<uint32_t>(W),
                 (static_cast<uint64_t>(static_cast<uint32_t>(lower)) << 32) | static_cast<uint32_t>(upper),
-                static_cast<uint64_t>(stride), (static_cast<uint64_t>(box_c) << 32) | box_pix,
+                static_cast<uint64_t>(stride) | (static_cast<uint64_t>(ld) << 32), (static_cast<uint64_t>(box_c) << 32) | box_pix,
                 static_cast<uint64_t>(elem_bytes) | (static_cast<uint64_t>(swizzle32) << 8), 4}};
   std::lock_guard<std::mutex> lock(g_mu);
   auto it = g_cache.find(k);
@@ -89,7 +89,7 @@ int get_tmap_im2col(const void* base, int N, int H, int W, int C, int lower, int
   if (int r = load_driver_fns()) return r;
   const uint64_t eb = static_cast<uint64_t>(elem_bytes);
   cuuint64_t dims[4] = {(cuuint64_t)C, (cuuint64_t)W, (cuuint64_t)H, (cuuint64_t)N};
-  cuuint64_t strides[3] = {C * eb, (uint64_t)W * C * eb, (uint64_t)H * W * C * eb};
+  cuuint64_t strides[3] = {ld * eb, (uint64_t)W * ld * eb, (uint64_t)H * W * ld * eb};
   int lo[2] = {lower, lower};
   int hi[2] = {upper, upper};
   cuuint32_t estr[4] = {1, (cuuint32_t)stride, (cuuint32_t)stride, 1};

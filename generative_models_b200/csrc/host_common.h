@@ -52,7 +52,7 @@ struct TmapKeyHash {
 int get_tmap_2d(const void* base, uint64_t rows, uint64_t cols, uint64_t ld_elems, uint32_t box_cols,
                 uint32_t box_rows, int elem_bytes, int swizzle32, CUtensorMap* out);
 // NHWC [N][H][W][C] im2col map: box = box_c channels x box_pix pixels; corners from the conv geometry.
-int get_tmap_im2col(const void* base, int N, int H, int W, int C, int lower, int upper, int stride, uint32_t box_c,
+int get_tmap_im2col(const void* base, int N, int H, int W, int C, int ld, int lower, int upper, int stride, uint32_t box_c,
                     uint32_t box_pix, int elem_bytes, int swizzle32, CUtensorMap* out);
 
 }  // namespace b200

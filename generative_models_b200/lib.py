@@ -21,6 +21,7 @@ class ConvArgs(C.Structure):
         ("R", C.c_int), ("S", C.c_int), ("stride", C.c_int), ("pad", C.c_int),
         ("mode", C.c_int), ("w_cout", C.c_int), ("w_cin", C.c_int), ("n_off", C.c_int),
         ("out_ld", C.c_int), ("emb_ld", C.c_int), ("res_ld", C.c_int),
+        ("x_ld", C.c_int), ("x2_ld", C.c_int),
     ]
 
 
@@ -30,8 +31,101 @@ class WgradArgs(C.Structure):
         ("N", C.c_int), ("H", C.c_int), ("W", C.c_int), ("C1", C.c_int), ("C2", C.c_int),
         ("Ho", C.c_int), ("Wo", C.c_int),
         ("R", C.c_int), ("S", C.c_int), ("stride", C.c_int), ("pad", C.c_int),
-        ("k_slices", C.c_int),
+        ("k_slices", C.c_int), ("x_ld", C.c_int), ("x2_ld", C.c_int), ("dy_ld", C.c_int),
     ]
+
+
+class GnArgs(C.Structure):
+    _fields_ = [
+        ("x", _f32p), ("x2", _f32p), ("stats", _f32p), ("gamma", _f32p), ("beta", _f32p), ("y", _f32p),
+        ("N", C.c_int), ("HW", C.c_int), ("C1", C.c_int), ("C2", C.c_int),
+        ("x_ld", C.c_int), ("x2_ld", C.c_int),
+        ("eps", C.c_float), ("silu", C.c_int), ("round_tf32", C.c_int),
+    ]
+
+
+class GnBwdArgs(C.Structure):
+    _fields_ = [
+        ("fwd", GnArgs), ("dy", _f32p), ("dx", _f32p), ("add1", _f32p), ("add2", _f32p),
+        ("add1_ld", C.c_int), ("add2_ld", C.c_int), ("add_c", C.c_int),
+        ("dgamma", _f32p), ("dbeta", _f32p),
+    ]
+
+
+class QSampleArgs(C.Structure):
+    _fields_ = [("x", _f32p), ("eps", _f32p), ("logsnr", _f32p), ("z", _f32p), ("B", C.c_int), ("D", C.c_int)]
+
+
+class LossArgs(C.Structure):
+    _fields_ = [
+        ("out", _f32p), ("z", _f32p), ("x", _f32p), ("eps", _f32p), ("logsnr", _f32p),
+        ("loss_b", _f32p), ("mse2", _f32p), ("dout", _f32p), ("loss_mean", _f32p),
+        ("B", C.c_int), ("D", C.c_int), ("mean_type", C.c_int), ("grad_scale", C.c_float),
+    ]
+
+
+class SamplerStepArgs(C.Structure):
+    _fields_ = [
+        ("z", _f32p), ("out_c", _f32p), ("out_u", _f32p), ("cond_w", _f32p), ("noise", _f32p), ("sched", _f32p),
+        ("step_dev", _f32p), ("z_next", _f32p), ("x_hist", _f32p), ("e_hist", _f32p),
+        ("n", C.c_int), ("D", C.c_int), ("step", C.c_int), ("mean_type", C.c_int), ("sampler", C.c_int),
+    ]
+
+
+class StepAdvanceArgs(C.Structure):
+    _fields_ = [("step_dev", _f32p)]
+
+
+class ConvInArgs(C.Structure):
+    _fields_ = [
+        ("x", _f32p), ("w", _f32p), ("bias", _f32p), ("out", _f32p), ("dy", _f32p), ("dw", _f32p), ("db", _f32p),
+        ("N", C.c_int), ("H", C.c_int), ("W", C.c_int),
+    ]
+
+
+class ConvOutArgs(C.Structure):
+    _fields_ = [
+        ("h", _f32p), ("w", _f32p), ("bias", _f32p), ("out", _f32p), ("dout", _f32p), ("dh", _f32p),
+        ("dw", _f32p), ("db", _f32p), ("N", C.c_int), ("H", C.c_int), ("W", C.c_int),
+    ]
+
+
+class ResampleArgs(C.Structure):
+    _fields_ = [("in_", _f32p), ("out", _f32p), ("N", C.c_int), ("H", C.c_int), ("W", C.c_int), ("C", C.c_int),
+                ("in_ld", C.c_int), ("mode", C.c_int)]
+
+
+class ColsumArgs(C.Structure):
+    _fields_ = [("dy", _f32p), ("per_sample", _f32p), ("total1", _f32p), ("total2", _f32p),
+                ("N", C.c_int), ("HW", C.c_int), ("ld", C.c_int), ("ps_ld", C.c_int)]
+
+
+class EmbedArgs(C.Structure):
+    _fields_ = [
+        ("t", _f32p), ("sched", _f32p), ("step_dev", _f32p), ("freqs", _f32p), ("guide", _f32p),
+        ("sincos", _f32p), ("onehot", _f32p), ("t_out", _f32p), ("t_emb", _f32p), ("g_emb", _f32p),
+        ("emb", _f32p), ("semb", _f32p), ("d_semb", _f32p), ("d_emb", _f32p), ("d_g_emb", _f32p),
+        ("B", C.c_int), ("E", C.c_int), ("step", C.c_int), ("force_uncond", C.c_int),
+    ]
+
+
+class LinearArgs(C.Structure):
+    _fields_ = [
+        ("X", _f32p), ("W", _f32p), ("bias", _f32p), ("Y", _f32p), ("dY", _f32p), ("dX", _f32p), ("dW", _f32p),
+        ("db", _f32p), ("M", C.c_int), ("N", C.c_int), ("K", C.c_int), ("act", C.c_int), ("mode", C.c_int),
+    ]
+
+
+class AdamArgs(C.Structure):
+    _fields_ = [
+        ("p", _f32p), ("g", _f32p), ("m", _f32p), ("v", _f32p), ("n", C.c_size_t),
+        ("lr", C.c_float), ("beta1", C.c_float), ("beta2", C.c_float), ("eps", C.c_float), ("grad_scale", C.c_float),
+        ("step_dev", _f32p), ("step", C.c_int),
+    ]
+
+
+class ZeroArgs(C.Structure):
+    _fields_ = [("ptr", _f32p), ("bytes", C.c_size_t)]
 
 
 class B200Error(RuntimeError):
@@ -72,6 +166,12 @@ def load():
 EXPORTS = [
     "b200_abi_version", "b200_init", "b200_last_error", "b200_launch_count",
     "b200_conv_igemm", "b200_conv_wgrad",
+    "b200_gn_stats", "b200_gn_apply", "b200_gn_bwd",
+    "b200_q_sample", "b200_loss", "b200_sampler_step", "b200_step_advance", "b200_int_increment",
+    "b200_conv_in_fwd", "b200_conv_in_bwd", "b200_conv_out_fwd", "b200_conv_out_bwd",
+    "b200_upsample2x", "b200_colsum",
+    "b200_embed_prep", "b200_embed_combine", "b200_embed_combine_bwd",
+    "b200_linear", "b200_adam", "b200_zero",
 ]
 
 

@@ -54,6 +54,7 @@ typedef struct {
   int w_cout, w_cin;     /* weight tensor is [w_cout][R*S*w_cin] */
   int n_off;             /* dgrad only: first input channel produced by this launch */
   int out_ld, emb_ld, res_ld;
+  int x_ld, x2_ld;       /* pixel stride (floats) of x / x2; 0 = dense (C1 / C2) */
 } b200_conv_args;
 int b200_conv_igemm(const b200_conv_args* a, void* ws, size_t ws_bytes, void* stream);
 
@@ -69,8 +70,218 @@ typedef struct {
   int Ho, Wo;
   int R, S, stride, pad;
   int k_slices; /* split of the pixel reduction; 0 = library picks */
+  int x_ld, x2_ld; /* pixel stride (floats) of x / x2; 0 = dense */
+  int dy_ld;       /* pixel stride of dy; 0 = dense (128) */
 } b200_wgrad_args;
 int b200_conv_wgrad(const b200_wgrad_args* a, void* ws, size_t ws_bytes, void* stream);
+
+/* ------------------------------------------------------------------ GroupNorm(32) + SiLU
+ * Replaces nn.GroupNorm(32, C) -> nn.SiLU (simple_unet.py:38-41 out head, :161-163 in_layers, :168-170 out_layers).
+ * x may be a virtual concat (x: C1 channels with pixel stride x_ld, x2: C2 channels with stride x2_ld; ld 0 = dense).
+ * stats is [N][32][2] = {sum, sum of squares}; b200_gn_stats ACCUMULATES into it (caller zeroes), b200_gn_apply
+ * writes y[N*HW][C1+C2] = silu?((x-mean)*rstd*gamma+beta), optionally rounded to TF32 for the following conv. */
+typedef struct {
+  const float* x;
+  const float* x2;
+  float* stats;
+  const float* gamma;
+  const float* beta;
+  float* y;
+  int N, HW, C1, C2;
+  int x_ld, x2_ld;
+  float eps;
+  int silu;
+  int round_tf32;
+} b200_gn_args;
+int b200_gn_stats(const b200_gn_args* a, void* ws, size_t ws_bytes, void* stream);
+int b200_gn_apply(const b200_gn_args* a, void* ws, size_t ws_bytes, void* stream);
+
+/* backward of the same block: dy is the gradient w.r.t. y.  dx[N*HW][C] = GN/SiLU backward (+ add1 + add2 on the
+ * first add_c channels: the other gradients that flow into the same tensor).  dgamma/dbeta are accumulated with
+ * atomics (caller zeroes the flat gradient buffer once per step).  ws: N*64 floats. */
+typedef struct {
+  b200_gn_args fwd;
+  const float* dy;
+  float* dx;
+  const float* add1;
+  const float* add2;
+  int add1_ld, add2_ld, add_c;
+  float* dgamma;
+  float* dbeta;
+} b200_gn_bwd_args;
+int b200_gn_bwd(const b200_gn_bwd_args* a, void* ws, size_t ws_bytes, void* stream);
+
+/* ------------------------------------------------------------------ diffusion math around the net (D = pixels/img)
+ * mean_type: 0 = 'eps', 1 = 'x', 2 = 'v' (gaussian_diffusion.py:55-63).  sampler: 0 = 'ddim', 1 = 'noisy'. */
+
+/* q_sample: z = x*sqrt(sigmoid(l)) + sqrt(sigmoid(-l))*eps  (diffusion_utils.py:65-73 + gaussian_diffusion.py:100) */
+typedef struct {
+  const float* x;
+  const float* eps;
+  const float* logsnr; /* [B] */
+  float* z;
+  int B, D;
+} b200_q_sample_args;
+int b200_q_sample(const b200_q_sample_args* a, void* ws, size_t ws_bytes, void* stream);
+
+/* loss: _run_model + x_mse/eps_mse/max (gaussian_diffusion.py:45-79,156-172) and, when dout != NULL, the gradient of
+ * grad_scale * loss_b w.r.t. the raw net output (grad_scale = 1/B for the batch-mean loss of diffusion_model.py:78).
+ * loss_mean (optional) receives mean_b(loss_b); mse2 (optional) receives [B][2] = {x_mse, eps_mse}. */
+typedef struct {
+  const float* out;
+  const float* z;
+  const float* x;
+  const float* eps;
+  const float* logsnr;
+  float* loss_b;
+  float* mse2;
+  float* dout;
+  float* loss_mean;
+  int B, D, mean_type;
+  float grad_scale;
+} b200_loss_args;
+int b200_loss(const b200_loss_args* a, void* ws, size_t ws_bytes, void* stream);
+
+/* one sampler update: _run_model on the conditional output, optional classifier-free guidance against the
+ * unconditional output (gaussian_diffusion.py:174-187), then reverse_dpm_step (:215-243, diffusion_utils.py:34-51
+ * with x_logvar='large') or ddim_step (:189-213); z_next = x_pred when the loop index is 0 (:292).
+ * sched is the [T][2] table {logsnr_t, logsnr_s} per loop index; the index is `step`, or *step_dev when given. */
+typedef struct {
+  const float* z;
+  const float* out_c;
+  const float* out_u;
+  const float* cond_w;
+  const float* noise;
+  const float* sched;
+  const int* step_dev;
+  float* z_next;
+  float* x_hist;
+  float* e_hist;
+  int n, D, step, mean_type, sampler;
+} b200_sampler_step_args;
+int b200_sampler_step(const b200_sampler_step_args* a, void* ws, size_t ws_bytes, void* stream);
+
+typedef struct {
+  int* step_dev;
+} b200_step_advance_args;
+int b200_step_advance(const b200_step_advance_args* a, void* ws, size_t ws_bytes, void* stream);
+
+/* also used to bump the device-side Adam step counter */
+int b200_int_increment(const b200_step_advance_args* a, void* ws, size_t ws_bytes, void* stream);
+
+/* ------------------------------------------------------------------ edge convolutions (not tensor-core shaped)
+ * conv_in: Conv2d(1, 128, 3, padding=1) (simple_unet.py:92-94); x [N,H,W], w [128][3][3], out/dy [N,H,W,128].
+ * conv_out: Conv2d(128, 1, 3, padding=1) (simple_unet.py:41); h/dh [N,H,W,128], w [3][3][128], out/dout [N,H,W]. */
+typedef struct {
+  const float* x;
+  const float* w;
+  const float* bias;
+  float* out;
+  const float* dy;
+  float* dw; /* accumulated with atomics */
+  float* db;
+  int N, H, W;
+} b200_conv_in_args;
+int b200_conv_in_fwd(const b200_conv_in_args* a, void* ws, size_t ws_bytes, void* stream);
+int b200_conv_in_bwd(const b200_conv_in_args* a, void* ws, size_t ws_bytes, void* stream);
+
+typedef struct {
+  const float* h;
+  const float* w;
+  const float* bias;
+  float* out;
+  const float* dout;
+  float* dh;
+  float* dw;
+  float* db;
+  int N, H, W;
+} b200_conv_out_args;
+int b200_conv_out_fwd(const b200_conv_out_args* a, void* ws, size_t ws_bytes, void* stream);
+int b200_conv_out_bwd(const b200_conv_out_args* a, void* ws, size_t ws_bytes, void* stream);
+
+/* ------------------------------------------------------------------ glue
+ * resample: mode 0 = nearest 2x upsample in [N,H,W,C] -> out [N,2H,2W,C] (F.interpolate, simple_unet.py:121);
+ *           mode 1 = its backward: in = dout [N,2H,2W,C] (pixel stride in_ld) -> out = din [N,H,W,C];
+ *           mode 2 = zero-stuffing: in = dy [N,ceil(H/2),ceil(W/2),C] (stride in_ld) -> out [N,H,W,C] with dy at
+ *                    even pixels (turns the stride-2 Downsample dgrad into a stride-1 one). */
+typedef struct {
+  const float* in;
+  float* out;
+  int N, H, W, C;
+  int in_ld;
+  int mode;
+} b200_resample_args;
+int b200_upsample2x(const b200_resample_args* a, void* ws, size_t ws_bytes, void* stream);
+
+/* channel sums of a [N,HW,128] gradient (pixel stride ld): per_sample[n*ps_ld + c] += sum_pix, total{1,2}[c] += sum_{n,pix}.
+ * These are the conv-bias gradients and the gradient of the emb_out broadcast add (simple_unet.py:183-184). */
+typedef struct {
+  const float* dy;
+  float* per_sample;
+  float* total1;
+  float* total2;
+  int N, HW, ld, ps_ld;
+} b200_colsum_args;
+int b200_colsum(const b200_colsum_args* a, void* ws, size_t ws_bytes, void* stream);
+
+/* embeddings (simple_unet.py:45-58, 205-224): prep writes sincos[B][64] of t (or of sched[2*step], the sampler's
+ * logsnr_t) and onehot[B][10]; combine writes emb = t_emb + masked g_emb and semb = silu(emb); combine_bwd inverts. */
+typedef struct {
+  const float* t;
+  const float* sched;
+  const int* step_dev;
+  const float* freqs;         /* [32], built by the reference expression on the host */
+  const long long* guide;     /* int64 labels, -1 = unconditional; may be NULL */
+  float* sincos;
+  float* onehot;
+  float* t_out;               /* optional [B]: the t actually used */
+  const float* t_emb;
+  const float* g_emb;
+  float* emb;
+  float* semb;
+  const float* d_semb;
+  float* d_emb;
+  float* d_g_emb;
+  int B, E, step, force_uncond;
+} b200_embed_args;
+int b200_embed_prep(const b200_embed_args* a, void* ws, size_t ws_bytes, void* stream);
+int b200_embed_combine(const b200_embed_args* a, void* ws, size_t ws_bytes, void* stream);
+int b200_embed_combine_bwd(const b200_embed_args* a, void* ws, size_t ws_bytes, void* stream);
+
+/* nn.Linear on CUDA cores (fp32): mode 0: Y = act(X) W^T + b; mode 1: dX = (dY W) * act'(X); mode 2: dW += dY^T act(X),
+ * db += colsum(dY).  act: 0 = identity, 1 = SiLU on the input (the nn.SiLU preceding the Linear).  W is [N][K]. */
+typedef struct {
+  const float* X;
+  const float* W;
+  const float* bias;
+  float* Y;
+  const float* dY;
+  float* dX;
+  float* dW;
+  float* db;
+  int M, N, K, act, mode;
+} b200_linear_args;
+int b200_linear(const b200_linear_args* a, void* ws, size_t ws_bytes, void* stream);
+
+/* cudaMemsetAsync(ptr, 0, bytes) on the stream (statistics / gradient arenas; replaces optimizer.zero_grad()). */
+typedef struct {
+  void* ptr;
+  size_t bytes;
+} b200_zero_args;
+int b200_zero(const b200_zero_args* a, void* ws, size_t ws_bytes, void* stream);
+
+/* torch.optim.Adam step (diffusion_model.py:56,71) over flat fp32 buffers; step = 1-based step number (or *step_dev). */
+typedef struct {
+  float* p;
+  const float* g;
+  float* m;
+  float* v;
+  size_t n;
+  float lr, beta1, beta2, eps, grad_scale;
+  const int* step_dev;
+  int step;
+} b200_adam_args;
+int b200_adam(const b200_adam_args* a, void* ws, size_t ws_bytes, void* stream);
 
 #ifdef __cplusplus
 }
