@@ -1,0 +1,398 @@
+"""DiffusionModelB200 — the drop-in for gms/diffusion/diffusion_model.py:14-111 (class DiffusionModel).
+
+Same plugin contract as the reference's `common.GM` subclasses: class attribute `DG`, ctor
+`Model(G=G)`, `loss(x, y) -> (loss, metrics)`, `train_step(x, y) -> metrics`, `sample(n, y)`,
+`evaluate(writer, x, y, epoch)`, `save(path)`, and a `state_dict()` with the reference's 160 `net.*` keys.
+Everything numeric runs in libb200ddpm.so (hand-written sm_100a kernels) through `plan.UNetPlan`; PyTorch supplies
+device memory, the RNG (so that eps / u / per-step noise are the reference's own draws, bit for bit), streams, CUDA
+graphs and the NCCL process group.  There is no CPU / eager fallback: constructing the model on a non-CUDA device
+raises.
+"""
+import ctypes as C
+import random
+from pathlib import Path
+
+import torch
+from torch import nn
+
+from . import lib
+from .plan import Op, UNetPlan, _p, run_ops
+from .schedule import logsnr_schedule_cosine, sampler_table
+from .unet_spec import ParamStore, build_module_tree
+
+MEAN_TYPES = {"eps": 0, "x": 1, "v": 2}
+SAMPLERS = {"ddim": 0, "noisy": 1}
+
+
+class AttrDict(dict):
+    """Same behaviour as gms/common.py:24-26."""
+    __setattr__ = dict.__setitem__
+    __getattr__ = dict.__getitem__
+
+
+def default_G(**over):
+    """The keys gms/main.py:20-40 puts in G that this model reads, with main.py's defaults."""
+    G = AttrDict(lr=3e-4, bs=64, device="cuda", pad32=0, weights_from=Path("."), logdir=Path("logs/"))
+    G.update(DiffusionModelB200.DG)
+    G.update(over)
+    return G
+
+
+class DiffusionModelB200(nn.Module):
+    # every key of the reference's DG (diffusion_model.py:15-29), same python types (they become argparse types)
+    DG = AttrDict()
+    DG.binarize = 0
+    DG.timesteps = 250
+    DG.hidden_size = 128
+    DG.dropout = 0.0
+    DG.sampler = "ddim"
+    DG.mean_type = "v"
+    DG.eval_heavy = 1
+    DG.class_cond = 1
+    DG.sample_cond_w = -1.0
+    DG.cf_drop_prob = 0.1
+    DG.teacher_path = Path(".")
+    DG.teacher_mode = "step1"
+    DG.lr_scheduler = "none"
+    # additions (defaults reproduce the reference's behaviour)
+    DG.graph = 1  # replay the train step / sampler step as CUDA graphs
+
+    def __init__(self, G):
+        super().__init__()
+        self.G = G
+        dev = torch.device(G.device)
+        if dev.type != "cuda":
+            raise lib.B200Error("DiffusionModelB200 runs on a CUDA (sm_100a) device only; there is no CPU fallback")
+        if dev.index is None:
+            dev = torch.device("cuda", torch.cuda.current_device())
+        self.device = dev
+        if G.mean_type not in MEAN_TYPES:
+            raise NotImplementedError(f"mean_type {G.mean_type!r} (the reference's 'both' is broken upstream)")
+        if G.sampler not in SAMPLERS:
+            raise NotImplementedError(f"sampler {G.sampler!r}")
+        if float(G.dropout) != 0.0:
+            raise NotImplementedError("dropout != 0 is not on the DDPM hot path (reference default is 0.0)")
+        if Path(G.teacher_path) != Path("."):
+            raise NotImplementedError("progressive distillation (teacher_path) is out of scope (SURVEY.md §8f)")
+        rc = lib.load().b200_init(dev.index)
+        if rc != 0:
+            raise lib.B200Error(f"b200_init failed: {lib.load().b200_last_error().decode()}")
+        self.size = 32 if G.pad32 else 28
+        self.store = ParamStore(G.hidden_size, dev)
+        self.store.init_like_reference()
+        self.net = build_module_tree(self.store, nn.Module())
+        self.optimizer = None  # the fused flat Adam below replaces torch.optim.Adam (diffusion_model.py:56)
+        self.store.ensure_adam_state()
+        self.adam_step = torch.zeros(1, dtype=torch.int32, device=dev)
+        self._plans = {}
+        self._tables = {}
+        self._train_graphs = {}
+        self.use_graph = bool(G.get("graph", 1))
+
+    # ------------------------------------------------------------------ plumbing
+    def _stream(self):
+        return C.c_void_p(torch.cuda.current_stream(self.device).cuda_stream)
+
+    def _apply(self, fn, recurse=True):
+        """`.to(device)` from gms/main.py:78 must not re-allocate: parameters are views of the flat store."""
+        probe = fn(torch.empty(0, device=self.device))
+        if probe.device != self.device or probe.dtype != torch.float32:
+            raise lib.B200Error("DiffusionModelB200 parameters live in one flat fp32 CUDA buffer; cannot move/cast them")
+        return self
+
+    def save(self, path, test_x=None, test_y=None):
+        """gms/common.py:154-156."""
+        torch.save(self.state_dict(), Path(path) / "model.pt")
+
+    def _table(self, T):
+        if T not in self._tables:
+            self._tables[T] = sampler_table(T, self.device)
+        return self._tables[T]
+
+    def _plan(self, B, kind):
+        """kind: 'train' | 'loss' | 'sample'.  At most two plans per kind are kept (activations are large)."""
+        key = (kind, B, self.size, int(self.G.timesteps))
+        p = self._plans.get(key)
+        if p is not None:
+            return p
+        same = [k for k in self._plans if k[0] == kind]
+        if len(same) >= 2:
+            old = same[0]
+            del self._plans[old]
+            self._train_graphs.pop(old, None)
+            torch.cuda.empty_cache()
+        p = _Bound(self, B, kind)
+        self._plans[key] = p
+        return p
+
+    # ------------------------------------------------------------------ training
+    def loss(self, x, y, eps=None, u=None):
+        """diffusion_model.py:76-80 → gaussian_diffusion.py:81-100,156-172.  Forward only (the reference's callers
+        use it under no_grad, main.py:163-176); the optimiser path is train_step.  `eps` / `u` inject the random
+        draws (tests); by default they are drawn like the reference: randn(x.shape) then rand(B)."""
+        b = self._plan(x.shape[0], "loss")
+        b.stage_inputs(x, y, eps, u)
+        st = self._stream()
+        run_ops(b.pre_ops, st)
+        b.plan.forward(st)
+        run_ops(b.loss_ops, st)
+        loss = b.loss_mean[0].clone()
+        return loss, {"loss": loss}
+
+    def train_step(self, x, y, eps=None, u=None):
+        """diffusion_model.py:63-74: class-label drop, loss, backward, Adam.  fp32 storage with TF32 tensor-core
+        convolutions needs no loss scaling, so `loss_scale` is reported as 1."""
+        if y is not None:
+            # same CPU-generator draw and in-place edit of the caller's y as diffusion_model.py:67
+            y[torch.rand(y.shape[0]) < self.G.cf_drop_prob] = -1
+        b = self._plan(x.shape[0], "train")
+        b.stage_inputs(x, y, eps, u)
+        world = torch.distributed.get_world_size() if torch.distributed.is_initialized() else 1
+        b.set_adam(float(self.G.lr), 1.0 / world)
+        if self.use_graph:
+            b.run_graphed(b.enqueue_fwd_bwd, "fwd_bwd")
+        else:
+            b.enqueue_fwd_bwd()
+        if world > 1:
+            # the one collective of the path: sum of the flat fp32 gradient over NVLink
+            torch.distributed.all_reduce(self.store.grad)
+        if self.use_graph:
+            b.run_graphed(b.enqueue_adam, "adam")
+        else:
+            b.enqueue_adam()
+        return {"loss": b.loss_mean[0].clone(), "loss_scale": torch.tensor(1.0)}
+
+    def loss_and_grads(self, x, y, eps=None, u=None):
+        """loss + backward without the optimiser step (parity tests: compare store.grad views with autograd)."""
+        b = self._plan(x.shape[0], "train")
+        b.stage_inputs(x, y, eps, u)
+        b.enqueue_fwd_bwd()
+        return b.loss_mean[0].clone(), b
+
+    # ------------------------------------------------------------------ sampling
+    def _sample_loop(self, init_z, y, cond_w, keep_history=False, noises=None):
+        """gaussian_diffusion.py:245-296 as T replays of one fused step:
+        UNet(z, logsnr_t | y) [+ UNet(z, logsnr_t | uncond)] → randn → b200_sampler_step (x/eps reconstruction,
+        guidance, posterior update, `where(i == 0, x, z_s)`) → device loop index -= 1."""
+        n = init_z.shape[0]
+        T = int(self.G.timesteps)
+        b = self._plan(n, "sample")
+        b.begin_sampling(init_z, y, cond_w)
+        hist = None
+        if keep_history:
+            hist = [torch.empty(T, n, 1, self.size, self.size, device=self.device) for _ in range(3)]
+        noisy = SAMPLERS[self.G.sampler] == 1
+        for k in range(T):
+            if noises is not None and noisy:
+                b.noise.copy_(noises[k].reshape(n, -1))
+                b.enqueue_sampler_step(draw_noise=False)
+            elif self.use_graph:
+                b.run_graphed(b.enqueue_sampler_step, "sampler_step")
+            else:
+                b.enqueue_sampler_step()
+            if hist is not None:
+                hist[0][k].view(n, -1).copy_(b.plan.z_in)
+                hist[1][k].view(n, -1).copy_(b.x_hist)
+                hist[2][k].view(n, -1).copy_(b.e_hist)
+        z = b.plan.z_in.view(n, 1, self.size, self.size).clone()
+        return z, hist
+
+    def sample(self, n, y=None):
+        """diffusion_model.py:82-87.  With labels: classifier-free guidance, per-sample w = 4*rand(n) unless
+        G.sample_cond_w is set (gaussian_diffusion.py:247-257).  y=None (a TypeError in the reference) samples
+        unconditionally without guidance."""
+        with torch.no_grad():
+            noise = torch.randn((n, 1, self.size, self.size), device=self.device)
+            cond_w = None
+            if y is not None:
+                net_cond_w = 4.0 * torch.rand(n, device=self.device)
+                scw = float(self.G.sample_cond_w)
+                cond_w = net_cond_w if scw == -1.0 else torch.full((n,), scw, device=self.device)
+            z, _ = self._sample_loop(noise, y, cond_w)
+            return z
+
+    def sample_trajectory(self, init_z, y=None, cond_w=None, noises=None):
+        """The three [T, n, 1, S, S] histories (z, x, eps) GaussianDiffusion.sample returns (gaussian_diffusion.py:293-296)."""
+        with torch.no_grad():
+            _, hist = self._sample_loop(init_z, y, cond_w, keep_history=True, noises=noises)
+            return hist
+
+    def evaluate(self, writer, x, y, epoch):
+        """diffusion_model.py:89-111: 25 class-conditional, unguided samples from seed 0; grid + three grid-videos."""
+        def proc(t):
+            t = ((t + 1) * 127.5).clamp(0, 255).to(torch.uint8).cpu()
+            if self.G.pad32:
+                t = t[..., 2:-2, 2:-2]
+            return t
+
+        torch.manual_seed(0)
+        noise = torch.randn((25, 1, self.size, self.size), device=self.device)
+        labels = torch.arange(25, dtype=torch.long, device=self.device) % 10
+        zs, xs, eps = self.sample_trajectory(noise, y=labels, cond_w=None)
+        zs, xs, eps = proc(zs), proc(xs), proc(eps)
+        _write_grid(writer, "samples", zs[-1], epoch)
+        _write_gridvid(writer, "sampling_process", zs, epoch)
+        _write_gridvid(writer, "diffusion_model/eps", eps, epoch)
+        _write_gridvid(writer, "diffusion_model/x", xs, epoch)
+        torch.manual_seed(random.randint(0, 2**32))
+
+
+def _grid(x):
+    """'(n1 n2) c h w -> c (n1 h) (n2 w)' with n1 = n2 = 5 (gms/common.py:177-180) without einops."""
+    n, c, h, w = x.shape[-4:]
+    lead = x.shape[:-4]
+    x = x.reshape(*lead, 5, 5, c, h, w)
+    nd = len(lead)
+    x = x.permute(*range(nd), nd + 2, nd + 0, nd + 3, nd + 1, nd + 4)
+    return x.reshape(*lead, c, 5 * h, 5 * w)
+
+
+def _write_grid(writer, tag, x, epoch):
+    writer.add_image(tag, _grid(x), epoch)
+
+
+def _write_gridvid(writer, tag, x, epoch):
+    """gms/common.py:183-193."""
+    T = x.shape[0]
+    vid = _grid(x)[None].repeat(1, 1, 3, 1, 1)
+    writer.add_video(tag, vid, epoch, fps=min(T // 3, 60))
+
+
+class _Bound:
+    """A UNetPlan bound to the diffusion-level buffers and ops of one use: 'train', 'loss' or 'sample'."""
+
+    def __init__(self, model, B, kind):
+        self.m = model
+        self.B, self.kind = B, kind
+        dev = model.device
+        S = model.size
+        D = S * S
+        G = model.G
+        f32 = dict(dtype=torch.float32, device=dev)
+        self.graphs = {}
+        mt = MEAN_TYPES[G.mean_type]
+        if kind == "sample":
+            T = int(G.timesteps)
+            self.sched = model._table(T)
+            self.step_dev = torch.zeros(1, dtype=torch.int32, device=dev)
+            self.plan = UNetPlan(model.store, B, S, train=False, sched=self.sched, step_dev=self.step_dev)
+            self.noise = torch.zeros(B, D, **f32)
+            self.cond_w = torch.zeros(B, **f32)
+            self.x_hist = torch.zeros(B, D, **f32)
+            self.e_hist = torch.zeros(B, D, **f32)
+            self.guided = False
+            self.T = T
+            p = self.plan
+
+            def step_args(guided):
+                return lib.SamplerStepArgs(z=_p(p.z_in), out_c=_p(p.out), out_u=_p(p.out2) if guided else None,
+                                           cond_w=_p(self.cond_w) if guided else None, noise=_p(self.noise),
+                                           sched=_p(self.sched), step_dev=_p(self.step_dev), z_next=_p(p.z_in),
+                                           x_hist=_p(self.x_hist), e_hist=_p(self.e_hist), n=B, D=D, step=0,
+                                           mean_type=mt, sampler=SAMPLERS[G.sampler])
+            self.step_ops = {g: [Op("b200_sampler_step", step_args(g)),
+                                 Op("b200_step_advance", lib.StepAdvanceArgs(step_dev=_p(self.step_dev)))]
+                             for g in (False, True)}
+            return
+        self.plan = UNetPlan(model.store, B, S, train=(kind == "train"))
+        p = self.plan
+        self.x = torch.zeros(B, D, **f32)
+        self.eps = torch.zeros(B, D, **f32)
+        self.u = torch.zeros(B, **f32)
+        self.loss_b = torch.zeros(B, **f32)
+        self.mse2 = torch.zeros(B, 2, **f32)
+        self.loss_mean = torch.zeros(1, **f32)
+        qa = lib.QSampleArgs(x=_p(self.x), eps=_p(self.eps), logsnr=_p(p.t), z=_p(p.z_in), B=B, D=D)
+        self.pre_ops = [Op("b200_q_sample", qa)]
+        la = lib.LossArgs(out=_p(p.out), z=_p(p.z_in), x=_p(self.x), eps=_p(self.eps), logsnr=_p(p.t),
+                          loss_b=_p(self.loss_b), mse2=_p(self.mse2), dout=_p(p.dout) if kind == "train" else None,
+                          loss_mean=_p(self.loss_mean), B=B, D=D, mean_type=mt, grad_scale=1.0 / B)
+        self.loss_ops = [Op("b200_loss", la)]
+        if kind == "train":
+            st = model.store
+            self.zero_ops = [Op("b200_zero", lib.ZeroArgs(ptr=_p(st.grad), bytes=st.numel * 4))]
+            self.adam_args = lib.AdamArgs(p=_p(st.flat), g=_p(st.grad), m=_p(st.exp_avg), v=_p(st.exp_avg_sq),
+                                          n=st.numel, lr=3e-4, beta1=0.9, beta2=0.999, eps=1e-8, grad_scale=1.0,
+                                          step_dev=_p(model.adam_step), step=0)
+            self.adam_ops = [Op("b200_int_increment", lib.StepAdvanceArgs(step_dev=_p(model.adam_step))),
+                             Op("b200_adam", self.adam_args)]
+
+    # ---- inputs
+    def stage_inputs(self, x, y, eps, u):
+        """Copy the batch into the plan's static buffers and draw eps / u in the reference's order
+        (gaussian_diffusion.py:83 randn(x.shape) first, :94 rand(B) second) from the device's default generator."""
+        B = self.B
+        assert x.shape[0] == B and x.dtype in (torch.float32, torch.float64)
+        self.x.copy_(x.reshape(B, -1))
+        if eps is None:
+            self.eps.normal_()
+        else:
+            self.eps.copy_(eps.reshape(B, -1))
+        if u is None:
+            self.u.uniform_()
+        else:
+            self.u.copy_(u)
+        # logsnr via the reference's torch expression (diffusion_utils.py:198-201): bit-identical per sample
+        self.plan.t.copy_(logsnr_schedule_cosine(self.u))
+        if y is None:
+            self.plan.guide.fill_(-1)
+        else:
+            self.plan.guide.copy_(y)
+
+    def set_adam(self, lr, grad_scale):
+        if self.adam_args.lr != lr or self.adam_args.grad_scale != grad_scale:
+            self.adam_args.lr = lr
+            self.adam_args.grad_scale = grad_scale
+            self.graphs.pop("adam", None)  # kernel parameters are baked into a captured graph
+
+    # ---- enqueue
+    def enqueue_fwd_bwd(self):
+        st = self.m._stream()
+        run_ops(self.zero_ops, st)
+        run_ops(self.pre_ops, st)
+        self.plan.forward(st)
+        run_ops(self.loss_ops, st)
+        self.plan.backward(st)
+
+    def enqueue_adam(self):
+        run_ops(self.adam_ops, self.m._stream())
+
+    def begin_sampling(self, init_z, y, cond_w):
+        B = self.B
+        self.plan.z_in.copy_(init_z.reshape(B, -1))
+        if y is None:
+            self.plan.guide.fill_(-1)
+        else:
+            self.plan.guide.copy_(y)
+        guided = cond_w is not None
+        if guided:
+            self.cond_w.copy_(cond_w)
+        if guided != self.guided:
+            self.guided = guided
+            self.graphs.pop("sampler_step", None)
+            self.graphs.pop(("warm", "sampler_step"), None)
+        self.step_dev.fill_(self.T - 1)
+
+    def enqueue_sampler_step(self, draw_noise=True):
+        st = self.m._stream()
+        self.plan.forward(st)  # conditional eval → plan.out
+        if self.guided:
+            self.plan.forward(st, uncond=True, to_out2=True)  # gaussian_diffusion.py:174-178
+        if draw_noise and SAMPLERS[self.m.G.sampler] == 1:
+            self.noise.normal_()  # drawn after the net evals, like gaussian_diffusion.py:241
+        run_ops(self.step_ops[self.guided], st)
+
+    # ---- CUDA graphs
+    def run_graphed(self, fn, key):
+        g = self.graphs.get(key)
+        if g is None:
+            if not self.graphs.get(("warm", key)):
+                # first call runs eagerly: it is the warm-up (lazy TMA-descriptor encoding, function attributes)
+                self.graphs[("warm", key)] = True
+                fn()
+                return
+            g = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(g):
+                fn()
+            self.graphs[key] = g
+        g.replay()

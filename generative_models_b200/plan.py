@@ -1,0 +1,479 @@
+"""Static execution plan of the UNet (gms/diffusion/simple_unet.py:16-186) over libb200ddpm.so.
+
+A plan is built once per (batch, image size, train/infer): it owns every activation buffer (allocated by torch,
+handed to the library as raw pointers), every pre-filled C argument struct, and two op lists — forward and, for
+training plans, backward.  Running a plan is a flat loop of `fn(&args, ws, ws_bytes, stream)` C-ABI calls: no
+autograd graph, no per-step allocation, no host<->device sync, so a whole train step or sampler step can be
+captured in a CUDA graph and replayed.
+
+Layout: activations are NHWC fp32 `[B, H*W, C]` pixel rows; the model's 1-channel input/output is `[B, H*W]`
+(NCHW == NHWC when C == 1).  `torch.cat([x, skip], 1)` (simple_unet.py:150) is never materialised: every consumer
+takes two base pointers.  The reverse pass accumulates parameter gradients straight into the flat gradient buffer of
+`unet_spec.ParamStore` (the NCCL allreduce bucket).
+"""
+import ctypes as C
+
+import torch
+
+from . import lib
+from .unet_spec import RESBLOCKS
+
+GN_EPS = 1e-5  # nn.GroupNorm default (simple_unet.py:39,162,169)
+MAX_TIMESTEPS = 256  # simple_unet.py:13
+
+
+def _p(t, off_floats=0):
+    """raw device pointer of a tensor (+ offset in fp32 elements)"""
+    if t is None:
+        return None
+    return C.c_void_p(t.data_ptr() + 4 * off_floats)
+
+
+class Op:
+    __slots__ = ("fn", "ref", "args", "ws", "wsb", "name")
+
+    def __init__(self, name, args, ws=None):
+        self.name = name
+        self.fn = getattr(lib.load(), name)
+        self.args = args  # keep the struct alive
+        self.ref = C.byref(args)
+        self.ws = C.c_void_p(ws.data_ptr()) if ws is not None else None
+        self.wsb = ws.numel() * ws.element_size() if ws is not None else 0
+
+
+def run_ops(ops, stream_ptr):
+    """Enqueue every op on the given raw cudaStream_t; raise on the first rejected call (no fallback)."""
+    for op in ops:
+        rc = op.fn(op.ref, op.ws, op.wsb, stream_ptr)
+        if rc != 0:
+            raise lib.B200Error(f"{op.name} failed (rc={rc}): {lib.load().b200_last_error().decode()}")
+
+
+class _Pool:
+    """Buffer pool: training plans keep every tensor (the backward reads them); inference plans recycle."""
+
+    def __init__(self, device, recycle):
+        self.device = device
+        self.recycle = recycle
+        self.free_list = {}
+        self.all = []
+
+    def get(self, *shape):
+        n = 1
+        for s in shape:
+            n *= s
+        if self.recycle and self.free_list.get(n):
+            return self.free_list[n].pop().view(*shape)
+        t = torch.empty(n, dtype=torch.float32, device=self.device)
+        self.all.append(t)
+        return t.view(*shape)
+
+    def release(self, t):
+        if self.recycle and t is not None:
+            self.free_list.setdefault(t.numel(), []).append(t.view(-1))
+
+    def bytes(self):
+        return sum(t.numel() * 4 for t in self.all)
+
+
+class _Grad:
+    """A gradient tensor seen as [B*HW] pixel rows of 128 channels with a pixel stride (a slice of a wider buffer)."""
+    __slots__ = ("t", "off", "ld")
+
+    def __init__(self, t, off=0, ld=None):
+        self.t = t
+        self.off = off
+        self.ld = ld if ld is not None else t.shape[-1]
+
+    def ptr(self):
+        return _p(self.t, self.off)
+
+
+class UNetPlan:
+    """Forward (and backward) op lists of SimpleUnet for a fixed batch `B` and image side `S`."""
+
+    def __init__(self, store, B, S, train, sched=None, step_dev=None):
+        assert S % 4 == 0, "image side must be divisible by 4 (two stride-2 levels)"
+        self.store = store
+        self.B, self.S, self.train = B, S, train
+        self.Cc = Cc = store.C
+        assert Cc == 128, "the tcgen05 conv kernels are specialised for hidden_size=128 (N tile = 128 channels)"
+        self.E = E = 2 * Cc
+        dev = store.device
+        self.pool = _Pool(dev, recycle=not train)
+        self.gpool = _Pool(dev, recycle=True)
+        f32 = dict(dtype=torch.float32, device=dev)
+        # ---- static inputs / outputs
+        self.z_in = torch.zeros(B, S * S, **f32)
+        self.t = torch.zeros(B, **f32)
+        self.guide = torch.full((B,), -1, dtype=torch.int64, device=dev)
+        self.out = torch.zeros(B, S * S, **f32)
+        self.out2 = torch.zeros(B, S * S, **f32)
+        self.sched, self.step_dev = sched, step_dev
+        self.freqs = torch.exp(
+            -torch.log(torch.tensor(float(MAX_TIMESTEPS))) * torch.arange(0, 32, dtype=torch.float32) / 32
+        ).to(dev)
+        import math
+        # the reference evaluates exp(-math.log(max_period) * arange / half) in fp32 on the CPU (simple_unet.py:216-220)
+        self.freqs = torch.exp(-math.log(MAX_TIMESTEPS) * torch.arange(0, 32, dtype=torch.float32) / 32).to(dev)
+        self.n_stats = 25
+        self.stats = torch.zeros(self.n_stats, B, 64, **f32)
+        self._stat_i = 0
+        self.records = {}
+        self.skips = {}
+        self._build_forward()
+        if train:
+            self.dout = torch.zeros(B, S * S, **f32)
+            self._build_backward()
+
+    # ------------------------------------------------------------------ small constructors
+    def _w(self, name):
+        return C.c_void_p(self.store.ptr(name))
+
+    def _g(self, name):
+        return C.c_void_p(self.store.gptr(name))
+
+    def _next_stats(self):
+        s = self.stats[self._stat_i]
+        self._stat_i += 1
+        return s
+
+    def _conv(self, x, x2, wname, out, H, Ho, R, stride, pad, C1, C2, bias=True, emb=None, residual=None,
+              res_ld=128, x_ld=0, x2_ld=0):
+        a = lib.ConvArgs(x=_p(x), x2=_p(x2), w=self._w(wname + ".weight"), out=_p(out),
+                         bias=self._w(wname + ".bias") if bias else None, emb=emb,
+                         residual=residual, N=self.B, H=H, W=H, C1=C1, C2=C2, Ho=Ho, Wo=Ho, R=R, S=R, stride=stride,
+                         pad=pad, mode=0, w_cout=128, w_cin=C1 + C2, n_off=0, out_ld=128, emb_ld=12 * self.Cc,
+                         res_ld=res_ld, x_ld=x_ld, x2_ld=x2_ld)
+        return Op("b200_conv_igemm", a)
+
+    def _dgrad(self, dy, wname, out, H, R, pad, w_cin, n_off, out_ld, residual=None, res_ld=0):
+        """dy: _Grad with 128 channels; writes 128 input channels [n_off, n_off+128) of `out`."""
+        a = lib.ConvArgs(x=dy.ptr(), x2=None, w=self._w(wname + ".weight"), out=_p(out, n_off), bias=None, emb=None,
+                         residual=residual, N=self.B, H=H, W=H, C1=128, C2=0, Ho=H, Wo=H, R=R, S=R, stride=1, pad=pad,
+                         mode=1, w_cout=128, w_cin=w_cin, n_off=n_off, out_ld=out_ld, emb_ld=0, res_ld=res_ld,
+                         x_ld=dy.ld, x2_ld=0)
+        return Op("b200_conv_igemm", a)
+
+    def _wgrad(self, x, x2, dy, wname, H, Ho, R, stride, pad, C1, C2):
+        a = lib.WgradArgs(x=_p(x), x2=_p(x2), dy=dy.ptr(), dw=self._g(wname + ".weight"), N=self.B, H=H, W=H, C1=C1,
+                          C2=C2, Ho=Ho, Wo=Ho, R=R, S=R, stride=stride, pad=pad, k_slices=0, x_ld=0, x2_ld=0,
+                          dy_ld=dy.ld)
+        return Op("b200_conv_wgrad", a)
+
+    def _gn(self, x, x2, gname, y, HW, C2, stats, silu=1, tf32=1):
+        return lib.GnArgs(x=_p(x), x2=_p(x2), stats=_p(stats), gamma=self._w(gname + ".weight"),
+                          beta=self._w(gname + ".bias"), y=_p(y), N=self.B, HW=HW, C1=128, C2=C2, x_ld=0, x2_ld=0,
+                          eps=GN_EPS, silu=silu, round_tf32=tf32)
+
+    def _linear(self, mode, M, N, K, act, X=None, W=None, bias=None, Y=None, dY=None, dX=None, dW=None, db=None):
+        a = lib.LinearArgs(X=_p(X), W=W, bias=bias, Y=_p(Y), dY=_p(dY), dX=_p(dX), dW=dW, db=db, M=M, N=N, K=K,
+                           act=act, mode=mode)
+        return Op("b200_linear", a)
+
+    # ------------------------------------------------------------------ forward
+    def _build_embed(self, force_uncond):
+        """simple_unet.py:45-58 + the 12 emb_layers (:165-167,183) as one [B,256]x[256,1536] GEMM."""
+        B, E = self.B, self.E
+        st = self.store
+        ops = []
+        ea = lib.EmbedArgs(t=_p(self.t) if self.sched is None else None, sched=_p(self.sched),
+                           step_dev=_p(self.step_dev), freqs=_p(self.freqs), guide=_p(self.guide),
+                           sincos=_p(self.sincos), onehot=_p(self.onehot), t_out=_p(self.t) if self.sched is not None else None,
+                           t_emb=_p(self.temb), g_emb=_p(self.gemb), emb=_p(self.emb), semb=_p(self.semb),
+                           d_semb=None, d_emb=None, d_g_emb=None, B=B, E=E, step=0, force_uncond=force_uncond)
+        ops.append(Op("b200_embed_prep", ea))
+        ops.append(self._linear(0, B, E, 64, 0, X=self.sincos, W=self._w("time_embed.0.weight"),
+                                bias=self._w("time_embed.0.bias"), Y=self.te0))
+        ops.append(self._linear(0, B, E, E, 1, X=self.te0, W=self._w("time_embed.2.weight"),
+                                bias=self._w("time_embed.2.bias"), Y=self.temb))
+        if not force_uncond:
+            ops.append(self._linear(0, B, E, 10, 0, X=self.onehot, W=self._w("guide_embed.0.weight"),
+                                    bias=self._w("guide_embed.0.bias"), Y=self.ge0))
+            ops.append(self._linear(0, B, E, E, 1, X=self.ge0, W=self._w("guide_embed.2.weight"),
+                                    bias=self._w("guide_embed.2.bias"), Y=self.gemb))
+        ops.append(Op("b200_embed_combine", ea))
+        ops.append(self._linear(0, B, 12 * self.Cc, E, 0, X=self.semb, W=C.c_void_p(st.flat.data_ptr() + 4 * st.emb_w_off),
+                                bias=C.c_void_p(st.flat.data_ptr() + 4 * st.emb_b_off), Y=self.embout))
+        return ops
+
+    def _rb_fwd(self, ops, name, x, x2, H):
+        """ResBlock (simple_unet.py:155-186): GN-SiLU-conv3x3 (+emb) - GN-SiLU-conv3x3 (+skip)."""
+        B, HW = self.B, H * H
+        k = RESBLOCKS.index(name)
+        C2 = 128 if x2 is not None else 0
+        Cin = 128 + C2
+        pool = self.pool
+        st1, st2 = self._next_stats(), self._next_stats()
+        a1 = pool.get(B, HW, Cin)
+        g1 = self._gn(x, x2, name + ".in_layers.0", a1, HW, C2, st1)
+        ops.append(Op("b200_gn_stats", g1))
+        ops.append(Op("b200_gn_apply", g1))
+        h1 = pool.get(B, HW, 128)
+        ops.append(self._conv(a1, None, name + ".in_layers.2", h1, H, H, 3, 1, 1, Cin, 0,
+                              emb=_p(self.embout, k * 128)))
+        pool.release(a1)
+        a2 = pool.get(B, HW, 128)
+        g2 = self._gn(h1, None, name + ".out_layers.0", a2, HW, 0, st2)
+        ops.append(Op("b200_gn_stats", g2))
+        ops.append(Op("b200_gn_apply", g2))
+        pool.release(h1)
+        skip = None
+        if x2 is not None:
+            skip = pool.get(B, HW, 128)
+            ops.append(self._conv(x, x2, name + ".skip_connection", skip, H, H, 1, 1, 0, 128, 128))
+            residual = skip
+        else:
+            residual = x
+        out = pool.get(B, HW, 128)
+        ops.append(self._conv(a2, None, name + ".out_layers.3", out, H, H, 3, 1, 1, 128, 0, residual=_p(residual)))
+        pool.release(a2)
+        pool.release(skip)
+        self.records[name] = dict(x=x, x2=x2, H=H, a1=a1, h1=h1, a2=a2, g1=g1, g2=g2, k=k)
+        return out
+
+    def _build_forward(self):
+        B, S, E = self.B, self.S, self.E
+        dev = self.store.device
+        f32 = dict(dtype=torch.float32, device=dev)
+        for nm, w in (("sincos", 64), ("onehot", 10), ("te0", E), ("temb", E), ("ge0", E), ("gemb", E), ("emb", E),
+                      ("semb", E), ("embout", 12 * self.Cc)):
+            setattr(self, nm, torch.zeros(B, w, **f32))
+        self.embed_ops = [self._build_embed(0), self._build_embed(1)]
+        ops = []
+        za = lib.ZeroArgs(ptr=_p(self.stats), bytes=self.stats.numel() * 4)
+        ops.append(Op("b200_zero", za))
+        pool = self.pool
+        H0, H1, H2 = S, S // 2, S // 4
+        # ---- Down (simple_unet.py:87-109)
+        d0 = pool.get(B, H0 * H0, 128)
+        cin = lib.ConvInArgs(x=_p(self.z_in), w=self._w("down.seq.0.conv.weight"), bias=self._w("down.seq.0.conv.bias"),
+                             out=_p(d0), dy=None, dw=None, db=None, N=B, H=H0, W=H0)
+        ops.append(Op("b200_conv_in_fwd", cin))
+        d1 = self._rb_fwd(ops, "down.seq.1", d0, None, H0)
+        d2 = self._rb_fwd(ops, "down.seq.2", d1, None, H0)
+        d3 = pool.get(B, H1 * H1, 128)
+        ops.append(self._conv(d2, None, "down.seq.3.conv", d3, H0, H1, 3, 2, 1, 128, 0))
+        d4 = self._rb_fwd(ops, "down.seq.4", d3, None, H1)
+        d5 = self._rb_fwd(ops, "down.seq.5", d4, None, H1)
+        d6 = pool.get(B, H2 * H2, 128)
+        ops.append(self._conv(d5, None, "down.seq.6.conv", d6, H1, H2, 3, 2, 1, 128, 0))
+        # ---- turn (simple_unet.py:36,68)
+        t = self._rb_fwd(ops, "turn", d6, None, H2)
+        # ---- Up (simple_unet.py:125-152): block i consumes cat([h, cache.pop()])
+        r0 = self._rb_fwd(ops, "up.seq.0.0", t, d6, H2)
+        pool.release(t), pool.release(d6)
+        up0 = pool.get(B, H1 * H1, 128)
+        ops.append(Op("b200_upsample2x", lib.ResampleArgs(in_=_p(r0), out=_p(up0), N=B, H=H2, W=H2, C=128, in_ld=0, mode=0)))
+        pool.release(r0)
+        u0 = pool.get(B, H1 * H1, 128)
+        ops.append(self._conv(up0, None, "up.seq.0.1.conv", u0, H1, H1, 3, 1, 1, 128, 0))
+        pool.release(up0)
+        u1 = self._rb_fwd(ops, "up.seq.1", u0, d5, H1)
+        pool.release(u0), pool.release(d5)
+        u2 = self._rb_fwd(ops, "up.seq.2", u1, d4, H1)
+        pool.release(u1), pool.release(d4)
+        r3 = self._rb_fwd(ops, "up.seq.3.0", u2, d3, H1)
+        pool.release(u2), pool.release(d3)
+        up3 = pool.get(B, H0 * H0, 128)
+        ops.append(Op("b200_upsample2x", lib.ResampleArgs(in_=_p(r3), out=_p(up3), N=B, H=H1, W=H1, C=128, in_ld=0, mode=0)))
+        pool.release(r3)
+        u3 = pool.get(B, H0 * H0, 128)
+        ops.append(self._conv(up3, None, "up.seq.3.1.conv", u3, H0, H0, 3, 1, 1, 128, 0))
+        pool.release(up3)
+        u4 = self._rb_fwd(ops, "up.seq.4", u3, d2, H0)
+        pool.release(u3), pool.release(d2)
+        u5 = self._rb_fwd(ops, "up.seq.5", u4, d1, H0)
+        pool.release(u4), pool.release(d1)
+        u6 = self._rb_fwd(ops, "up.seq.6", u5, d0, H0)
+        pool.release(u5), pool.release(d0)
+        # ---- out head (simple_unet.py:38-42,70)
+        sth = self._next_stats()
+        ah = pool.get(B, H0 * H0, 128)
+        gh = self._gn(u6, None, "out.0", ah, H0 * H0, 0, sth, silu=1, tf32=0)
+        ops.append(Op("b200_gn_stats", gh))
+        ops.append(Op("b200_gn_apply", gh))
+        self.body_ops = ops
+        self.head_ops = []
+        for o in (self.out, self.out2):
+            ca = lib.ConvOutArgs(h=_p(ah), w=self._w("out.2.weight"), bias=self._w("out.2.bias"), out=_p(o), dout=None,
+                                 dh=None, dw=None, db=None, N=B, H=H0, W=H0)
+            self.head_ops.append(Op("b200_conv_out_fwd", ca))
+        self.saved = dict(d0=d0, d1=d1, d2=d2, d3=d3, d4=d4, d5=d5, d6=d6, t=t, r0=r0, up0=up0, u0=u0, u1=u1, u2=u2,
+                          r3=r3, up3=up3, u3=u3, u4=u4, u5=u5, u6=u6, ah=ah, gh=gh)
+
+    def forward(self, stream_ptr, uncond=False, to_out2=False):
+        """Enqueue embeddings + UNet body + head.  Inputs are the static buffers z_in / t (or sched+step_dev) / guide."""
+        run_ops(self.embed_ops[1 if uncond else 0], stream_ptr)
+        run_ops(self.body_ops, stream_ptr)
+        run_ops(self.head_ops[1 if to_out2 else 0:][:1], stream_ptr)
+
+    # ------------------------------------------------------------------ backward
+    def _gn_bwd(self, ops, g_fwd, dy, dx, gname, add1=None, add2=None, add_c=0):
+        a = lib.GnBwdArgs(fwd=g_fwd, dy=_p(dy), dx=_p(dx), add1=add1.ptr() if add1 else None,
+                          add2=add2.ptr() if add2 else None, add1_ld=add1.ld if add1 else 0,
+                          add2_ld=add2.ld if add2 else 0, add_c=add_c, dgamma=self._g(gname + ".weight"),
+                          dbeta=self._g(gname + ".bias"))
+        ops.append(Op("b200_gn_bwd", a, ws=self.gn_ws))
+
+    def _colsum(self, ops, dy, HW, per_sample=None, ps_ld=0, total1=None, total2=None):
+        a = lib.ColsumArgs(dy=dy.ptr(), per_sample=per_sample, total1=total1, total2=total2, N=self.B, HW=HW, ld=dy.ld,
+                           ps_ld=ps_ld)
+        ops.append(Op("b200_colsum", a))
+
+    def _rb_bwd(self, ops, name, dOut, extra=None):
+        """Reverse of _rb_fwd.  dOut: _Grad w.r.t. the block output; extra: _Grad that also flows into the block
+        input (the skip-concat consumer of a Down tensor).  Returns the dense [B,HW,Cin] gradient of the input."""
+        r = self.records[name]
+        B, H = self.B, r["H"]
+        HW = H * H
+        x, x2 = r["x"], r["x2"]
+        Cin = 256 if x2 is not None else 128
+        gp = self.gpool
+        has_skip = x2 is not None
+        # conv2 (out_layers.3): bias, weight, data gradients
+        self._colsum(ops, dOut, HW, total1=self._g(name + ".out_layers.3.bias"),
+                     total2=self._g(name + ".skip_connection.bias") if has_skip else None)
+        ops.append(self._wgrad(r["a2"], None, dOut, name + ".out_layers.3", H, H, 3, 1, 1, 128, 0))
+        da2 = gp.get(B, HW, 128)
+        ops.append(self._dgrad(dOut, name + ".out_layers.3", da2, H, 3, 1, 128, 0, 128))
+        dh1 = gp.get(B, HW, 128)
+        self._gn_bwd(ops, r["g2"], da2, dh1, name + ".out_layers.0")
+        gp.release(da2)
+        # emb_out broadcast add (simple_unet.py:183-184) and conv1 bias
+        dh1g = _Grad(dh1)
+        self._colsum(ops, dh1g, HW, per_sample=_p(self.d_embout, r["k"] * 128), ps_ld=12 * self.Cc,
+                     total1=self._g(name + ".in_layers.2.bias"))
+        ops.append(self._wgrad(r["a1"], None, dh1g, name + ".in_layers.2", H, H, 3, 1, 1, Cin, 0))
+        da1 = gp.get(B, HW, Cin)
+        for n_off in range(0, Cin, 128):
+            ops.append(self._dgrad(dh1g, name + ".in_layers.2", da1, H, 3, 1, Cin, n_off, Cin))
+        gp.release(dh1)
+        dsk = None
+        if has_skip:
+            dsk = gp.get(B, HW, 256)
+            for n_off in (0, 128):
+                ops.append(self._dgrad(dOut, name + ".skip_connection", dsk, H, 1, 0, 256, n_off, 256))
+            ops.append(self._wgrad(x, x2, dOut, name + ".skip_connection", H, H, 1, 1, 0, 128, 128))
+            add1, add_c = _Grad(dsk), 256
+        else:
+            add1, add_c = dOut, 128
+        dx = (self.pool_dcat if has_skip else gp).get(B, HW, Cin)
+        self._gn_bwd(ops, r["g1"], da1, dx, name + ".in_layers.0", add1=add1, add2=extra, add_c=add_c)
+        gp.release(da1)
+        gp.release(dsk)
+        return dx
+
+    def _conv_bwd(self, ops, name, x, dy, H, Ho, stride, residual=None):
+        """Backward of a plain 3x3 conv layer (Downsample / Upsample conv).  dy: _Grad at the output resolution.
+        Returns the dense input gradient (+ residual: another _Grad flowing into the same tensor)."""
+        B = self.B
+        gp = self.gpool
+        self._colsum(ops, dy, Ho * Ho, total1=self._g(name + ".bias"))
+        ops.append(self._wgrad(x, None, dy, name, H, Ho, 3, stride, 1, 128, 0))
+        src, zs = dy, None
+        if stride == 2:
+            # zero-stuff dY to the input resolution so the stride-1 dgrad kernel applies
+            zs = gp.get(B, H * H, 128)
+            ops.append(Op("b200_upsample2x", lib.ResampleArgs(in_=dy.ptr(), out=_p(zs), N=B, H=H, W=H, C=128,
+                                                              in_ld=dy.ld, mode=2)))
+            src = _Grad(zs)
+        dx = gp.get(B, H * H, 128)
+        ops.append(self._dgrad(src, name, dx, H, 3, 1, 128, 0, 128,
+                               residual=residual.ptr() if residual else None, res_ld=residual.ld if residual else 0))
+        gp.release(zs)
+        return dx
+
+    def _build_backward(self):
+        B, S, E = self.B, self.S, self.E
+        st = self.store
+        dev = st.device
+        f32 = dict(dtype=torch.float32, device=dev)
+        H0, H1, H2 = S, S // 2, S // 4
+        sv = self.saved
+        gp = self.gpool
+        self.pool_dcat = _Pool(dev, recycle=False)  # concat gradients live until the Down path consumes their 2nd half
+        self.gn_ws = torch.zeros(B * 64, **f32)
+        self.d_embout = torch.zeros(B, 12 * self.Cc, **f32)
+        for nm in ("d_semb", "d_emb", "d_gemb", "d_te0", "d_ge0"):
+            setattr(self, nm, torch.zeros(B, E, **f32))
+        ops = []
+        ops.append(Op("b200_zero", lib.ZeroArgs(ptr=_p(self.d_embout), bytes=self.d_embout.numel() * 4)))
+        # ---- out head
+        dah = gp.get(B, H0 * H0, 128)
+        ca = lib.ConvOutArgs(h=_p(sv["ah"]), w=self._w("out.2.weight"), bias=self._w("out.2.bias"), out=None,
+                             dout=_p(self.dout), dh=_p(dah), dw=self._g("out.2.weight"), db=self._g("out.2.bias"), N=B,
+                             H=H0, W=H0)
+        ops.append(Op("b200_conv_out_bwd", ca))
+        du6 = gp.get(B, H0 * H0, 128)
+        self._gn_bwd(ops, sv["gh"], dah, du6, "out.0")
+        gp.release(dah)
+        # ---- Up, reversed
+        half = lambda t: _Grad(t, 0, 256)       # gradient of the running tensor h
+        tail = lambda t: _Grad(t, 128, 256)     # gradient of the cached Down tensor
+        dc6 = self._rb_bwd(ops, "up.seq.6", _Grad(du6))
+        gp.release(du6)
+        dc5 = self._rb_bwd(ops, "up.seq.5", half(dc6))
+        dc4 = self._rb_bwd(ops, "up.seq.4", half(dc5))
+        dup3 = self._conv_bwd(ops, "up.seq.3.1.conv", sv["up3"], half(dc4), H0, H0, 1)
+        dr3 = gp.get(B, H1 * H1, 128)
+        ops.append(Op("b200_upsample2x", lib.ResampleArgs(in_=_p(dup3), out=_p(dr3), N=B, H=H1, W=H1, C=128, in_ld=0, mode=1)))
+        gp.release(dup3)
+        dc3 = self._rb_bwd(ops, "up.seq.3.0", _Grad(dr3))
+        gp.release(dr3)
+        dc2 = self._rb_bwd(ops, "up.seq.2", half(dc3))
+        dc1 = self._rb_bwd(ops, "up.seq.1", half(dc2))
+        dup0 = self._conv_bwd(ops, "up.seq.0.1.conv", sv["up0"], half(dc1), H1, H1, 1)
+        dr0 = gp.get(B, H2 * H2, 128)
+        ops.append(Op("b200_upsample2x", lib.ResampleArgs(in_=_p(dup0), out=_p(dr0), N=B, H=H2, W=H2, C=128, in_ld=0, mode=1)))
+        gp.release(dup0)
+        dc0 = self._rb_bwd(ops, "up.seq.0.0", _Grad(dr0))
+        gp.release(dr0)
+        # ---- turn, then Down reversed; each Down tensor also receives the tail of its concat consumer
+        dd6 = self._rb_bwd(ops, "turn", half(dc0), extra=tail(dc0))
+        dd5 = self._conv_bwd(ops, "down.seq.6.conv", sv["d5"], _Grad(dd6), H1, H2, 2, residual=tail(dc1))
+        gp.release(dd6)
+        dd4 = self._rb_bwd(ops, "down.seq.5", _Grad(dd5), extra=tail(dc2))
+        gp.release(dd5)
+        dd3 = self._rb_bwd(ops, "down.seq.4", _Grad(dd4), extra=tail(dc3))
+        gp.release(dd4)
+        dd2 = self._conv_bwd(ops, "down.seq.3.conv", sv["d2"], _Grad(dd3), H0, H1, 2, residual=tail(dc4))
+        gp.release(dd3)
+        dd1 = self._rb_bwd(ops, "down.seq.2", _Grad(dd2), extra=tail(dc5))
+        gp.release(dd2)
+        dd0 = self._rb_bwd(ops, "down.seq.1", _Grad(dd1), extra=tail(dc6))
+        gp.release(dd1)
+        cin = lib.ConvInArgs(x=_p(self.z_in), w=self._w("down.seq.0.conv.weight"), bias=None, out=None, dy=_p(dd0),
+                             dw=self._g("down.seq.0.conv.weight"), db=self._g("down.seq.0.conv.bias"), N=B, H=H0, W=H0)
+        ops.append(Op("b200_conv_in_bwd", cin))
+        gp.release(dd0)
+        # ---- embeddings (simple_unet.py:45-58 and the emb_layers), reversed
+        embw = C.c_void_p(st.flat.data_ptr() + 4 * st.emb_w_off)
+        ops.append(self._linear(2, B, 12 * self.Cc, E, 0, X=self.semb, W=embw, dY=self.d_embout,
+                                dW=C.c_void_p(st.grad.data_ptr() + 4 * st.emb_w_off),
+                                db=C.c_void_p(st.grad.data_ptr() + 4 * st.emb_b_off)))
+        ops.append(self._linear(1, B, 12 * self.Cc, E, 0, W=embw, dY=self.d_embout, dX=self.d_semb))
+        ea = lib.EmbedArgs(t=None, sched=None, step_dev=None, freqs=_p(self.freqs), guide=_p(self.guide), sincos=None,
+                           onehot=None, t_out=None, t_emb=None, g_emb=None, emb=_p(self.emb), semb=None,
+                           d_semb=_p(self.d_semb), d_emb=_p(self.d_emb), d_g_emb=_p(self.d_gemb), B=B, E=E, step=0,
+                           force_uncond=0)
+        ops.append(Op("b200_embed_combine_bwd", ea))
+        for pre, dY, X0, K0, dmid in (("time_embed", self.d_emb, self.sincos, 64, self.d_te0),
+                                      ("guide_embed", self.d_gemb, self.onehot, 10, self.d_ge0)):
+            mid = self.te0 if pre == "time_embed" else self.ge0
+            ops.append(self._linear(2, B, E, E, 1, X=mid, W=self._w(pre + ".2.weight"), dY=dY,
+                                    dW=self._g(pre + ".2.weight"), db=self._g(pre + ".2.bias")))
+            ops.append(self._linear(1, B, E, E, 1, X=mid, W=self._w(pre + ".2.weight"), dY=dY, dX=dmid))
+            ops.append(self._linear(2, B, E, K0, 0, X=X0, W=self._w(pre + ".0.weight"), dY=dmid,
+                                    dW=self._g(pre + ".0.weight"), db=self._g(pre + ".0.bias")))
+        self.bwd_ops = ops
+
+    def backward(self, stream_ptr):
+        """Enqueue the reverse pass: reads self.dout, accumulates into store.grad (caller zeroes it once per step)."""
+        run_ops(self.bwd_ops, stream_ptr)
+
+    def activation_bytes(self):
+        n = self.pool.bytes() + self.gpool.bytes()
+        if self.train:
+            n += self.pool_dcat.bytes()
+        return n

@@ -1,0 +1,290 @@
+"""-m gpu parity of the tensor-core convolutions (fprop / dgrad / wgrad), GroupNorm+SiLU, the edge convs and the glue
+kernels, through the C ABI, against fp32 CPU torch (the operators oracle/ddpm_oracle.py is made of).
+Tolerance for TF32 tensor-core results: 2e-3 of max|ref| (TF32 keeps 10 mantissa bits: inputs carry 2^-11 relative
+rounding each; K up to 2304 products accumulate in fp32).  fp32 CUDA-core kernels: 1e-5."""
+import pytest
+import torch
+import torch.nn.functional as F
+
+from tests.gpu_util import nhwc, ptr, rel, stream, w_khwc
+
+pytestmark = pytest.mark.gpu
+DEV = "cuda:0"
+TF32_TOL = 2e-3
+
+
+@pytest.fixture(scope="module")
+def lib(built_lib):
+    built_lib.load().b200_init(0)
+    return built_lib
+
+
+def rn(g, *s):
+    return torch.randn(*s, generator=g)
+
+
+def run_fprop(lib, x, w, stride, pad, x2=None, bias=None, emb=None, residual=None):
+    N, C1, H, W = x.shape
+    C2 = 0 if x2 is None else x2.shape[1]
+    R = w.shape[2]
+    Ho = (H + 2 * pad - R) // stride + 1
+    xh = nhwc(x).to(DEV)
+    x2h = nhwc(x2).to(DEV) if x2 is not None else None
+    wk = w_khwc(w).to(DEV)
+    out = torch.full((N, Ho, Ho, 128), float("nan"), device=DEV)
+    resh = nhwc(residual).to(DEV) if residual is not None else None
+    bd = bias.to(DEV) if bias is not None else None
+    ed = emb.to(DEV) if emb is not None else None
+    a = lib.ConvArgs(x=ptr(xh), x2=ptr(x2h), w=ptr(wk), out=ptr(out), bias=ptr(bd), emb=ptr(ed), residual=ptr(resh), N=N,
+                     H=H, W=W, C1=C1, C2=C2, Ho=Ho, Wo=Ho, R=R, S=R, stride=stride, pad=pad, mode=0, w_cout=128,
+                     w_cin=C1 + C2, n_off=0, out_ld=128, emb_ld=128, res_ld=128)
+    lib.call("b200_conv_igemm", a, stream())
+    return out.permute(0, 3, 1, 2).cpu()
+
+
+def run_dgrad(lib, dy, w, pad, residual=None):
+    N, Co, H, W = dy.shape
+    Cin, R = w.shape[1], w.shape[2]
+    dyh = nhwc(dy).to(DEV)
+    wk = w_khwc(w).to(DEV)
+    out = torch.full((N, H, W, Cin), float("nan"), device=DEV)
+    resh = nhwc(residual).to(DEV) if residual is not None else None
+    for n_off in range(0, Cin, 128):
+        a = lib.ConvArgs(x=ptr(dyh), x2=None, w=ptr(wk), out=ptr(out, n_off), bias=None, emb=None,
+                         residual=ptr(resh, n_off) if resh is not None else None, N=N, H=H, W=W, C1=Co, C2=0, Ho=H, Wo=W,
+                         R=R, S=R, stride=1, pad=pad, mode=1, w_cout=Co, w_cin=Cin, n_off=n_off, out_ld=Cin, emb_ld=0,
+                         res_ld=Cin)
+        lib.call("b200_conv_igemm", a, stream())
+    return out.permute(0, 3, 1, 2).cpu()
+
+
+def run_wgrad(lib, x, dy, R, stride, pad, x2=None, k_slices=0):
+    N, C1, H, W = x.shape
+    C2 = 0 if x2 is None else x2.shape[1]
+    Ho = dy.shape[2]
+    xh = nhwc(x).to(DEV)
+    x2h = nhwc(x2).to(DEV) if x2 is not None else None
+    dyh = nhwc(dy).to(DEV)
+    dw = torch.zeros((128, R, R, C1 + C2), device=DEV)
+    a = lib.WgradArgs(x=ptr(xh), x2=ptr(x2h), dy=ptr(dyh), dw=ptr(dw), N=N, H=H, W=W, C1=C1, C2=C2, Ho=Ho, Wo=Ho, R=R,
+                      S=R, stride=stride, pad=pad, k_slices=k_slices)
+    lib.call("b200_conv_wgrad", a, stream())
+    return dw.permute(0, 3, 1, 2).cpu()
+
+
+# (N, H, Cin, R, stride, pad): the layer shapes of Appendix A + ragged tails (M not a multiple of 128)
+FPROP_CASES = [(8, 28, 128, 3, 1, 1), (3, 7, 128, 3, 1, 1), (8, 28, 128, 3, 2, 1), (5, 14, 128, 3, 2, 1),
+               (4, 14, 256, 3, 1, 1), (2, 28, 256, 1, 1, 0), (1, 7, 256, 3, 1, 1), (2, 32, 128, 3, 1, 1),
+               (3, 16, 128, 3, 2, 1)]
+
+
+@pytest.mark.parametrize("N,H,Cin,R,stride,pad", FPROP_CASES)
+def test_conv_fprop(lib, N, H, Cin, R, stride, pad):
+    g = torch.Generator().manual_seed(N * 100 + H)
+    x = rn(g, N, 128, H, H)
+    x2 = rn(g, N, 128, H, H) if Cin == 256 else None
+    w = rn(g, 128, Cin, R, R) / (Cin * R * R) ** 0.5
+    xin = x if x2 is None else torch.cat([x, x2], 1)
+    ref = F.conv2d(xin, w, stride=stride, padding=pad)
+    assert rel(run_fprop(lib, x, w, stride, pad, x2=x2), ref) < TF32_TOL
+
+
+def test_conv_fprop_fused_epilogue(lib):
+    g = torch.Generator().manual_seed(5)
+    x, w = rn(g, 4, 128, 14, 14), rn(g, 128, 128, 3, 3) * 0.03
+    bias, emb, res = rn(g, 128), rn(g, 4, 128), rn(g, 4, 128, 14, 14)
+    ref = F.conv2d(x, w, bias=bias, padding=1) + emb[:, :, None, None] + res
+    assert rel(run_fprop(lib, x, w, 1, 1, bias=bias, emb=emb, residual=res), ref) < TF32_TOL
+
+
+def test_conv_fprop_tap_and_channel_order(lib):
+    """single-tap identity / permutation weights: exact up to TF32 rounding of x, catches swizzle or tap mix-ups."""
+    g = torch.Generator().manual_seed(6)
+    x = rn(g, 2, 128, 14, 14)
+    perm = torch.randperm(128, generator=g)
+    for kh, kw in [(0, 0), (1, 1), (2, 2), (0, 2), (1, 0)]:
+        w = torch.zeros(128, 128, 3, 3)
+        w[torch.arange(128), perm, kh, kw] = 1.0
+        assert rel(run_fprop(lib, x, w, 1, 1), F.conv2d(x, w, padding=1)) < 1e-3
+
+
+@pytest.mark.parametrize("N,H,Cin,R,pad", [(8, 28, 128, 3, 1), (2, 28, 256, 3, 1), (2, 14, 256, 1, 0), (3, 7, 128, 3, 1)])
+def test_conv_dgrad(lib, N, H, Cin, R, pad):
+    g = torch.Generator().manual_seed(N + H)
+    dy = rn(g, N, 128, H, H)
+    w = rn(g, 128, Cin, R, R) / (128 * R * R) ** 0.5
+    res = rn(g, N, Cin, H, H)
+    ref = torch.nn.grad.conv2d_input((N, Cin, H, H), w, dy, padding=pad)
+    assert rel(run_dgrad(lib, dy, w, pad), ref) < TF32_TOL
+    assert rel(run_dgrad(lib, dy, w, pad, residual=res), ref + res) < TF32_TOL
+
+
+@pytest.mark.parametrize("H", [28, 14, 32])
+def test_strided_dgrad_via_zero_stuffing(lib, H):
+    """Downsample conv backward-data: zero-stuff dY to the input resolution, then the stride-1 dgrad kernel."""
+    g = torch.Generator().manual_seed(H)
+    N, Ho = 3, H // 2
+    dy = rn(g, N, 128, Ho, Ho)
+    w = rn(g, 128, 128, 3, 3) * 0.03
+    ref = torch.nn.grad.conv2d_input((N, 128, H, H), w, dy, stride=2, padding=1)
+    dyh = nhwc(dy).to(DEV)
+    zs = torch.full((N, H, H, 128), float("nan"), device=DEV)
+    lib.call("b200_upsample2x", lib.ResampleArgs(in_=ptr(dyh), out=ptr(zs), N=N, H=H, W=H, C=128, in_ld=0, mode=2), stream())
+    got = run_dgrad(lib, zs.permute(0, 3, 1, 2).cpu(), w, 1)
+    assert rel(got, ref) < TF32_TOL
+
+
+@pytest.mark.parametrize("N,H,Cin,R,stride,pad,ks", [(8, 28, 128, 3, 1, 1, 0), (8, 28, 128, 3, 1, 1, 1),
+                                                    (8, 28, 128, 3, 2, 1, 0), (4, 14, 256, 1, 1, 0, 0),
+                                                    (4, 14, 256, 3, 1, 1, 0), (3, 7, 128, 3, 1, 1, 0),
+                                                    (5, 14, 128, 3, 2, 1, 3)])
+def test_conv_wgrad(lib, N, H, Cin, R, stride, pad, ks):
+    g = torch.Generator().manual_seed(N * 7 + H)
+    x = rn(g, N, 128, H, H)
+    x2 = rn(g, N, 128, H, H) if Cin == 256 else None
+    Ho = (H + 2 * pad - R) // stride + 1
+    dy = rn(g, N, 128, Ho, Ho)
+    xin = x if x2 is None else torch.cat([x, x2], 1)
+    ref = torch.nn.grad.conv2d_weight(xin, (128, Cin, R, R), dy, stride=stride, padding=pad)
+    assert rel(run_wgrad(lib, x, dy, R, stride, pad, x2=x2, k_slices=ks), ref) < TF32_TOL
+
+
+# ------------------------------------------------------------------------------------------------ GroupNorm + SiLU
+@pytest.mark.parametrize("N,HW,C2", [(3, 784, 0), (2, 196, 128), (5, 49, 0), (2, 1024, 128)])
+def test_gn_silu_fwd_bwd(lib, N, HW, C2):
+    g = torch.Generator().manual_seed(HW + C2)
+    Cc = 128 + C2
+    x = (rn(g, N, Cc, HW) * 2 + 0.5).requires_grad_(True)
+    gamma = (1 + 0.2 * rn(g, Cc)).requires_grad_(True)
+    beta = (0.1 * rn(g, Cc)).requires_grad_(True)
+    y = F.silu(F.group_norm(x, 32, gamma, beta, eps=1e-5))
+    dy = rn(g, N, Cc, HW)
+    add1 = rn(g, N, Cc, HW)
+    y.backward(dy)
+    xr = x.detach().permute(0, 2, 1).contiguous()  # [N, HW, C]
+    x1 = xr[..., :128].contiguous().to(DEV)
+    x2 = xr[..., 128:].contiguous().to(DEV) if C2 else None
+    stats = torch.zeros(N, 64, device=DEV)
+    yd = torch.full((N, HW, Cc), float("nan"), device=DEV)
+    gd, bd = gamma.detach().to(DEV), beta.detach().to(DEV)
+    a = lib.GnArgs(x=ptr(x1), x2=ptr(x2), stats=ptr(stats), gamma=ptr(gd), beta=ptr(bd), y=ptr(yd), N=N, HW=HW, C1=128,
+                   C2=C2, x_ld=0, x2_ld=0, eps=1e-5, silu=1, round_tf32=0)
+    lib.call("b200_gn_stats", a, stream())
+    lib.call("b200_gn_apply", a, stream())
+    assert rel(yd.cpu().permute(0, 2, 1), y.detach()) < 1e-5
+    # TF32-rounded output: within 2^-11 relative of the unrounded one
+    a.round_tf32 = 1
+    y32 = torch.empty_like(yd)
+    a.y = ptr(y32)
+    lib.call("b200_gn_apply", a, stream())
+    assert ((y32 - yd).abs() <= yd.abs() * 2 ** -11 + 1e-30).all()
+    # backward
+    dyd = dy.permute(0, 2, 1).contiguous().to(DEV)
+    a1 = add1.permute(0, 2, 1).contiguous().to(DEV)
+    dx = torch.full((N, HW, Cc), float("nan"), device=DEV)
+    dgam, dbet = torch.zeros(Cc, device=DEV), torch.zeros(Cc, device=DEV)
+    ws = torch.zeros(N * 64, device=DEV)
+    a.y = ptr(yd)
+    b = lib.GnBwdArgs(fwd=a, dy=ptr(dyd), dx=ptr(dx), add1=ptr(a1), add2=None, add1_ld=Cc, add2_ld=0, add_c=Cc,
+                      dgamma=ptr(dgam), dbeta=ptr(dbet))
+    lib.call("b200_gn_bwd", b, stream(), ws=ptr(ws), ws_bytes=ws.numel() * 4)
+    assert rel(dx.cpu().permute(0, 2, 1), x.grad + add1) < 1e-4
+    assert rel(dgam.cpu(), gamma.grad) < 1e-4
+    assert rel(dbet.cpu(), beta.grad) < 1e-4
+
+
+# ------------------------------------------------------------------------------------------------ edge convs
+@pytest.mark.parametrize("N,H", [(3, 28), (2, 32), (1, 7)])
+def test_conv_in_fwd_bwd(lib, N, H):
+    g = torch.Generator().manual_seed(H)
+    x = rn(g, N, 1, H, H)
+    w = (rn(g, 128, 1, 3, 3) * 0.3).requires_grad_(True)
+    b = rn(g, 128).requires_grad_(True)
+    y = F.conv2d(x, w, b, padding=1)
+    dy = rn(g, N, 128, H, H)
+    y.backward(dy)
+    xd, wd, bd = x.to(DEV).contiguous(), w.detach().reshape(128, 9).contiguous().to(DEV), b.detach().to(DEV)
+    out = torch.full((N, H, H, 128), float("nan"), device=DEV)
+    dyd = nhwc(dy).to(DEV)
+    dw, db = torch.zeros(128, 9, device=DEV), torch.zeros(128, device=DEV)
+    a = lib.ConvInArgs(x=ptr(xd), w=ptr(wd), bias=ptr(bd), out=ptr(out), dy=ptr(dyd), dw=ptr(dw), db=ptr(db), N=N, H=H, W=H)
+    lib.call("b200_conv_in_fwd", a, stream())
+    lib.call("b200_conv_in_bwd", a, stream())
+    assert rel(out.permute(0, 3, 1, 2).cpu(), y.detach()) < 1e-5
+    assert rel(dw.cpu().view(128, 1, 3, 3), w.grad) < 1e-4
+    assert rel(db.cpu(), b.grad) < 1e-4
+
+
+@pytest.mark.parametrize("N,H", [(3, 28), (2, 32)])
+def test_conv_out_fwd_bwd(lib, N, H):
+    g = torch.Generator().manual_seed(H + 1)
+    h = rn(g, N, 128, H, H).requires_grad_(True)
+    w = (rn(g, 1, 128, 3, 3) * 0.05).requires_grad_(True)
+    b = rn(g, 1).requires_grad_(True)
+    y = F.conv2d(h, w, b, padding=1)
+    dout = rn(g, N, 1, H, H)
+    y.backward(dout)
+    hd = nhwc(h.detach()).to(DEV)
+    wd = w_khwc(w.detach()).contiguous().to(DEV)  # [1][3][3][128]
+    bd = b.detach().to(DEV)
+    out = torch.full((N, H * H), float("nan"), device=DEV)
+    dd = dout.reshape(N, H * H).contiguous().to(DEV)
+    dh = torch.full((N, H, H, 128), float("nan"), device=DEV)
+    dw, db = torch.zeros(9 * 128, device=DEV), torch.zeros(1, device=DEV)
+    a = lib.ConvOutArgs(h=ptr(hd), w=ptr(wd), bias=ptr(bd), out=ptr(out), dout=ptr(dd), dh=ptr(dh), dw=ptr(dw), db=ptr(db),
+                        N=N, H=H, W=H)
+    lib.call("b200_conv_out_fwd", a, stream())
+    lib.call("b200_conv_out_bwd", a, stream())
+    assert rel(out.cpu().view(N, 1, H, H), y.detach()) < 1e-5
+    assert rel(dh.permute(0, 3, 1, 2).cpu(), h.grad) < 1e-5
+    assert rel(dw.cpu().view(1, 3, 3, 128).permute(0, 3, 1, 2), w.grad) < 1e-4
+    assert rel(db.cpu(), b.grad) < 1e-4
+
+
+# ------------------------------------------------------------------------------------------------ glue
+def test_upsample_fwd_bwd_colsum(lib):
+    g = torch.Generator().manual_seed(11)
+    N, H = 3, 7
+    x = rn(g, N, 128, H, H).requires_grad_(True)
+    y = F.interpolate(x, scale_factor=2, mode="nearest")
+    dy = rn(g, N, 128, 2 * H, 2 * H)
+    y.backward(dy)
+    xd = nhwc(x.detach()).to(DEV)
+    out = torch.empty(N, 2 * H, 2 * H, 128, device=DEV)
+    lib.call("b200_upsample2x", lib.ResampleArgs(in_=ptr(xd), out=ptr(out), N=N, H=H, W=H, C=128, in_ld=0, mode=0), stream())
+    assert torch.equal(out.permute(0, 3, 1, 2).cpu(), y.detach())
+    dyd = nhwc(dy).to(DEV)
+    din = torch.empty(N, H, H, 128, device=DEV)
+    lib.call("b200_upsample2x", lib.ResampleArgs(in_=ptr(dyd), out=ptr(din), N=N, H=H, W=H, C=128, in_ld=0, mode=1), stream())
+    assert rel(din.permute(0, 3, 1, 2).cpu(), x.grad) < 1e-6
+    # colsum: per-sample and total channel sums of a [N, HW, 128] gradient
+    ps = torch.zeros(N, 1536, device=DEV)
+    t1, t2 = torch.zeros(128, device=DEV), torch.zeros(128, device=DEV)
+    a = lib.ColsumArgs(dy=ptr(dyd), per_sample=ptr(ps, 256), total1=ptr(t1), total2=ptr(t2), N=N, HW=4 * H * H, ld=128, ps_ld=1536)
+    lib.call("b200_colsum", a, stream())
+    assert rel(ps[:, 256:384].cpu(), dy.sum((2, 3))) < 1e-5
+    assert rel(t1.cpu(), dy.sum((0, 2, 3))) < 1e-5 and torch.equal(t1, t2)
+    assert ps[:, :256].abs().max().item() == 0 and ps[:, 384:].abs().max().item() == 0
+
+
+@pytest.mark.parametrize("M,N,K,act", [(5, 256, 64, 0), (33, 256, 256, 1), (7, 256, 10, 0), (16, 1536, 256, 0)])
+def test_linear_modes(lib, M, N, K, act):
+    g = torch.Generator().manual_seed(M + K)
+    X = rn(g, M, K).requires_grad_(True)
+    W = (rn(g, N, K) / K ** 0.5).requires_grad_(True)
+    b = rn(g, N).requires_grad_(True)
+    Y = F.linear(F.silu(X) if act else X, W, b)
+    dY = rn(g, M, N)
+    Y.backward(dY)
+    Xd, Wd, bd, dYd = X.detach().to(DEV), W.detach().to(DEV), b.detach().to(DEV), dY.to(DEV)
+    Yd = torch.empty(M, N, device=DEV)
+    dX = torch.empty(M, K, device=DEV)
+    dW, db = torch.zeros(N, K, device=DEV), torch.zeros(N, device=DEV)
+    for mode in (0, 1, 2):
+        a = lib.LinearArgs(X=ptr(Xd), W=ptr(Wd), bias=ptr(bd), Y=ptr(Yd), dY=ptr(dYd), dX=ptr(dX), dW=ptr(dW), db=ptr(db),
+                           M=M, N=N, K=K, act=act, mode=mode)
+        lib.call("b200_linear", a, stream())
+    assert rel(Yd.cpu(), Y.detach()) < 1e-5
+    assert rel(dX.cpu(), X.grad) < 1e-5
+    assert rel(dW.cpu(), W.grad) < 1e-5
+    assert rel(db.cpu(), b.grad) < 1e-5
