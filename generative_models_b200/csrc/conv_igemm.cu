@@ -12,6 +12,7 @@
 // 3-stage smem ring (32 KB per stage) so two CTAs are co-resident per SM (one's epilogue overlaps the other's MMAs).
 #include "host_common.h"
 #include "ptx.cuh"
+#include "dev_common.cuh"
 
 #include "../../include/b200ddpm.h"
 
@@ -35,6 +36,7 @@ struct ConvK {
   int w_rowlen_tap;     // columns per tap in the weight matrix (= Cin of the weight tensor)
   int n_off;
   int out_ld, emb_ld, res_ld;
+  int round_out;
 };
 
 __global__ void __launch_bounds__(192)
@@ -167,6 +169,7 @@ conv_igemm_tf32_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_con
             const float4 e = *reinterpret_cast<const float4*>(rrow + c);
             v.x += e.x; v.y += e.y; v.z += e.z; v.w += e.w;
           }
+          if (a.round_out) v = round_tf32(v);
           *reinterpret_cast<float4*>(orow + c) = v;
         }
       }
@@ -247,6 +250,7 @@ extern "C" int b200_conv_igemm(const b200_conv_args* a, void* ws, size_t ws_byte
   k.out_ld = a->out_ld;
   k.emb_ld = a->emb_ld;
   k.res_ld = a->res_ld;
+  k.round_out = a->round_out;
 
   static bool attr_set = false;
   if (!attr_set) {

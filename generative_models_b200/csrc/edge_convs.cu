@@ -3,6 +3,7 @@
 // warp-shuffle / shared-memory reductions.  Forward, weight/bias gradients and (for the output conv) data gradient.
 // Reference: simple_unet.py:92-94 (Downsample(1, C, 1) = Conv2d(1, C, 3, padding=1)) and :41 (Conv2d(C, 1, 3, padding=1)).
 #include "host_common.h"
+#include "dev_common.cuh"
 
 #include "../../include/b200ddpm.h"
 
@@ -12,7 +13,7 @@ namespace b200 {
 // out[n,y,x,c] = b[c] + sum_{kh,kw} x[n,y+kh-1,x+kw-1] * w[c][kh][kw];  one thread = one pixel x 4 channels.
 __global__ void __launch_bounds__(256)
 conv_in_fwd_kernel(const float* __restrict__ x, const float* __restrict__ w, const float* __restrict__ bias,
-                   float* __restrict__ out, int N, int H, int W) {
+                   float* __restrict__ out, int N, int H, int W, int round_out) {
   __shared__ float sw[9][128];
   __shared__ float sb[128];
   for (int i = threadIdx.x; i < 9 * 128; i += blockDim.x) sw[i % 9][i / 9] = w[i];  // w is [c][tap]
@@ -41,6 +42,7 @@ conv_in_fwd_kernel(const float* __restrict__ x, const float* __restrict__ w, con
         acc.x += v * wv.x; acc.y += v * wv.y; acc.z += v * wv.z; acc.w += v * wv.w;
       }
     }
+    if (round_out) acc = round_tf32(acc);
     *reinterpret_cast<float4*>(out + pix * 128 + c) = acc;
   }
 }
@@ -142,7 +144,7 @@ conv_out_fwd_kernel(const float* __restrict__ h, const float* __restrict__ w, co
 // db += sum dout.  One CTA per image; dout of the image lives in smem.
 __global__ void __launch_bounds__(256)
 conv_out_bwd_kernel(const float* __restrict__ h, const float* __restrict__ w, const float* __restrict__ dout,
-                    float* __restrict__ dh, float* __restrict__ dw, float* __restrict__ db, int H, int W) {
+                    float* __restrict__ dh, float* __restrict__ dw, float* __restrict__ db, int H, int W, int round_dh) {
   extern __shared__ float sm[];  // [HW] dout, then [8][9][128] dw partials
   const int n = blockIdx.x;
   const int HW = H * W;
@@ -177,6 +179,7 @@ conv_out_bwd_kernel(const float* __restrict__ h, const float* __restrict__ w, co
         g.x += d * wv[t].x; g.y += d * wv[t].y; g.z += d * wv[t].z; g.w += d * wv[t].w;
         aw[t].x += d * v.x; aw[t].y += d * v.y; aw[t].z += d * v.z; aw[t].w += d * v.w;
       }
+    if (round_dh) g = round_tf32(g);
     *reinterpret_cast<float4*>(dh + off) = g;
   }
 #pragma unroll
@@ -204,7 +207,7 @@ extern "C" int b200_conv_in_fwd(const b200_conv_in_args* a, void* ws, size_t ws_
   size_t blocks = (total + 255) / 256;
   if (blocks > 148 * 8) blocks = 148 * 8;
   conv_in_fwd_kernel<<<static_cast<int>(blocks), 256, 0, static_cast<cudaStream_t>(stream)>>>(a->x, a->w, a->bias, a->out,
-                                                                                              a->N, a->H, a->W);
+                                                                                              a->N, a->H, a->W, a->round_out);
   return after_launch("conv_in_fwd_kernel");
 }
 
@@ -244,6 +247,6 @@ extern "C" int b200_conv_out_bwd(const b200_conv_out_args* a, void* ws, size_t w
     attr_set = true;
   }
   conv_out_bwd_kernel<<<a->N, 256, smem, static_cast<cudaStream_t>(stream)>>>(a->h, a->w, a->dout, a->dh, a->dw, a->db,
-                                                                              a->H, a->W);
+                                                                              a->H, a->W, a->round_dh);
   return after_launch("conv_out_bwd_kernel");
 }

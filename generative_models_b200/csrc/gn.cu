@@ -3,6 +3,7 @@
 // moments are reduced with warp/smem reductions and a handful of global atomics.
 // Reference: nn.GroupNorm(32, C) -> nn.SiLU in gms/diffusion/simple_unet.py:38-41,161-163,168-170.
 #include "host_common.h"
+#include "dev_common.cuh"
 
 #include "../../include/b200ddpm.h"
 
@@ -20,11 +21,6 @@ __device__ __forceinline__ float4 ld_src(const GnSrc& s, size_t pix, int c) {
                     : *reinterpret_cast<const float4*>(s.x2 + pix * s.ld2 + (c - s.C1));
 }
 __device__ __forceinline__ float silu_f(float u) { return u / (1.0f + expf(-u)); }
-__device__ __forceinline__ float round_tf32(float v) {
-  uint32_t r;
-  asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(r) : "f"(v));
-  return __uint_as_float(r);
-}
 
 // ---------------------------------------------------------------------------------------------------- forward stats
 // grid (chunks, N), block 256.  stats[n][g] = {sum, sumsq}; caller zeroes stats.
@@ -169,7 +165,7 @@ __global__ void __launch_bounds__(256)
 gn_bwd_apply_kernel(GnSrc s, const float* __restrict__ stats, const float* __restrict__ gamma,
                     const float* __restrict__ beta, const float* __restrict__ dy, const float* __restrict__ red,
                     float* __restrict__ dx, const float* __restrict__ add1, int add1_ld,
-                    const float* __restrict__ add2, int add2_ld, int add_c, float eps, int silu) {
+                    const float* __restrict__ add2, int add2_ld, int add_c, float eps, int silu, int round_dx) {
   const int lanes = s.C >> 2;
   const size_t total = static_cast<size_t>(s.N) * s.HW * lanes;
   const int cpg = s.C >> 5;
@@ -210,7 +206,9 @@ gn_bwd_apply_kernel(GnSrc s, const float* __restrict__ stats, const float* __res
         o[0] += a.x; o[1] += a.y; o[2] += a.z; o[3] += a.w;
       }
     }
-    *reinterpret_cast<float4*>(dx + pix * s.C + c) = make_float4(o[0], o[1], o[2], o[3]);
+    float4 ov = make_float4(o[0], o[1], o[2], o[3]);
+    if (round_dx) ov = round_tf32(ov);
+    *reinterpret_cast<float4*>(dx + pix * s.C + c) = ov;
   }
 }
 
@@ -286,6 +284,6 @@ extern "C" int b200_gn_bwd(const b200_gn_bwd_args* b, void* ws, size_t ws_bytes,
   const size_t total = static_cast<size_t>(s.N) * s.HW * (s.C / 4);
   gn_bwd_apply_kernel<<<ew_grid(total), 256, 0, st>>>(s, b->fwd.stats, b->fwd.gamma, b->fwd.beta, b->dy, red, b->dx,
                                                       b->add1, b->add1_ld, b->add2, b->add2_ld,
-                                                      b->add_c ? b->add_c : s.C, b->fwd.eps, b->fwd.silu);
+                                                      b->add_c ? b->add_c : s.C, b->fwd.eps, b->fwd.silu, b->round_dx);
   return after_launch("gn_bwd_apply_kernel");
 }

@@ -4,6 +4,7 @@
 // Reference: simple_unet.py:45-58 (embeddings), :112-122 (Upsample), :165-167,183-184 (emb_layers);
 // diffusion_model.py:56,70-72 (torch.optim.Adam defaults).
 #include "host_common.h"
+#include "dev_common.cuh"
 
 #include "../../include/b200ddpm.h"
 
@@ -34,7 +35,8 @@ upsample2x_fwd_kernel(const float4* __restrict__ in, float4* __restrict__ out, i
 }
 // din[n,y,x,c] = sum of the 2x2 block of dout; dout pixel stride is ld4 float4s (it may be a slice of a wider buffer)
 __global__ void __launch_bounds__(256)
-upsample2x_bwd_kernel(const float4* __restrict__ dout, float4* __restrict__ din, int N, int H, int W, int C4, int ld4) {
+upsample2x_bwd_kernel(const float4* __restrict__ dout, float4* __restrict__ din, int N, int H, int W, int C4, int ld4,
+                      int round_out) {
   const size_t total = static_cast<size_t>(N) * H * W * C4;
   GRID_STRIDE(i, total) {
     const int c = static_cast<int>(i % C4);
@@ -46,8 +48,10 @@ upsample2x_bwd_kernel(const float4* __restrict__ dout, float4* __restrict__ din,
     const size_t r0 = ((static_cast<size_t>(n) * 2 * H + 2 * y) * 2 * W + 2 * x) * ld4 + c;
     const size_t r1 = r0 + static_cast<size_t>(2 * W) * ld4;
     const float4 a = dout[r0], b = dout[r0 + ld4], d = dout[r1], e = dout[r1 + ld4];
-    din[i] = make_float4((a.x + b.x) + (d.x + e.x), (a.y + b.y) + (d.y + e.y), (a.z + b.z) + (d.z + e.z),
-                         (a.w + b.w) + (d.w + e.w));
+    float4 o = make_float4((a.x + b.x) + (d.x + e.x), (a.y + b.y) + (d.y + e.y), (a.z + b.z) + (d.z + e.z),
+                           (a.w + b.w) + (d.w + e.w));
+    if (round_out) o = round_tf32(o);
+    din[i] = o;
   }
 }
 // out[n,y,x,:] = (y,x both even) ? dy[n,y/2,x/2,:] : 0   — turns a stride-2 dgrad into a stride-1 one.
@@ -243,6 +247,10 @@ adam_kernel(float* __restrict__ p, const float* __restrict__ g, float* __restric
     p[i] = p[i] - step_size * (mi / denom);
   }
 }
+// dst = round_to_nearest_tf32(src): the tensor-core shadow copy of the flat parameter buffer
+__global__ void __launch_bounds__(256) round_tf32_kernel(const float4* __restrict__ src, float4* __restrict__ dst, size_t n4) {
+  GRID_STRIDE(i, n4) dst[i] = round_tf32(src[i]);
+}
 __global__ void int_increment_kernel(int* v) {
   if (threadIdx.x == 0 && blockIdx.x == 0) *v += 1;
 }
@@ -265,7 +273,8 @@ extern "C" int b200_upsample2x(const b200_resample_args* a, void* ws, size_t ws_
     const size_t total = static_cast<size_t>(a->N) * a->H * a->W * C4;
     const int ld4 = (a->in_ld ? a->in_ld : a->C) / 4;
     upsample2x_bwd_kernel<<<ew_grid2(total), 256, 0, ST(stream)>>>(reinterpret_cast<const float4*>(a->in),
-                                                                    reinterpret_cast<float4*>(a->out), a->N, a->H, a->W, C4, ld4);
+                                                                    reinterpret_cast<float4*>(a->out), a->N, a->H, a->W, C4, ld4,
+                                                                    a->round_out);
     return after_launch("upsample2x_bwd_kernel");
   } else if (a->mode == 2) {
     const size_t total = static_cast<size_t>(a->N) * a->H * a->W * C4;
@@ -345,6 +354,14 @@ extern "C" int b200_adam(const b200_adam_args* a, void* ws, size_t ws_bytes, voi
                                                       a->grad_scale, a->step_dev, a->step);
   if (int r = after_launch("adam_kernel")) return r;
   return 0;
+}
+
+extern "C" int b200_round_tf32(const b200_round_args* a, void* ws, size_t ws_bytes, void* stream) {
+  (void)ws; (void)ws_bytes;
+  if (!a || !a->src || !a->dst || a->n % 4) return fail_arg("round_tf32: null pointer or n not a multiple of 4");
+  round_tf32_kernel<<<ew_grid2(a->n / 4), 256, 0, ST(stream)>>>(reinterpret_cast<const float4*>(a->src),
+                                                               reinterpret_cast<float4*>(a->dst), a->n / 4);
+  return after_launch("round_tf32_kernel");
 }
 
 extern "C" int b200_zero(const b200_zero_args* a, void* ws, size_t ws_bytes, void* stream) {

@@ -21,7 +21,7 @@ class ConvArgs(C.Structure):
         ("R", C.c_int), ("S", C.c_int), ("stride", C.c_int), ("pad", C.c_int),
         ("mode", C.c_int), ("w_cout", C.c_int), ("w_cin", C.c_int), ("n_off", C.c_int),
         ("out_ld", C.c_int), ("emb_ld", C.c_int), ("res_ld", C.c_int),
-        ("x_ld", C.c_int), ("x2_ld", C.c_int),
+        ("x_ld", C.c_int), ("x2_ld", C.c_int), ("round_out", C.c_int),
     ]
 
 
@@ -48,7 +48,7 @@ class GnBwdArgs(C.Structure):
     _fields_ = [
         ("fwd", GnArgs), ("dy", _f32p), ("dx", _f32p), ("add1", _f32p), ("add2", _f32p),
         ("add1_ld", C.c_int), ("add2_ld", C.c_int), ("add_c", C.c_int),
-        ("dgamma", _f32p), ("dbeta", _f32p),
+        ("dgamma", _f32p), ("dbeta", _f32p), ("round_dx", C.c_int),
     ]
 
 
@@ -79,20 +79,20 @@ class StepAdvanceArgs(C.Structure):
 class ConvInArgs(C.Structure):
     _fields_ = [
         ("x", _f32p), ("w", _f32p), ("bias", _f32p), ("out", _f32p), ("dy", _f32p), ("dw", _f32p), ("db", _f32p),
-        ("N", C.c_int), ("H", C.c_int), ("W", C.c_int),
+        ("N", C.c_int), ("H", C.c_int), ("W", C.c_int), ("round_out", C.c_int),
     ]
 
 
 class ConvOutArgs(C.Structure):
     _fields_ = [
         ("h", _f32p), ("w", _f32p), ("bias", _f32p), ("out", _f32p), ("dout", _f32p), ("dh", _f32p),
-        ("dw", _f32p), ("db", _f32p), ("N", C.c_int), ("H", C.c_int), ("W", C.c_int),
+        ("dw", _f32p), ("db", _f32p), ("N", C.c_int), ("H", C.c_int), ("W", C.c_int), ("round_dh", C.c_int),
     ]
 
 
 class ResampleArgs(C.Structure):
     _fields_ = [("in_", _f32p), ("out", _f32p), ("N", C.c_int), ("H", C.c_int), ("W", C.c_int), ("C", C.c_int),
-                ("in_ld", C.c_int), ("mode", C.c_int)]
+                ("in_ld", C.c_int), ("mode", C.c_int), ("round_out", C.c_int)]
 
 
 class ColsumArgs(C.Structure):
@@ -124,6 +124,10 @@ class AdamArgs(C.Structure):
     ]
 
 
+class RoundArgs(C.Structure):
+    _fields_ = [("src", _f32p), ("dst", _f32p), ("n", C.c_size_t)]
+
+
 class ZeroArgs(C.Structure):
     _fields_ = [("ptr", _f32p), ("bytes", C.c_size_t)]
 
@@ -150,7 +154,7 @@ def load():
     lib.b200_last_error.restype = C.c_char_p
     lib.b200_launch_count.restype = C.c_ulonglong
     lib.b200_init.argtypes = [C.c_int]
-    if lib.b200_abi_version() != 1:
+    if lib.b200_abi_version() != 2:
         raise B200Error("libb200ddpm.so ABI version mismatch")
     for name in EXPORTS:
         fn = getattr(lib, name)  # AttributeError if the symbol is missing
@@ -171,7 +175,7 @@ EXPORTS = [
     "b200_conv_in_fwd", "b200_conv_in_bwd", "b200_conv_out_fwd", "b200_conv_out_bwd",
     "b200_upsample2x", "b200_colsum",
     "b200_embed_prep", "b200_embed_combine", "b200_embed_combine_bwd",
-    "b200_linear", "b200_adam", "b200_zero",
+    "b200_linear", "b200_adam", "b200_zero", "b200_round_tf32",
 ]
 
 

@@ -372,12 +372,13 @@ class _Bound:
             self.graphs.pop("sampler_step", None)
             self.graphs.pop(("warm", "sampler_step"), None)
         self.step_dev.fill_(self.T - 1)
+        run_ops(self.plan.refresh_ops, self.m._stream())  # weights are fixed for the whole loop
 
     def enqueue_sampler_step(self, draw_noise=True):
         st = self.m._stream()
-        self.plan.forward(st)  # conditional eval → plan.out
+        self.plan.forward(st, refresh=False)  # conditional eval → plan.out
         if self.guided:
-            self.plan.forward(st, uncond=True, to_out2=True)  # gaussian_diffusion.py:174-178
+            self.plan.forward(st, uncond=True, to_out2=True, refresh=False)  # gaussian_diffusion.py:174-178
         if draw_noise and SAMPLERS[self.m.G.sampler] == 1:
             self.noise.normal_()  # drawn after the net evals, like gaussian_diffusion.py:241
         run_ops(self.step_ops[self.guided], st)

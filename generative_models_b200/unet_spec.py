@@ -103,6 +103,8 @@ class ParamStore:
         self.numel = off
         self.flat = torch.zeros(off, dtype=torch.float32, device=self.device)
         self.grad = torch.zeros(off, dtype=torch.float32, device=self.device)
+        # TF32-rounded (round-to-nearest) shadow of `flat`: what the tensor-core convolutions read as their B operand
+        self.flat_tc = torch.zeros(off, dtype=torch.float32, device=self.device)
         self.exp_avg = None
         self.exp_avg_sq = None
         self.shapes = {n: s for n, s, _ in self.specs}
@@ -125,6 +127,9 @@ class ParamStore:
 
     def ptr(self, name):
         return self.flat.data_ptr() + 4 * self.offsets[name]
+
+    def tc_ptr(self, name):
+        return self.flat_tc.data_ptr() + 4 * self.offsets[name]
 
     def gptr(self, name):
         return self.grad.data_ptr() + 4 * self.offsets[name]

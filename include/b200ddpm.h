@@ -21,7 +21,7 @@
 extern "C" {
 #endif
 
-#define B200_ABI_VERSION 1
+#define B200_ABI_VERSION 2
 
 int b200_abi_version(void);
 int b200_init(int device);
@@ -55,6 +55,7 @@ typedef struct {
   int n_off;             /* dgrad only: first input channel produced by this launch */
   int out_ld, emb_ld, res_ld;
   int x_ld, x2_ld;       /* pixel stride (floats) of x / x2; 0 = dense (C1 / C2) */
+  int round_out;         /* store the result rounded to TF32 (it feeds another tensor-core operand) */
 } b200_conv_args;
 int b200_conv_igemm(const b200_conv_args* a, void* ws, size_t ws_bytes, void* stream);
 
@@ -108,6 +109,7 @@ typedef struct {
   int add1_ld, add2_ld, add_c;
   float* dgamma;
   float* dbeta;
+  int round_dx; /* store dx rounded to TF32 */
 } b200_gn_bwd_args;
 int b200_gn_bwd(const b200_gn_bwd_args* a, void* ws, size_t ws_bytes, void* stream);
 
@@ -181,6 +183,7 @@ typedef struct {
   float* dw; /* accumulated with atomics */
   float* db;
   int N, H, W;
+  int round_out; /* fwd: store out rounded to TF32 */
 } b200_conv_in_args;
 int b200_conv_in_fwd(const b200_conv_in_args* a, void* ws, size_t ws_bytes, void* stream);
 int b200_conv_in_bwd(const b200_conv_in_args* a, void* ws, size_t ws_bytes, void* stream);
@@ -195,6 +198,7 @@ typedef struct {
   float* dw;
   float* db;
   int N, H, W;
+  int round_dh; /* store dh rounded to TF32 */
 } b200_conv_out_args;
 int b200_conv_out_fwd(const b200_conv_out_args* a, void* ws, size_t ws_bytes, void* stream);
 int b200_conv_out_bwd(const b200_conv_out_args* a, void* ws, size_t ws_bytes, void* stream);
@@ -210,6 +214,7 @@ typedef struct {
   int N, H, W, C;
   int in_ld;
   int mode;
+  int round_out; /* mode 1: store the summed gradient rounded to TF32 */
 } b200_resample_args;
 int b200_upsample2x(const b200_resample_args* a, void* ws, size_t ws_bytes, void* stream);
 
@@ -262,6 +267,15 @@ typedef struct {
   int M, N, K, act, mode;
 } b200_linear_args;
 int b200_linear(const b200_linear_args* a, void* ws, size_t ws_bytes, void* stream);
+
+/* dst[i] = round-to-nearest TF32 of src[i] (n a multiple of 4): the tensor-core shadow copy of the flat parameters.
+ * tcgen05 kind::tf32 truncates its operands; pre-rounding them removes the bias (see csrc/dev_common.cuh). */
+typedef struct {
+  const float* src;
+  float* dst;
+  size_t n;
+} b200_round_args;
+int b200_round_tf32(const b200_round_args* a, void* ws, size_t ws_bytes, void* stream);
 
 /* cudaMemsetAsync(ptr, 0, bytes) on the stream (statistics / gradient arenas; replaces optimizer.zero_grad()). */
 typedef struct {

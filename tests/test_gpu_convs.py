@@ -263,7 +263,7 @@ def test_upsample_fwd_bwd_colsum(lib):
     a = lib.ColsumArgs(dy=ptr(dyd), per_sample=ptr(ps, 256), total1=ptr(t1), total2=ptr(t2), N=N, HW=4 * H * H, ld=128, ps_ld=1536)
     lib.call("b200_colsum", a, stream())
     assert rel(ps[:, 256:384].cpu(), dy.sum((2, 3))) < 1e-5
-    assert rel(t1.cpu(), dy.sum((0, 2, 3))) < 1e-5 and torch.equal(t1, t2)
+    assert rel(t1.cpu(), dy.sum((0, 2, 3))) < 1e-5 and rel(t2, t1) < 1e-6  # atomics: order differs
     assert ps[:, :256].abs().max().item() == 0 and ps[:, 384:].abs().max().item() == 0
 
 
