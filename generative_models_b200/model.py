@@ -15,7 +15,7 @@ from pathlib import Path
 import torch
 from torch import nn
 
-from . import lib
+from . import dist, lib
 from .plan import Op, UNetPlan, _p, run_ops
 from .schedule import logsnr_schedule_cosine, sampler_table
 from .unet_spec import ParamStore, build_module_tree
@@ -153,9 +153,8 @@ class DiffusionModelB200(nn.Module):
             b.run_graphed(b.enqueue_fwd_bwd, "fwd_bwd")
         else:
             b.enqueue_fwd_bwd()
-        if world > 1:
-            # the one collective of the path: sum of the flat fp32 gradient over NVLink
-            torch.distributed.all_reduce(self.store.grad)
+        # the one collective of the path: sum of the flat fp32 gradient over NVLink; no-op at world 1
+        dist.allreduce_flat_grad(self.store.grad)
         if self.use_graph:
             b.run_graphed(b.enqueue_adam, "adam")
         else:

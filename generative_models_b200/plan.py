@@ -30,10 +30,11 @@ def _p(t, off_floats=0):
 
 
 class Op:
-    __slots__ = ("fn", "ref", "args", "ws", "wsb", "name")
+    __slots__ = ("fn", "ref", "args", "ws", "wsb", "name", "alg_scale")
 
     def __init__(self, name, args, ws=None):
         self.name = name
+        self.alg_scale = 1.0  # algorithmic / executed work of this launch (bench.py's roofline accounting)
         self.fn = getattr(lib.load(), name)
         self.args = args  # keep the struct alive
         self.ref = C.byref(args)
@@ -390,6 +391,8 @@ class UNetPlan:
         dx = gp.get(B, H * H, 128)
         ops.append(self._dgrad(src, name, dx, H, 3, 1, 128, 0, 128,
                                residual=residual.ptr() if residual else None, res_ld=residual.ld if residual else 0))
+        if stride == 2:
+            ops[-1].alg_scale = 0.25  # 3/4 of the zero-stuffed rows are zeros
         gp.release(zs)
         return dx
 
