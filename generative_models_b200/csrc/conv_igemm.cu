@@ -16,6 +16,8 @@
 
 #include "../../include/b200ddpm.h"
 
+#include <stdlib.h>
+
 namespace b200 {
 
 constexpr int kStages = 3;
@@ -187,6 +189,8 @@ conv_igemm_tf32_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_con
 
 using namespace b200;
 
+int conv_strip_launch(const b200_conv_args* a, void* stream);  // conv_strip.cu
+
 extern "C" int b200_conv_igemm(const b200_conv_args* a, void* ws, size_t ws_bytes, void* stream) {
   (void)ws;
   (void)ws_bytes;
@@ -217,6 +221,17 @@ extern "C" int b200_conv_igemm(const b200_conv_args* a, void* ws, size_t ws_byte
     lower = -pad_eff;
     upper = -a->pad;
   }
+  // stride-1 3x3/pad-1 and 1x1/pad-0 layers (all but the two Downsample convs) go to the strip kernel
+  static int use_strip = -1;
+  if (use_strip < 0) {
+    const char* e = getenv("B200_CONV_STRIP");
+    use_strip = e ? atoi(e) : 1;
+  }
+  if (use_strip && a->stride == 1 && ((a->R == 3 && a->pad == 1) || (a->R == 1 && a->pad == 0))) {
+    const int rs = conv_strip_launch(a, stream);
+    if (rs != -100) return rs;
+  }
+  if (a->skip_x) return fail_arg("conv_igemm: the fused skip segment needs a stride-1 3x3/pad-1 or 1x1/pad-0 layer");
   CUtensorMap tmA, tmA2, tmB;
   int r = get_tmap_im2col(a->x, a->N, a->H, a->W, a->C1, a->x_ld ? a->x_ld : a->C1, lower, upper, a->stride, 32, 128, 4, 0, &tmA);
   if (r) return r;

@@ -1,0 +1,451 @@
+// Stride-1 convolutions (3x3 pad 1, 1x1 pad 0; fprop and dgrad) as a "strip" implicit GEMM on tcgen05, TF32.
+//
+// Why a second kernel: the TMA-im2col kernel (conv_igemm.cu) re-fetches every input pixel once per filter tap and
+// every weight tile once per 128 output pixels (32 KB of L2->SM traffic per 128x128x32 MMA block; ncu shows it pinned
+// at ~7.1 KB/clk of L2->SM fabric bandwidth with the tensor pipe 40 % busy), and SS-mode TF32 MMAs turned out to be
+// bound by shared-memory OPERAND bandwidth (~64 B/clk: a 128x128x8 instruction reads 8 KB).  This kernel attacks both:
+//
+//   * positions: the batch is viewed as one tall raster with ONE shared zero column per image row and ONE shared zero
+//     row per image (pitch Wp = W+1, Hp = H+1).  In that raster a filter tap is a constant row shift
+//     (kh-1)*Wp + (kw-1), so a tile of 256 consecutive positions needs one contiguous "strip" of input rows
+//     (256 + 2*Wp + 2 positions) per 32-channel chunk, loaded ONCE (TMA, one box per image row, halo = OOB zero fill)
+//     and read by all 9 taps as 9 shifted views: the UMMA smem descriptor simply starts 128 B * shift further on
+//     (the 128B-swizzle XOR is a function of the absolute smem address, so row-shifted views stay consistent);
+//   * orientation: D^T[out channel (128 TMEM lanes)][position (256 columns)] = W * X^T, i.e. the weight tile is the
+//     M=128 A operand and the strip view the N=256 B operand: one instruction reads 4 KB + 8 KB for twice the FLOPs
+//     of a 128x128x8 one (measured issue rate 480 -> 680 TFLOP/s);
+//   * persistent CTAs (one per SM), TMEM accumulators double-buffered (2 x 256 columns) so the epilogue of tile i
+//     overlaps the MMAs of tile i+1; epilogue thread = output channel, so a warp stores 128 contiguous bytes per pixel;
+//   * optional fused "skip" K-segment (extra 1-tap chunks over a second tensor pair: identity = residual add on the
+//     tensor cores, or the ResBlock's 1x1 skip conv).
+//   1x1 convolutions use the same kernel in "flat" mode (positions = pixels, one 256-row box per chunk).
+//
+// CTA = 320 threads: warp 0 TMA producer, warp 1 TMEM owner + MMA issuer, warps 2-9 epilogue.
+#include "host_common.h"
+#include "ptx.cuh"
+#include "dev_common.cuh"
+
+#include "../../include/b200ddpm.h"
+
+#include <stdlib.h>
+
+namespace b200 {
+
+constexpr int kSB = 6;                    // weight-tile ring
+constexpr int kSS = 2;                    // strip double buffer
+constexpr int kBTile = 16384;             // 128 x 128 B
+constexpr int kStripBytes = 48 * 1024;    // >= (256 + 2*Wp + 2 rounded up to whole rows) * 128 B for W <= 64
+constexpr int kTileM = 256;               // positions per CTA tile (the N of one UMMA)
+constexpr int kStripSmem = kSS * kStripBytes + kSB * kBTile + 1024 + 256 + 2 * 512 * 4;
+
+struct StripK {
+  float* out;
+  const float* bias;
+  const float* bias2;
+  const float* emb;
+  const float* residual;
+  int N, H, W, Wp, Hp;
+  int flat;        // 1: positions are pixels (1x1 conv), strip = 256 rows of a 2-D map
+  int P_total;     // number of positions
+  int num_tiles;
+  int taps;        // 9 or 1
+  int chunks1, chunks;
+  int skip_chunks1, skip_chunks;  // fused 1x1 "skip" segment over a second pair of tensors (0 = none)
+  int mode;        // 0 fprop, 1 dgrad
+  int w_rowlen_tap;
+  int n_off;
+  int out_ld, emb_ld, res_ld;
+  int round_out;
+  int strip_rows;  // image rows per strip (non-flat)
+  int dbg;         // developer knobs (B200_STRIP_DBG): 1 = skip TMA loads (timing of the MMA issue path only)
+};
+
+__device__ __forceinline__ int floor_div(int a, int b) {
+  int q = a / b;
+  if ((a % b) != 0 && ((a < 0) != (b < 0))) --q;
+  return q;
+}
+
+__global__ void __launch_bounds__(320, 1)
+conv_strip_tf32_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmA2,
+                       const __grid_constant__ CUtensorMap tmB, const __grid_constant__ CUtensorMap tmS,
+                       const __grid_constant__ CUtensorMap tmS2, const __grid_constant__ CUtensorMap tmW2,
+                       const StripK a) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* strip0 = smem;
+  uint8_t* bring = smem + kSS * kStripBytes;
+  uint64_t* bars = reinterpret_cast<uint64_t*>(bring + kSB * kBTile);
+  uint64_t* s_full = bars;             // [kSS]
+  uint64_t* s_empty = s_full + kSS;    // [kSS]
+  uint64_t* b_full = s_empty + kSS;    // [kSB]
+  uint64_t* b_empty = b_full + kSB;    // [kSB]
+  uint64_t* acc_full = b_empty + kSB;  // [2]
+  uint64_t* acc_empty = acc_full + 2;  // [2]
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(acc_empty + 2);
+  int* tab = reinterpret_cast<int*>(bars + 32);  // 256 B past the barriers, 16 B-aligned: [2 acc stages][m[256], n[256]]
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+
+  if (threadIdx.x == 0) {
+    tma_prefetch_desc(&tmA);
+    tma_prefetch_desc(&tmA2);
+    tma_prefetch_desc(&tmB);
+    if (a.skip_chunks) {
+      tma_prefetch_desc(&tmS);
+      tma_prefetch_desc(&tmS2);
+      tma_prefetch_desc(&tmW2);
+    }
+    for (int s = 0; s < kSS; ++s) {
+      mbar_init(&s_full[s], 1);
+      mbar_init(&s_empty[s], 1);
+    }
+    for (int s = 0; s < kSB; ++s) {
+      mbar_init(&b_full[s], 1);
+      mbar_init(&b_empty[s], 1);
+    }
+    for (int s = 0; s < 2; ++s) {
+      mbar_init(&acc_full[s], 1);
+      mbar_init(&acc_empty[s], 256);  // every epilogue thread arrives
+    }
+    fence_mbar_init();
+  }
+  if (warp == 1) {
+    tmem_alloc(tmem_slot, 512);
+    tmem_relinquish();
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  const int strip_bytes = a.flat ? kTileM * 128 : a.strip_rows * a.Wp * 128;
+  const int CH = a.chunks + a.skip_chunks;  // K-chunks (32 channels each) per tile: main conv, then the skip segment
+
+  if (warp == 0) {
+    if (lane == 0) {
+      // ---------------------------------------------------------------- TMA producer
+      // Order of issue: strip(0); then per chunk: weight taps 0..3, strip(next chunk), weight taps 4..8 — the next
+      // strip is requested ~1.5 chunks of MMA time before it is needed, and never blocks the weight stream (its buffer
+      // was released by the chunk before the one in flight).
+      uint32_t bc = 0;
+      const int tiles_mine = (a.num_tiles - static_cast<int>(blockIdx.x) + static_cast<int>(gridDim.x) - 1) / static_cast<int>(gridDim.x);
+      const int total_chunks = tiles_mine * CH;
+      auto load_strip = [&](int q) {  // q = running chunk index of this CTA
+        const int t = blockIdx.x + (q / CH) * gridDim.x;
+        const int ch = q % CH;
+        const uint32_t ss = q % kSS;
+        mbar_wait(&s_empty[ss], ((q / kSS) & 1) ^ 1);
+        if (a.dbg & 1) {
+          mbar_arrive(&s_full[ss]);
+          return;
+        }
+        mbar_expect_tx(&s_full[ss], strip_bytes);
+        uint8_t* sdst = strip0 + ss * kStripBytes;
+        const CUtensorMap* m;
+        int c0;
+        if (ch < a.chunks) {
+          m = (ch < a.chunks1) ? &tmA : &tmA2;
+          c0 = ((ch < a.chunks1) ? ch : ch - a.chunks1) * 32;
+        } else {
+          const int sk = ch - a.chunks;
+          m = (sk < a.skip_chunks1) ? &tmS : &tmS2;
+          c0 = ((sk < a.skip_chunks1) ? sk : sk - a.skip_chunks1) * 32;
+        }
+        const int p0 = t * kTileM;
+        if (a.flat) {
+          tma_load_2d(sdst, m, &s_full[ss], c0, p0);
+        } else {
+          const int g0 = floor_div(p0 - a.Wp - 1, a.Wp);  // first padded row of the strip
+          for (int r = 0; r < a.strip_rows; ++r) {
+            const int g = g0 + r;
+            const int n = floor_div(g, a.Hp);
+            const int hh = g - n * a.Hp - 1;  // -1 = the shared zero row (OOB -> zeros)
+            tma_load_4d(sdst + r * a.Wp * 128, m, &s_full[ss], c0, -1, hh, n);
+          }
+        }
+      };
+      if (total_chunks > 0) load_strip(0);
+      for (int q = 0; q < total_chunks; ++q) {
+        const int ch = q % CH;
+        const bool is_skip = ch >= a.chunks;
+        const int ntaps = is_skip ? 1 : a.taps;
+        const int split = ntaps > 4 ? 4 : 0;
+        for (int tap = 0; tap < ntaps; ++tap, ++bc) {
+          if (tap == split && q + 1 < total_chunks) load_strip(q + 1);
+          const uint32_t bs = bc % kSB;
+          mbar_wait(&b_empty[bs], ((bc / kSB) & 1) ^ 1);
+          if (a.dbg & 1) {
+            mbar_arrive(&b_full[bs]);
+            continue;
+          }
+          mbar_expect_tx(&b_full[bs], kBTile);
+          uint8_t* sB = bring + bs * kBTile;
+          if (is_skip) {
+            const int sk = ch - a.chunks;
+            if (a.mode == 0) {
+              tma_load_2d(sB, &tmW2, &b_full[bs], sk * 32, 0);
+            } else {
+#pragma unroll
+              for (int jj = 0; jj < 4; ++jj) tma_load_2d(sB + jj * 4096, &tmW2, &b_full[bs], jj * 32, sk * 32);
+            }
+          } else if (a.mode == 0) {
+            tma_load_2d(sB, &tmB, &b_full[bs], tap * a.w_rowlen_tap + ch * 32, 0);
+          } else {
+            const int wtap = a.taps - 1 - tap;  // dgrad walks the filter flipped
+#pragma unroll
+            for (int jj = 0; jj < 4; ++jj)
+              tma_load_2d(sB + jj * 4096, &tmB, &b_full[bs], wtap * a.w_rowlen_tap + a.n_off + jj * 32, ch * 32);
+          }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    if (lane == 0) {
+      // ---------------------------------------------------------------- MMA issuer
+      // D^T[out channel (128 TMEM lanes)][position (256 TMEM columns)] += W[co][k] * X^T[k][position]:
+      // A = weight tile (K-major for fprop, MN-major for dgrad), B = the shifted strip view (K-major, N = 256 rows).
+      // One N=256 instruction reads 4 KB of A + 8 KB of B for twice the FLOPs of a 128x128x8 one: SS-mode TF32 is
+      // bound by smem operand bandwidth (measured: 480 -> 680 TFLOP/s issue rate), hence this orientation.
+      const uint32_t idesc = make_idesc(2u, 128u, 256u, a.mode == 0 ? 0u : 1u, 0u);
+      uint32_t sc = 0, bc = 0, tc = 0;
+      for (int t = blockIdx.x; t < a.num_tiles; t += gridDim.x, ++tc) {
+        const uint32_t as = tc & 1;
+        mbar_wait(&acc_empty[as], ((tc >> 1) & 1) ^ 1);
+        tc_fence_after();
+        const int p0 = t * kTileM;
+        const int g0 = a.flat ? 0 : floor_div(p0 - a.Wp - 1, a.Wp);
+        const int row0 = a.flat ? 0 : p0 - g0 * a.Wp;  // strip row of position p0 (centre tap)
+        const uint32_t d_tmem = tmem_base + as * 256;
+        for (int ch = 0; ch < CH; ++ch, ++sc) {
+          const uint32_t ss = sc % kSS;
+          mbar_wait(&s_full[ss], (sc / kSS) & 1);
+          tc_fence_after();
+          const uint32_t strip_addr = smem_u32(strip0 + ss * kStripBytes);
+          const bool is_skip = ch >= a.chunks;
+          const int ntaps = is_skip ? 1 : a.taps;
+          for (int tap = 0; tap < ntaps; ++tap, ++bc) {
+            const uint32_t bs = bc % kSB;
+            mbar_wait(&b_full[bs], (bc / kSB) & 1);
+            tc_fence_after();
+            const uint32_t w_base = smem_u32(bring + bs * kBTile);
+            int shift = 0;
+            if (ntaps == 9) {
+              const int kh = tap / 3, kw = tap - kh * 3;
+              shift = (kh - 1) * a.Wp + (kw - 1);
+            }
+            // strip view: start address only 128 B-aligned.  The 128B-swizzle XOR uses absolute smem address bits
+            // [7,10) (as TMA's does), so row-shifted views need no descriptor base offset (verified on B200).
+            const uint32_t x_base = strip_addr + static_cast<uint32_t>(row0 + shift) * 128u;
+#pragma unroll
+            for (int k = 0; k < 4; ++k) {
+              const uint64_t adesc = (a.mode == 0) ? make_smem_desc_sw128(w_base + k * 32, 16, 1024)
+                                                   : make_smem_desc_sw128(w_base + k * 1024, 4096, 512, 1);
+              const uint64_t bdesc = make_smem_desc_sw128(x_base + k * 32, 16, 1024);
+              mma_tf32_ss(d_tmem, adesc, bdesc, idesc, (ch | tap | k) != 0 ? 1u : 0u);
+            }
+            tc_commit(&b_empty[bs]);
+          }
+          tc_commit(&s_empty[ss]);
+        }
+        tc_commit(&acc_full[as]);
+      }
+    }
+  } else {
+    // ---------------------------------------------------------------- epilogue: TMEM -> regs -> (+bias +emb +res) -> global
+    // thread = output channel (TMEM lane), registers = 32 consecutive positions; a warp stores 32 consecutive
+    // channels of one pixel = one coalesced 128 B segment per instruction.
+    // 8 warps: warp e reads TMEM lane quarter (e & 3) and position columns [128*(e>>2), +128).
+    const int ew = warp - 2;
+    const int quarter = warp & 3;
+    const int colhalf = ((ew >> 2) ^ (quarter >> 1)) & 1;  // warps 2..9 -> quarters 2,3,0,1,2,3,0,1; halves 0 then 1
+    const int co = quarter * 32 + lane;
+    const int et = threadIdx.x - 64;  // 0..255
+    const float bias_v = (a.bias ? a.bias[co] : 0.f) + (a.bias2 ? a.bias2[co] : 0.f);
+    uint32_t tc = 0;
+    for (int t = blockIdx.x; t < a.num_tiles; t += gridDim.x, ++tc) {
+      const uint32_t as = tc & 1;
+      // position -> (pixel row m, sample n) table of this tile (m = -1: halo position, nothing to store)
+      int* tm = tab + as * 512;
+      int* tn = tm + 256;
+      {
+        const int P = t * kTileM + et;
+        int m, n;
+        if (a.flat) {
+          m = P < a.P_total ? P : -1;
+          n = P / (a.H * a.W);
+        } else {
+          const int g = P / a.Wp;
+          const int w = P - g * a.Wp - 1;
+          n = g / a.Hp;
+          const int h = g - n * a.Hp - 1;
+          m = ((w >= 0) && (h >= 0) && (n < a.N)) ? (n * a.H + h) * a.W + w : -1;
+        }
+        tm[et] = m;
+        tn[et] = n;
+      }
+      asm volatile("bar.sync 1, 256;" ::: "memory");
+      mbar_wait(&acc_full[as], (tc >> 1) & 1);
+      tc_fence_after();
+#pragma unroll 1
+      for (int c4 = 0; c4 < 4; ++c4) {
+        const int cb = colhalf * 128 + c4 * 32;  // first position column of this chunk
+        uint32_t r[32];
+        tmem_ld_32x32(tmem_base + (static_cast<uint32_t>(quarter * 32) << 16) + as * 256 + cb, r);
+        int mm[32];
+#pragma unroll
+        for (int j = 0; j < 32; j += 4) {
+          const int4 q = *reinterpret_cast<const int4*>(tm + cb + j);
+          mm[j] = q.x; mm[j + 1] = q.y; mm[j + 2] = q.z; mm[j + 3] = q.w;
+        }
+        float add[32];
+#pragma unroll
+        for (int j = 0; j < 32; ++j) add[j] = bias_v;
+        if (a.residual) {  // 32 independent loads in flight per thread
+#pragma unroll
+          for (int j = 0; j < 32; ++j)  // unconditional (halo positions read row 0): predicates would serialise them
+            add[j] += __ldg(a.residual + static_cast<size_t>(mm[j] < 0 ? 0 : mm[j]) * a.res_ld + co);
+        }
+        if (a.emb) {
+          const int n0 = tn[cb], n1 = tn[cb + 31];
+          if (n0 == n1) {
+            const float e = (n0 < a.N) ? __ldg(a.emb + static_cast<size_t>(n0) * a.emb_ld + co) : 0.f;
+#pragma unroll
+            for (int j = 0; j < 32; ++j) add[j] += e;
+          } else {
+#pragma unroll
+            for (int j = 0; j < 32; ++j)
+              if (mm[j] >= 0) add[j] += __ldg(a.emb + static_cast<size_t>(tn[cb + j]) * a.emb_ld + co);
+          }
+        }
+        tmem_ld_wait();
+#pragma unroll
+        for (int j = 0; j < 32; ++j) {
+          if (mm[j] >= 0) {
+            const float v = __uint_as_float(r[j]) + add[j];
+            a.out[static_cast<size_t>(mm[j]) * a.out_ld + co] = a.round_out ? round_tf32(v) : v;
+          }
+        }
+      }
+      tc_fence_before();
+      mbar_arrive(&acc_empty[as]);
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    tc_fence_after();
+    tmem_dealloc(tmem_base, 512);
+  }
+}
+
+}  // namespace b200
+
+using namespace b200;
+
+// Called by b200_conv_igemm for stride-1 3x3/pad-1 and 1x1/pad-0 layers.  Returns -100 when the geometry does not fit
+// the strip buffers (caller falls back to the im2col kernel).
+int conv_strip_launch(const b200_conv_args* a, void* stream) {
+  const int Cin = a->C1 + a->C2;
+  const int flat = (a->R == 1);
+  const int Wp = a->W + 1, Hp = a->H + 1;
+  const int strip_rows = 3 + (257 + Wp - 1) / Wp;
+  if (!flat && strip_rows * Wp * 128 > kStripBytes) return -100;
+  if (!flat && Wp > 256) return -100;
+
+  CUtensorMap tmA, tmA2, tmB;
+  int r;
+  const long long M = static_cast<long long>(a->N) * a->H * a->W;
+  if (flat) {
+    r = get_tmap_2d(a->x, M, a->C1, a->x_ld ? a->x_ld : a->C1, 32, 256, 4, 0, &tmA);
+    if (r) return r;
+    if (a->C2 > 0) {
+      r = get_tmap_2d(a->x2, M, a->C2, a->x2_ld ? a->x2_ld : a->C2, 32, 256, 4, 0, &tmA2);
+      if (r) return r;
+    } else {
+      tmA2 = tmA;
+    }
+  } else {
+    r = get_tmap_rows4d(a->x, a->N, a->H, a->W, a->C1, a->x_ld ? a->x_ld : a->C1, 32, Wp, &tmA);
+    if (r) return r;
+    if (a->C2 > 0) {
+      r = get_tmap_rows4d(a->x2, a->N, a->H, a->W, a->C2, a->x2_ld ? a->x2_ld : a->C2, 32, Wp, &tmA2);
+      if (r) return r;
+    } else {
+      tmA2 = tmA;
+    }
+  }
+  const uint64_t wcols = static_cast<uint64_t>(a->R) * a->S * a->w_cin;
+  r = get_tmap_2d(a->w, a->w_cout, wcols, wcols, 32, a->mode == 0 ? 128 : 32, 4, a->mode == 0 ? 0 : 1, &tmB);
+  if (r) return r;
+  // fused skip segment: a 1x1 convolution over (skip_x | skip_x2) with weights skip_w [128][skip_c1 + skip_c2],
+  // accumulated into the same TMEM tile as extra K-chunks (identity weights = a residual add on the tensor cores,
+  // exact because every activation is stored pre-rounded to TF32)
+  CUtensorMap tmS = tmA, tmS2 = tmA, tmW2 = tmB;
+  const int skip_c = a->skip_x ? a->skip_c1 + a->skip_c2 : 0;
+  if (skip_c) {
+    if (!a->skip_w || a->skip_c1 <= 0 || a->skip_c1 % 32 || a->skip_c2 % 32 || (a->skip_c2 && !a->skip_x2))
+      return fail_arg("conv_igemm: bad skip segment");
+    if (a->mode == 1 && skip_c != 128) return fail_arg("conv_igemm dgrad: the skip segment must have 128 channels");
+    const int l1 = a->skip_x_ld ? a->skip_x_ld : a->skip_c1, l2 = a->skip_x2_ld ? a->skip_x2_ld : a->skip_c2;
+    if (flat) {
+      r = get_tmap_2d(a->skip_x, M, a->skip_c1, l1, 32, 256, 4, 0, &tmS);
+      if (r) return r;
+      if (a->skip_c2) r = get_tmap_2d(a->skip_x2, M, a->skip_c2, l2, 32, 256, 4, 0, &tmS2);
+    } else {
+      r = get_tmap_rows4d(a->skip_x, a->N, a->H, a->W, a->skip_c1, l1, 32, Wp, &tmS);
+      if (r) return r;
+      if (a->skip_c2) r = get_tmap_rows4d(a->skip_x2, a->N, a->H, a->W, a->skip_c2, l2, 32, Wp, &tmS2);
+    }
+    if (r) return r;
+    if (!a->skip_c2) tmS2 = tmS;
+    r = get_tmap_2d(a->skip_w, 128, skip_c, skip_c, 32, a->mode == 0 ? 128 : 32, 4, a->mode == 0 ? 0 : 1, &tmW2);
+    if (r) return r;
+  }
+
+  StripK k;
+  k.out = a->out;
+  k.bias = a->bias;
+  k.bias2 = a->bias2;
+  k.emb = a->emb;
+  k.residual = a->residual;
+  k.N = a->N; k.H = a->H; k.W = a->W; k.Wp = Wp; k.Hp = Hp;
+  k.flat = flat;
+  k.P_total = flat ? static_cast<int>(M) : a->N * Hp * Wp;
+  k.num_tiles = (k.P_total + kTileM - 1) / kTileM;
+  // few tiles (small spatial levels at small batch): one 256-position tile per SM leaves the machine under-filled and
+  // the im2col kernel (128-position tiles, 2 CTAs/SM) is faster there — measured crossover ~4 tiles per SM
+  if (!a->skip_x && k.num_tiles < 4 * 148 && !flat) return -100;
+  k.taps = a->R * a->S;
+  k.chunks1 = a->C1 / 32;
+  k.chunks = Cin / 32;
+  k.skip_chunks1 = skip_c ? a->skip_c1 / 32 : 0;
+  k.skip_chunks = skip_c / 32;
+  k.mode = a->mode;
+  k.w_rowlen_tap = a->w_cin;
+  k.n_off = a->n_off;
+  k.out_ld = a->out_ld; k.emb_ld = a->emb_ld; k.res_ld = a->res_ld;
+  k.round_out = a->round_out;
+  k.strip_rows = strip_rows;
+
+  static int dbg = -1;
+  if (dbg < 0) {
+    const char* e = getenv("B200_STRIP_DBG");
+    dbg = e ? atoi(e) : 0;
+  }
+  k.dbg = dbg;
+  static bool attr_set = false;
+  static int num_sms = 148;
+  if (!attr_set) {
+    cudaError_t e = cudaFuncSetAttribute(conv_strip_tf32_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kStripSmem);
+    if (e != cudaSuccess) return check_cuda(e, "cudaFuncSetAttribute(conv_strip)");
+    int dev = 0;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&num_sms, cudaDevAttrMultiProcessorCount, dev);
+    attr_set = true;
+  }
+  const int grid = k.num_tiles < num_sms ? k.num_tiles : num_sms;
+  conv_strip_tf32_kernel<<<grid, 320, kStripSmem, static_cast<cudaStream_t>(stream)>>>(tmA, tmA2, tmB, tmS, tmS2, tmW2, k);
+  return after_launch("conv_strip_tf32_kernel");
+}

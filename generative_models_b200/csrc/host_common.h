@@ -55,4 +55,8 @@ int get_tmap_2d(const void* base, uint64_t rows, uint64_t cols, uint64_t ld_elem
 int get_tmap_im2col(const void* base, int N, int H, int W, int C, int ld, int lower, int upper, int stride, uint32_t box_c,
                     uint32_t box_pix, int elem_bytes, int swizzle32, CUtensorMap* out);
 
+// NHWC [N][H][W][C] plain tiled 4-D map {C, W, H, N}: box = box_c channels x box_w pixels of ONE image row
+// (out-of-range w / h / n coordinates are zero-filled: the convolution halo).
+int get_tmap_rows4d(const void* base, int N, int H, int W, int C, int ld, uint32_t box_c, uint32_t box_w, CUtensorMap* out);
+
 }  // namespace b200

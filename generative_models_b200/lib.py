@@ -22,6 +22,8 @@ class ConvArgs(C.Structure):
         ("mode", C.c_int), ("w_cout", C.c_int), ("w_cin", C.c_int), ("n_off", C.c_int),
         ("out_ld", C.c_int), ("emb_ld", C.c_int), ("res_ld", C.c_int),
         ("x_ld", C.c_int), ("x2_ld", C.c_int), ("round_out", C.c_int),
+        ("skip_x", _f32p), ("skip_x2", _f32p), ("skip_w", _f32p), ("bias2", _f32p),
+        ("skip_c1", C.c_int), ("skip_c2", C.c_int), ("skip_x_ld", C.c_int), ("skip_x2_ld", C.c_int),
     ]
 
 

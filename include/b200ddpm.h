@@ -56,6 +56,14 @@ typedef struct {
   int out_ld, emb_ld, res_ld;
   int x_ld, x2_ld;       /* pixel stride (floats) of x / x2; 0 = dense (C1 / C2) */
   int round_out;         /* store the result rounded to TF32 (it feeds another tensor-core operand) */
+  /* fused skip segment (stride-1 layers): out += Conv1x1(cat(skip_x, skip_x2), skip_w) + bias2, accumulated on the
+   * tensor cores as extra K-chunks.  skip_w is [128][skip_c1+skip_c2]; with the 128x128 identity it is the residual
+   * add of ResBlock.forward (simple_unet.py:186), with skip_connection.weight it is the 1x1 skip conv (:177). */
+  const float* skip_x;
+  const float* skip_x2;
+  const float* skip_w;
+  const float* bias2;
+  int skip_c1, skip_c2, skip_x_ld, skip_x2_ld;
 } b200_conv_args;
 int b200_conv_igemm(const b200_conv_args* a, void* ws, size_t ws_bytes, void* stream);
 

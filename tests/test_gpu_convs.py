@@ -288,3 +288,65 @@ def test_linear_modes(lib, M, N, K, act):
     assert rel(dX.cpu(), X.grad) < 1e-5
     assert rel(dW.cpu(), W.grad) < 1e-5
     assert rel(db.cpu(), b.grad) < 1e-5
+
+
+# ------------------------------------------------------------------------------------------------ fused skip segment
+def _tf32_round(t):
+    """round-to-nearest-even-ish to 10 mantissa bits on the host (what the producers store)"""
+    i = t.contiguous().view(torch.int32)
+    return ((i + 0x1000) & ~0x1FFF).view(torch.float32)
+
+
+@pytest.mark.parametrize("N,H,skipc", [(4, 28, 128), (3, 14, 256), (2, 7, 128), (2, 28, 256)])
+def test_conv_fprop_fused_skip(lib, N, H, skipc):
+    """conv2 of a ResBlock with the skip path on the tensor cores: identity (residual add, exact for TF32-rounded
+    activations) or the 1x1 skip_connection conv over a virtual concat, plus both biases and nothing in the epilogue."""
+    g = torch.Generator().manual_seed(N + H + skipc)
+    x = rn(g, N, 128, H, H)
+    w = rn(g, 128, 128, 3, 3) * 0.03
+    bias, bias2 = rn(g, 128), rn(g, 128)
+    s1 = _tf32_round(rn(g, N, 128, H, H))
+    s2 = _tf32_round(rn(g, N, 128, H, H)) if skipc == 256 else None
+    if skipc == 128:
+        wskip = torch.eye(128)
+        ref = F.conv2d(x, w, bias, padding=1) + s1 + bias2[None, :, None, None]
+    else:
+        wskip = rn(g, 128, 256) / 16
+        ref = F.conv2d(x, w, bias, padding=1) + F.conv2d(torch.cat([s1, s2], 1), wskip[:, :, None, None], bias2)
+    xh, wk = nhwc(x).to(DEV), w_khwc(w).to(DEV)
+    s1h = nhwc(s1).to(DEV)
+    s2h = nhwc(s2).to(DEV) if s2 is not None else None
+    wsd, bd, b2d = wskip.contiguous().to(DEV), bias.to(DEV), bias2.to(DEV)
+    out = torch.full((N, H, H, 128), float("nan"), device=DEV)
+    a = lib.ConvArgs(x=ptr(xh), x2=None, w=ptr(wk), out=ptr(out), bias=ptr(bd), emb=None, residual=None, N=N, H=H, W=H,
+                     C1=128, C2=0, Ho=H, Wo=H, R=3, S=3, stride=1, pad=1, mode=0, w_cout=128, w_cin=128, n_off=0,
+                     out_ld=128, emb_ld=0, res_ld=0, x_ld=0, x2_ld=0, round_out=0, skip_x=ptr(s1h), skip_x2=ptr(s2h),
+                     skip_w=ptr(wsd), bias2=ptr(b2d), skip_c1=128, skip_c2=skipc - 128, skip_x_ld=0, skip_x2_ld=0)
+    lib.call("b200_conv_igemm", a, stream())
+    got = out.permute(0, 3, 1, 2).cpu()
+    assert rel(got, ref) < TF32_TOL
+    if skipc == 128:
+        # the residual itself is carried exactly: with zero conv weights the output is s1 + biases to fp32 rounding
+        a.w = ptr(torch.zeros_like(wk))
+        lib.call("b200_conv_igemm", a, stream())
+        exact = s1 + (bias + bias2)[None, :, None, None]
+        assert rel(out.permute(0, 3, 1, 2).cpu(), exact) < 1e-6
+
+
+def test_conv_dgrad_fused_residual(lib):
+    """dgrad + identity skip segment over a 256-wide gradient buffer slice (the Down-path `tail` gradients)."""
+    g = torch.Generator().manual_seed(99)
+    N, H = 3, 14
+    dy = rn(g, N, 128, H, H)
+    w = rn(g, 128, 128, 3, 3) * 0.03
+    wide = _tf32_round(rn(g, N, H, H, 256))
+    ref = torch.nn.grad.conv2d_input((N, 128, H, H), w, dy, padding=1) + wide[..., 128:].permute(0, 3, 1, 2)
+    dyh, wk, wd = nhwc(dy).to(DEV), w_khwc(w).to(DEV), wide.to(DEV)
+    eye = torch.eye(128, device=DEV)
+    out = torch.full((N, H, H, 128), float("nan"), device=DEV)
+    a = lib.ConvArgs(x=ptr(dyh), x2=None, w=ptr(wk), out=ptr(out), bias=None, emb=None, residual=None, N=N, H=H, W=H,
+                     C1=128, C2=0, Ho=H, Wo=H, R=3, S=3, stride=1, pad=1, mode=1, w_cout=128, w_cin=128, n_off=0,
+                     out_ld=128, emb_ld=0, res_ld=0, x_ld=0, x2_ld=0, round_out=0, skip_x=ptr(wd, 128), skip_x2=None,
+                     skip_w=ptr(eye), bias2=None, skip_c1=128, skip_c2=0, skip_x_ld=256, skip_x2_ld=0)
+    lib.call("b200_conv_igemm", a, stream())
+    assert rel(out.permute(0, 3, 1, 2).cpu(), ref) < TF32_TOL
