@@ -167,6 +167,9 @@ def test_sampler_vs_reference_fixture(built_lib, golden, tag, graph):
     assert frac_far(zs.cpu(), f["zs"], 5e-3) < 0.03, tag
     # teacher-forced single steps: z_t from the reference trajectory, same noise, compare x~ and z_s (posterior sample)
     T, n = f["T"], f["init"].shape[0]
+    # classifier-free guidance extrapolates e = (1+w) e_c - w e_u with w up to 4 (gaussian_diffusion.py:181): the TF32
+    # net error is amplified up to (1+2w) = 9x before the x^ reconstruction, so the guided case gets a wider pixel budget
+    far = 0.03 if cw is not None else 0.01
     b = m._plan(n, "sample")
     for k in range(T):
         z_t = f["init"] if k == 0 else f["zs"][k - 1]
@@ -176,10 +179,10 @@ def test_sampler_vs_reference_fixture(built_lib, golden, tag, graph):
             b.noise.copy_(noises[k].reshape(n, -1))
         b.enqueue_sampler_step(draw_noise=False)
         x_ours, z_ours = b.x_hist.cpu().view(n, 1, 28, 28), b.plan.z_in.cpu().view(n, 1, 28, 28)
-        assert frac_far(x_ours, f["xs"][k], 5e-3) < 0.01, (tag, k)
-        assert frac_far(z_ours, f["zs"][k], 5e-3) < 0.01, (tag, k)
+        assert frac_far(x_ours, f["xs"][k], 5e-3) < far, (tag, k)
+        assert frac_far(z_ours, f["zs"][k], 5e-3) < far, (tag, k)
         if k > 0:  # away from logsnr = -20 the step is well conditioned: max-norm bar
-            assert rel(z_ours, f["zs"][k]) < 5e-3, (tag, k)
+            assert rel(z_ours, f["zs"][k]) < (3e-2 if cw is not None else 5e-3), (tag, k)
 
 
 def test_rng_draw_order_is_the_references(built_lib):
