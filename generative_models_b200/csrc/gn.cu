@@ -1,6 +1,14 @@
 // GroupNorm(32 groups) + SiLU, forward and backward, over NHWC fp32 rows (optionally a virtual channel concat of two
-// tensors).  Bandwidth-bound: every kernel moves float4s with fully coalesced pixel rows; per-(sample, group)
-// moments are reduced with warp/smem reductions and a handful of global atomics.
+// tensors).  Bandwidth-bound, so the design goal is the algorithmic minimum of HBM traffic:
+//   forward  = read x once, write y once                  (8 B per element)
+//   backward = read x and dy once (+ the residual adds), write dx once   (12 B per element + adds)
+// A CTA owns one (sample, 16/32-channel slice): whole groups, all HW pixels.  It pulls the slice into shared memory with
+// cp.async (everything in flight at once, no register staging), computes the group moments from smem (two-pass
+// variance), then streams the result out — so the second and third read of the classic stats/apply split never leave the
+// SM.  Slices are 64/128 B per pixel row: every global access is a whole number of 32 B sectors, and neighbouring
+// slices of the same pixel rows are processed by neighbouring CTAs.  Shapes whose slice does not fit in smem (HW > ~1800)
+// use the streaming three-kernel path at the end of this file.
+// stats is [N][32][2] = {mean, rstd}: written by the forward, read by the backward.
 // Reference: nn.GroupNorm(32, C) -> nn.SiLU in gms/diffusion/simple_unet.py:38-41,161-163,168-170.
 #include "host_common.h"
 #include "dev_common.cuh"
@@ -20,11 +28,241 @@ __device__ __forceinline__ float4 ld_src(const GnSrc& s, size_t pix, int c) {
   return (c < s.C1) ? *reinterpret_cast<const float4*>(s.x + pix * s.ld1 + c)
                     : *reinterpret_cast<const float4*>(s.x2 + pix * s.ld2 + (c - s.C1));
 }
-__device__ __forceinline__ float silu_f(float u) { return u / (1.0f + expf(-u)); }
+// SiLU with the hardware exp2 / reciprocal (2 MUFU ops, ~1e-6 relative): the IEEE expf + division sequence costs about
+// as many issue slots as the kernel's whole memory phase.
+__device__ __forceinline__ float sigmoid_f(float u) { return __frcp_rn(1.0f + __expf(-u)); }
+__device__ __forceinline__ float silu_f(float u) { return u * sigmoid_f(u); }
+// d silu(u) / du
+__device__ __forceinline__ float dsilu_f(float u) {
+  const float sg = sigmoid_f(u);
+  return sg * (1.0f + u * (1.0f - sg));
+}
+__device__ __forceinline__ void cp_async16(void* smem_dst, const void* gsrc) {
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(
+                   static_cast<uint32_t>(__cvta_generic_to_shared(smem_dst))), "l"(gsrc) : "memory");
+}
+__device__ __forceinline__ void cp_async_wait_all() {
+  asm volatile("cp.async.commit_group;\n\tcp.async.wait_group 0;" ::: "memory");
+}
 
-// ---------------------------------------------------------------------------------------------------- forward stats
-// grid (chunks, N), block 256.  stats[n][g] = {sum, sumsq}; caller zeroes stats.
-__global__ void __launch_bounds__(256) gn_stats_kernel(GnSrc s, float* __restrict__ stats, int pix_per_chunk) {
+
+// reduce `v` over the threads of a warp that share the same float4 lane (and, for 8-channel groups, its neighbour)
+template <int L>
+__device__ __forceinline__ float lane_group_sum(float v, bool pair) {
+#pragma unroll
+  for (int o = 16; o >= L; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  if (pair) v += __shfl_xor_sync(0xffffffffu, v, 1);
+  return v;
+}
+
+// ---------------------------------------------------------------------------------------------------- fused forward
+// grid = N * (C / CS); block 256; dynamic smem = HW * CS * 4 bytes.
+template <int CS, int kGnThreads>
+__global__ void __launch_bounds__(kGnThreads)
+gn_fwd_fused_kernel(GnSrc s, float* __restrict__ stats, const float* __restrict__ gamma, const float* __restrict__ beta,
+                    float* __restrict__ y, float eps, int silu, int tf32) {
+  extern __shared__ float4 gn_smem[];
+  __shared__ float red[16];
+  constexpr int L = CS / 4;  // float4 lanes per pixel of the slice
+  const int slices = s.C / CS;
+  const int n = blockIdx.x / slices;
+  const int c0 = (blockIdx.x - n * slices) * CS;
+  const int cpg = s.C >> 5;
+  const int tid = threadIdx.x;
+  const int lane = tid & 31;
+  const int l = tid % L;  // fixed per thread: kGnThreads % L == 0
+  const int c = c0 + l * 4;
+  const int gl = (l * 4) / cpg;  // group within the slice
+  const int total = s.HW * L;
+  const float* src;
+  int ld;
+  if (c < s.C1) {
+    src = s.x + c;
+    ld = s.ld1;
+  } else {
+    src = s.x2 + (c - s.C1);
+    ld = s.ld2;
+  }
+  src += static_cast<size_t>(n) * s.HW * ld;
+  if (tid < 16) red[tid] = 0.f;
+  for (int idx = tid; idx < total; idx += kGnThreads) cp_async16(&gn_smem[idx], src + static_cast<size_t>(idx / L) * ld);
+  cp_async_wait_all();
+  __syncthreads();
+  const bool pair = (cpg == 8);
+  const bool leader = (lane < L) && (!pair || !(lane & 1));
+  const float inv_cnt = 1.0f / static_cast<float>(s.HW * cpg);
+  float sum = 0.f;
+  for (int idx = tid; idx < total; idx += kGnThreads) {
+    const float4 v = gn_smem[idx];
+    sum += (v.x + v.y) + (v.z + v.w);
+  }
+  sum = lane_group_sum<L>(sum, pair);
+  if (leader) atomicAdd(&red[gl], sum);
+  __syncthreads();
+  const float mean = red[gl] * inv_cnt;
+  float sq = 0.f;
+  for (int idx = tid; idx < total; idx += kGnThreads) {
+    const float4 v = gn_smem[idx];
+    const float a = v.x - mean, b = v.y - mean, cc = v.z - mean, d = v.w - mean;
+    sq += (a * a + b * b) + (cc * cc + d * d);
+  }
+  sq = lane_group_sum<L>(sq, pair);
+  if (leader) atomicAdd(&red[8 + gl], sq);
+  __syncthreads();
+  const float rstd = rsqrtf(red[8 + gl] * inv_cnt + eps);
+  if (tid < L && (!pair || !(tid & 1)))
+    *reinterpret_cast<float2*>(stats + (static_cast<size_t>(n) * 32 + c / cpg) * 2) = make_float2(mean, rstd);
+  const float4 ga = *reinterpret_cast<const float4*>(gamma + c);
+  const float4 be = *reinterpret_cast<const float4*>(beta + c);
+  const float4 sc = make_float4(rstd * ga.x, rstd * ga.y, rstd * ga.z, rstd * ga.w);
+  float* dst = y + static_cast<size_t>(n) * s.HW * s.C + c;
+  for (int idx = tid; idx < total; idx += kGnThreads) {
+    const float4 v = gn_smem[idx];
+    float4 o;
+    o.x = (v.x - mean) * sc.x + be.x;
+    o.y = (v.y - mean) * sc.y + be.y;
+    o.z = (v.z - mean) * sc.z + be.z;
+    o.w = (v.w - mean) * sc.w + be.w;
+    if (silu) {
+      o.x = silu_f(o.x); o.y = silu_f(o.y); o.z = silu_f(o.z); o.w = silu_f(o.w);
+    }
+    if (tf32) o = round_tf32(o);
+    *reinterpret_cast<float4*>(dst + static_cast<size_t>(idx / L) * s.C) = o;
+  }
+}
+
+// ---------------------------------------------------------------------------------------------------- fused backward
+// du = dy * silu'(u), dxhat = du * gamma.  Per (n, g): m1 = mean(dxhat), m2 = mean(dxhat * xhat);
+// dx = rstd * (dxhat - m1 - xhat * m2) (+ add1 + add2 on the first add_c channels); per channel dgamma += sum du * xhat,
+// dbeta += sum du.  grid = N * (C / CS); dynamic smem = 2 * HW * CS * 4 bytes (x slice, then dy slice; overwritten in
+// place by xhat and du).  A variant that kept only dy in smem and re-read x through L2 (twice the CTAs per SM) measured
+// slower (201 vs 159 us at N512 HW784 C128): the register-staged global loads of phase 1 do not stay in flight the way
+// the cp.async bulk does.
+template <int CS, int kGnThreads>
+__global__ void __launch_bounds__(kGnThreads)
+gn_bwd_fused_kernel(GnSrc s, const float* __restrict__ stats, const float* __restrict__ gamma,
+                    const float* __restrict__ beta, const float* __restrict__ dy, float* __restrict__ dx,
+                    const float* __restrict__ add1, int add1_ld, const float* __restrict__ add2, int add2_ld, int add_c,
+                    float* __restrict__ dgamma, float* __restrict__ dbeta, int silu, int round_dx) {
+  extern __shared__ float4 gn_smem[];
+  __shared__ float red[16];
+  __shared__ float chan[2 * CS];
+  constexpr int L = CS / 4;
+  const int slices = s.C / CS;
+  const int n = blockIdx.x / slices;
+  const int c0 = (blockIdx.x - n * slices) * CS;
+  const int cpg = s.C >> 5;
+  const int tid = threadIdx.x;
+  const int lane = tid & 31;
+  const int l = tid % L;
+  const int c = c0 + l * 4;
+  const int gl = (l * 4) / cpg;
+  const int total = s.HW * L;
+  float4* xs = gn_smem;
+  float4* ds = gn_smem + total;
+  const float* src;
+  int ld;
+  if (c < s.C1) {
+    src = s.x + c;
+    ld = s.ld1;
+  } else {
+    src = s.x2 + (c - s.C1);
+    ld = s.ld2;
+  }
+  src += static_cast<size_t>(n) * s.HW * ld;
+  const size_t row0 = static_cast<size_t>(n) * s.HW;
+  const float* dsrc = dy + row0 * s.C + c;
+  if (tid < 16) red[tid] = 0.f;
+  if (tid < 2 * CS) chan[tid] = 0.f;
+  for (int idx = tid; idx < total; idx += kGnThreads) {
+    const size_t pix = idx / L;
+    cp_async16(&xs[idx], src + pix * ld);
+    cp_async16(&ds[idx], dsrc + pix * s.C);
+  }
+  cp_async_wait_all();
+  __syncthreads();
+  const float2 st = *reinterpret_cast<const float2*>(stats + (static_cast<size_t>(n) * 32 + c / cpg) * 2);
+  const float mean = st.x, rstd = st.y;
+  const float4 ga4 = *reinterpret_cast<const float4*>(gamma + c);
+  const float4 be4 = *reinterpret_cast<const float4*>(beta + c);
+  const float ga[4] = {ga4.x, ga4.y, ga4.z, ga4.w};
+  const float be[4] = {be4.x, be4.y, be4.z, be4.w};
+  float dg[4] = {0.f, 0.f, 0.f, 0.f}, db[4] = {0.f, 0.f, 0.f, 0.f};
+  float s1 = 0.f, s2 = 0.f;
+  for (int idx = tid; idx < total; idx += kGnThreads) {
+    const float4 v = xs[idx];
+    const float4 d = ds[idx];
+    const float xv[4] = {v.x, v.y, v.z, v.w};
+    const float dv[4] = {d.x, d.y, d.z, d.w};
+    float xh[4], du[4];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      xh[j] = (xv[j] - mean) * rstd;
+      du[j] = silu ? dv[j] * dsilu_f(xh[j] * ga[j] + be[j]) : dv[j];
+      dg[j] += du[j] * xh[j];
+      db[j] += du[j];
+      const float dxh = du[j] * ga[j];
+      s1 += dxh;
+      s2 += dxh * xh[j];
+    }
+    xs[idx] = make_float4(xh[0], xh[1], xh[2], xh[3]);  // own slot: re-read by this thread only
+    ds[idx] = make_float4(du[0], du[1], du[2], du[3]);
+  }
+  const bool pair = (cpg == 8);
+  s1 = lane_group_sum<L>(s1, pair);
+  s2 = lane_group_sum<L>(s2, pair);
+#pragma unroll
+  for (int j = 0; j < 4; ++j) {
+    dg[j] = lane_group_sum<L>(dg[j], false);
+    db[j] = lane_group_sum<L>(db[j], false);
+  }
+  if (lane < L) {
+    if (!pair || !(lane & 1)) {
+      atomicAdd(&red[gl], s1);
+      atomicAdd(&red[8 + gl], s2);
+    }
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      atomicAdd(&chan[l * 4 + j], dg[j]);
+      atomicAdd(&chan[CS + l * 4 + j], db[j]);
+    }
+  }
+  __syncthreads();
+  if (tid < CS) atomicAdd(&dgamma[c0 + tid], chan[tid]);
+  else if (tid < 2 * CS) atomicAdd(&dbeta[c0 + tid - CS], chan[tid]);
+  const float inv_cnt = 1.0f / static_cast<float>(s.HW * cpg);
+  const float m1 = red[gl] * inv_cnt, m2 = red[8 + gl] * inv_cnt;
+  const bool has_add = c < add_c;
+  const float* a1 = (has_add && add1) ? add1 + row0 * add1_ld + c : nullptr;
+  const float* a2 = (has_add && add2) ? add2 + row0 * add2_ld + c : nullptr;
+  float* dst = dx + row0 * s.C + c;
+  for (int idx = tid; idx < total; idx += kGnThreads) {
+    const size_t pix = idx / L;
+    const float4 xh = xs[idx];
+    const float4 du = ds[idx];
+    float4 o;
+    o.x = rstd * (du.x * ga[0] - m1 - xh.x * m2);
+    o.y = rstd * (du.y * ga[1] - m1 - xh.y * m2);
+    o.z = rstd * (du.z * ga[2] - m1 - xh.z * m2);
+    o.w = rstd * (du.w * ga[3] - m1 - xh.w * m2);
+    if (a1) {
+      const float4 a = __ldg(reinterpret_cast<const float4*>(a1 + pix * add1_ld));
+      o.x += a.x; o.y += a.y; o.z += a.z; o.w += a.w;
+    }
+    if (a2) {
+      const float4 a = __ldg(reinterpret_cast<const float4*>(a2 + pix * add2_ld));
+      o.x += a.x; o.y += a.y; o.z += a.z; o.w += a.w;
+    }
+    if (round_dx) o = round_tf32(o);
+    *reinterpret_cast<float4*>(dst + pix * s.C) = o;
+  }
+}
+
+// ---------------------------------------------------------------------------------------------------- streaming path
+// For slices that do not fit in shared memory (e.g. 64x64 images): stats (atomics on {sum, sumsq}) -> finalize
+// ({mean, rstd}) -> apply; backward: reduce -> apply.  One more read of x (and dy) than the fused kernels.
+// grid (chunks, N), block 256.  acc[n][g] = {sum, sumsq}; zeroed by the caller.
+__global__ void __launch_bounds__(256) gn_stats_kernel(GnSrc s, float* __restrict__ acc, int pix_per_chunk) {
   __shared__ float sh[64];
   const int n = blockIdx.y;
   const int lanes = s.C >> 2;  // float4 lanes per pixel: 32 or 64
@@ -47,27 +285,31 @@ __global__ void __launch_bounds__(256) gn_stats_kernel(GnSrc s, float* __restric
   atomicAdd(&sh[g * 2], sum);
   atomicAdd(&sh[g * 2 + 1], sq);
   __syncthreads();
-  if (threadIdx.x < 64) atomicAdd(&stats[n * 64 + threadIdx.x], sh[threadIdx.x]);
+  if (threadIdx.x < 64) atomicAdd(&acc[n * 64 + threadIdx.x], sh[threadIdx.x]);
 }
 
-// ---------------------------------------------------------------------------------------------------- forward apply
+__global__ void gn_finalize_kernel(float* __restrict__ stats, int n_groups, float inv_cnt, float eps) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n_groups) return;
+  const float2 a = *reinterpret_cast<const float2*>(stats + 2 * i);
+  const float mean = a.x * inv_cnt;
+  const float var = fmaxf(a.y * inv_cnt - mean * mean, 0.f);
+  *reinterpret_cast<float2*>(stats + 2 * i) = make_float2(mean, rsqrtf(var + eps));
+}
+
 __global__ void __launch_bounds__(256)
 gn_apply_kernel(GnSrc s, const float* __restrict__ stats, const float* __restrict__ gamma,
-                const float* __restrict__ beta, float* __restrict__ y, float eps, int silu, int tf32) {
+                const float* __restrict__ beta, float* __restrict__ y, int silu, int tf32) {
   const int lanes = s.C >> 2;
   const size_t total = static_cast<size_t>(s.N) * s.HW * lanes;
   const int cpg = s.C >> 5;
-  const float inv_cnt = 1.0f / static_cast<float>(s.HW * cpg);
   for (size_t i = blockIdx.x * static_cast<size_t>(blockDim.x) + threadIdx.x; i < total;
        i += static_cast<size_t>(gridDim.x) * blockDim.x) {
     const size_t pix = i / lanes;
     const int c = static_cast<int>(i - pix * lanes) * 4;
     const int n = static_cast<int>(pix / s.HW);
-    const int g = c / cpg;
-    const float2 st = *reinterpret_cast<const float2*>(stats + (n * 32 + g) * 2);
-    const float mean = st.x * inv_cnt;
-    const float var = fmaxf(st.y * inv_cnt - mean * mean, 0.f);
-    const float rstd = rsqrtf(var + eps);
+    const float2 st = *reinterpret_cast<const float2*>(stats + (n * 32 + c / cpg) * 2);
+    const float mean = st.x, rstd = st.y;
     const float4 v = ld_src(s, pix, c);
     const float4 ga = *reinterpret_cast<const float4*>(gamma + c);
     const float4 be = *reinterpret_cast<const float4*>(beta + c);
@@ -79,25 +321,15 @@ gn_apply_kernel(GnSrc s, const float* __restrict__ stats, const float* __restric
     if (silu) {
       o.x = silu_f(o.x); o.y = silu_f(o.y); o.z = silu_f(o.z); o.w = silu_f(o.w);
     }
-    if (tf32) {
-      o.x = round_tf32(o.x); o.y = round_tf32(o.y); o.z = round_tf32(o.z); o.w = round_tf32(o.w);
-    }
+    if (tf32) o = round_tf32(o);
     *reinterpret_cast<float4*>(y + pix * s.C + c) = o;
   }
-}
-
-// ---------------------------------------------------------------------------------------------------- backward
-// du = dy * silu'(u), dxhat = du * gamma.  Pass 1 reduces, per (n, g): s1 = sum dxhat, s2 = sum dxhat * xhat, and per
-// channel dgamma += sum du * xhat, dbeta += sum du.  Pass 2 writes dx = rstd * (dxhat - s1/cnt - xhat * s2/cnt) (+adds).
-__device__ __forceinline__ float dsilu_f(float u) {
-  const float sg = 1.0f / (1.0f + expf(-u));
-  return sg * (1.0f + u * (1.0f - sg));
 }
 
 __global__ void __launch_bounds__(256)
 gn_bwd_reduce_kernel(GnSrc s, const float* __restrict__ stats, const float* __restrict__ gamma,
                      const float* __restrict__ beta, const float* __restrict__ dy, float* __restrict__ red,
-                     float* __restrict__ dgamma, float* __restrict__ dbeta, float eps, int silu, int pix_per_chunk) {
+                     float* __restrict__ dgamma, float* __restrict__ dbeta, int silu, int pix_per_chunk) {
   __shared__ float sh[64];
   __shared__ float shg[256 * 8];
   const int n = blockIdx.y;
@@ -110,10 +342,8 @@ gn_bwd_reduce_kernel(GnSrc s, const float* __restrict__ stats, const float* __re
   const int g = c / cpg;
   if (threadIdx.x < 64) sh[threadIdx.x] = 0.f;
   __syncthreads();
-  const float inv_cnt = 1.0f / static_cast<float>(s.HW * cpg);
   const float2 st = *reinterpret_cast<const float2*>(stats + (n * 32 + g) * 2);
-  const float mean = st.x * inv_cnt;
-  const float rstd = rsqrtf(fmaxf(st.y * inv_cnt - mean * mean, 0.f) + eps);
+  const float mean = st.x, rstd = st.y;
   const float4 ga = *reinterpret_cast<const float4*>(gamma + c);
   const float4 be = *reinterpret_cast<const float4*>(beta + c);
   const float gav[4] = {ga.x, ga.y, ga.z, ga.w};
@@ -165,7 +395,7 @@ __global__ void __launch_bounds__(256)
 gn_bwd_apply_kernel(GnSrc s, const float* __restrict__ stats, const float* __restrict__ gamma,
                     const float* __restrict__ beta, const float* __restrict__ dy, const float* __restrict__ red,
                     float* __restrict__ dx, const float* __restrict__ add1, int add1_ld,
-                    const float* __restrict__ add2, int add2_ld, int add_c, float eps, int silu, int round_dx) {
+                    const float* __restrict__ add2, int add2_ld, int add_c, int silu, int round_dx) {
   const int lanes = s.C >> 2;
   const size_t total = static_cast<size_t>(s.N) * s.HW * lanes;
   const int cpg = s.C >> 5;
@@ -178,8 +408,7 @@ gn_bwd_apply_kernel(GnSrc s, const float* __restrict__ stats, const float* __res
     const int g = c / cpg;
     const float2 st = *reinterpret_cast<const float2*>(stats + (n * 32 + g) * 2);
     const float2 rd = *reinterpret_cast<const float2*>(red + (n * 32 + g) * 2);
-    const float mean = st.x * inv_cnt;
-    const float rstd = rsqrtf(fmaxf(st.y * inv_cnt - mean * mean, 0.f) + eps);
+    const float mean = st.x, rstd = st.y;
     const float m1 = rd.x * inv_cnt, m2 = rd.y * inv_cnt;
     const float4 v = ld_src(s, pix, c);
     const float4 d = *reinterpret_cast<const float4*>(dy + pix * s.C + c);
@@ -234,6 +463,7 @@ static int gn_src(const b200_gn_args* a, GnSrc* s) {
   const int C = a->C1 + a->C2;
   if (C != 128 && C != 256) return fail_arg("gn: C1+C2 must be 128 or 256");
   if (a->C1 % 4 || a->C2 % 4 || (a->C2 && !a->x2)) return fail_arg("gn: bad channel split");
+  if (a->N <= 0 || a->HW <= 0) return fail_arg("gn: empty tensor");
   s->x = a->x;
   s->x2 = a->x2;
   s->ld1 = a->x_ld ? a->x_ld : a->C1;
@@ -245,24 +475,85 @@ static int gn_src(const b200_gn_args* a, GnSrc* s) {
   return 0;
 }
 
-extern "C" int b200_gn_stats(const b200_gn_args* a, void* ws, size_t ws_bytes, void* stream) {
-  (void)ws; (void)ws_bytes;
-  GnSrc s;
-  if (int r = gn_src(a, &s)) return r;
-  const int chunks = gn_chunks(s.N, s.HW);
-  const int ppc = (s.HW + chunks - 1) / chunks;
-  gn_stats_kernel<<<dim3(chunks, s.N), 256, 0, static_cast<cudaStream_t>(stream)>>>(s, a->stats, ppc);
-  return after_launch("gn_stats_kernel");
+// Shared-memory budget of the fused kernels; 0 = not initialised.  Developer knobs: B200_GN_STREAM=1 forces the
+// streaming path, B200_GN_CS=16|32 the slice width, B200_GN_THREADS=256|512 the CTA size.
+static int g_gn_max_dyn = 0;
+static int g_gn_stream = 0, g_gn_cs = 0, g_gn_threads = 0;
+template <typename K>
+static cudaError_t gn_optin(K kernel, int bytes) {
+  return cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
+}
+static int gn_init() {
+  if (g_gn_max_dyn) return 0;
+  int dev = 0, optin = 0;
+  cudaGetDevice(&dev);
+  cudaError_t e = cudaDeviceGetAttribute(&optin, cudaDevAttrMaxSharedMemoryPerBlockOptin, dev);
+  if (e != cudaSuccess) return check_cuda(e, "cudaDeviceGetAttribute(smem optin)");
+  const int max_dyn = optin - 1024;
+  e = gn_optin(gn_fwd_fused_kernel<32, 256>, max_dyn);
+  if (e == cudaSuccess) e = gn_optin(gn_fwd_fused_kernel<16, 256>, max_dyn);
+  if (e == cudaSuccess) e = gn_optin(gn_fwd_fused_kernel<32, 512>, max_dyn);
+  if (e == cudaSuccess) e = gn_optin(gn_fwd_fused_kernel<16, 512>, max_dyn);
+  if (e == cudaSuccess) e = gn_optin(gn_bwd_fused_kernel<32, 256>, max_dyn);
+  if (e == cudaSuccess) e = gn_optin(gn_bwd_fused_kernel<16, 256>, max_dyn);
+  if (e == cudaSuccess) e = gn_optin(gn_bwd_fused_kernel<32, 512>, max_dyn);
+  if (e == cudaSuccess) e = gn_optin(gn_bwd_fused_kernel<16, 512>, max_dyn);
+  if (e != cudaSuccess) return check_cuda(e, "cudaFuncSetAttribute(gn fused)");
+  const char* env = getenv("B200_GN_STREAM");
+  g_gn_stream = env ? atoi(env) : 0;
+  env = getenv("B200_GN_CS");
+  g_gn_cs = env ? atoi(env) : 0;
+  env = getenv("B200_GN_THREADS");
+  g_gn_threads = env ? atoi(env) : 0;
+  g_gn_max_dyn = max_dyn;
+  return 0;
+}
+// channels per slice for `bufs` resident copies of the slice (1 forward, 2 backward); 0 = use the streaming path.
+// Several CTAs per SM are wanted (some stream in while others compute / stream out).
+static int gn_slice(const GnSrc& s, int bufs) {
+  if (g_gn_stream || s.C1 % 32) return 0;
+  const size_t b16 = static_cast<size_t>(s.HW) * 16 * 4 * bufs;
+  if (b16 > static_cast<size_t>(g_gn_max_dyn)) return 0;
+  if (g_gn_cs == 32 && 2 * b16 <= static_cast<size_t>(g_gn_max_dyn)) return 32;
+  if (g_gn_cs == 16) return 16;
+  return (2 * b16 <= 50 * 1024) ? 32 : 16;
+}
+static int gn_threads(size_t smem) {
+  if (g_gn_threads == 256 || g_gn_threads == 512) return g_gn_threads;
+  return smem > 64 * 1024 ? 512 : 256;
 }
 
-extern "C" int b200_gn_apply(const b200_gn_args* a, void* ws, size_t ws_bytes, void* stream) {
+extern "C" int b200_gn_fwd(const b200_gn_args* a, void* ws, size_t ws_bytes, void* stream) {
   (void)ws; (void)ws_bytes;
   GnSrc s;
   if (int r = gn_src(a, &s)) return r;
-  if (!a->y) return fail_arg("gn_apply: null y");
+  if (!a->y) return fail_arg("gn_fwd: null y");
+  if (int r = gn_init()) return r;
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  const int cs = gn_slice(s, 1);
+  if (cs) {
+    const int grid = s.N * (s.C / cs);
+    const size_t smem = static_cast<size_t>(s.HW) * cs * 4;
+    const int th = gn_threads(smem);
+#define GN_FWD(CS, TH) \
+  gn_fwd_fused_kernel<CS, TH><<<grid, TH, smem, st>>>(s, a->stats, a->gamma, a->beta, a->y, a->eps, a->silu, a->round_tf32)
+    if (cs == 32 && th == 256) GN_FWD(32, 256);
+    else if (cs == 32) GN_FWD(32, 512);
+    else if (th == 256) GN_FWD(16, 256);
+    else GN_FWD(16, 512);
+#undef GN_FWD
+    return after_launch("gn_fwd_fused_kernel");
+  }
+  if (int r = check_cuda(cudaMemsetAsync(a->stats, 0, static_cast<size_t>(s.N) * 64 * sizeof(float), st), "gn_fwd memset")) return r;
+  const int chunks = gn_chunks(s.N, s.HW);
+  const int ppc = (s.HW + chunks - 1) / chunks;
+  gn_stats_kernel<<<dim3(chunks, s.N), 256, 0, st>>>(s, a->stats, ppc);
+  if (int r = after_launch("gn_stats_kernel")) return r;
+  const int ng = s.N * 32;
+  gn_finalize_kernel<<<(ng + 255) / 256, 256, 0, st>>>(a->stats, ng, 1.0f / static_cast<float>(s.HW * (s.C >> 5)), a->eps);
+  if (int r = after_launch("gn_finalize_kernel")) return r;
   const size_t total = static_cast<size_t>(s.N) * s.HW * (s.C / 4);
-  gn_apply_kernel<<<ew_grid(total), 256, 0, static_cast<cudaStream_t>(stream)>>>(s, a->stats, a->gamma, a->beta, a->y,
-                                                                                 a->eps, a->silu, a->round_tf32);
+  gn_apply_kernel<<<ew_grid(total), 256, 0, st>>>(s, a->stats, a->gamma, a->beta, a->y, a->silu, a->round_tf32);
   return after_launch("gn_apply_kernel");
 }
 
@@ -271,19 +562,37 @@ extern "C" int b200_gn_bwd(const b200_gn_bwd_args* b, void* ws, size_t ws_bytes,
   GnSrc s;
   if (int r = gn_src(&b->fwd, &s)) return r;
   if (!b->dy || !b->dx || !b->dgamma || !b->dbeta) return fail_arg("gn_bwd: null pointer");
-  const size_t need = static_cast<size_t>(s.N) * 64 * sizeof(float);
-  if (!ws || ws_bytes < need) return fail_arg("gn_bwd: workspace of N*64 floats required");
+  if (int r = gn_init()) return r;
   cudaStream_t st = static_cast<cudaStream_t>(stream);
+  const int add_c = b->add_c ? b->add_c : s.C;
+  const int cs = gn_slice(s, 2);
+  if (cs) {
+    const int grid = s.N * (s.C / cs);
+    const size_t smem = static_cast<size_t>(s.HW) * cs * 4 * 2;
+    const int th = gn_threads(smem);
+#define GN_BWD(CS, TH)                                                                                                  \
+  gn_bwd_fused_kernel<CS, TH><<<grid, TH, smem, st>>>(s, b->fwd.stats, b->fwd.gamma, b->fwd.beta, b->dy, b->dx, b->add1, \
+                                                      b->add1_ld, b->add2, b->add2_ld, add_c, b->dgamma, b->dbeta,       \
+                                                      b->fwd.silu, b->round_dx)
+    if (cs == 32 && th == 256) GN_BWD(32, 256);
+    else if (cs == 32) GN_BWD(32, 512);
+    else if (th == 256) GN_BWD(16, 256);
+    else GN_BWD(16, 512);
+#undef GN_BWD
+    return after_launch("gn_bwd_fused_kernel");
+  }
+  const size_t need = static_cast<size_t>(s.N) * 64 * sizeof(float);
+  if (!ws || ws_bytes < need) return fail_arg("gn_bwd: workspace of N*64 floats required for the streaming path");
   float* red = static_cast<float*>(ws);
   if (int r = check_cuda(cudaMemsetAsync(red, 0, need, st), "gn_bwd memset")) return r;
   const int chunks = gn_chunks(s.N, s.HW);
   const int ppc = (s.HW + chunks - 1) / chunks;
   gn_bwd_reduce_kernel<<<dim3(chunks, s.N), 256, 0, st>>>(s, b->fwd.stats, b->fwd.gamma, b->fwd.beta, b->dy, red,
-                                                          b->dgamma, b->dbeta, b->fwd.eps, b->fwd.silu, ppc);
+                                                          b->dgamma, b->dbeta, b->fwd.silu, ppc);
   if (int r = after_launch("gn_bwd_reduce_kernel")) return r;
   const size_t total = static_cast<size_t>(s.N) * s.HW * (s.C / 4);
   gn_bwd_apply_kernel<<<ew_grid(total), 256, 0, st>>>(s, b->fwd.stats, b->fwd.gamma, b->fwd.beta, b->dy, red, b->dx,
-                                                      b->add1, b->add1_ld, b->add2, b->add2_ld,
-                                                      b->add_c ? b->add_c : s.C, b->fwd.eps, b->fwd.silu, b->round_dx);
+                                                      b->add1, b->add1_ld, b->add2, b->add2_ld, add_c, b->fwd.silu,
+                                                      b->round_dx);
   return after_launch("gn_bwd_apply_kernel");
 }

@@ -156,7 +156,7 @@ def load():
     lib.b200_last_error.restype = C.c_char_p
     lib.b200_launch_count.restype = C.c_ulonglong
     lib.b200_init.argtypes = [C.c_int]
-    if lib.b200_abi_version() != 2:
+    if lib.b200_abi_version() != 3:
         raise B200Error("libb200ddpm.so ABI version mismatch")
     for name in EXPORTS:
         fn = getattr(lib, name)  # AttributeError if the symbol is missing
@@ -172,7 +172,7 @@ def load():
 EXPORTS = [
     "b200_abi_version", "b200_init", "b200_last_error", "b200_launch_count",
     "b200_conv_igemm", "b200_conv_wgrad",
-    "b200_gn_stats", "b200_gn_apply", "b200_gn_bwd",
+    "b200_gn_fwd", "b200_gn_bwd",
     "b200_q_sample", "b200_loss", "b200_sampler_step", "b200_step_advance", "b200_int_increment",
     "b200_conv_in_fwd", "b200_conv_in_bwd", "b200_conv_out_fwd", "b200_conv_out_bwd",
     "b200_upsample2x", "b200_colsum",

@@ -212,16 +212,14 @@ class UNetPlan:
         st1, st2 = self._next_stats(), self._next_stats()
         a1 = pool.get(B, HW, Cin)
         g1 = self._gn(x, x2, name + ".in_layers.0", a1, HW, C2, st1)
-        ops.append(Op("b200_gn_stats", g1))
-        ops.append(Op("b200_gn_apply", g1))
+        ops.append(Op("b200_gn_fwd", g1))
         h1 = pool.get(B, HW, 128)
         ops.append(self._conv(a1, None, name + ".in_layers.2", h1, H, H, 3, 1, 1, Cin, 0,
                               emb=_p(self.embout, k * 128)))
         pool.release(a1)
         a2 = pool.get(B, HW, 128)
         g2 = self._gn(h1, None, name + ".out_layers.0", a2, HW, 0, st2)
-        ops.append(Op("b200_gn_stats", g2))
-        ops.append(Op("b200_gn_apply", g2))
+        ops.append(Op("b200_gn_fwd", g2))
         pool.release(h1)
         skip = None
         if x2 is not None:
@@ -248,8 +246,6 @@ class UNetPlan:
         st = self.store
         self.refresh_ops = [Op("b200_round_tf32", lib.RoundArgs(src=_p(st.flat), dst=_p(st.flat_tc), n=st.numel))]
         ops = []
-        za = lib.ZeroArgs(ptr=_p(self.stats), bytes=self.stats.numel() * 4)
-        ops.append(Op("b200_zero", za))
         pool = self.pool
         H0, H1, H2 = S, S // 2, S // 4
         # ---- Down (simple_unet.py:87-109)
@@ -298,8 +294,7 @@ class UNetPlan:
         sth = self._next_stats()
         ah = pool.get(B, H0 * H0, 128)
         gh = self._gn(u6, None, "out.0", ah, H0 * H0, 0, sth, silu=1, tf32=0)
-        ops.append(Op("b200_gn_stats", gh))
-        ops.append(Op("b200_gn_apply", gh))
+        ops.append(Op("b200_gn_fwd", gh))
         self.body_ops = ops
         self.head_ops = []
         for o in (self.out, self.out2):

@@ -21,7 +21,7 @@
 extern "C" {
 #endif
 
-#define B200_ABI_VERSION 2
+#define B200_ABI_VERSION 3
 
 int b200_abi_version(void);
 int b200_init(int device);
@@ -87,8 +87,9 @@ int b200_conv_wgrad(const b200_wgrad_args* a, void* ws, size_t ws_bytes, void* s
 /* ------------------------------------------------------------------ GroupNorm(32) + SiLU
  * Replaces nn.GroupNorm(32, C) -> nn.SiLU (simple_unet.py:38-41 out head, :161-163 in_layers, :168-170 out_layers).
  * x may be a virtual concat (x: C1 channels with pixel stride x_ld, x2: C2 channels with stride x2_ld; ld 0 = dense).
- * stats is [N][32][2] = {sum, sum of squares}; b200_gn_stats ACCUMULATES into it (caller zeroes), b200_gn_apply
- * writes y[N*HW][C1+C2] = silu?((x-mean)*rstd*gamma+beta), optionally rounded to TF32 for the following conv. */
+ * b200_gn_fwd writes stats[N][32][2] = {mean, rstd} (kept for the backward) and
+ * y[N*HW][C1+C2] = silu?((x-mean)*rstd*gamma+beta), optionally rounded to TF32 for the following conv.  One kernel:
+ * a CTA holds a whole (sample, channel-slice) in shared memory, so x is read from HBM once (8 B per element). */
 typedef struct {
   const float* x;
   const float* x2;
@@ -102,12 +103,12 @@ typedef struct {
   int silu;
   int round_tf32;
 } b200_gn_args;
-int b200_gn_stats(const b200_gn_args* a, void* ws, size_t ws_bytes, void* stream);
-int b200_gn_apply(const b200_gn_args* a, void* ws, size_t ws_bytes, void* stream);
+int b200_gn_fwd(const b200_gn_args* a, void* ws, size_t ws_bytes, void* stream);
 
 /* backward of the same block: dy is the gradient w.r.t. y.  dx[N*HW][C] = GN/SiLU backward (+ add1 + add2 on the
  * first add_c channels: the other gradients that flow into the same tensor).  dgamma/dbeta are accumulated with
- * atomics (caller zeroes the flat gradient buffer once per step).  ws: N*64 floats. */
+ * atomics (caller zeroes the flat gradient buffer once per step).  fwd.stats must hold what b200_gn_fwd wrote.
+ * ws: N*64 floats (used only when HW is too large for the shared-memory-resident kernel). */
 typedef struct {
   b200_gn_args fwd;
   const float* dy;

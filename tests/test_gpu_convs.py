@@ -150,8 +150,10 @@ def test_conv_wgrad(lib, N, H, Cin, R, stride, pad, ks):
 
 
 # ------------------------------------------------------------------------------------------------ GroupNorm + SiLU
-@pytest.mark.parametrize("N,HW,C2", [(3, 784, 0), (2, 196, 128), (5, 49, 0), (2, 1024, 128)])
+@pytest.mark.parametrize("N,HW,C2", [(3, 784, 0), (2, 784, 128), (2, 196, 128), (5, 196, 0), (5, 49, 0), (3, 49, 128),
+                                     (2, 1024, 128), (2, 1024, 0), (1, 4096, 128), (2, 4096, 0)])
 def test_gn_silu_fwd_bwd(lib, N, HW, C2):
+    """HW <= 1024 runs the shared-memory-resident kernels (32- and 16-channel slices), HW = 4096 the streaming path."""
     g = torch.Generator().manual_seed(HW + C2)
     Cc = 128 + C2
     x = (rn(g, N, Cc, HW) * 2 + 0.5).requires_grad_(True)
@@ -169,15 +171,17 @@ def test_gn_silu_fwd_bwd(lib, N, HW, C2):
     gd, bd = gamma.detach().to(DEV), beta.detach().to(DEV)
     a = lib.GnArgs(x=ptr(x1), x2=ptr(x2), stats=ptr(stats), gamma=ptr(gd), beta=ptr(bd), y=ptr(yd), N=N, HW=HW, C1=128,
                    C2=C2, x_ld=0, x2_ld=0, eps=1e-5, silu=1, round_tf32=0)
-    lib.call("b200_gn_stats", a, stream())
-    lib.call("b200_gn_apply", a, stream())
+    lib.call("b200_gn_fwd", a, stream())
     assert rel(yd.cpu().permute(0, 2, 1), y.detach()) < 1e-5
+    xd = x.detach().double().view(N, 32, -1)
+    assert rel(stats.cpu().view(N, 32, 2)[..., 0].double(), xd.mean(-1)) < 1e-5
+    assert rel(stats.cpu().view(N, 32, 2)[..., 1].double(), (xd.var(-1, unbiased=False) + 1e-5).rsqrt()) < 1e-5
     # TF32-rounded output: within 2^-11 relative of the unrounded one
     a.round_tf32 = 1
     y32 = torch.empty_like(yd)
     a.y = ptr(y32)
-    lib.call("b200_gn_apply", a, stream())
-    assert ((y32 - yd).abs() <= yd.abs() * 2 ** -11 + 1e-30).all()
+    lib.call("b200_gn_fwd", a, stream())
+    assert ((y32 - yd).abs() <= yd.abs() * 2 ** -11 * 1.01 + 1e-6).all()  # (+ atomics-order jitter of mean/rstd)
     # backward
     dyd = dy.permute(0, 2, 1).contiguous().to(DEV)
     a1 = add1.permute(0, 2, 1).contiguous().to(DEV)
