@@ -5,8 +5,12 @@
 //   Both operands are "MN-major" (the reduction index — pixels — is the slow dimension of the NHWC rows), which
 //   tcgen05 takes directly from 128B-swizzled smem tiles: dY rows come from a 2-D TMA tile, shifted X rows from
 //   the same im2col TMA map the forward uses (border pixels arrive as zeros).
-//   grid = (pixel slices, taps * ci blocks); every CTA reduces its slice in TMEM and adds the 128x128 fp32 tile
-//   into dW with red.global.add.f32 (dW is zeroed once per step by the caller).
+//   A CTA owns one filter ROW (kh) of one 128-channel ci block and a slice of the pixels: every pipeline stage loads
+//   the dY tile once and the three kw-shifted X tiles, and accumulates three 128x128 tiles in TMEM (384 columns).
+//   Sharing dY across the three taps cuts the L2->SM operand feed from 32 KB to 21 KB per 128x128x32 MMA block, which
+//   is what bound the one-tap-per-CTA version (ncu: L2->SM fabric saturated, tensor pipe 40 % busy).
+//   grid = (pixel slices, kh * ci blocks) sized to one CTA per SM; the epilogue adds the fp32 tiles into dW with
+//   red.global.add.v4.f32 (dW is zeroed once per step by the caller) — a quarter of the scalar atomics.
 #include "host_common.h"
 #include "ptx.cuh"
 
@@ -16,25 +20,30 @@ namespace b200 {
 
 constexpr int kWgStages = 3;
 constexpr int kWgTileBytes = 16384;  // 4 boxes of (32 pixels x 128 B)
-constexpr int kWgStageBytes = 2 * kWgTileBytes;
-constexpr int kWgSmem = kWgStages * kWgStageBytes + 1024 + 256;
-constexpr int kWgPix = 32;  // pixels (reduction elements) per pipeline stage
+constexpr int kWgPix = 32;           // pixels (reduction elements) per pipeline stage
+constexpr int wg_smem_bytes(int taps) { return kWgStages * (1 + taps) * kWgTileBytes + 1024 + 256; }
 
 struct WgradK {
   float* dw;
   int M_total, HoWo, Wo;
   int stride, pad;
-  int S;
+  int S;      // filter width (= height)
+  int taps;   // filter taps handled by one CTA: S (one filter row)
   int C1, Cin;
   int steps_total, steps_per_slice;
 };
+
+__device__ __forceinline__ void red_add_v4(float* p, float a, float b, float c, float d) {
+  asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(p), "f"(a), "f"(b), "f"(c), "f"(d) : "memory");
+}
 
 __global__ void __launch_bounds__(192)
 conv_wgrad_tf32_kernel(const __grid_constant__ CUtensorMap tmDY, const __grid_constant__ CUtensorMap tmX,
                        const __grid_constant__ CUtensorMap tmX2, const WgradK a) {
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
-  uint64_t* full = reinterpret_cast<uint64_t*>(smem + kWgStages * kWgStageBytes);
+  const int stage_bytes = (1 + a.taps) * kWgTileBytes;
+  uint64_t* full = reinterpret_cast<uint64_t*>(smem + kWgStages * stage_bytes);
   uint64_t* empty = full + kWgStages;
   uint64_t* tmem_full = empty + kWgStages;
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_full + 1);
@@ -48,9 +57,9 @@ conv_wgrad_tf32_kernel(const __grid_constant__ CUtensorMap tmDY, const __grid_co
   if (num_it <= 0) return;  // uniform for the whole CTA
 
   const int ci_blocks = a.Cin / 128;
-  const int tap = blockIdx.y / ci_blocks;
-  const int cib = blockIdx.y - tap * ci_blocks;
-  const int kh = tap / a.S, kw = tap - kh * a.S;
+  const int kh = blockIdx.y / ci_blocks;
+  const int cib = blockIdx.y - kh * ci_blocks;
+  const uint32_t tmem_cols = a.taps > 2 ? 512u : (a.taps == 2 ? 256u : 128u);
 
   if (threadIdx.x == 0) {
     tma_prefetch_desc(&tmDY);
@@ -64,7 +73,7 @@ conv_wgrad_tf32_kernel(const __grid_constant__ CUtensorMap tmDY, const __grid_co
     fence_mbar_init();
   }
   if (warp == 1) {
-    tmem_alloc(tmem_slot, 128);
+    tmem_alloc(tmem_slot, tmem_cols);
     tmem_relinquish();
   }
   tc_fence_before();
@@ -81,19 +90,21 @@ conv_wgrad_tf32_kernel(const __grid_constant__ CUtensorMap tmDY, const __grid_co
         const int s = it % kWgStages;
         const uint32_t ph = (it / kWgStages) & 1;
         mbar_wait(&empty[s], ph ^ 1);
-        mbar_expect_tx(&full[s], kWgStageBytes);
+        mbar_expect_tx(&full[s], stage_bytes);
         const int pix0 = (step_begin + it) * kWgPix;
         const int n = pix0 / a.HoWo;
         const int rem = pix0 - n * a.HoWo;
         const int p = rem / a.Wo;
         const int q = rem - p * a.Wo;
-        uint8_t* sA = smem + s * kWgStageBytes;
-        uint8_t* sB = sA + kWgTileBytes;
+        uint8_t* sA = smem + s * stage_bytes;
 #pragma unroll
-        for (int j = 0; j < 4; ++j) {
-          tma_load_2d(sA + j * 4096, &tmDY, &full[s], j * 32, pix0);
-          tma_load_im2col_4d(sB + j * 4096, xm, &full[s], c_src + j * 32, q * a.stride - a.pad, p * a.stride - a.pad, n,
-                             (uint16_t)kw, (uint16_t)kh);
+        for (int j = 0; j < 4; ++j) tma_load_2d(sA + j * 4096, &tmDY, &full[s], j * 32, pix0);
+        for (int kw = 0; kw < a.taps; ++kw) {
+          uint8_t* sB = sA + (1 + kw) * kWgTileBytes;
+#pragma unroll
+          for (int j = 0; j < 4; ++j)
+            tma_load_im2col_4d(sB + j * 4096, xm, &full[s], c_src + j * 32, q * a.stride - a.pad, p * a.stride - a.pad, n,
+                               (uint16_t)kw, (uint16_t)kh);
         }
       }
     }
@@ -105,13 +116,15 @@ conv_wgrad_tf32_kernel(const __grid_constant__ CUtensorMap tmDY, const __grid_co
         const uint32_t ph = (it / kWgStages) & 1;
         mbar_wait(&full[s], ph);
         tc_fence_after();
-        const uint32_t a_base = smem_u32(smem + s * kWgStageBytes);
-        const uint32_t b_base = a_base + kWgTileBytes;
+        const uint32_t a_base = smem_u32(smem + s * stage_bytes);
+        for (int kw = 0; kw < a.taps; ++kw) {
+          const uint32_t b_base = a_base + (1 + kw) * kWgTileBytes;
 #pragma unroll
-        for (int k = 0; k < 4; ++k) {
-          const uint64_t adesc = make_smem_desc_sw128(a_base + k * 1024, 4096, 512, 1);
-          const uint64_t bdesc = make_smem_desc_sw128(b_base + k * 1024, 4096, 512, 1);
-          mma_tf32_ss(tmem_base, adesc, bdesc, idesc, (it | k) != 0 ? 1u : 0u);
+          for (int k = 0; k < 4; ++k) {
+            const uint64_t adesc = make_smem_desc_sw128(a_base + k * 1024, 4096, 512, 1);
+            const uint64_t bdesc = make_smem_desc_sw128(b_base + k * 1024, 4096, 512, 1);
+            mma_tf32_ss(tmem_base + kw * 128, adesc, bdesc, idesc, (it | k) != 0 ? 1u : 0u);
+          }
         }
         tc_commit(&empty[s]);
       }
@@ -123,21 +136,26 @@ conv_wgrad_tf32_kernel(const __grid_constant__ CUtensorMap tmDY, const __grid_co
     mbar_wait(tmem_full, 0);
     tc_fence_after();
     const int row_len = a.S * a.S * a.Cin;
-    float* drow = a.dw + static_cast<size_t>(co) * row_len + tap * a.Cin + cib * 128;
+    float* drow = a.dw + static_cast<size_t>(co) * row_len + (kh * a.S) * a.Cin + cib * 128;
+    for (int kw = 0; kw < a.taps; ++kw) {
 #pragma unroll 1
-    for (int cc = 0; cc < 4; ++cc) {
-      uint32_t r[32];
-      tmem_ld_32x32(tmem_base + (static_cast<uint32_t>(quarter * 32) << 16) + cc * 32, r);
-      tmem_ld_wait();
+      for (int cc = 0; cc < 4; ++cc) {
+        uint32_t r[32];
+        tmem_ld_32x32(tmem_base + (static_cast<uint32_t>(quarter * 32) << 16) + kw * 128 + cc * 32, r);
+        tmem_ld_wait();
+        float* d = drow + kw * a.Cin + cc * 32;
 #pragma unroll
-      for (int j = 0; j < 32; ++j) atomicAdd(drow + cc * 32 + j, __uint_as_float(r[j]));
+        for (int j = 0; j < 32; j += 4)
+          red_add_v4(d + j, __uint_as_float(r[j]), __uint_as_float(r[j + 1]), __uint_as_float(r[j + 2]),
+                     __uint_as_float(r[j + 3]));
+      }
     }
   }
   tc_fence_before();
   __syncthreads();
   if (warp == 1) {
     tc_fence_after();
-    tmem_dealloc(tmem_base, 128);
+    tmem_dealloc(tmem_base, tmem_cols);
   }
 }
 
@@ -155,6 +173,14 @@ extern "C" int b200_conv_wgrad(const b200_wgrad_args* a, void* ws, size_t ws_byt
   if (a->stride != 1 && a->stride != 2) return fail_arg("conv_wgrad: stride must be 1 or 2");
   const int ho = (a->H + 2 * a->pad - a->R) / a->stride + 1, wo = (a->W + 2 * a->pad - a->S) / a->stride + 1;
   if (ho != a->Ho || wo != a->Wo) return fail_arg("conv_wgrad: Ho/Wo do not match the geometry");
+  static int num_sms = 0;
+  if (!num_sms) {
+    cudaError_t e = cudaFuncSetAttribute(conv_wgrad_tf32_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, wg_smem_bytes(3));
+    if (e != cudaSuccess) return check_cuda(e, "cudaFuncSetAttribute(conv_wgrad)");
+    int dev = 0;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&num_sms, cudaDevAttrMultiProcessorCount, dev);
+  }
   const int Cin = a->C1 + a->C2;
   const int M_total = a->N * a->Ho * a->Wo;
   const int lower = -a->pad, upper = a->pad - (a->R - 1);
@@ -171,7 +197,7 @@ extern "C" int b200_conv_wgrad(const b200_wgrad_args* a, void* ws, size_t ws_byt
     tmX2 = tmX;
   }
 
-  const int tiles = a->R * a->S * (Cin / 128);
+  const int tiles = a->R * (Cin / 128);  // one CTA per (filter row, 128-channel ci block, pixel slice)
   WgradK k;
   k.dw = a->dw;
   k.M_total = M_total;
@@ -180,12 +206,14 @@ extern "C" int b200_conv_wgrad(const b200_wgrad_args* a, void* ws, size_t ws_byt
   k.stride = a->stride;
   k.pad = a->pad;
   k.S = a->S;
+  k.taps = a->S;
   k.C1 = a->C1;
   k.Cin = Cin;
   k.steps_total = (M_total + kWgPix - 1) / kWgPix;
   int slices = a->k_slices;
   if (slices <= 0) {
-    slices = (148 * 4 + tiles - 1) / tiles;
+    // one CTA per SM for 3-tap CTAs (they own all 512 TMEM columns and 192 KB of smem), two for 1x1 filters
+    slices = (num_sms * (k.taps > 1 ? 1 : 2)) / tiles;
     const int max_slices = (k.steps_total + 7) / 8;  // at least 8 pipeline steps per CTA
     if (slices > max_slices) slices = max_slices;
     if (slices < 1) slices = 1;
@@ -193,13 +221,7 @@ extern "C" int b200_conv_wgrad(const b200_wgrad_args* a, void* ws, size_t ws_byt
   k.steps_per_slice = (k.steps_total + slices - 1) / slices;
   slices = (k.steps_total + k.steps_per_slice - 1) / k.steps_per_slice;
 
-  static bool attr_set = false;
-  if (!attr_set) {
-    cudaError_t e = cudaFuncSetAttribute(conv_wgrad_tf32_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kWgSmem);
-    if (e != cudaSuccess) return check_cuda(e, "cudaFuncSetAttribute(conv_wgrad)");
-    attr_set = true;
-  }
   dim3 grid(slices, tiles);
-  conv_wgrad_tf32_kernel<<<grid, 192, kWgSmem, static_cast<cudaStream_t>(stream)>>>(tmDY, tmX, tmX2, k);
+  conv_wgrad_tf32_kernel<<<grid, 192, wg_smem_bytes(k.taps), static_cast<cudaStream_t>(stream)>>>(tmDY, tmX, tmX2, k);
   return after_launch("conv_wgrad_tf32_kernel");
 }

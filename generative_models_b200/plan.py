@@ -144,12 +144,12 @@ class UNetPlan:
         return s
 
     def _conv(self, x, x2, wname, out, H, Ho, R, stride, pad, C1, C2, bias=True, emb=None, residual=None,
-              res_ld=128, x_ld=0, x2_ld=0):
+              res_ld=128, x_ld=0, x2_ld=0, round_out=1):
         a = lib.ConvArgs(x=_p(x), x2=_p(x2), w=self._wtc(wname + ".weight"), out=_p(out),
                          bias=self._w(wname + ".bias") if bias else None, emb=emb,
                          residual=residual, N=self.B, H=H, W=H, C1=C1, C2=C2, Ho=Ho, Wo=Ho, R=R, S=R, stride=stride,
                          pad=pad, mode=0, w_cout=128, w_cin=C1 + C2, n_off=0, out_ld=128, emb_ld=12 * self.Cc,
-                         res_ld=res_ld, x_ld=x_ld, x2_ld=x2_ld, round_out=1)
+                         res_ld=res_ld, x_ld=x_ld, x2_ld=x2_ld, round_out=round_out)
         return Op("b200_conv_igemm", a)
 
     def _dgrad(self, dy, wname, out, H, R, pad, w_cin, n_off, out_ld, residual=None, res_ld=0):
@@ -214,8 +214,9 @@ class UNetPlan:
         g1 = self._gn(x, x2, name + ".in_layers.0", a1, HW, C2, st1)
         ops.append(Op("b200_gn_fwd", g1))
         h1 = pool.get(B, HW, 128)
+        # h1 feeds only the GroupNorm (never a tensor-core operand), so it keeps its full fp32 mantissa
         ops.append(self._conv(a1, None, name + ".in_layers.2", h1, H, H, 3, 1, 1, Cin, 0,
-                              emb=_p(self.embout, k * 128)))
+                              emb=_p(self.embout, k * 128), round_out=0))
         pool.release(a1)
         a2 = pool.get(B, HW, 128)
         g2 = self._gn(h1, None, name + ".out_layers.0", a2, HW, 0, st2)
