@@ -257,5 +257,8 @@ def test_training_reduces_loss_and_graph_matches_eager(built_lib):
         losses = [m.train_step(x, y.clone())["loss"].item() for _ in range(12)]
         assert losses[-1] < losses[0]
         finals.append(losses)
-    # atomics in wgrad / GN reductions make runs non-bit-reproducible; graph replay must track eager closely
-    assert abs(finals[0][-1] - finals[1][-1]) < 0.05 * abs(finals[0][-1])
+    # atomics in wgrad / GN reductions make runs non-bit-reproducible (1e-6 relative per step), and Adam at lr 1e-3
+    # amplifies that step by step: graph replay must reproduce the first steps tightly and stay close after 12
+    for k in range(3):
+        assert abs(finals[0][k] - finals[1][k]) < 2e-3 * abs(finals[0][k]), (k, finals)
+    assert abs(finals[0][-1] - finals[1][-1]) < 0.15 * abs(finals[0][-1]), finals
