@@ -195,7 +195,9 @@ def profile_ops(model, bound, kind):
     for i, o in enumerate(ops):
         name = o.name
         if name == "b200_conv_igemm":
-            name += "[dgrad]" if o.args.mode == 1 else "[fprop]"
+            from generative_models_b200 import lib as _lib
+            strip = _lib.load().b200_conv_kernel_of(o.ref) == 1
+            name = ("conv_strip_tf32_kernel" if strip else "conv_igemm_tf32_kernel") + ("[dgrad]" if o.args.mode == 1 else "[fprop]")
         d = out.setdefault(name, {"ms": 0.0, "launches": 0, "flops": 0.0})
         d["ms"] += evs[i].elapsed_time(evs[i + 1])
         d["launches"] += 1
@@ -337,9 +339,9 @@ def run_ours(args, rank, world, local_rank):
     prof = profile_ops(model, bound, "train")
     prof = profile_ops(model, bound, "train")  # second pass: warm
     total_ms = sum(d["ms"] for d in prof.values())
-    conv_ms = sum(d["ms"] for k, d in prof.items() if k.startswith("b200_conv_igemm"))
-    conv_fl = sum(d["flops"] for k, d in prof.items() if k.startswith("b200_conv_igemm"))
-    conv_n = sum(d["launches"] for k, d in prof.items() if k.startswith("b200_conv_igemm"))
+    conv_ms = sum(d["ms"] for k, d in prof.items() if k.startswith("conv_strip_tf32_kernel"))
+    conv_fl = sum(d["flops"] for k, d in prof.items() if k.startswith("conv_strip_tf32_kernel"))
+    conv_n = sum(d["launches"] for k, d in prof.items() if k.startswith("conv_strip_tf32_kernel"))
     peaks = {}
     try:
         peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
@@ -348,8 +350,12 @@ def run_ours(args, rank, world, local_rank):
     tf32_live = measure_tf32_peak()
     achieved = conv_fl / (conv_ms / 1e3) / 1e12
     roofline = {
-        "kernel": "conv_igemm_tf32_kernel (fprop + dgrad launches of one train step)", "bound": "tensor",
-        "achieved": achieved, "peak": tf32_live, "unit": "TFLOP/s", "frac": achieved / tf32_live, "traffic": None,
+        "kernel": "conv_strip_tf32_kernel (all its fprop + dgrad launches of one train step; the top kernel of "
+                  "profiles/r01_launches_summary.md)", "bound": "tensor",
+        "achieved": achieved, "peak": tf32_live, "unit": "TFLOP/s", "frac": achieved / tf32_live,
+        # dram__bytes_read.sum + dram__bytes_write.sum of one captured launch (28x28 128->128 3x3 fprop, batch 512):
+        # profiles/r01_ncu_full_summary.md; algorithmic bytes of that launch = 205.5 MB in + 205.5 MB out + 0.6 MB weights
+        "traffic": 363.5e6, "traffic_launch": "fprop 3x3 128->128 @28x28, N=512 (algorithmic 411.6e6 B)",
         "peak_source": "cuBLAS TF32 8192^3 measured live in this run (MEASURED_PEAKS.json has no TF32 figure; its bf16 "
                        f"burst is {peaks.get('bf16_tflops')} TFLOP/s, i.e. nominal TF32 = half = "
                        f"{(peaks.get('bf16_tflops') or 0) / 2:.1f})",

@@ -190,6 +190,24 @@ conv_igemm_tf32_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_con
 using namespace b200;
 
 int conv_strip_launch(const b200_conv_args* a, void* stream);  // conv_strip.cu
+int conv_strip_applicable(const b200_conv_args* a);
+
+static int strip_enabled() {
+  static int use_strip = -1;
+  if (use_strip < 0) {
+    const char* e = getenv("B200_CONV_STRIP");
+    use_strip = e ? atoi(e) : 1;
+  }
+  return use_strip;
+}
+static bool strip_shape(const b200_conv_args* a) {
+  return a->stride == 1 && ((a->R == 3 && a->pad == 1) || (a->R == 1 && a->pad == 0));
+}
+
+extern "C" int b200_conv_kernel_of(const b200_conv_args* a) {
+  if (!a) return fail_arg("conv_kernel_of: null args");
+  return (strip_enabled() && strip_shape(a) && conv_strip_applicable(a)) ? 1 : 0;
+}
 
 extern "C" int b200_conv_igemm(const b200_conv_args* a, void* ws, size_t ws_bytes, void* stream) {
   (void)ws;
@@ -222,12 +240,7 @@ extern "C" int b200_conv_igemm(const b200_conv_args* a, void* ws, size_t ws_byte
     upper = -a->pad;
   }
   // stride-1 3x3/pad-1 and 1x1/pad-0 layers (all but the two Downsample convs) go to the strip kernel
-  static int use_strip = -1;
-  if (use_strip < 0) {
-    const char* e = getenv("B200_CONV_STRIP");
-    use_strip = e ? atoi(e) : 1;
-  }
-  if (use_strip && a->stride == 1 && ((a->R == 3 && a->pad == 1) || (a->R == 1 && a->pad == 0))) {
+  if (strip_enabled() && strip_shape(a)) {
     const int rs = conv_strip_launch(a, stream);
     if (rs != -100) return rs;
   }

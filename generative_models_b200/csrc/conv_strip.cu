@@ -346,13 +346,27 @@ using namespace b200;
 
 // Called by b200_conv_igemm for stride-1 3x3/pad-1 and 1x1/pad-0 layers.  Returns -100 when the geometry does not fit
 // the strip buffers (caller falls back to the im2col kernel).
+// 1 when the strip kernel takes this (stride-1 3x3/pad-1 or 1x1/pad-0) layer, 0 when the im2col kernel does.
+int conv_strip_applicable(const b200_conv_args* a) {
+  const int flat = (a->R == 1);
+  const int Wp = a->W + 1, Hp = a->H + 1;
+  const int strip_rows = 3 + (257 + Wp - 1) / Wp;
+  if (!flat && strip_rows * Wp * 128 > kStripBytes) return 0;
+  if (!flat && Wp > 256) return 0;
+  const long long positions = flat ? static_cast<long long>(a->N) * a->H * a->W : static_cast<long long>(a->N) * Hp * Wp;
+  const long long num_tiles = (positions + kTileM - 1) / kTileM;
+  // few tiles (small spatial levels at small batch): one 256-position tile per SM leaves the machine under-filled and
+  // the im2col kernel (128-position tiles, 2 CTAs/SM) is faster there — measured crossover ~4 tiles per SM
+  if (!a->skip_x && num_tiles < 4 * 148 && !flat) return 0;
+  return 1;
+}
+
 int conv_strip_launch(const b200_conv_args* a, void* stream) {
+  if (!conv_strip_applicable(a)) return -100;
   const int Cin = a->C1 + a->C2;
   const int flat = (a->R == 1);
   const int Wp = a->W + 1, Hp = a->H + 1;
   const int strip_rows = 3 + (257 + Wp - 1) / Wp;
-  if (!flat && strip_rows * Wp * 128 > kStripBytes) return -100;
-  if (!flat && Wp > 256) return -100;
 
   CUtensorMap tmA, tmA2, tmB;
   int r;
@@ -414,9 +428,6 @@ int conv_strip_launch(const b200_conv_args* a, void* stream) {
   k.flat = flat;
   k.P_total = flat ? static_cast<int>(M) : a->N * Hp * Wp;
   k.num_tiles = (k.P_total + kTileM - 1) / kTileM;
-  // few tiles (small spatial levels at small batch): one 256-position tile per SM leaves the machine under-filled and
-  // the im2col kernel (128-position tiles, 2 CTAs/SM) is faster there — measured crossover ~4 tiles per SM
-  if (!a->skip_x && k.num_tiles < 4 * 148 && !flat) return -100;
   k.taps = a->R * a->S;
   k.chunks1 = a->C1 / 32;
   k.chunks = Cin / 32;

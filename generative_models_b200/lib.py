@@ -160,8 +160,11 @@ def load():
         raise B200Error("libb200ddpm.so ABI version mismatch")
     for name in EXPORTS:
         fn = getattr(lib, name)  # AttributeError if the symbol is missing
-        if name.startswith("b200_") and name not in ("b200_abi_version", "b200_init", "b200_last_error",
-                                                       "b200_launch_count"):
+        if name == "b200_conv_kernel_of":
+            fn.restype = C.c_int
+            fn.argtypes = [C.c_void_p]
+        elif name.startswith("b200_") and name not in ("b200_abi_version", "b200_init", "b200_last_error",
+                                                         "b200_launch_count"):
             fn.restype = C.c_int
             fn.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p]
     _lib = lib
@@ -171,7 +174,7 @@ def load():
 # every symbol include/b200ddpm.h declares (tests check the .so exports each of them)
 EXPORTS = [
     "b200_abi_version", "b200_init", "b200_last_error", "b200_launch_count",
-    "b200_conv_igemm", "b200_conv_wgrad",
+    "b200_conv_igemm", "b200_conv_kernel_of", "b200_conv_wgrad",
     "b200_gn_fwd", "b200_gn_bwd",
     "b200_q_sample", "b200_loss", "b200_sampler_step", "b200_step_advance", "b200_int_increment",
     "b200_conv_in_fwd", "b200_conv_in_bwd", "b200_conv_out_fwd", "b200_conv_out_bwd",

@@ -66,6 +66,9 @@ typedef struct {
   int skip_c1, skip_c2, skip_x_ld, skip_x2_ld;
 } b200_conv_args;
 int b200_conv_igemm(const b200_conv_args* a, void* ws, size_t ws_bytes, void* stream);
+/* which kernel b200_conv_igemm launches for these arguments: 1 = conv_strip_tf32_kernel (strip implicit GEMM, stride-1
+ * layers with enough tiles), 0 = conv_igemm_tf32_kernel (TMA-im2col).  Used by bench.py's per-kernel roofline. */
+int b200_conv_kernel_of(const b200_conv_args* a);
 
 /* weight gradient (nn.Conv2d backward-weight of the same layers):
  *   dw[co, kh, kw, ci] += sum_{n,p,q} dy[(n,p,q), co] * x[n, p*stride-pad+kh, q*stride-pad+kw, ci]
