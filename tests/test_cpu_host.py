@@ -130,3 +130,28 @@ def test_dg_keys_and_types_match_reference_contract():
     for k, t in want.items():
         assert k in M.DG and type(M.DG[k]) is t, k
     assert (M.DG.timesteps, M.DG.sampler, M.DG.mean_type, M.DG.hidden_size) == (250, "ddim", "v", 128)
+
+
+def test_launcher_registers_model_in_reference_registry():
+    """tools/run_gms_main.py: the unmodified registry lookup of gms/main.py:64,66 resolves to the B200 model, and the
+    synthetic loader stands in for common.load_mnist (needs the reference tree: build container only)."""
+    import importlib.util
+    import os
+
+    import pytest
+
+    if not os.path.isdir("/root/reference/gms"):
+        pytest.skip("reference tree absent (GPU box)")
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    spec = importlib.util.spec_from_file_location("run_gms_main", os.path.join(root, "tools", "run_gms_main.py"))
+    mod = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(mod)
+    common = mod.install("/root/reference", synthetic=True)
+    from generative_models_b200.model import DiffusionModelB200
+
+    models = common.discover_models()
+    assert models["diffusion_model"] is DiffusionModelB200
+    assert "vae" in models  # the stock registry is still there
+    train, test = common.load_mnist(8, binarize=False)
+    x, y = next(iter(train))
+    assert x.shape == (8, 1, 28, 28) and x.min() >= -1 and x.max() <= 1 and y.dtype == torch.int64
