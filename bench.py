@@ -197,7 +197,10 @@ def profile_ops(model, bound, kind):
         if name == "b200_conv_igemm":
             from generative_models_b200 import lib as _lib
             strip = _lib.load().b200_conv_kernel_of(o.ref) == 1
-            name = ("conv_strip_tf32_kernel" if strip else "conv_igemm_tf32_kernel") + ("[dgrad]" if o.args.mode == 1 else "[fprop]")
+            prec = "bf16" if o.args.op_dtype == 1 else "tf32"
+            name = (f"conv_strip_kernel<{prec}>" if strip else "conv_igemm_tf32_kernel") + ("[dgrad]" if o.args.mode == 1 else "[fprop]")
+        elif name == "b200_conv_wgrad":
+            name = f"conv_wgrad_kernel<{'bf16' if o.args.op_dtype == 1 else 'tf32'}>"
         d = out.setdefault(name, {"ms": 0.0, "launches": 0, "flops": 0.0})
         d["ms"] += evs[i].elapsed_time(evs[i + 1])
         d["launches"] += 1
@@ -243,13 +246,19 @@ def run_ours(args, rank, world, local_rank):
 
     B = args.batch
     torch.manual_seed(0)
-    G = default_G(device=dev, mean_type="eps", sampler="noisy", timesteps=args.sample_steps, bs=B, graph=1)
-    model = DiffusionModelB200(G)
-    # reference init at seed 0, then a small fill of the zero-initialised convs so every layer does real work
-    gen = torch.Generator().manual_seed(1)
-    for k, p in model.net.named_parameters():
-        if ".out_layers.3." in k:
-            p.data.copy_((torch.randn(p.shape, generator=gen) * 0.02).to(dev))
+    def make_model(precision):
+        torch.manual_seed(0)
+        G = default_G(device=dev, mean_type="eps", sampler="noisy", timesteps=args.sample_steps, bs=B, graph=1,
+                      precision=precision)
+        m = DiffusionModelB200(G)
+        # reference init at seed 0, then a small fill of the zero-initialised convs so every layer does real work
+        gen = torch.Generator().manual_seed(1)
+        for k, p in m.net.named_parameters():
+            if ".out_layers.3." in k:
+                p.data.copy_((torch.randn(p.shape, generator=gen) * 0.02).to(dev))
+        return m
+
+    model = make_model(args.precision)
 
     def barrier():
         if world > 1:
@@ -312,23 +321,61 @@ def run_ours(args, rank, world, local_rank):
 
     # ---- sampling leg: fused ancestral loop, sharded by batch, no communication
     n, T = args.sample_n, args.sample_steps
-    samp = None
-    if T > 0 and n > 0:
+
+    def time_sampling(mdl):
+        if T <= 0 or n <= 0:
+            return None
         labels = (torch.arange(n, device=dev) % 10)
         init = torch.randn(n, 1, 28, 28, device=dev)
-        bs = model._plan(n, "sample")  # warm-up: 3 steps of the real plan (eager, capture, replay)
+        bs = mdl._plan(n, "sample")  # warm-up: 3 steps of the real plan (eager, capture, replay)
         bs.begin_sampling(init, labels, None)
         for _ in range(min(3, T)):
             bs.run_graphed(bs.enqueue_sampler_step, "sampler_step")
         barrier()
         e0.record()
-        z = model._sample_loop(init, labels, None)[0]
+        z = mdl._sample_loop(init, labels, None)[0]
         e1.record()
         barrier()
         ms_s = max_over_ranks(e0.elapsed_time(e1))
-        samp = {"value": n * world / (ms_s / 1e3), "unit": "img/s", "n_per_gpu": n, "timesteps": T, "guided": False,
+        return {"value": n * world / (ms_s / 1e3), "unit": "img/s", "n_per_gpu": n, "timesteps": T, "guided": False,
                 "seconds": ms_s / 1e3, "tensor_tflops": n * world * T * FWD_FLOP_PER_IMG / (ms_s / 1e3) / 1e12,
                 "finite": bool(torch.isfinite(z).all().item())}
+
+    samp = time_sampling(model)
+
+    # ---- BASELINE.json configs[2]: the same step with bf16 tensor-core operands in the ResBlock convolutions
+    # (reported beside the headline, which stays the fp32/TF32 parity configuration)
+    bf16 = None
+    if args.precision == "tf32" and args.bf16_leg:
+        m2 = make_model("bf16")
+        for i in range(max(W, 6)):
+            x, y = devb[i % nb]
+            m2.train_step(x, y.clone())
+        barrier()
+        e0.record()
+        for i in range(K):
+            x, y = devb[i % nb]
+            m2.train_step(x, y.clone())
+        e1.record()
+        barrier()
+        ms_b = max_over_ranks(e0.elapsed_time(e1))
+        bound2 = m2._plan(B, "train")
+        prof2 = profile_ops(m2, bound2, "train") if rank == 0 else None
+        prof2 = profile_ops(m2, bound2, "train") if rank == 0 else None
+        sb = time_sampling(m2)
+        bf16 = {"config": "configs[2]: ResBlock 3x3 convs with bf16 operands / fp32 accumulate, everything else fp32/TF32; "
+                          f"batch {B}/GPU",
+                "train_img_s": B * world * K / (ms_b / 1e3), "ms_per_step": ms_b / K,
+                "tensor_tflops": B * K / (ms_b / 1e3) * TRAIN_FLOP_PER_IMG / 1e12,
+                "sampling_img_s": sb["value"] if sb else None, "sampling_seconds": sb["seconds"] if sb else None,
+                "activation_bytes": bound2.plan.activation_bytes()}
+        if prof2:
+            tot2 = sum(d["ms"] for d in prof2.values())
+            bf16["breakdown"] = {k: {"ms": round(d["ms"], 4), "launches": d["launches"], "share": round(d["ms"] / tot2, 4),
+                                     **({"tflops": round(d["flops"] / (d["ms"] / 1e3) / 1e12, 1)} if d["flops"] else {})}
+                                 for k, d in sorted(prof2.items(), key=lambda kv: -kv[1]["ms"])[:10]}
+        del m2, bound2
+        torch.cuda.empty_cache()
 
     if rank != 0:
         if world > 1:
@@ -339,9 +386,10 @@ def run_ours(args, rank, world, local_rank):
     prof = profile_ops(model, bound, "train")
     prof = profile_ops(model, bound, "train")  # second pass: warm
     total_ms = sum(d["ms"] for d in prof.values())
-    conv_ms = sum(d["ms"] for k, d in prof.items() if k.startswith("conv_strip_tf32_kernel"))
-    conv_fl = sum(d["flops"] for k, d in prof.items() if k.startswith("conv_strip_tf32_kernel"))
-    conv_n = sum(d["launches"] for k, d in prof.items() if k.startswith("conv_strip_tf32_kernel"))
+    strip_name = f"conv_strip_kernel<{args.precision}>"
+    conv_ms = sum(d["ms"] for k, d in prof.items() if k.startswith(strip_name))
+    conv_fl = sum(d["flops"] for k, d in prof.items() if k.startswith(strip_name))
+    conv_n = sum(d["launches"] for k, d in prof.items() if k.startswith(strip_name))
     peaks = {}
     try:
         peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
@@ -350,7 +398,7 @@ def run_ours(args, rank, world, local_rank):
     tf32_live = measure_tf32_peak()
     achieved = conv_fl / (conv_ms / 1e3) / 1e12
     roofline = {
-        "kernel": "conv_strip_tf32_kernel (all its fprop + dgrad launches of one train step; the top kernel of "
+        "kernel": strip_name + " (all its fprop + dgrad launches of one train step; the top kernel of "
                   "profiles/r01_launches_summary.md)", "bound": "tensor",
         "achieved": achieved, "peak": tf32_live, "unit": "TFLOP/s", "frac": achieved / tf32_live,
         # dram__bytes_read.sum + dram__bytes_write.sum of one captured launch (28x28 128->128 3x3 fprop, batch 512):
@@ -369,9 +417,10 @@ def run_ours(args, rank, world, local_rank):
     cpu_rate, cpu_s = cpu_reference_rate(args.cpu_batch, 2, 1, threads)
     line = {
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": K, "warmup": W,
-        "ms_per_step": ms / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "tf32",
+        "ms_per_step": ms / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": args.precision,
         "data": "synthetic",
-        "config": {"workload": f"DDPM UNet C=128 1x28x28, train step, batch {B}/GPU fp32/TF32 (configs[1]) + "
+        "config": {"workload": f"DDPM UNet C=128 1x28x28, train step, batch {B}/GPU "
+                               + ("fp32/TF32 (configs[1])" if args.precision == "tf32" else "bf16 ResBlock convs (configs[2])") + " + "
                                f"{T}-step ancestral sampling of {n} img/GPU",
                    "global_batch": B * world, "mean_type": "eps", "sampler": "noisy", "timesteps": T,
                    "parallelism": f"dp{world}", "cuda_graph": True,
@@ -387,6 +436,7 @@ def run_ours(args, rank, world, local_rank):
                          "sample": f"2 train steps (fwd+bwd+Adam) of {args.cpu_batch} images with oracle/ddpm_oracle.py "
                                    "on torch CPU fp32"},
         "sampling": samp,
+        "bf16": bf16,
         "breakdown": breakdown,
         "activation_bytes": bound.plan.activation_bytes(),
     }
@@ -406,6 +456,9 @@ def main():
     ap.add_argument("--sample-n", type=int, default=512, help="images per GPU in the sampling leg")
     ap.add_argument("--sample-steps", type=int, default=1000)
     ap.add_argument("--cpu-batch", type=int, default=16, help="bounded CPU sample: images per CPU train step")
+    ap.add_argument("--precision", default="tf32", choices=["tf32", "bf16"],
+                    help="tensor-core operand type of the ResBlock convs (tf32 = configs[1], the headline)")
+    ap.add_argument("--bf16-leg", type=int, default=1, help="also time the bf16 configuration (configs[2]) beside the headline")
     args = ap.parse_args()
     rank, world, local_rank = env_int("RANK", 0), env_int("WORLD_SIZE", 1), env_int("LOCAL_RANK", 0)
     if args.impl == "reference":

@@ -217,6 +217,7 @@ extern "C" int b200_conv_igemm(const b200_conv_args* a, void* ws, size_t ws_byte
   if (a->C2 > 0 && !a->x2) return fail_arg("conv_igemm: C2 > 0 needs x2");
   if (a->R != a->S || (a->R != 1 && a->R != 3)) return fail_arg("conv_igemm: only 1x1 and 3x3 filters");
   if (a->mode != 0 && a->mode != 1) return fail_arg("conv_igemm: mode must be 0 (fprop) or 1 (dgrad)");
+  if (a->op_dtype != 0 && a->op_dtype != 1) return fail_arg("conv_igemm: op_dtype must be 0 (fp32/TF32) or 1 (bf16)");
   if (a->out_ld % 4 || (a->residual && a->res_ld % 4) || (a->emb && a->emb_ld % 4))
     return fail_arg("conv_igemm: leading dimensions must be multiples of 4 floats");
   const int Cin = a->C1 + a->C2;
@@ -245,6 +246,7 @@ extern "C" int b200_conv_igemm(const b200_conv_args* a, void* ws, size_t ws_byte
     if (rs != -100) return rs;
   }
   if (a->skip_x) return fail_arg("conv_igemm: the fused skip segment needs a stride-1 3x3/pad-1 or 1x1/pad-0 layer");
+  if (a->op_dtype != 0) return fail_arg("conv_igemm: bf16 operands need a stride-1 3x3/pad-1 or 1x1/pad-0 layer (strip kernel)");
   CUtensorMap tmA, tmA2, tmB;
   int r = get_tmap_im2col(a->x, a->N, a->H, a->W, a->C1, a->x_ld ? a->x_ld : a->C1, lower, upper, a->stride, 32, 128, 4, 0, &tmA);
   if (r) return r;

@@ -66,8 +66,13 @@ __device__ __forceinline__ int floor_div(int a, int b) {
   return q;
 }
 
+// BF16 = false: fp32 operands in smem, kind::tf32, 32 channels per 128 B row.
+// BF16 = true:  bf16 operands, kind::f16, 64 channels per 128 B row — the byte geometry of every tile, strip, box and
+// descriptor step is identical (a K-step is 32 B either way), only the channel count per chunk doubles, so one
+// instruction does twice the FLOPs for the same shared-memory operand bytes.
+template <bool BF16>
 __global__ void __launch_bounds__(320, 1)
-conv_strip_tf32_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmA2,
+conv_strip_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmA2,
                        const __grid_constant__ CUtensorMap tmB, const __grid_constant__ CUtensorMap tmS,
                        const __grid_constant__ CUtensorMap tmS2, const __grid_constant__ CUtensorMap tmW2,
                        const StripK a) {
@@ -120,6 +125,7 @@ conv_strip_tf32_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_con
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
 
+  constexpr int CK = BF16 ? 64 : 32;  // channels per K-chunk (one 128 B smem row)
   const int strip_bytes = a.flat ? kTileM * 128 : a.strip_rows * a.Wp * 128;
   const int CH = a.chunks + a.skip_chunks;  // K-chunks (32 channels each) per tile: main conv, then the skip segment
 
@@ -147,11 +153,11 @@ conv_strip_tf32_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_con
         int c0;
         if (ch < a.chunks) {
           m = (ch < a.chunks1) ? &tmA : &tmA2;
-          c0 = ((ch < a.chunks1) ? ch : ch - a.chunks1) * 32;
+          c0 = ((ch < a.chunks1) ? ch : ch - a.chunks1) * CK;
         } else {
           const int sk = ch - a.chunks;
           m = (sk < a.skip_chunks1) ? &tmS : &tmS2;
-          c0 = ((sk < a.skip_chunks1) ? sk : sk - a.skip_chunks1) * 32;
+          c0 = ((sk < a.skip_chunks1) ? sk : sk - a.skip_chunks1) * CK;
         }
         const int p0 = t * kTileM;
         if (a.flat) {
@@ -185,18 +191,19 @@ conv_strip_tf32_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_con
           if (is_skip) {
             const int sk = ch - a.chunks;
             if (a.mode == 0) {
-              tma_load_2d(sB, &tmW2, &b_full[bs], sk * 32, 0);
-            } else {
+              tma_load_2d(sB, &tmW2, &b_full[bs], sk * CK, 0);
+            } else {  // MN-major weight tile: 128 / CK boxes of [CK co rows][CK ci = 128 B]
 #pragma unroll
-              for (int jj = 0; jj < 4; ++jj) tma_load_2d(sB + jj * 4096, &tmW2, &b_full[bs], jj * 32, sk * 32);
+              for (int jj = 0; jj < 128 / CK; ++jj)
+                tma_load_2d(sB + jj * (CK * 128), &tmW2, &b_full[bs], jj * CK, sk * CK);
             }
           } else if (a.mode == 0) {
-            tma_load_2d(sB, &tmB, &b_full[bs], tap * a.w_rowlen_tap + ch * 32, 0);
+            tma_load_2d(sB, &tmB, &b_full[bs], tap * a.w_rowlen_tap + ch * CK, 0);
           } else {
             const int wtap = a.taps - 1 - tap;  // dgrad walks the filter flipped
 #pragma unroll
-            for (int jj = 0; jj < 4; ++jj)
-              tma_load_2d(sB + jj * 4096, &tmB, &b_full[bs], wtap * a.w_rowlen_tap + a.n_off + jj * 32, ch * 32);
+            for (int jj = 0; jj < 128 / CK; ++jj)
+              tma_load_2d(sB + jj * (CK * 128), &tmB, &b_full[bs], wtap * a.w_rowlen_tap + a.n_off + jj * CK, ch * CK);
           }
         }
       }
@@ -208,7 +215,7 @@ conv_strip_tf32_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_con
       // A = weight tile (K-major for fprop, MN-major for dgrad), B = the shifted strip view (K-major, N = 256 rows).
       // One N=256 instruction reads 4 KB of A + 8 KB of B for twice the FLOPs of a 128x128x8 one: SS-mode TF32 is
       // bound by smem operand bandwidth (measured: 480 -> 680 TFLOP/s issue rate), hence this orientation.
-      const uint32_t idesc = make_idesc(2u, 128u, 256u, a.mode == 0 ? 0u : 1u, 0u);
+      const uint32_t idesc = make_idesc(BF16 ? 1u : 2u, 128u, 256u, a.mode == 0 ? 0u : 1u, 0u);
       uint32_t sc = 0, bc = 0, tc = 0;
       for (int t = blockIdx.x; t < a.num_tiles; t += gridDim.x, ++tc) {
         const uint32_t as = tc & 1;
@@ -240,10 +247,14 @@ conv_strip_tf32_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_con
             const uint32_t x_base = strip_addr + static_cast<uint32_t>(row0 + shift) * 128u;
 #pragma unroll
             for (int k = 0; k < 4; ++k) {
+              // MN-major A (dgrad): TF32 = 32 B-atom layout, 4 boxes of 32 ci; bf16 = plain SWIZZLE_128B, 2 boxes of
+              // 64 ci (LBO = box pitch, SBO = pitch of the 8-row K groups)
               const uint64_t adesc = (a.mode == 0) ? make_smem_desc_sw128(w_base + k * 32, 16, 1024)
+                                     : BF16        ? make_smem_desc_sw128(w_base + k * 2048, 8192, 1024, 2)
                                                    : make_smem_desc_sw128(w_base + k * 1024, 4096, 512, 1);
               const uint64_t bdesc = make_smem_desc_sw128(x_base + k * 32, 16, 1024);
-              mma_tf32_ss(d_tmem, adesc, bdesc, idesc, (ch | tap | k) != 0 ? 1u : 0u);
+              if (BF16) mma_f16_ss(d_tmem, adesc, bdesc, idesc, (ch | tap | k) != 0 ? 1u : 0u);
+              else mma_tf32_ss(d_tmem, adesc, bdesc, idesc, (ch | tap | k) != 0 ? 1u : 0u);
             }
             tc_commit(&b_empty[bs]);
           }
@@ -356,8 +367,9 @@ int conv_strip_applicable(const b200_conv_args* a) {
   const long long positions = flat ? static_cast<long long>(a->N) * a->H * a->W : static_cast<long long>(a->N) * Hp * Wp;
   const long long num_tiles = (positions + kTileM - 1) / kTileM;
   // few tiles (small spatial levels at small batch): one 256-position tile per SM leaves the machine under-filled and
-  // the im2col kernel (128-position tiles, 2 CTAs/SM) is faster there — measured crossover ~4 tiles per SM
-  if (!a->skip_x && num_tiles < 4 * 148 && !flat) return 0;
+  // the im2col kernel (128-position tiles, 2 CTAs/SM) is faster there — measured crossover ~4 tiles per SM.
+  // bf16 operands exist only in this kernel.
+  if (!a->skip_x && num_tiles < 4 * 148 && !flat && a->op_dtype == 0) return 0;
   return 1;
 }
 
@@ -367,31 +379,35 @@ int conv_strip_launch(const b200_conv_args* a, void* stream) {
   const int flat = (a->R == 1);
   const int Wp = a->W + 1, Hp = a->H + 1;
   const int strip_rows = 3 + (257 + Wp - 1) / Wp;
+  const bool bf = a->op_dtype == 1;
+  const int eb = bf ? 2 : 4;        // operand element bytes
+  const uint32_t CK = bf ? 64 : 32;  // channels per 128 B row
+  if (a->C1 % CK || a->C2 % CK) return fail_arg("conv_igemm: C1/C2 must be multiples of the K-chunk (32 fp32 / 64 bf16)");
 
   CUtensorMap tmA, tmA2, tmB;
   int r;
   const long long M = static_cast<long long>(a->N) * a->H * a->W;
   if (flat) {
-    r = get_tmap_2d(a->x, M, a->C1, a->x_ld ? a->x_ld : a->C1, 32, 256, 4, 0, &tmA);
+    r = get_tmap_2d(a->x, M, a->C1, a->x_ld ? a->x_ld : a->C1, CK, 256, eb, 0, &tmA);
     if (r) return r;
     if (a->C2 > 0) {
-      r = get_tmap_2d(a->x2, M, a->C2, a->x2_ld ? a->x2_ld : a->C2, 32, 256, 4, 0, &tmA2);
+      r = get_tmap_2d(a->x2, M, a->C2, a->x2_ld ? a->x2_ld : a->C2, CK, 256, eb, 0, &tmA2);
       if (r) return r;
     } else {
       tmA2 = tmA;
     }
   } else {
-    r = get_tmap_rows4d(a->x, a->N, a->H, a->W, a->C1, a->x_ld ? a->x_ld : a->C1, 32, Wp, &tmA);
+    r = get_tmap_rows4d(a->x, a->N, a->H, a->W, a->C1, a->x_ld ? a->x_ld : a->C1, CK, Wp, &tmA, eb);
     if (r) return r;
     if (a->C2 > 0) {
-      r = get_tmap_rows4d(a->x2, a->N, a->H, a->W, a->C2, a->x2_ld ? a->x2_ld : a->C2, 32, Wp, &tmA2);
+      r = get_tmap_rows4d(a->x2, a->N, a->H, a->W, a->C2, a->x2_ld ? a->x2_ld : a->C2, CK, Wp, &tmA2, eb);
       if (r) return r;
     } else {
       tmA2 = tmA;
     }
   }
   const uint64_t wcols = static_cast<uint64_t>(a->R) * a->S * a->w_cin;
-  r = get_tmap_2d(a->w, a->w_cout, wcols, wcols, 32, a->mode == 0 ? 128 : 32, 4, a->mode == 0 ? 0 : 1, &tmB);
+  r = get_tmap_2d(a->w, a->w_cout, wcols, wcols, CK, a->mode == 0 ? 128 : CK, eb, (a->mode == 1 && !bf) ? 1 : 0, &tmB);
   if (r) return r;
   // fused skip segment: a 1x1 convolution over (skip_x | skip_x2) with weights skip_w [128][skip_c1 + skip_c2],
   // accumulated into the same TMEM tile as extra K-chunks (identity weights = a residual add on the tensor cores,
@@ -399,22 +415,22 @@ int conv_strip_launch(const b200_conv_args* a, void* stream) {
   CUtensorMap tmS = tmA, tmS2 = tmA, tmW2 = tmB;
   const int skip_c = a->skip_x ? a->skip_c1 + a->skip_c2 : 0;
   if (skip_c) {
-    if (!a->skip_w || a->skip_c1 <= 0 || a->skip_c1 % 32 || a->skip_c2 % 32 || (a->skip_c2 && !a->skip_x2))
+    if (!a->skip_w || a->skip_c1 <= 0 || a->skip_c1 % CK || a->skip_c2 % CK || (a->skip_c2 && !a->skip_x2))
       return fail_arg("conv_igemm: bad skip segment");
     if (a->mode == 1 && skip_c != 128) return fail_arg("conv_igemm dgrad: the skip segment must have 128 channels");
     const int l1 = a->skip_x_ld ? a->skip_x_ld : a->skip_c1, l2 = a->skip_x2_ld ? a->skip_x2_ld : a->skip_c2;
     if (flat) {
-      r = get_tmap_2d(a->skip_x, M, a->skip_c1, l1, 32, 256, 4, 0, &tmS);
+      r = get_tmap_2d(a->skip_x, M, a->skip_c1, l1, CK, 256, eb, 0, &tmS);
       if (r) return r;
-      if (a->skip_c2) r = get_tmap_2d(a->skip_x2, M, a->skip_c2, l2, 32, 256, 4, 0, &tmS2);
+      if (a->skip_c2) r = get_tmap_2d(a->skip_x2, M, a->skip_c2, l2, CK, 256, eb, 0, &tmS2);
     } else {
-      r = get_tmap_rows4d(a->skip_x, a->N, a->H, a->W, a->skip_c1, l1, 32, Wp, &tmS);
+      r = get_tmap_rows4d(a->skip_x, a->N, a->H, a->W, a->skip_c1, l1, CK, Wp, &tmS, eb);
       if (r) return r;
-      if (a->skip_c2) r = get_tmap_rows4d(a->skip_x2, a->N, a->H, a->W, a->skip_c2, l2, 32, Wp, &tmS2);
+      if (a->skip_c2) r = get_tmap_rows4d(a->skip_x2, a->N, a->H, a->W, a->skip_c2, l2, CK, Wp, &tmS2, eb);
     }
     if (r) return r;
     if (!a->skip_c2) tmS2 = tmS;
-    r = get_tmap_2d(a->skip_w, 128, skip_c, skip_c, 32, a->mode == 0 ? 128 : 32, 4, a->mode == 0 ? 0 : 1, &tmW2);
+    r = get_tmap_2d(a->skip_w, 128, skip_c, skip_c, CK, a->mode == 0 ? 128 : CK, eb, (a->mode == 1 && !bf) ? 1 : 0, &tmW2);
     if (r) return r;
   }
 
@@ -429,10 +445,10 @@ int conv_strip_launch(const b200_conv_args* a, void* stream) {
   k.P_total = flat ? static_cast<int>(M) : a->N * Hp * Wp;
   k.num_tiles = (k.P_total + kTileM - 1) / kTileM;
   k.taps = a->R * a->S;
-  k.chunks1 = a->C1 / 32;
-  k.chunks = Cin / 32;
-  k.skip_chunks1 = skip_c ? a->skip_c1 / 32 : 0;
-  k.skip_chunks = skip_c / 32;
+  k.chunks1 = a->C1 / CK;
+  k.chunks = Cin / CK;
+  k.skip_chunks1 = skip_c ? a->skip_c1 / CK : 0;
+  k.skip_chunks = skip_c / CK;
   k.mode = a->mode;
   k.w_rowlen_tap = a->w_cin;
   k.n_off = a->n_off;
@@ -449,14 +465,20 @@ int conv_strip_launch(const b200_conv_args* a, void* stream) {
   static bool attr_set = false;
   static int num_sms = 148;
   if (!attr_set) {
-    cudaError_t e = cudaFuncSetAttribute(conv_strip_tf32_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kStripSmem);
+    cudaError_t e = cudaFuncSetAttribute(conv_strip_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kStripSmem);
     if (e != cudaSuccess) return check_cuda(e, "cudaFuncSetAttribute(conv_strip)");
+    e = cudaFuncSetAttribute(conv_strip_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kStripSmem);
+    if (e != cudaSuccess) return check_cuda(e, "cudaFuncSetAttribute(conv_strip bf16)");
     int dev = 0;
     cudaGetDevice(&dev);
     cudaDeviceGetAttribute(&num_sms, cudaDevAttrMultiProcessorCount, dev);
     attr_set = true;
   }
   const int grid = k.num_tiles < num_sms ? k.num_tiles : num_sms;
-  conv_strip_tf32_kernel<<<grid, 320, kStripSmem, static_cast<cudaStream_t>(stream)>>>(tmA, tmA2, tmB, tmS, tmS2, tmW2, k);
-  return after_launch("conv_strip_tf32_kernel");
+  if (bf) {
+    conv_strip_kernel<true><<<grid, 320, kStripSmem, static_cast<cudaStream_t>(stream)>>>(tmA, tmA2, tmB, tmS, tmS2, tmW2, k);
+    return after_launch("conv_strip_kernel<bf16>");
+  }
+  conv_strip_kernel<false><<<grid, 320, kStripSmem, static_cast<cudaStream_t>(stream)>>>(tmA, tmA2, tmB, tmS, tmS2, tmW2, k);
+  return after_launch("conv_strip_kernel<tf32>");
 }

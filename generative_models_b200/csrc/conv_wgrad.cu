@@ -20,7 +20,8 @@ namespace b200 {
 
 constexpr int kWgStages = 3;
 constexpr int kWgTileBytes = 16384;  // 4 boxes of (32 pixels x 128 B)
-constexpr int kWgPix = 32;           // pixels (reduction elements) per pipeline stage
+constexpr int kWgPix = 32;           // pixels (reduction elements) per pipeline stage, fp32/TF32 operands
+constexpr int kWgPixBf = 64;         // ... bf16 operands: same 16 KB tiles, 2 boxes of (64 pixels x 128 B = 64 channels)
 constexpr int wg_smem_bytes(int taps) { return kWgStages * (1 + taps) * kWgTileBytes + 1024 + 256; }
 
 struct WgradK {
@@ -37,8 +38,9 @@ __device__ __forceinline__ void red_add_v4(float* p, float a, float b, float c, 
   asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(p), "f"(a), "f"(b), "f"(c), "f"(d) : "memory");
 }
 
+template <bool BF16>
 __global__ void __launch_bounds__(192)
-conv_wgrad_tf32_kernel(const __grid_constant__ CUtensorMap tmDY, const __grid_constant__ CUtensorMap tmX,
+conv_wgrad_kernel(const __grid_constant__ CUtensorMap tmDY, const __grid_constant__ CUtensorMap tmX,
                        const __grid_constant__ CUtensorMap tmX2, const WgradK a) {
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
@@ -50,6 +52,10 @@ conv_wgrad_tf32_kernel(const __grid_constant__ CUtensorMap tmDY, const __grid_co
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
+  constexpr int PIX = BF16 ? kWgPixBf : kWgPix;  // pixels per stage
+  constexpr int CB = BF16 ? 64 : 32;             // channels per TMA box (128 B)
+  constexpr int NB = 128 / CB;                   // boxes per 128-channel tile
+  constexpr int BOXB = kWgTileBytes / NB;
 
   const int step_begin = blockIdx.x * a.steps_per_slice;
   const int step_end = min(step_begin + a.steps_per_slice, a.steps_total);
@@ -91,26 +97,26 @@ conv_wgrad_tf32_kernel(const __grid_constant__ CUtensorMap tmDY, const __grid_co
         const uint32_t ph = (it / kWgStages) & 1;
         mbar_wait(&empty[s], ph ^ 1);
         mbar_expect_tx(&full[s], stage_bytes);
-        const int pix0 = (step_begin + it) * kWgPix;
+        const int pix0 = (step_begin + it) * PIX;
         const int n = pix0 / a.HoWo;
         const int rem = pix0 - n * a.HoWo;
         const int p = rem / a.Wo;
         const int q = rem - p * a.Wo;
         uint8_t* sA = smem + s * stage_bytes;
 #pragma unroll
-        for (int j = 0; j < 4; ++j) tma_load_2d(sA + j * 4096, &tmDY, &full[s], j * 32, pix0);
+        for (int j = 0; j < NB; ++j) tma_load_2d(sA + j * BOXB, &tmDY, &full[s], j * CB, pix0);
         for (int kw = 0; kw < a.taps; ++kw) {
           uint8_t* sB = sA + (1 + kw) * kWgTileBytes;
 #pragma unroll
-          for (int j = 0; j < 4; ++j)
-            tma_load_im2col_4d(sB + j * 4096, xm, &full[s], c_src + j * 32, q * a.stride - a.pad, p * a.stride - a.pad, n,
+          for (int j = 0; j < NB; ++j)
+            tma_load_im2col_4d(sB + j * BOXB, xm, &full[s], c_src + j * CB, q * a.stride - a.pad, p * a.stride - a.pad, n,
                                (uint16_t)kw, (uint16_t)kh);
         }
       }
     }
   } else if (warp == 1) {
     if (lane == 0) {
-      const uint32_t idesc = make_idesc(2u, 128u, 128u, 1u, 1u);
+      const uint32_t idesc = make_idesc(BF16 ? 1u : 2u, 128u, 128u, 1u, 1u);
       for (int it = 0; it < num_it; ++it) {
         const int s = it % kWgStages;
         const uint32_t ph = (it / kWgStages) & 1;
@@ -121,9 +127,17 @@ conv_wgrad_tf32_kernel(const __grid_constant__ CUtensorMap tmDY, const __grid_co
           const uint32_t b_base = a_base + (1 + kw) * kWgTileBytes;
 #pragma unroll
           for (int k = 0; k < 4; ++k) {
-            const uint64_t adesc = make_smem_desc_sw128(a_base + k * 1024, 4096, 512, 1);
-            const uint64_t bdesc = make_smem_desc_sw128(b_base + k * 1024, 4096, 512, 1);
-            mma_tf32_ss(tmem_base + kw * 128, adesc, bdesc, idesc, (it | k) != 0 ? 1u : 0u);
+            // MN-major operands: TF32 = 32 B-atom layout (4 boxes of 32 channels, K-step = 8 pixel rows);
+            // bf16 = SWIZZLE_128B (2 boxes of 64 channels, K-step = 16 pixel rows = two 8-row groups 1024 B apart)
+            if (BF16) {
+              const uint64_t adesc = make_smem_desc_sw128(a_base + k * 2048, 8192, 1024, 2);
+              const uint64_t bdesc = make_smem_desc_sw128(b_base + k * 2048, 8192, 1024, 2);
+              mma_f16_ss(tmem_base + kw * 128, adesc, bdesc, idesc, (it | k) != 0 ? 1u : 0u);
+            } else {
+              const uint64_t adesc = make_smem_desc_sw128(a_base + k * 1024, 4096, 512, 1);
+              const uint64_t bdesc = make_smem_desc_sw128(b_base + k * 1024, 4096, 512, 1);
+              mma_tf32_ss(tmem_base + kw * 128, adesc, bdesc, idesc, (it | k) != 0 ? 1u : 0u);
+            }
           }
         }
         tc_commit(&empty[s]);
@@ -175,7 +189,9 @@ extern "C" int b200_conv_wgrad(const b200_wgrad_args* a, void* ws, size_t ws_byt
   if (ho != a->Ho || wo != a->Wo) return fail_arg("conv_wgrad: Ho/Wo do not match the geometry");
   static int num_sms = 0;
   if (!num_sms) {
-    cudaError_t e = cudaFuncSetAttribute(conv_wgrad_tf32_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, wg_smem_bytes(3));
+    cudaError_t e = cudaFuncSetAttribute(conv_wgrad_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, wg_smem_bytes(3));
+    if (e == cudaSuccess)
+      e = cudaFuncSetAttribute(conv_wgrad_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, wg_smem_bytes(3));
     if (e != cudaSuccess) return check_cuda(e, "cudaFuncSetAttribute(conv_wgrad)");
     int dev = 0;
     cudaGetDevice(&dev);
@@ -185,13 +201,17 @@ extern "C" int b200_conv_wgrad(const b200_wgrad_args* a, void* ws, size_t ws_byt
   const int M_total = a->N * a->Ho * a->Wo;
   const int lower = -a->pad, upper = a->pad - (a->R - 1);
 
+  if (a->op_dtype != 0 && a->op_dtype != 1) return fail_arg("conv_wgrad: op_dtype must be 0 (fp32/TF32) or 1 (bf16)");
+  const bool bf = a->op_dtype == 1;
+  const int eb = bf ? 2 : 4, sw32 = bf ? 0 : 1;
+  const uint32_t cb = bf ? 64 : 32, pixs = bf ? kWgPixBf : kWgPix;
   CUtensorMap tmDY, tmX, tmX2;
-  int r = get_tmap_2d(a->dy, M_total, 128, a->dy_ld ? a->dy_ld : 128, 32, kWgPix, 4, 1, &tmDY);
+  int r = get_tmap_2d(a->dy, M_total, 128, a->dy_ld ? a->dy_ld : 128, cb, pixs, eb, sw32, &tmDY);
   if (r) return r;
-  r = get_tmap_im2col(a->x, a->N, a->H, a->W, a->C1, a->x_ld ? a->x_ld : a->C1, lower, upper, a->stride, 32, kWgPix, 4, 1, &tmX);
+  r = get_tmap_im2col(a->x, a->N, a->H, a->W, a->C1, a->x_ld ? a->x_ld : a->C1, lower, upper, a->stride, cb, pixs, eb, sw32, &tmX);
   if (r) return r;
   if (a->C2 > 0) {
-    r = get_tmap_im2col(a->x2, a->N, a->H, a->W, a->C2, a->x2_ld ? a->x2_ld : a->C2, lower, upper, a->stride, 32, kWgPix, 4, 1, &tmX2);
+    r = get_tmap_im2col(a->x2, a->N, a->H, a->W, a->C2, a->x2_ld ? a->x2_ld : a->C2, lower, upper, a->stride, cb, pixs, eb, sw32, &tmX2);
     if (r) return r;
   } else {
     tmX2 = tmX;
@@ -209,7 +229,7 @@ extern "C" int b200_conv_wgrad(const b200_wgrad_args* a, void* ws, size_t ws_byt
   k.taps = a->S;
   k.C1 = a->C1;
   k.Cin = Cin;
-  k.steps_total = (M_total + kWgPix - 1) / kWgPix;
+  k.steps_total = (M_total + static_cast<int>(pixs) - 1) / static_cast<int>(pixs);
   int slices = a->k_slices;
   if (slices <= 0) {
     // one CTA per SM for 3-tap CTAs (they own all 512 TMEM columns and 192 KB of smem), two for 1x1 filters
@@ -222,6 +242,10 @@ extern "C" int b200_conv_wgrad(const b200_wgrad_args* a, void* ws, size_t ws_byt
   slices = (k.steps_total + k.steps_per_slice - 1) / k.steps_per_slice;
 
   dim3 grid(slices, tiles);
-  conv_wgrad_tf32_kernel<<<grid, 192, wg_smem_bytes(k.taps), static_cast<cudaStream_t>(stream)>>>(tmDY, tmX, tmX2, k);
-  return after_launch("conv_wgrad_tf32_kernel");
+  if (bf) {
+    conv_wgrad_kernel<true><<<grid, 192, wg_smem_bytes(k.taps), static_cast<cudaStream_t>(stream)>>>(tmDY, tmX, tmX2, k);
+    return after_launch("conv_wgrad_kernel<bf16>");
+  }
+  conv_wgrad_kernel<false><<<grid, 192, wg_smem_bytes(k.taps), static_cast<cudaStream_t>(stream)>>>(tmDY, tmX, tmX2, k);
+  return after_launch("conv_wgrad_kernel<tf32>");
 }

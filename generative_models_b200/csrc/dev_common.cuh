@@ -18,4 +18,12 @@ __device__ __forceinline__ float4 round_tf32(float4 v) {
   return make_float4(round_tf32(v.x), round_tf32(v.y), round_tf32(v.z), round_tf32(v.w));
 }
 
+// 4 floats -> 4 bf16 (round to nearest even) packed in 8 bytes, element 0 in the low half of .x
+__device__ __forceinline__ uint2 pack_bf16x4(float4 v) {
+  uint2 r;
+  asm("cvt.rn.bf16x2.f32 %0, %1, %2;" : "=r"(r.x) : "f"(v.y), "f"(v.x));
+  asm("cvt.rn.bf16x2.f32 %0, %1, %2;" : "=r"(r.y) : "f"(v.w), "f"(v.z));
+  return r;
+}
+
 }  // namespace b200

@@ -115,7 +115,9 @@ gn_fwd_fused_kernel(GnSrc s, float* __restrict__ stats, const float* __restrict_
   const float4 ga = *reinterpret_cast<const float4*>(gamma + c);
   const float4 be = *reinterpret_cast<const float4*>(beta + c);
   const float4 sc = make_float4(rstd * ga.x, rstd * ga.y, rstd * ga.z, rstd * ga.w);
+  // tf32: 0 = plain fp32, 1 = fp32 rounded to TF32, 2 = bf16 (y then holds 2-byte elements)
   float* dst = y + static_cast<size_t>(n) * s.HW * s.C + c;
+  uint16_t* dstb = reinterpret_cast<uint16_t*>(y) + static_cast<size_t>(n) * s.HW * s.C + c;
   for (int idx = tid; idx < total; idx += kGnThreads) {
     const float4 v = gn_smem[idx];
     float4 o;
@@ -126,8 +128,12 @@ gn_fwd_fused_kernel(GnSrc s, float* __restrict__ stats, const float* __restrict_
     if (silu) {
       o.x = silu_f(o.x); o.y = silu_f(o.y); o.z = silu_f(o.z); o.w = silu_f(o.w);
     }
-    if (tf32) o = round_tf32(o);
-    *reinterpret_cast<float4*>(dst + static_cast<size_t>(idx / L) * s.C) = o;
+    if (tf32 == 2) {
+      *reinterpret_cast<uint2*>(dstb + static_cast<size_t>(idx / L) * s.C) = pack_bf16x4(o);
+    } else {
+      if (tf32) o = round_tf32(o);
+      *reinterpret_cast<float4*>(dst + static_cast<size_t>(idx / L) * s.C) = o;
+    }
   }
 }
 
@@ -143,7 +149,8 @@ __global__ void __launch_bounds__(kGnThreads)
 gn_bwd_fused_kernel(GnSrc s, const float* __restrict__ stats, const float* __restrict__ gamma,
                     const float* __restrict__ beta, const float* __restrict__ dy, float* __restrict__ dx,
                     const float* __restrict__ add1, int add1_ld, const float* __restrict__ add2, int add2_ld, int add_c,
-                    float* __restrict__ dgamma, float* __restrict__ dbeta, int silu, int round_dx) {
+                    float* __restrict__ dgamma, float* __restrict__ dbeta, int silu, int round_dx,
+                    uint16_t* __restrict__ dxb, int dxb_c) {
   extern __shared__ float4 gn_smem[];
   __shared__ float red[16];
   __shared__ float chan[2 * CS];
@@ -236,6 +243,7 @@ gn_bwd_fused_kernel(GnSrc s, const float* __restrict__ stats, const float* __res
   const float* a1 = (has_add && add1) ? add1 + row0 * add1_ld + c : nullptr;
   const float* a2 = (has_add && add2) ? add2 + row0 * add2_ld + c : nullptr;
   float* dst = dx + row0 * s.C + c;
+  uint16_t* dstb = (dxb && c < dxb_c) ? dxb + row0 * dxb_c + c : nullptr;  // bf16 copy of the first dxb_c channels
   for (int idx = tid; idx < total; idx += kGnThreads) {
     const size_t pix = idx / L;
     const float4 xh = xs[idx];
@@ -253,6 +261,7 @@ gn_bwd_fused_kernel(GnSrc s, const float* __restrict__ stats, const float* __res
       const float4 a = __ldg(reinterpret_cast<const float4*>(a2 + pix * add2_ld));
       o.x += a.x; o.y += a.y; o.z += a.z; o.w += a.w;
     }
+    if (dstb) *reinterpret_cast<uint2*>(dstb + pix * dxb_c) = pack_bf16x4(o);
     if (round_dx) o = round_tf32(o);
     *reinterpret_cast<float4*>(dst + pix * s.C) = o;
   }
@@ -321,8 +330,12 @@ gn_apply_kernel(GnSrc s, const float* __restrict__ stats, const float* __restric
     if (silu) {
       o.x = silu_f(o.x); o.y = silu_f(o.y); o.z = silu_f(o.z); o.w = silu_f(o.w);
     }
-    if (tf32) o = round_tf32(o);
-    *reinterpret_cast<float4*>(y + pix * s.C + c) = o;
+    if (tf32 == 2) {
+      *reinterpret_cast<uint2*>(reinterpret_cast<uint16_t*>(y) + pix * s.C + c) = pack_bf16x4(o);
+    } else {
+      if (tf32) o = round_tf32(o);
+      *reinterpret_cast<float4*>(y + pix * s.C + c) = o;
+    }
   }
 }
 
@@ -395,7 +408,8 @@ __global__ void __launch_bounds__(256)
 gn_bwd_apply_kernel(GnSrc s, const float* __restrict__ stats, const float* __restrict__ gamma,
                     const float* __restrict__ beta, const float* __restrict__ dy, const float* __restrict__ red,
                     float* __restrict__ dx, const float* __restrict__ add1, int add1_ld,
-                    const float* __restrict__ add2, int add2_ld, int add_c, int silu, int round_dx) {
+                    const float* __restrict__ add2, int add2_ld, int add_c, int silu, int round_dx,
+                    uint16_t* __restrict__ dxb, int dxb_c) {
   const int lanes = s.C >> 2;
   const size_t total = static_cast<size_t>(s.N) * s.HW * lanes;
   const int cpg = s.C >> 5;
@@ -436,6 +450,7 @@ gn_bwd_apply_kernel(GnSrc s, const float* __restrict__ stats, const float* __res
       }
     }
     float4 ov = make_float4(o[0], o[1], o[2], o[3]);
+    if (dxb && c < dxb_c) *reinterpret_cast<uint2*>(dxb + pix * dxb_c + c) = pack_bf16x4(ov);
     if (round_dx) ov = round_tf32(ov);
     *reinterpret_cast<float4*>(dx + pix * s.C + c) = ov;
   }
@@ -498,6 +513,8 @@ static int gn_init() {
   if (e == cudaSuccess) e = gn_optin(gn_bwd_fused_kernel<16, 256>, max_dyn);
   if (e == cudaSuccess) e = gn_optin(gn_bwd_fused_kernel<32, 512>, max_dyn);
   if (e == cudaSuccess) e = gn_optin(gn_bwd_fused_kernel<16, 512>, max_dyn);
+  if (e == cudaSuccess) e = gn_optin(gn_fwd_fused_kernel<8, 256>, max_dyn);
+  if (e == cudaSuccess) e = gn_optin(gn_bwd_fused_kernel<8, 256>, max_dyn);
   if (e != cudaSuccess) return check_cuda(e, "cudaFuncSetAttribute(gn fused)");
   const char* env = getenv("B200_GN_STREAM");
   g_gn_stream = env ? atoi(env) : 0;
@@ -516,6 +533,7 @@ static int gn_slice(const GnSrc& s, int bufs) {
   if (b16 > static_cast<size_t>(g_gn_max_dyn)) return 0;
   if (g_gn_cs == 32 && 2 * b16 <= static_cast<size_t>(g_gn_max_dyn)) return 32;
   if (g_gn_cs == 16) return 16;
+  if (g_gn_cs == 8) return 8;
   return (2 * b16 <= 50 * 1024) ? 32 : 16;
 }
 static int gn_threads(size_t smem) {
@@ -528,6 +546,8 @@ extern "C" int b200_gn_fwd(const b200_gn_args* a, void* ws, size_t ws_bytes, voi
   GnSrc s;
   if (int r = gn_src(a, &s)) return r;
   if (!a->y) return fail_arg("gn_fwd: null y");
+  if (a->y_dtype != 0 && a->y_dtype != 1) return fail_arg("gn_fwd: y_dtype must be 0 (fp32) or 1 (bf16)");
+  const int ymode = a->y_dtype == 1 ? 2 : (a->round_tf32 ? 1 : 0);
   if (int r = gn_init()) return r;
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   const int cs = gn_slice(s, 1);
@@ -536,8 +556,9 @@ extern "C" int b200_gn_fwd(const b200_gn_args* a, void* ws, size_t ws_bytes, voi
     const size_t smem = static_cast<size_t>(s.HW) * cs * 4;
     const int th = gn_threads(smem);
 #define GN_FWD(CS, TH) \
-  gn_fwd_fused_kernel<CS, TH><<<grid, TH, smem, st>>>(s, a->stats, a->gamma, a->beta, a->y, a->eps, a->silu, a->round_tf32)
-    if (cs == 32 && th == 256) GN_FWD(32, 256);
+  gn_fwd_fused_kernel<CS, TH><<<grid, TH, smem, st>>>(s, a->stats, a->gamma, a->beta, static_cast<float*>(a->y), a->eps, a->silu, ymode)
+    if (cs == 8) GN_FWD(8, 256);
+    else if (cs == 32 && th == 256) GN_FWD(32, 256);
     else if (cs == 32) GN_FWD(32, 512);
     else if (th == 256) GN_FWD(16, 256);
     else GN_FWD(16, 512);
@@ -553,7 +574,7 @@ extern "C" int b200_gn_fwd(const b200_gn_args* a, void* ws, size_t ws_bytes, voi
   gn_finalize_kernel<<<(ng + 255) / 256, 256, 0, st>>>(a->stats, ng, 1.0f / static_cast<float>(s.HW * (s.C >> 5)), a->eps);
   if (int r = after_launch("gn_finalize_kernel")) return r;
   const size_t total = static_cast<size_t>(s.N) * s.HW * (s.C / 4);
-  gn_apply_kernel<<<ew_grid(total), 256, 0, st>>>(s, a->stats, a->gamma, a->beta, a->y, a->silu, a->round_tf32);
+  gn_apply_kernel<<<ew_grid(total), 256, 0, st>>>(s, a->stats, a->gamma, a->beta, static_cast<float*>(a->y), a->silu, ymode);
   return after_launch("gn_apply_kernel");
 }
 
@@ -565,6 +586,9 @@ extern "C" int b200_gn_bwd(const b200_gn_bwd_args* b, void* ws, size_t ws_bytes,
   if (int r = gn_init()) return r;
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   const int add_c = b->add_c ? b->add_c : s.C;
+  uint16_t* dxb = static_cast<uint16_t*>(b->dx_bf16);
+  const int dxb_c = dxb ? b->dx_bf16_c : 0;
+  if (dxb && (dxb_c <= 0 || dxb_c > s.C || dxb_c % 32)) return fail_arg("gn_bwd: dx_bf16_c must be a multiple of 32 in (0, C]");
   const int cs = gn_slice(s, 2);
   if (cs) {
     const int grid = s.N * (s.C / cs);
@@ -573,8 +597,9 @@ extern "C" int b200_gn_bwd(const b200_gn_bwd_args* b, void* ws, size_t ws_bytes,
 #define GN_BWD(CS, TH)                                                                                                  \
   gn_bwd_fused_kernel<CS, TH><<<grid, TH, smem, st>>>(s, b->fwd.stats, b->fwd.gamma, b->fwd.beta, b->dy, b->dx, b->add1, \
                                                       b->add1_ld, b->add2, b->add2_ld, add_c, b->dgamma, b->dbeta,       \
-                                                      b->fwd.silu, b->round_dx)
-    if (cs == 32 && th == 256) GN_BWD(32, 256);
+                                                      b->fwd.silu, b->round_dx, dxb, dxb_c)
+    if (cs == 8) GN_BWD(8, 256);
+    else if (cs == 32 && th == 256) GN_BWD(32, 256);
     else if (cs == 32) GN_BWD(32, 512);
     else if (th == 256) GN_BWD(16, 256);
     else GN_BWD(16, 512);
@@ -593,6 +618,6 @@ extern "C" int b200_gn_bwd(const b200_gn_bwd_args* b, void* ws, size_t ws_bytes,
   const size_t total = static_cast<size_t>(s.N) * s.HW * (s.C / 4);
   gn_bwd_apply_kernel<<<ew_grid(total), 256, 0, st>>>(s, b->fwd.stats, b->fwd.gamma, b->fwd.beta, b->dy, red, b->dx,
                                                       b->add1, b->add1_ld, b->add2, b->add2_ld, add_c, b->fwd.silu,
-                                                      b->round_dx);
+                                                      b->round_dx, dxb, dxb_c);
   return after_launch("gn_bwd_apply_kernel");
 }

@@ -109,10 +109,11 @@ int get_tmap_im2col(const void* base, int N, int H, int W, int C, int ld, int lo
   return 0;
 }
 
-int get_tmap_rows4d(const void* base, int N, int H, int W, int C, int ld, uint32_t box_c, uint32_t box_w, CUtensorMap* out) {
+int get_tmap_rows4d(const void* base, int N, int H, int W, int C, int ld, uint32_t box_c, uint32_t box_w, CUtensorMap* out,
+                    int elem_bytes) {
   TmapKey k = {{reinterpret_cast<uint64_t>(base), (static_cast<uint64_t>(N) << 32) | static_cast<uint32_t>(C),
                 (static_cast<uint64_t>(H) << 32) | static_cast<uint32_t>(W), static_cast<uint64_t>(ld),
-                (static_cast<uint64_t>(box_c) << 32) | box_w, 0, 0, 44}};
+                (static_cast<uint64_t>(box_c) << 32) | box_w, static_cast<uint64_t>(elem_bytes), 0, 44}};
   std::lock_guard<std::mutex> lock(g_mu);
   auto it = g_cache.find(k);
   if (it != g_cache.end()) {
@@ -121,11 +122,12 @@ int get_tmap_rows4d(const void* base, int N, int H, int W, int C, int ld, uint32
   }
   if (int r = load_driver_fns()) return r;
   cuuint64_t dims[4] = {(cuuint64_t)C, (cuuint64_t)W, (cuuint64_t)H, (cuuint64_t)N};
-  cuuint64_t strides[3] = {(uint64_t)ld * 4, (uint64_t)W * ld * 4, (uint64_t)H * W * ld * 4};
+  const uint64_t eb4 = static_cast<uint64_t>(elem_bytes);
+  cuuint64_t strides[3] = {(uint64_t)ld * eb4, (uint64_t)W * ld * eb4, (uint64_t)H * W * ld * eb4};
   cuuint32_t box[4] = {box_c, box_w, 1, 1};
   cuuint32_t estr[4] = {1, 1, 1, 1};
   CUtensorMap m;
-  CUresult r = g_encode_tiled(&m, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 4, const_cast<void*>(base), dims, strides, box, estr,
+  CUresult r = g_encode_tiled(&m, dtype_of(elem_bytes), 4, const_cast<void*>(base), dims, strides, box, estr,
                               CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
                               CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   if (r != CUDA_SUCCESS) {

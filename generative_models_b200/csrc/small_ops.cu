@@ -364,6 +364,29 @@ extern "C" int b200_round_tf32(const b200_round_args* a, void* ws, size_t ws_byt
   return after_launch("round_tf32_kernel");
 }
 
+// fp32 -> bf16 (RNE) of a strided 2-D slice; 4 elements per thread, 16 B loads / 8 B stores.
+__global__ void __launch_bounds__(256) cast_bf16_kernel(const float* __restrict__ src, uint2* __restrict__ dst,
+                                                        size_t total4, int cols4, int src_ld) {
+  for (size_t i = blockIdx.x * static_cast<size_t>(blockDim.x) + threadIdx.x; i < total4;
+       i += static_cast<size_t>(gridDim.x) * blockDim.x) {
+    const size_t r = i / cols4;
+    const int c = static_cast<int>(i - r * cols4) * 4;
+    const float4 v = *reinterpret_cast<const float4*>(src + r * src_ld + c);
+    dst[i] = pack_bf16x4(v);
+  }
+}
+
+extern "C" int b200_cast_bf16(const b200_cast_args* a, void* ws, size_t ws_bytes, void* stream) {
+  (void)ws; (void)ws_bytes;
+  if (!a || !a->src || !a->dst || a->cols <= 0 || a->cols % 4) return fail_arg("cast_bf16: null pointer or cols not a multiple of 4");
+  const int ld = a->src_ld ? a->src_ld : a->cols;
+  if (ld % 4) return fail_arg("cast_bf16: src_ld must be a multiple of 4");
+  const size_t total4 = a->rows * static_cast<size_t>(a->cols / 4);
+  if (total4 == 0) return 0;
+  cast_bf16_kernel<<<ew_grid2(total4), 256, 0, ST(stream)>>>(a->src, reinterpret_cast<uint2*>(a->dst), total4, a->cols / 4, ld);
+  return after_launch("cast_bf16_kernel");
+}
+
 extern "C" int b200_zero(const b200_zero_args* a, void* ws, size_t ws_bytes, void* stream) {
   (void)ws; (void)ws_bytes;
   if (!a || !a->ptr) return fail_arg("zero: null pointer");

@@ -24,6 +24,7 @@ class ConvArgs(C.Structure):
         ("x_ld", C.c_int), ("x2_ld", C.c_int), ("round_out", C.c_int),
         ("skip_x", _f32p), ("skip_x2", _f32p), ("skip_w", _f32p), ("bias2", _f32p),
         ("skip_c1", C.c_int), ("skip_c2", C.c_int), ("skip_x_ld", C.c_int), ("skip_x2_ld", C.c_int),
+        ("op_dtype", C.c_int),
     ]
 
 
@@ -33,7 +34,7 @@ class WgradArgs(C.Structure):
         ("N", C.c_int), ("H", C.c_int), ("W", C.c_int), ("C1", C.c_int), ("C2", C.c_int),
         ("Ho", C.c_int), ("Wo", C.c_int),
         ("R", C.c_int), ("S", C.c_int), ("stride", C.c_int), ("pad", C.c_int),
-        ("k_slices", C.c_int), ("x_ld", C.c_int), ("x2_ld", C.c_int), ("dy_ld", C.c_int),
+        ("k_slices", C.c_int), ("x_ld", C.c_int), ("x2_ld", C.c_int), ("dy_ld", C.c_int), ("op_dtype", C.c_int),
     ]
 
 
@@ -42,7 +43,7 @@ class GnArgs(C.Structure):
         ("x", _f32p), ("x2", _f32p), ("stats", _f32p), ("gamma", _f32p), ("beta", _f32p), ("y", _f32p),
         ("N", C.c_int), ("HW", C.c_int), ("C1", C.c_int), ("C2", C.c_int),
         ("x_ld", C.c_int), ("x2_ld", C.c_int),
-        ("eps", C.c_float), ("silu", C.c_int), ("round_tf32", C.c_int),
+        ("eps", C.c_float), ("silu", C.c_int), ("round_tf32", C.c_int), ("y_dtype", C.c_int),
     ]
 
 
@@ -50,7 +51,7 @@ class GnBwdArgs(C.Structure):
     _fields_ = [
         ("fwd", GnArgs), ("dy", _f32p), ("dx", _f32p), ("add1", _f32p), ("add2", _f32p),
         ("add1_ld", C.c_int), ("add2_ld", C.c_int), ("add_c", C.c_int),
-        ("dgamma", _f32p), ("dbeta", _f32p), ("round_dx", C.c_int),
+        ("dgamma", _f32p), ("dbeta", _f32p), ("round_dx", C.c_int), ("dx_bf16", _f32p), ("dx_bf16_c", C.c_int),
     ]
 
 
@@ -130,6 +131,10 @@ class RoundArgs(C.Structure):
     _fields_ = [("src", _f32p), ("dst", _f32p), ("n", C.c_size_t)]
 
 
+class CastArgs(C.Structure):
+    _fields_ = [("src", _f32p), ("dst", _f32p), ("rows", C.c_size_t), ("cols", C.c_int), ("src_ld", C.c_int)]
+
+
 class ZeroArgs(C.Structure):
     _fields_ = [("ptr", _f32p), ("bytes", C.c_size_t)]
 
@@ -156,7 +161,7 @@ def load():
     lib.b200_last_error.restype = C.c_char_p
     lib.b200_launch_count.restype = C.c_ulonglong
     lib.b200_init.argtypes = [C.c_int]
-    if lib.b200_abi_version() != 3:
+    if lib.b200_abi_version() != 4:
         raise B200Error("libb200ddpm.so ABI version mismatch")
     for name in EXPORTS:
         fn = getattr(lib, name)  # AttributeError if the symbol is missing
@@ -180,7 +185,7 @@ EXPORTS = [
     "b200_conv_in_fwd", "b200_conv_in_bwd", "b200_conv_out_fwd", "b200_conv_out_bwd",
     "b200_upsample2x", "b200_colsum",
     "b200_embed_prep", "b200_embed_combine", "b200_embed_combine_bwd",
-    "b200_linear", "b200_adam", "b200_zero", "b200_round_tf32",
+    "b200_linear", "b200_adam", "b200_zero", "b200_round_tf32", "b200_cast_bf16",
 ]
 
 

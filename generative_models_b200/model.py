@@ -56,6 +56,10 @@ class DiffusionModelB200(nn.Module):
     DG.lr_scheduler = "none"
     # additions (defaults reproduce the reference's behaviour)
     DG.graph = 1  # replay the train step / sampler step as CUDA graphs
+    # 'tf32': fp32 storage, TF32 tensor-core operands everywhere (BASELINE.json configs[1], the parity configuration).
+    # 'bf16': the ResBlock 3x3 convolutions (87 % of the FLOPs) take bf16 operands with fp32 accumulation — the
+    # counterpart of the reference's torch.autocast step (diffusion_model.py:66) — everything else as in 'tf32'.
+    DG.precision = "tf32"
 
     def __init__(self, G):
         super().__init__()
@@ -70,6 +74,9 @@ class DiffusionModelB200(nn.Module):
             raise NotImplementedError(f"mean_type {G.mean_type!r} (the reference's 'both' is broken upstream)")
         if G.sampler not in SAMPLERS:
             raise NotImplementedError(f"sampler {G.sampler!r}")
+        if G.get("precision", "tf32") not in ("tf32", "bf16"):
+            raise NotImplementedError(f"precision {G.precision!r} (tf32 | bf16)")
+        self.bf16 = G.get("precision", "tf32") == "bf16"
         if float(G.dropout) != 0.0:
             raise NotImplementedError("dropout != 0 is not on the DDPM hot path (reference default is 0.0)")
         if Path(G.teacher_path) != Path("."):
@@ -274,7 +281,8 @@ class _Bound:
             T = int(G.timesteps)
             self.sched = model._table(T)
             self.step_dev = torch.zeros(1, dtype=torch.int32, device=dev)
-            self.plan = UNetPlan(model.store, B, S, train=False, sched=self.sched, step_dev=self.step_dev)
+            self.plan = UNetPlan(model.store, B, S, train=False, sched=self.sched, step_dev=self.step_dev,
+                                 bf16=model.bf16)
             self.noise = torch.zeros(B, D, **f32)
             self.cond_w = torch.zeros(B, **f32)
             self.x_hist = torch.zeros(B, D, **f32)
@@ -293,7 +301,7 @@ class _Bound:
                                  Op("b200_step_advance", lib.StepAdvanceArgs(step_dev=_p(self.step_dev)))]
                              for g in (False, True)}
             return
-        self.plan = UNetPlan(model.store, B, S, train=(kind == "train"))
+        self.plan = UNetPlan(model.store, B, S, train=(kind == "train"), bf16=model.bf16)
         p = self.plan
         self.x = torch.zeros(B, D, **f32)
         self.eps = torch.zeros(B, D, **f32)

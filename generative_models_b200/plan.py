@@ -78,13 +78,15 @@ class _Pool:
 
 
 class _Grad:
-    """A gradient tensor seen as [B*HW] pixel rows of 128 channels with a pixel stride (a slice of a wider buffer)."""
-    __slots__ = ("t", "off", "ld")
+    """A gradient tensor seen as [B*HW] pixel rows of 128 channels with a pixel stride (a slice of a wider buffer).
+    bf: optional dense bf16 copy [B*HW, 128] of the same slice (the dY operand of the bf16 dgrad / wgrad)."""
+    __slots__ = ("t", "off", "ld", "bf")
 
-    def __init__(self, t, off=0, ld=None):
+    def __init__(self, t, off=0, ld=None, bf=None):
         self.t = t
         self.off = off
         self.ld = ld if ld is not None else t.shape[-1]
+        self.bf = bf if bf is not None else (getattr(t, "bf16_copy", None) if off == 0 else None)
 
     def ptr(self):
         return _p(self.t, self.off)
@@ -93,8 +95,15 @@ class _Grad:
 class UNetPlan:
     """Forward (and backward) op lists of SimpleUnet for a fixed batch `B` and image side `S`."""
 
-    def __init__(self, store, B, S, train, sched=None, step_dev=None):
+    def __init__(self, store, B, S, train, sched=None, step_dev=None, bf16=False):
+        """bf16: the 24 ResBlock 3x3 convolutions (87 % of the FLOPs) take bf16 operands — GroupNorm writes its output
+        as bf16, the weights come from a bf16 shadow, the backward's dY operands are bf16 copies written by the
+        producing GroupNorm-backward — with fp32 accumulation; the residual stream, GroupNorm statistics, every
+        gradient that is summed, and the plain / skip / edge convolutions stay fp32 (TF32 tensor cores)."""
         assert S % 4 == 0, "image side must be divisible by 4 (two stride-2 levels)"
+        self.bf16 = bool(bf16)
+        if self.bf16:
+            store.ensure_bf16()
         self.store = store
         self.B, self.S, self.train = B, S, train
         self.Cc = Cc = store.C
@@ -135,8 +144,17 @@ class UNetPlan:
         """tensor-core operand: the TF32-rounded shadow of the parameter (refreshed by self.refresh_ops)"""
         return C.c_void_p(self.store.tc_ptr(name))
 
+    def _wbf(self, name):
+        return C.c_void_p(self.store.bf_ptr(name))
+
     def _g(self, name):
         return C.c_void_p(self.store.gptr(name))
+
+    @staticmethod
+    def _get_bf(pool, *shape):
+        """storage for a bf16 tensor of `shape` from an fp32 pool (half the floats); only its pointer is used"""
+        assert shape[-1] % 2 == 0
+        return pool.get(*shape[:-1], shape[-1] // 2)
 
     def _next_stats(self):
         s = self.stats[self._stat_i]
@@ -144,32 +162,41 @@ class UNetPlan:
         return s
 
     def _conv(self, x, x2, wname, out, H, Ho, R, stride, pad, C1, C2, bias=True, emb=None, residual=None,
-              res_ld=128, x_ld=0, x2_ld=0, round_out=1):
-        a = lib.ConvArgs(x=_p(x), x2=_p(x2), w=self._wtc(wname + ".weight"), out=_p(out),
+              res_ld=128, x_ld=0, x2_ld=0, round_out=1, bf=False):
+        a = lib.ConvArgs(x=_p(x), x2=_p(x2), w=(self._wbf if bf else self._wtc)(wname + ".weight"), out=_p(out),
                          bias=self._w(wname + ".bias") if bias else None, emb=emb,
                          residual=residual, N=self.B, H=H, W=H, C1=C1, C2=C2, Ho=Ho, Wo=Ho, R=R, S=R, stride=stride,
                          pad=pad, mode=0, w_cout=128, w_cin=C1 + C2, n_off=0, out_ld=128, emb_ld=12 * self.Cc,
-                         res_ld=res_ld, x_ld=x_ld, x2_ld=x2_ld, round_out=round_out)
+                         res_ld=res_ld, x_ld=x_ld, x2_ld=x2_ld, round_out=round_out, op_dtype=1 if bf else 0)
         return Op("b200_conv_igemm", a)
 
-    def _dgrad(self, dy, wname, out, H, R, pad, w_cin, n_off, out_ld, residual=None, res_ld=0):
-        """dy: _Grad with 128 channels; writes 128 input channels [n_off, n_off+128) of `out`."""
-        a = lib.ConvArgs(x=dy.ptr(), x2=None, w=self._wtc(wname + ".weight"), out=_p(out, n_off), bias=None, emb=None,
+    def _dgrad(self, dy, wname, out, H, R, pad, w_cin, n_off, out_ld, residual=None, res_ld=0, bf=False):
+        """dy: _Grad with 128 channels; writes 128 input channels [n_off, n_off+128) of `out`.
+        bf: read the dense bf16 copy dy.bf and the bf16 weight shadow."""
+        a = lib.ConvArgs(x=_p(dy.bf) if bf else dy.ptr(), x2=None, w=(self._wbf if bf else self._wtc)(wname + ".weight"),
+                         out=_p(out, n_off), bias=None, emb=None,
                          residual=residual, N=self.B, H=H, W=H, C1=128, C2=0, Ho=H, Wo=H, R=R, S=R, stride=1, pad=pad,
                          mode=1, w_cout=128, w_cin=w_cin, n_off=n_off, out_ld=out_ld, emb_ld=0, res_ld=res_ld,
-                         x_ld=dy.ld, x2_ld=0, round_out=1)
+                         x_ld=128 if bf else dy.ld, x2_ld=0, round_out=1, op_dtype=1 if bf else 0)
         return Op("b200_conv_igemm", a)
 
-    def _wgrad(self, x, x2, dy, wname, H, Ho, R, stride, pad, C1, C2):
-        a = lib.WgradArgs(x=_p(x), x2=_p(x2), dy=dy.ptr(), dw=self._g(wname + ".weight"), N=self.B, H=H, W=H, C1=C1,
-                          C2=C2, Ho=Ho, Wo=Ho, R=R, S=R, stride=stride, pad=pad, k_slices=0, x_ld=0, x2_ld=0,
-                          dy_ld=dy.ld)
+    def _wgrad(self, x, x2, dy, wname, H, Ho, R, stride, pad, C1, C2, bf=False):
+        a = lib.WgradArgs(x=_p(x), x2=_p(x2), dy=_p(dy.bf) if bf else dy.ptr(), dw=self._g(wname + ".weight"), N=self.B,
+                          H=H, W=H, C1=C1, C2=C2, Ho=Ho, Wo=Ho, R=R, S=R, stride=stride, pad=pad, k_slices=0, x_ld=0,
+                          x2_ld=0, dy_ld=128 if bf else dy.ld, op_dtype=1 if bf else 0)
         return Op("b200_conv_wgrad", a)
 
-    def _gn(self, x, x2, gname, y, HW, C2, stats, silu=1, tf32=1):
+    def _gn(self, x, x2, gname, y, HW, C2, stats, silu=1, tf32=1, bf=False):
         return lib.GnArgs(x=_p(x), x2=_p(x2), stats=_p(stats), gamma=self._w(gname + ".weight"),
                           beta=self._w(gname + ".bias"), y=_p(y), N=self.B, HW=HW, C1=128, C2=C2, x_ld=0, x2_ld=0,
-                          eps=GN_EPS, silu=silu, round_tf32=tf32)
+                          eps=GN_EPS, silu=silu, round_tf32=tf32, y_dtype=1 if bf else 0)
+
+    def _ensure_bf(self, ops, g, HW):
+        """bf16 mode: make sure the 128-channel gradient slice `g` has its dense bf16 copy (producers that are not a
+        GroupNorm backward — upsample backward, plain-conv dgrad — get one cast pass)."""
+        if g.bf is None:
+            g.bf = self._get_bf(self.bfpool, self.B, HW, 128)
+            ops.append(Op("b200_cast_bf16", lib.CastArgs(src=g.ptr(), dst=_p(g.bf), rows=self.B * HW, cols=128, src_ld=g.ld)))
 
     def _linear(self, mode, M, N, K, act, X=None, W=None, bias=None, Y=None, dY=None, dX=None, dW=None, db=None):
         a = lib.LinearArgs(X=_p(X), W=W, bias=bias, Y=_p(Y), dY=_p(dY), dX=_p(dX), dW=dW, db=db, M=M, N=N, K=K,
@@ -210,16 +237,17 @@ class UNetPlan:
         Cin = 128 + C2
         pool = self.pool
         st1, st2 = self._next_stats(), self._next_stats()
-        a1 = pool.get(B, HW, Cin)
-        g1 = self._gn(x, x2, name + ".in_layers.0", a1, HW, C2, st1)
+        bf = self.bf16
+        a1 = self._get_bf(pool, B, HW, Cin) if bf else pool.get(B, HW, Cin)
+        g1 = self._gn(x, x2, name + ".in_layers.0", a1, HW, C2, st1, bf=bf)
         ops.append(Op("b200_gn_fwd", g1))
         h1 = pool.get(B, HW, 128)
         # h1 feeds only the GroupNorm (never a tensor-core operand), so it keeps its full fp32 mantissa
         ops.append(self._conv(a1, None, name + ".in_layers.2", h1, H, H, 3, 1, 1, Cin, 0,
-                              emb=_p(self.embout, k * 128), round_out=0))
+                              emb=_p(self.embout, k * 128), round_out=0, bf=bf))
         pool.release(a1)
-        a2 = pool.get(B, HW, 128)
-        g2 = self._gn(h1, None, name + ".out_layers.0", a2, HW, 0, st2)
+        a2 = self._get_bf(pool, B, HW, 128) if bf else pool.get(B, HW, 128)
+        g2 = self._gn(h1, None, name + ".out_layers.0", a2, HW, 0, st2, bf=bf)
         ops.append(Op("b200_gn_fwd", g2))
         pool.release(h1)
         skip = None
@@ -230,7 +258,7 @@ class UNetPlan:
         else:
             residual = x
         out = pool.get(B, HW, 128)
-        ops.append(self._conv(a2, None, name + ".out_layers.3", out, H, H, 3, 1, 1, 128, 0, residual=_p(residual)))
+        ops.append(self._conv(a2, None, name + ".out_layers.3", out, H, H, 3, 1, 1, 128, 0, residual=_p(residual), bf=bf))
         pool.release(a2)
         pool.release(skip)
         self.records[name] = dict(x=x, x2=x2, H=H, a1=a1, h1=h1, a2=a2, g1=g1, g2=g2, k=k)
@@ -246,6 +274,9 @@ class UNetPlan:
         self.embed_ops = [self._build_embed(0), self._build_embed(1)]
         st = self.store
         self.refresh_ops = [Op("b200_round_tf32", lib.RoundArgs(src=_p(st.flat), dst=_p(st.flat_tc), n=st.numel))]
+        if self.bf16:
+            self.refresh_ops.append(Op("b200_cast_bf16", lib.CastArgs(src=_p(st.flat), dst=_p(st.flat_bf), rows=1,
+                                                                      cols=st.numel, src_ld=0)))
         ops = []
         pool = self.pool
         H0, H1, H2 = S, S // 2, S // 4
@@ -315,12 +346,16 @@ class UNetPlan:
         run_ops(self.head_ops[1 if to_out2 else 0:][:1], stream_ptr)
 
     # ------------------------------------------------------------------ backward
-    def _gn_bwd(self, ops, g_fwd, dy, dx, gname, add1=None, add2=None, add_c=0):
+    def _gn_bwd(self, ops, g_fwd, dy, dx, gname, add1=None, add2=None, add_c=0, dx_bf=None):
+        """dx_bf: storage for the bf16 copy of dx[:, :128] (bf16 mode: the dY operand of the conv that produced x)."""
         a = lib.GnBwdArgs(fwd=g_fwd, dy=_p(dy), dx=_p(dx), add1=add1.ptr() if add1 else None,
                           add2=add2.ptr() if add2 else None, add1_ld=add1.ld if add1 else 0,
                           add2_ld=add2.ld if add2 else 0, add_c=add_c, dgamma=self._g(gname + ".weight"),
-                          dbeta=self._g(gname + ".bias"), round_dx=1)
+                          dbeta=self._g(gname + ".bias"), round_dx=1, dx_bf16=_p(dx_bf),
+                          dx_bf16_c=128 if dx_bf is not None else 0)
         ops.append(Op("b200_gn_bwd", a, ws=self.gn_ws))
+        if dx_bf is not None:
+            dx.bf16_copy = dx_bf
 
     def _colsum(self, ops, dy, HW, per_sample=None, ps_ld=0, total1=None, total2=None):
         a = lib.ColsumArgs(dy=dy.ptr(), per_sample=per_sample, total1=total1, total2=total2, N=self.B, HW=HW, ld=dy.ld,
@@ -337,24 +372,29 @@ class UNetPlan:
         Cin = 256 if x2 is not None else 128
         gp = self.gpool
         has_skip = x2 is not None
+        bf = self.bf16
+        if bf:
+            self._ensure_bf(ops, dOut, HW)
         # conv2 (out_layers.3): bias, weight, data gradients
         self._colsum(ops, dOut, HW, total1=self._g(name + ".out_layers.3.bias"),
                      total2=self._g(name + ".skip_connection.bias") if has_skip else None)
-        ops.append(self._wgrad(r["a2"], None, dOut, name + ".out_layers.3", H, H, 3, 1, 1, 128, 0))
+        ops.append(self._wgrad(r["a2"], None, dOut, name + ".out_layers.3", H, H, 3, 1, 1, 128, 0, bf=bf))
         da2 = gp.get(B, HW, 128)
-        ops.append(self._dgrad(dOut, name + ".out_layers.3", da2, H, 3, 1, 128, 0, 128))
+        ops.append(self._dgrad(dOut, name + ".out_layers.3", da2, H, 3, 1, 128, 0, 128, bf=bf))
         dh1 = gp.get(B, HW, 128)
-        self._gn_bwd(ops, r["g2"], da2, dh1, name + ".out_layers.0")
+        dh1_bf = self._get_bf(gp, B, HW, 128) if bf else None
+        self._gn_bwd(ops, r["g2"], da2, dh1, name + ".out_layers.0", dx_bf=dh1_bf)
         gp.release(da2)
         # emb_out broadcast add (simple_unet.py:183-184) and conv1 bias
         dh1g = _Grad(dh1)
         self._colsum(ops, dh1g, HW, per_sample=_p(self.d_embout, r["k"] * 128), ps_ld=12 * self.Cc,
                      total1=self._g(name + ".in_layers.2.bias"))
-        ops.append(self._wgrad(r["a1"], None, dh1g, name + ".in_layers.2", H, H, 3, 1, 1, Cin, 0))
+        ops.append(self._wgrad(r["a1"], None, dh1g, name + ".in_layers.2", H, H, 3, 1, 1, Cin, 0, bf=bf))
         da1 = gp.get(B, HW, Cin)
         for n_off in range(0, Cin, 128):
-            ops.append(self._dgrad(dh1g, name + ".in_layers.2", da1, H, 3, 1, Cin, n_off, Cin))
+            ops.append(self._dgrad(dh1g, name + ".in_layers.2", da1, H, 3, 1, Cin, n_off, Cin, bf=bf))
         gp.release(dh1)
+        gp.release(dh1_bf)
         dsk = None
         if has_skip:
             dsk = gp.get(B, HW, 256)
@@ -365,7 +405,9 @@ class UNetPlan:
         else:
             add1, add_c = dOut, 128
         dx = (self.pool_dcat if has_skip else gp).get(B, HW, Cin)
-        self._gn_bwd(ops, r["g1"], da1, dx, name + ".in_layers.0", add1=add1, add2=extra, add_c=add_c)
+        # the first 128 channels of dx are the output gradient of whatever produced x: give it its bf16 copy here
+        dx_bf = self._get_bf(self.bfpool, B, HW, 128) if bf else None
+        self._gn_bwd(ops, r["g1"], da1, dx, name + ".in_layers.0", add1=add1, add2=extra, add_c=add_c, dx_bf=dx_bf)
         gp.release(da1)
         gp.release(dsk)
         return dx
@@ -401,6 +443,7 @@ class UNetPlan:
         sv = self.saved
         gp = self.gpool
         self.pool_dcat = _Pool(dev, recycle=False)  # concat gradients live until the Down path consumes their 2nd half
+        self.bfpool = _Pool(dev, recycle=False)     # bf16 copies of block-output gradients (live across blocks)
         self.gn_ws = torch.zeros(B * 64, **f32)
         self.d_embout = torch.zeros(B, 12 * self.Cc, **f32)
         for nm in ("d_semb", "d_emb", "d_gemb", "d_te0", "d_ge0"):
@@ -414,7 +457,8 @@ class UNetPlan:
                              H=H0, W=H0, round_dh=1)
         ops.append(Op("b200_conv_out_bwd", ca))
         du6 = gp.get(B, H0 * H0, 128)
-        self._gn_bwd(ops, sv["gh"], dah, du6, "out.0")
+        self._gn_bwd(ops, sv["gh"], dah, du6, "out.0",
+                     dx_bf=self._get_bf(self.bfpool, B, H0 * H0, 128) if self.bf16 else None)
         gp.release(dah)
         # ---- Up, reversed
         half = lambda t: _Grad(t, 0, 256)       # gradient of the running tensor h
@@ -483,5 +527,5 @@ class UNetPlan:
     def activation_bytes(self):
         n = self.pool.bytes() + self.gpool.bytes()
         if self.train:
-            n += self.pool_dcat.bytes()
+            n += self.pool_dcat.bytes() + self.bfpool.bytes()
         return n

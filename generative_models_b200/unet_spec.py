@@ -105,6 +105,7 @@ class ParamStore:
         self.grad = torch.zeros(off, dtype=torch.float32, device=self.device)
         # TF32-rounded (round-to-nearest) shadow of `flat`: what the tensor-core convolutions read as their B operand
         self.flat_tc = torch.zeros(off, dtype=torch.float32, device=self.device)
+        self.flat_bf = None  # bf16 shadow (ensure_bf16): the operands of the bf16 ResBlock convolutions
         self.exp_avg = None
         self.exp_avg_sq = None
         self.shapes = {n: s for n, s, _ in self.specs}
@@ -130,6 +131,13 @@ class ParamStore:
 
     def tc_ptr(self, name):
         return self.flat_tc.data_ptr() + 4 * self.offsets[name]
+
+    def ensure_bf16(self):
+        if self.flat_bf is None:
+            self.flat_bf = torch.zeros(self.numel, dtype=torch.bfloat16, device=self.device)
+
+    def bf_ptr(self, name):
+        return self.flat_bf.data_ptr() + 2 * self.offsets[name]
 
     def gptr(self, name):
         return self.grad.data_ptr() + 4 * self.offsets[name]

@@ -21,7 +21,7 @@
 extern "C" {
 #endif
 
-#define B200_ABI_VERSION 3
+#define B200_ABI_VERSION 4
 
 int b200_abi_version(void);
 int b200_init(int device);
@@ -40,9 +40,9 @@ unsigned long long b200_launch_count(void);
  * simple_unet.py:150.  C1, C2 multiples of 32; Cout (fprop) must be 128; N-tile is 128 columns per launch.
  */
 typedef struct {
-  const float* x;
-  const float* x2; /* NULL when C2 == 0 */
-  const float* w;
+  const void* x;   /* fp32, or bf16 when op_dtype == 1 */
+  const void* x2;  /* NULL when C2 == 0 */
+  const void* w;   /* same element type as x */
   float* out;
   const float* bias;     /* [128] or NULL */
   const float* emb;      /* [N][emb_ld] or NULL */
@@ -59,11 +59,15 @@ typedef struct {
   /* fused skip segment (stride-1 layers): out += Conv1x1(cat(skip_x, skip_x2), skip_w) + bias2, accumulated on the
    * tensor cores as extra K-chunks.  skip_w is [128][skip_c1+skip_c2]; with the 128x128 identity it is the residual
    * add of ResBlock.forward (simple_unet.py:186), with skip_connection.weight it is the 1x1 skip conv (:177). */
-  const float* skip_x;
-  const float* skip_x2;
-  const float* skip_w;
+  const void* skip_x;
+  const void* skip_x2;
+  const void* skip_w;
   const float* bias2;
   int skip_c1, skip_c2, skip_x_ld, skip_x2_ld;
+  /* tensor-core operand type: 0 = fp32 storage, kind::tf32 MMAs; 1 = x / x2 / w (/ skip_*) hold bf16, kind::f16 MMAs
+   * with fp32 accumulation (stride-1 3x3/pad-1 and 1x1/pad-0 layers only; C1, C2 multiples of 64; x_ld in elements).
+   * out / bias / emb / residual are fp32 either way. */
+  int op_dtype;
 } b200_conv_args;
 int b200_conv_igemm(const b200_conv_args* a, void* ws, size_t ws_bytes, void* stream);
 /* which kernel b200_conv_igemm launches for these arguments: 1 = conv_strip_tf32_kernel (strip implicit GEMM, stride-1
@@ -74,9 +78,9 @@ int b200_conv_kernel_of(const b200_conv_args* a);
  *   dw[co, kh, kw, ci] += sum_{n,p,q} dy[(n,p,q), co] * x[n, p*stride-pad+kh, q*stride-pad+kw, ci]
  * Accumulates with fp32 atomics into dw (caller zeroes it once per step). */
 typedef struct {
-  const float* x;
-  const float* x2;
-  const float* dy; /* [N*Ho*Wo][128] */
+  const void* x;   /* fp32, or bf16 when op_dtype == 1 */
+  const void* x2;
+  const void* dy;  /* [N*Ho*Wo][128], same element type as x */
   float* dw;       /* [128][R*S*(C1+C2)] */
   int N, H, W, C1, C2;
   int Ho, Wo;
@@ -84,6 +88,7 @@ typedef struct {
   int k_slices; /* split of the pixel reduction; 0 = library picks */
   int x_ld, x2_ld; /* pixel stride (floats) of x / x2; 0 = dense */
   int dy_ld;       /* pixel stride of dy; 0 = dense (128) */
+  int op_dtype;    /* 0 = fp32 storage / TF32 MMAs, 1 = bf16 operands (fp32 accumulation and dw) */
 } b200_wgrad_args;
 int b200_conv_wgrad(const b200_wgrad_args* a, void* ws, size_t ws_bytes, void* stream);
 
@@ -99,12 +104,13 @@ typedef struct {
   float* stats;
   const float* gamma;
   const float* beta;
-  float* y;
+  void* y;         /* fp32, or bf16 when y_dtype == 1 */
   int N, HW, C1, C2;
   int x_ld, x2_ld;
   float eps;
   int silu;
   int round_tf32;
+  int y_dtype;     /* 0 = fp32 (optionally TF32-rounded), 1 = bf16 (the operand of a bf16 convolution) */
 } b200_gn_args;
 int b200_gn_fwd(const b200_gn_args* a, void* ws, size_t ws_bytes, void* stream);
 
@@ -122,6 +128,9 @@ typedef struct {
   float* dgamma;
   float* dbeta;
   int round_dx; /* store dx rounded to TF32 */
+  void* dx_bf16;  /* optional second output: bf16 copy of the first dx_bf16_c channels of dx, dense [N*HW][dx_bf16_c]
+                   * (the dY operand of the bf16 dgrad / wgrad of the producing convolution) */
+  int dx_bf16_c;
 } b200_gn_bwd_args;
 int b200_gn_bwd(const b200_gn_bwd_args* a, void* ws, size_t ws_bytes, void* stream);
 
@@ -288,6 +297,18 @@ typedef struct {
   size_t n;
 } b200_round_args;
 int b200_round_tf32(const b200_round_args* a, void* ws, size_t ws_bytes, void* stream);
+
+/* dst[r][c] = bf16(src[r * src_ld + c]) (round to nearest even), dst dense [rows][cols]; cols a multiple of 4.
+ * Builds the bf16 weight shadow (rows = 1) and the bf16 copy of a gradient slice that feeds a bf16 dgrad / wgrad.
+ * No reference counterpart (torch.autocast's casts, diffusion_model.py:66). */
+typedef struct {
+  const float* src;
+  void* dst;
+  size_t rows;
+  int cols;
+  int src_ld; /* floats between rows of src; 0 = dense (cols) */
+} b200_cast_args;
+int b200_cast_bf16(const b200_cast_args* a, void* ws, size_t ws_bytes, void* stream);
 
 /* cudaMemsetAsync(ptr, 0, bytes) on the stream (statistics / gradient arenas; replaces optimizer.zero_grad()). */
 typedef struct {

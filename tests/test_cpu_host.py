@@ -20,7 +20,7 @@ def test_library_exports_every_declared_symbol(built_lib):
     so = C.CDLL(built_lib.LIB_PATH)
     for name in declared:
         assert hasattr(so, name), name
-    assert built_lib.load().b200_abi_version() == 3
+    assert built_lib.load().b200_abi_version() == 4
 
 
 def test_ctypes_structs_match_header_field_order(built_lib):
@@ -33,7 +33,7 @@ def test_ctypes_structs_match_header_field_order(built_lib):
               "b200_conv_out_args": built_lib.ConvOutArgs, "b200_resample_args": built_lib.ResampleArgs,
               "b200_colsum_args": built_lib.ColsumArgs, "b200_embed_args": built_lib.EmbedArgs,
               "b200_linear_args": built_lib.LinearArgs, "b200_zero_args": built_lib.ZeroArgs,
-              "b200_round_args": built_lib.RoundArgs,
+              "b200_round_args": built_lib.RoundArgs, "b200_cast_args": built_lib.CastArgs,
               "b200_adam_args": built_lib.AdamArgs}
     for m in re.finditer(r"typedef struct \{(.*?)\}\s*(b200_\w+);", hdr, re.S):
         body, name = m.group(1), m.group(2)

@@ -41,7 +41,17 @@ def main():
         out = torch.empty(B, H, H, 128, device=dev)
         res = torch.randn(B, H, H, 128, device=dev)
         eye = torch.eye(128, device=dev)
-        for with_res in (0, 1, 2):
+        xb, x2b, wb = x.bfloat16(), (x2.bfloat16() if x2 is not None else None), w.bfloat16()
+        for with_res in (0, 1, 2, 3):
+            if with_res == 3:  # bf16 operands, no residual
+                a = lib.ConvArgs(x=ptr(xb), x2=ptr(x2b), w=ptr(wb), out=ptr(out), bias=None, emb=None, residual=None, N=B,
+                                 H=H, W=H, C1=C1, C2=C2, Ho=H, Wo=H, R=R, S=R, stride=1, pad=R // 2, mode=mode, w_cout=128,
+                                 w_cin=Cin, n_off=0, out_ld=128, emb_ld=0, res_ld=128, x_ld=0, x2_ld=0, round_out=1,
+                                 op_dtype=1)
+                ms = timeit(lambda: lib.call("b200_conv_igemm", a, st))
+                fl = 2.0 * B * H * H * 128 * R * R * (Cin if mode == 0 else 128)
+                print(f"H={H} Cin={Cin} R={R} mode={mode} bf16: {ms*1e3:8.1f} us  {fl/ms/1e9:7.1f} TFLOP/s", flush=True)
+                continue
             a = lib.ConvArgs(x=ptr(x), x2=ptr(x2), w=ptr(w), out=ptr(out), bias=None, emb=None,
                              residual=ptr(res) if with_res == 1 else None, N=B, H=H, W=H, C1=C1, C2=C2, Ho=H, Wo=H, R=R, S=R,
                              stride=1, pad=R // 2, mode=mode, w_cout=128, w_cin=Cin, n_off=0, out_ld=128, emb_ld=0,
@@ -51,6 +61,17 @@ def main():
             ms = timeit(lambda: lib.call("b200_conv_igemm", a, st))
             fl = 2.0 * B * H * H * 128 * R * R * (Cin if mode == 0 else 128)
             print(f"H={H} Cin={Cin} R={R} mode={mode} res={with_res}: {ms*1e3:8.1f} us  {fl/ms/1e9:7.1f} TFLOP/s", flush=True)
+    for (H, Cin) in [(28, 128), (28, 256), (14, 128), (7, 128)]:
+        x = torch.randn(B, H, H, Cin, device=dev)
+        dy = torch.randn(B, H, H, 128, device=dev)
+        dw = torch.zeros(128, 3, 3, Cin, device=dev)
+        for bfm in (0, 1):
+            xx, dd = (x.bfloat16(), dy.bfloat16()) if bfm else (x, dy)
+            a = lib.WgradArgs(x=ptr(xx), x2=None, dy=ptr(dd), dw=ptr(dw), N=B, H=H, W=H, C1=Cin, C2=0, Ho=H, Wo=H, R=3, S=3,
+                              stride=1, pad=1, k_slices=0, op_dtype=bfm)
+            ms = timeit(lambda: lib.call("b200_conv_wgrad", a, st))
+            fl = 2.0 * B * H * H * 128 * 9 * Cin
+            print(f"wgrad H={H} Cin={Cin} {'bf16' if bfm else 'tf32'}: {ms*1e3:8.1f} us  {fl/ms/1e9:7.1f} TFLOP/s", flush=True)
 
 
 if __name__ == "__main__":
