@@ -17,6 +17,16 @@
 
 namespace b200 {
 
+// optional fused column sums of dx over channels [0, c): total1/total2[ch] += sum over (n, pixels),
+// per_sample[n * ps_ld + ch] += sum over the pixels of sample n
+struct GnColsum {
+  float* per_sample;
+  int ps_ld;
+  float* total1;
+  float* total2;
+  int c;
+};
+
 struct GnSrc {
   const float* x;
   const float* x2;
@@ -145,15 +155,16 @@ gn_fwd_fused_kernel(GnSrc s, float* __restrict__ stats, const float* __restrict_
 // slower (201 vs 159 us at N512 HW784 C128): the register-staged global loads of phase 1 do not stay in flight the way
 // the cp.async bulk does.
 template <int CS, int kGnThreads>
-__global__ void __launch_bounds__(kGnThreads)
+__global__ void __launch_bounds__(kGnThreads, 1024 / kGnThreads)  // <= 64 registers: two 512-thread CTAs per SM
 gn_bwd_fused_kernel(GnSrc s, const float* __restrict__ stats, const float* __restrict__ gamma,
                     const float* __restrict__ beta, const float* __restrict__ dy, float* __restrict__ dx,
                     const float* __restrict__ add1, int add1_ld, const float* __restrict__ add2, int add2_ld, int add_c,
                     float* __restrict__ dgamma, float* __restrict__ dbeta, int silu, int round_dx,
-                    uint16_t* __restrict__ dxb, int dxb_c) {
+                    uint16_t* __restrict__ dxb, int dxb_c, GnColsum cs) {
   extern __shared__ float4 gn_smem[];
   __shared__ float red[16];
   __shared__ float chan[2 * CS];
+  __shared__ float csum[CS];
   constexpr int L = CS / 4;
   const int slices = s.C / CS;
   const int n = blockIdx.x / slices;
@@ -181,6 +192,7 @@ gn_bwd_fused_kernel(GnSrc s, const float* __restrict__ stats, const float* __res
   const float* dsrc = dy + row0 * s.C + c;
   if (tid < 16) red[tid] = 0.f;
   if (tid < 2 * CS) chan[tid] = 0.f;
+  if (tid < CS) csum[tid] = 0.f;
   for (int idx = tid; idx < total; idx += kGnThreads) {
     const size_t pix = idx / L;
     cp_async16(&xs[idx], src + pix * ld);
@@ -244,6 +256,7 @@ gn_bwd_fused_kernel(GnSrc s, const float* __restrict__ stats, const float* __res
   const float* a2 = (has_add && add2) ? add2 + row0 * add2_ld + c : nullptr;
   float* dst = dx + row0 * s.C + c;
   uint16_t* dstb = (dxb && c < dxb_c) ? dxb + row0 * dxb_c + c : nullptr;  // bf16 copy of the first dxb_c channels
+  float4 cacc = make_float4(0.f, 0.f, 0.f, 0.f);  // per-channel sum of dx over this sample's pixels (fused colsum)
   for (int idx = tid; idx < total; idx += kGnThreads) {
     const size_t pix = idx / L;
     const float4 xh = xs[idx];
@@ -264,6 +277,25 @@ gn_bwd_fused_kernel(GnSrc s, const float* __restrict__ stats, const float* __res
     if (dstb) *reinterpret_cast<uint2*>(dstb + pix * dxb_c) = pack_bf16x4(o);
     if (round_dx) o = round_tf32(o);
     *reinterpret_cast<float4*>(dst + pix * s.C) = o;
+    cacc.x += o.x; cacc.y += o.y; cacc.z += o.z; cacc.w += o.w;
+  }
+  // fused column sums of dx (bias gradient of the convolution that produced x, and the per-sample gradient of the
+  // timestep-embedding broadcast add): this CTA owns all pixels of (n, channel slice)
+  if (cs.c > 0 && c0 < cs.c) {  // uniform per CTA
+    float ca[4] = {cacc.x, cacc.y, cacc.z, cacc.w};
+#pragma unroll
+    for (int j = 0; j < 4; ++j) ca[j] = lane_group_sum<L>(ca[j], false);
+    if (lane < L) {
+#pragma unroll
+      for (int j = 0; j < 4; ++j) atomicAdd(&csum[l * 4 + j], ca[j]);
+    }
+    __syncthreads();
+    if (tid < CS) {
+      const float v = csum[tid];
+      if (cs.per_sample) atomicAdd(&cs.per_sample[static_cast<size_t>(n) * cs.ps_ld + c0 + tid], v);
+      if (cs.total1) atomicAdd(&cs.total1[c0 + tid], v);
+      if (cs.total2) atomicAdd(&cs.total2[c0 + tid], v);
+    }
   }
 }
 
@@ -589,6 +621,11 @@ extern "C" int b200_gn_bwd(const b200_gn_bwd_args* b, void* ws, size_t ws_bytes,
   uint16_t* dxb = static_cast<uint16_t*>(b->dx_bf16);
   const int dxb_c = dxb ? b->dx_bf16_c : 0;
   if (dxb && (dxb_c <= 0 || dxb_c > s.C || dxb_c % 32)) return fail_arg("gn_bwd: dx_bf16_c must be a multiple of 32 in (0, C]");
+  GnColsum csm = {b->colsum_per_sample, b->colsum_ps_ld, b->colsum_total1, b->colsum_total2, 0};
+  if (csm.per_sample || csm.total1 || csm.total2) {
+    if (b->colsum_c != 128) return fail_arg("gn_bwd: colsum_c must be 128");
+    csm.c = 128;
+  }
   const int cs = gn_slice(s, 2);
   if (cs) {
     const int grid = s.N * (s.C / cs);
@@ -597,7 +634,7 @@ extern "C" int b200_gn_bwd(const b200_gn_bwd_args* b, void* ws, size_t ws_bytes,
 #define GN_BWD(CS, TH)                                                                                                  \
   gn_bwd_fused_kernel<CS, TH><<<grid, TH, smem, st>>>(s, b->fwd.stats, b->fwd.gamma, b->fwd.beta, b->dy, b->dx, b->add1, \
                                                       b->add1_ld, b->add2, b->add2_ld, add_c, b->dgamma, b->dbeta,       \
-                                                      b->fwd.silu, b->round_dx, dxb, dxb_c)
+                                                      b->fwd.silu, b->round_dx, dxb, dxb_c, csm)
     if (cs == 8) GN_BWD(8, 256);
     else if (cs == 32 && th == 256) GN_BWD(32, 256);
     else if (cs == 32) GN_BWD(32, 512);
@@ -619,5 +656,10 @@ extern "C" int b200_gn_bwd(const b200_gn_bwd_args* b, void* ws, size_t ws_bytes,
   gn_bwd_apply_kernel<<<ew_grid(total), 256, 0, st>>>(s, b->fwd.stats, b->fwd.gamma, b->fwd.beta, b->dy, red, b->dx,
                                                       b->add1, b->add1_ld, b->add2, b->add2_ld, add_c, b->fwd.silu,
                                                       b->round_dx, dxb, dxb_c);
-  return after_launch("gn_bwd_apply_kernel");
+  if (int r = after_launch("gn_bwd_apply_kernel")) return r;
+  if (csm.c) {  // streaming path: the column sums take their own pass over dx
+    b200_colsum_args ca = {b->dx, csm.per_sample, csm.total1, csm.total2, s.N, s.HW, s.C, csm.ps_ld};
+    return b200_colsum(&ca, nullptr, 0, stream);
+  }
+  return 0;
 }

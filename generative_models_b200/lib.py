@@ -52,6 +52,8 @@ class GnBwdArgs(C.Structure):
         ("fwd", GnArgs), ("dy", _f32p), ("dx", _f32p), ("add1", _f32p), ("add2", _f32p),
         ("add1_ld", C.c_int), ("add2_ld", C.c_int), ("add_c", C.c_int),
         ("dgamma", _f32p), ("dbeta", _f32p), ("round_dx", C.c_int), ("dx_bf16", _f32p), ("dx_bf16_c", C.c_int),
+        ("colsum_per_sample", _f32p), ("colsum_ps_ld", C.c_int), ("colsum_total1", _f32p), ("colsum_total2", _f32p),
+        ("colsum_c", C.c_int),
     ]
 
 

@@ -80,13 +80,16 @@ class _Pool:
 class _Grad:
     """A gradient tensor seen as [B*HW] pixel rows of 128 channels with a pixel stride (a slice of a wider buffer).
     bf: optional dense bf16 copy [B*HW, 128] of the same slice (the dY operand of the bf16 dgrad / wgrad)."""
-    __slots__ = ("t", "off", "ld", "bf")
+    __slots__ = ("t", "off", "ld", "bf", "prod")
 
     def __init__(self, t, off=0, ld=None, bf=None):
         self.t = t
         self.off = off
         self.ld = ld if ld is not None else t.shape[-1]
         self.bf = bf if bf is not None else (getattr(t, "bf16_copy", None) if off == 0 else None)
+        # the b200_gn_bwd argument struct that writes t (its first 128 channels = this slice): column sums of the
+        # slice are fused into that launch instead of a separate b200_colsum pass
+        self.prod = getattr(t, "producer_gn", None) if off == 0 else None
 
     def ptr(self):
         return _p(self.t, self.off)
@@ -102,6 +105,7 @@ class UNetPlan:
         gradient that is summed, and the plain / skip / edge convolutions stay fp32 (TF32 tensor cores)."""
         assert S % 4 == 0, "image side must be divisible by 4 (two stride-2 levels)"
         self.bf16 = bool(bf16)
+        self.fuse_colsum = True
         if self.bf16:
             store.ensure_bf16()
         self.store = store
@@ -354,10 +358,16 @@ class UNetPlan:
                           dbeta=self._g(gname + ".bias"), round_dx=1, dx_bf16=_p(dx_bf),
                           dx_bf16_c=128 if dx_bf is not None else 0)
         ops.append(Op("b200_gn_bwd", a, ws=self.gn_ws))
+        dx.producer_gn = a
         if dx_bf is not None:
             dx.bf16_copy = dx_bf
 
     def _colsum(self, ops, dy, HW, per_sample=None, ps_ld=0, total1=None, total2=None):
+        g = dy.prod
+        if g is not None and not g.colsum_c and self.fuse_colsum:
+            g.colsum_per_sample, g.colsum_ps_ld, g.colsum_total1, g.colsum_total2 = per_sample, ps_ld, total1, total2
+            g.colsum_c = 128
+            return
         a = lib.ColsumArgs(dy=dy.ptr(), per_sample=per_sample, total1=total1, total2=total2, N=self.B, HW=HW, ld=dy.ld,
                            ps_ld=ps_ld)
         ops.append(Op("b200_colsum", a))

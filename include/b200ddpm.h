@@ -131,6 +131,14 @@ typedef struct {
   void* dx_bf16;  /* optional second output: bf16 copy of the first dx_bf16_c channels of dx, dense [N*HW][dx_bf16_c]
                    * (the dY operand of the bf16 dgrad / wgrad of the producing convolution) */
   int dx_bf16_c;
+  /* optional fused column sums of dx over its first colsum_c (= 128) channels — what b200_colsum would compute from
+   * dx: total1/total2[c] += sum over (n, pixel) (bias gradients of the convolution(s) that produced x),
+   * per_sample[n * ps_ld + c] += sum over the pixels of sample n (gradient of the emb broadcast add). */
+  float* colsum_per_sample;
+  int colsum_ps_ld;
+  float* colsum_total1;
+  float* colsum_total2;
+  int colsum_c;
 } b200_gn_bwd_args;
 int b200_gn_bwd(const b200_gn_bwd_args* a, void* ws, size_t ws_bytes, void* stream);
 
