@@ -246,6 +246,7 @@ extern "C" int b200_conv_igemm(const b200_conv_args* a, void* ws, size_t ws_byte
     if (rs != -100) return rs;
   }
   if (a->skip_x) return fail_arg("conv_igemm: the fused skip segment needs a stride-1 3x3/pad-1 or 1x1/pad-0 layer");
+  if (a->out_bf16) return fail_arg("conv_igemm: out_bf16 needs a stride-1 3x3/pad-1 or 1x1/pad-0 layer (strip kernel)");
   if (a->op_dtype != 0) return fail_arg("conv_igemm: bf16 operands need a stride-1 3x3/pad-1 or 1x1/pad-0 layer (strip kernel)");
   CUtensorMap tmA, tmA2, tmB;
   int r = get_tmap_im2col(a->x, a->N, a->H, a->W, a->C1, a->x_ld ? a->x_ld : a->C1, lower, upper, a->stride, 32, 128, 4, 0, &tmA);

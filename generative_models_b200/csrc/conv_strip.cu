@@ -40,6 +40,7 @@ constexpr int kStripSmem = kSS * kStripBytes + kSB * kBTile + 1024 + 256 + 2 * 5
 
 struct StripK {
   float* out;
+  uint16_t* out_bf;  // optional dense bf16 copy [M][128] of out
   const float* bias;
   const float* bias2;
   const float* emb;
@@ -336,6 +337,7 @@ conv_strip_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
           if (mm[j] >= 0) {
             const float v = __uint_as_float(r[j]) + add[j];
             a.out[static_cast<size_t>(mm[j]) * a.out_ld + co] = a.round_out ? round_tf32(v) : v;
+            if (a.out_bf) a.out_bf[static_cast<size_t>(mm[j]) * 128 + co] = bf16_bits(v);
           }
         }
       }
@@ -383,6 +385,8 @@ int conv_strip_launch(const b200_conv_args* a, void* stream) {
   const int eb = bf ? 2 : 4;        // operand element bytes
   const uint32_t CK = bf ? 64 : 32;  // channels per 128 B row
   if (a->C1 % CK || a->C2 % CK) return fail_arg("conv_igemm: C1/C2 must be multiples of the K-chunk (32 fp32 / 64 bf16)");
+
+  if (a->out_bf16 && a->mode != 0) return fail_arg("conv_igemm: out_bf16 is an fprop output");
 
   CUtensorMap tmA, tmA2, tmB;
   int r;
@@ -436,6 +440,7 @@ int conv_strip_launch(const b200_conv_args* a, void* stream) {
 
   StripK k;
   k.out = a->out;
+  k.out_bf = static_cast<uint16_t*>(a->out_bf16);
   k.bias = a->bias;
   k.bias2 = a->bias2;
   k.emb = a->emb;

@@ -18,6 +18,11 @@ __device__ __forceinline__ float4 round_tf32(float4 v) {
   return make_float4(round_tf32(v.x), round_tf32(v.y), round_tf32(v.z), round_tf32(v.w));
 }
 
+__device__ __forceinline__ uint16_t bf16_bits(float v) {
+  uint16_t r;
+  asm("cvt.rn.bf16.f32 %0, %1;" : "=h"(r) : "f"(v));
+  return r;
+}
 // 4 floats -> 4 bf16 (round to nearest even) packed in 8 bytes, element 0 in the low half of .x
 __device__ __forceinline__ uint2 pack_bf16x4(float4 v) {
   uint2 r;

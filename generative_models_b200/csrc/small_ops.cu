@@ -33,6 +33,19 @@ upsample2x_fwd_kernel(const float4* __restrict__ in, float4* __restrict__ out, i
     out[i] = in[((static_cast<size_t>(n) * H + (y >> 1)) * W + (x >> 1)) * C4 + c];
   }
 }
+__global__ void __launch_bounds__(256)
+upsample2x_fwd_bf16_kernel(const float4* __restrict__ in, uint2* __restrict__ out, int N, int H, int W, int C4) {
+  const size_t total = static_cast<size_t>(N) * 4 * H * W * C4;
+  GRID_STRIDE(i, total) {
+    const int c = static_cast<int>(i % C4);
+    size_t p = i / C4;
+    const int x = static_cast<int>(p % (2 * W));
+    p /= (2 * W);
+    const int y = static_cast<int>(p % (2 * H));
+    const int n = static_cast<int>(p / (2 * H));
+    out[i] = pack_bf16x4(in[((static_cast<size_t>(n) * H + (y >> 1)) * W + (x >> 1)) * C4 + c]);
+  }
+}
 // din[n,y,x,c] = sum of the 2x2 block of dout; dout pixel stride is ld4 float4s (it may be a slice of a wider buffer)
 __global__ void __launch_bounds__(256)
 upsample2x_bwd_kernel(const float4* __restrict__ dout, float4* __restrict__ din, int N, int H, int W, int C4, int ld4,
@@ -266,6 +279,11 @@ extern "C" int b200_upsample2x(const b200_resample_args* a, void* ws, size_t ws_
   const int C4 = a->C / 4;
   if (a->mode == 0) {
     const size_t total = static_cast<size_t>(a->N) * 4 * a->H * a->W * C4;
+    if (a->out_dtype == 1) {
+      upsample2x_fwd_bf16_kernel<<<ew_grid2(total), 256, 0, ST(stream)>>>(reinterpret_cast<const float4*>(a->in),
+                                                                           reinterpret_cast<uint2*>(a->out), a->N, a->H, a->W, C4);
+      return after_launch("upsample2x_fwd_bf16_kernel");
+    }
     upsample2x_fwd_kernel<<<ew_grid2(total), 256, 0, ST(stream)>>>(reinterpret_cast<const float4*>(a->in),
                                                                     reinterpret_cast<float4*>(a->out), a->N, a->H, a->W, C4);
     return after_launch("upsample2x_fwd_kernel");

@@ -24,7 +24,7 @@ class ConvArgs(C.Structure):
         ("x_ld", C.c_int), ("x2_ld", C.c_int), ("round_out", C.c_int),
         ("skip_x", _f32p), ("skip_x2", _f32p), ("skip_w", _f32p), ("bias2", _f32p),
         ("skip_c1", C.c_int), ("skip_c2", C.c_int), ("skip_x_ld", C.c_int), ("skip_x2_ld", C.c_int),
-        ("op_dtype", C.c_int),
+        ("op_dtype", C.c_int), ("out_bf16", _f32p),
     ]
 
 
@@ -97,7 +97,7 @@ class ConvOutArgs(C.Structure):
 
 class ResampleArgs(C.Structure):
     _fields_ = [("in_", _f32p), ("out", _f32p), ("N", C.c_int), ("H", C.c_int), ("W", C.c_int), ("C", C.c_int),
-                ("in_ld", C.c_int), ("mode", C.c_int), ("round_out", C.c_int)]
+                ("in_ld", C.c_int), ("mode", C.c_int), ("round_out", C.c_int), ("out_dtype", C.c_int)]
 
 
 class ColsumArgs(C.Structure):

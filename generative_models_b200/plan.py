@@ -166,13 +166,27 @@ class UNetPlan:
         return s
 
     def _conv(self, x, x2, wname, out, H, Ho, R, stride, pad, C1, C2, bias=True, emb=None, residual=None,
-              res_ld=128, x_ld=0, x2_ld=0, round_out=1, bf=False):
+              res_ld=128, x_ld=0, x2_ld=0, round_out=1, bf=False, out_bf=None):
+        if out_bf is not None:
+            out.bf16_copy = out_bf
         a = lib.ConvArgs(x=_p(x), x2=_p(x2), w=(self._wbf if bf else self._wtc)(wname + ".weight"), out=_p(out),
                          bias=self._w(wname + ".bias") if bias else None, emb=emb,
                          residual=residual, N=self.B, H=H, W=H, C1=C1, C2=C2, Ho=Ho, Wo=Ho, R=R, S=R, stride=stride,
                          pad=pad, mode=0, w_cout=128, w_cin=C1 + C2, n_off=0, out_ld=128, emb_ld=12 * self.Cc,
-                         res_ld=res_ld, x_ld=x_ld, x2_ld=x2_ld, round_out=round_out, op_dtype=1 if bf else 0)
+                         res_ld=res_ld, x_ld=x_ld, x2_ld=x2_ld, round_out=round_out, op_dtype=1 if bf else 0,
+                         out_bf16=_p(out_bf))
         return Op("b200_conv_igemm", a)
+
+    def _rel(self, t):
+        """release an activation and its bf16 copy (inference plans recycle; training plans keep everything)"""
+        if t is not None:
+            self.pool.release(t)
+            self.pool.release(getattr(t, "bf16_copy", None))
+
+    def _cast_copy(self, ops, t, rows):
+        """bf16 mode: dense bf16 copy of a [rows, 128] fp32 activation whose producer cannot dual-write"""
+        t.bf16_copy = self._get_bf(self.pool, rows, 128)
+        ops.append(Op("b200_cast_bf16", lib.CastArgs(src=_p(t), dst=_p(t.bf16_copy), rows=rows, cols=128, src_ld=0)))
 
     def _dgrad(self, dy, wname, out, H, R, pad, w_cin, n_off, out_ld, residual=None, res_ld=0, bf=False):
         """dy: _Grad with 128 channels; writes 128 input channels [n_off, n_off+128) of `out`.
@@ -255,17 +269,24 @@ class UNetPlan:
         ops.append(Op("b200_gn_fwd", g2))
         pool.release(h1)
         skip = None
+        x_bf = x2_bf = None
         if x2 is not None:
             skip = pool.get(B, HW, 128)
-            ops.append(self._conv(x, x2, name + ".skip_connection", skip, H, H, 1, 1, 0, 128, 128))
+            if bf:  # the 1x1 skip conv reads the bf16 copies of the running tensor and of the cached Down tensor
+                x_bf, x2_bf = x.bf16_copy, x2.bf16_copy
+                ops.append(self._conv(x_bf, x2_bf, name + ".skip_connection", skip, H, H, 1, 1, 0, 128, 128, bf=True))
+            else:
+                ops.append(self._conv(x, x2, name + ".skip_connection", skip, H, H, 1, 1, 0, 128, 128))
             residual = skip
         else:
             residual = x
         out = pool.get(B, HW, 128)
-        ops.append(self._conv(a2, None, name + ".out_layers.3", out, H, H, 3, 1, 1, 128, 0, residual=_p(residual), bf=bf))
+        out_bf = self._get_bf(pool, B, HW, 128) if bf else None
+        ops.append(self._conv(a2, None, name + ".out_layers.3", out, H, H, 3, 1, 1, 128, 0, residual=_p(residual), bf=bf,
+                              out_bf=out_bf))
         pool.release(a2)
         pool.release(skip)
-        self.records[name] = dict(x=x, x2=x2, H=H, a1=a1, h1=h1, a2=a2, g1=g1, g2=g2, k=k)
+        self.records[name] = dict(x=x, x2=x2, H=H, a1=a1, h1=h1, a2=a2, g1=g1, g2=g2, k=k, x_bf=x_bf, x2_bf=x2_bf)
         return out
 
     def _build_forward(self):
@@ -289,43 +310,56 @@ class UNetPlan:
         cin = lib.ConvInArgs(x=_p(self.z_in), w=self._w("down.seq.0.conv.weight"), bias=self._w("down.seq.0.conv.bias"),
                              out=_p(d0), dy=None, dw=None, db=None, N=B, H=H0, W=H0, round_out=1)
         ops.append(Op("b200_conv_in_fwd", cin))
+        bf = self.bf16
+        if bf:
+            self._cast_copy(ops, d0, B * H0 * H0)
         d1 = self._rb_fwd(ops, "down.seq.1", d0, None, H0)
         d2 = self._rb_fwd(ops, "down.seq.2", d1, None, H0)
         d3 = pool.get(B, H1 * H1, 128)
         ops.append(self._conv(d2, None, "down.seq.3.conv", d3, H0, H1, 3, 2, 1, 128, 0))
+        if bf:
+            self._cast_copy(ops, d3, B * H1 * H1)
         d4 = self._rb_fwd(ops, "down.seq.4", d3, None, H1)
         d5 = self._rb_fwd(ops, "down.seq.5", d4, None, H1)
         d6 = pool.get(B, H2 * H2, 128)
         ops.append(self._conv(d5, None, "down.seq.6.conv", d6, H1, H2, 3, 2, 1, 128, 0))
+        if bf:
+            self._cast_copy(ops, d6, B * H2 * H2)
         # ---- turn (simple_unet.py:36,68)
         t = self._rb_fwd(ops, "turn", d6, None, H2)
         # ---- Up (simple_unet.py:125-152): block i consumes cat([h, cache.pop()])
         r0 = self._rb_fwd(ops, "up.seq.0.0", t, d6, H2)
-        pool.release(t), pool.release(d6)
-        up0 = pool.get(B, H1 * H1, 128)
-        ops.append(Op("b200_upsample2x", lib.ResampleArgs(in_=_p(r0), out=_p(up0), N=B, H=H2, W=H2, C=128, in_ld=0, mode=0)))
-        pool.release(r0)
+        self._rel(t), self._rel(d6)
+        # nearest 2x upsample feeds only the following conv (fprop + wgrad): in bf16 mode it is written as bf16
+        up0 = self._get_bf(pool, B, H1 * H1, 128) if bf else pool.get(B, H1 * H1, 128)
+        ops.append(Op("b200_upsample2x", lib.ResampleArgs(in_=_p(r0), out=_p(up0), N=B, H=H2, W=H2, C=128, in_ld=0, mode=0,
+                                                          out_dtype=1 if bf else 0)))
+        self._rel(r0)
         u0 = pool.get(B, H1 * H1, 128)
-        ops.append(self._conv(up0, None, "up.seq.0.1.conv", u0, H1, H1, 3, 1, 1, 128, 0))
+        ops.append(self._conv(up0, None, "up.seq.0.1.conv", u0, H1, H1, 3, 1, 1, 128, 0, bf=bf,
+                              out_bf=self._get_bf(pool, B, H1 * H1, 128) if bf else None))
         pool.release(up0)
         u1 = self._rb_fwd(ops, "up.seq.1", u0, d5, H1)
-        pool.release(u0), pool.release(d5)
+        self._rel(u0), self._rel(d5)
         u2 = self._rb_fwd(ops, "up.seq.2", u1, d4, H1)
-        pool.release(u1), pool.release(d4)
+        self._rel(u1), self._rel(d4)
         r3 = self._rb_fwd(ops, "up.seq.3.0", u2, d3, H1)
-        pool.release(u2), pool.release(d3)
-        up3 = pool.get(B, H0 * H0, 128)
-        ops.append(Op("b200_upsample2x", lib.ResampleArgs(in_=_p(r3), out=_p(up3), N=B, H=H1, W=H1, C=128, in_ld=0, mode=0)))
-        pool.release(r3)
+        self._rel(u2), self._rel(d3)
+        # nearest 2x upsample feeds only the following conv (fprop + wgrad): in bf16 mode it is written as bf16
+        up3 = self._get_bf(pool, B, H0 * H0, 128) if bf else pool.get(B, H0 * H0, 128)
+        ops.append(Op("b200_upsample2x", lib.ResampleArgs(in_=_p(r3), out=_p(up3), N=B, H=H1, W=H1, C=128, in_ld=0, mode=0,
+                                                          out_dtype=1 if bf else 0)))
+        self._rel(r3)
         u3 = pool.get(B, H0 * H0, 128)
-        ops.append(self._conv(up3, None, "up.seq.3.1.conv", u3, H0, H0, 3, 1, 1, 128, 0))
+        ops.append(self._conv(up3, None, "up.seq.3.1.conv", u3, H0, H0, 3, 1, 1, 128, 0, bf=bf,
+                              out_bf=self._get_bf(pool, B, H0 * H0, 128) if bf else None))
         pool.release(up3)
         u4 = self._rb_fwd(ops, "up.seq.4", u3, d2, H0)
-        pool.release(u3), pool.release(d2)
+        self._rel(u3), self._rel(d2)
         u5 = self._rb_fwd(ops, "up.seq.5", u4, d1, H0)
-        pool.release(u4), pool.release(d1)
+        self._rel(u4), self._rel(d1)
         u6 = self._rb_fwd(ops, "up.seq.6", u5, d0, H0)
-        pool.release(u5), pool.release(d0)
+        self._rel(u5), self._rel(d0)
         # ---- out head (simple_unet.py:38-42,70)
         sth = self._next_stats()
         ah = pool.get(B, H0 * H0, 128)
@@ -409,8 +443,11 @@ class UNetPlan:
         if has_skip:
             dsk = gp.get(B, HW, 256)
             for n_off in (0, 128):
-                ops.append(self._dgrad(dOut, name + ".skip_connection", dsk, H, 1, 0, 256, n_off, 256))
-            ops.append(self._wgrad(x, x2, dOut, name + ".skip_connection", H, H, 1, 1, 0, 128, 128))
+                ops.append(self._dgrad(dOut, name + ".skip_connection", dsk, H, 1, 0, 256, n_off, 256, bf=bf))
+            if bf:
+                ops.append(self._wgrad(r["x_bf"], r["x2_bf"], dOut, name + ".skip_connection", H, H, 1, 1, 0, 128, 128, bf=True))
+            else:
+                ops.append(self._wgrad(x, x2, dOut, name + ".skip_connection", H, H, 1, 1, 0, 128, 128))
             add1, add_c = _Grad(dsk), 256
         else:
             add1, add_c = dOut, 128
@@ -427,8 +464,11 @@ class UNetPlan:
         Returns the dense input gradient (+ residual: another _Grad flowing into the same tensor)."""
         B = self.B
         gp = self.gpool
+        bf = self.bf16 and stride == 1  # the Upsample convs (x is the bf16 upsampled tensor); Downsample convs stay TF32
+        if bf:
+            self._ensure_bf(ops, dy, Ho * Ho)
         self._colsum(ops, dy, Ho * Ho, total1=self._g(name + ".bias"))
-        ops.append(self._wgrad(x, None, dy, name, H, Ho, 3, stride, 1, 128, 0))
+        ops.append(self._wgrad(x, None, dy, name, H, Ho, 3, stride, 1, 128, 0, bf=bf))
         src, zs = dy, None
         if stride == 2:
             # zero-stuff dY to the input resolution so the stride-1 dgrad kernel applies
@@ -438,7 +478,7 @@ class UNetPlan:
             src = _Grad(zs)
         dx = gp.get(B, H * H, 128)
         ops.append(self._dgrad(src, name, dx, H, 3, 1, 128, 0, 128,
-                               residual=residual.ptr() if residual else None, res_ld=residual.ld if residual else 0))
+                               residual=residual.ptr() if residual else None, res_ld=residual.ld if residual else 0, bf=bf))
         if stride == 2:
             ops[-1].alg_scale = 0.25  # 3/4 of the zero-stuffed rows are zeros
         gp.release(zs)

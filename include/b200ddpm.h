@@ -68,6 +68,9 @@ typedef struct {
    * with fp32 accumulation (stride-1 3x3/pad-1 and 1x1/pad-0 layers only; C1, C2 multiples of 64; x_ld in elements).
    * out / bias / emb / residual are fp32 either way. */
   int op_dtype;
+  /* optional second output: dense bf16 copy [M][128] of what is stored to out (the operand a following bf16
+   * convolution reads); fprop only */
+  void* out_bf16;
 } b200_conv_args;
 int b200_conv_igemm(const b200_conv_args* a, void* ws, size_t ws_bytes, void* stream);
 /* which kernel b200_conv_igemm launches for these arguments: 1 = conv_strip_tf32_kernel (strip implicit GEMM, stride-1
@@ -239,11 +242,12 @@ int b200_conv_out_bwd(const b200_conv_out_args* a, void* ws, size_t ws_bytes, vo
  *                    even pixels (turns the stride-2 Downsample dgrad into a stride-1 one). */
 typedef struct {
   const float* in;
-  float* out;
+  void* out;
   int N, H, W, C;
   int in_ld;
   int mode;
   int round_out; /* mode 1: store the summed gradient rounded to TF32 */
+  int out_dtype; /* mode 0: 0 = fp32, 1 = write bf16 (the operand of a bf16 convolution) */
 } b200_resample_args;
 int b200_upsample2x(const b200_resample_args* a, void* ws, size_t ws_bytes, void* stream);
 
