@@ -18,10 +18,12 @@ def main():
     ap.add_argument("--batch", type=int, default=512)
     ap.add_argument("--warm", type=int, default=2)
     ap.add_argument("--no-sample", action="store_true")
+    ap.add_argument("--precision", default="tf32", choices=["tf32", "bf16"])
     a = ap.parse_args()
     dev = "cuda:0"
     torch.manual_seed(0)
-    m = DiffusionModelB200(default_G(device=dev, mean_type="eps", sampler="noisy", timesteps=1000, graph=0))
+    m = DiffusionModelB200(default_G(device=dev, mean_type="eps", sampler="noisy", timesteps=1000, graph=0,
+                                     precision=a.precision))
     gen = torch.Generator().manual_seed(1)
     for k, p in m.net.named_parameters():
         if ".out_layers.3." in k:
