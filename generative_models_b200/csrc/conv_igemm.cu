@@ -246,6 +246,7 @@ extern "C" int b200_conv_igemm(const b200_conv_args* a, void* ws, size_t ws_byte
     if (rs != -100) return rs;
   }
   if (a->skip_x) return fail_arg("conv_igemm: the fused skip segment needs a stride-1 3x3/pad-1 or 1x1/pad-0 layer");
+  if (a->out_dtype != 0) return fail_arg("conv_igemm: a bf16 out needs a stride-1 3x3/pad-1 or 1x1/pad-0 layer (strip kernel)");
   if (a->out_bf16) return fail_arg("conv_igemm: out_bf16 needs a stride-1 3x3/pad-1 or 1x1/pad-0 layer (strip kernel)");
   if (a->op_dtype != 0) return fail_arg("conv_igemm: bf16 operands need a stride-1 3x3/pad-1 or 1x1/pad-0 layer (strip kernel)");
   CUtensorMap tmA, tmA2, tmB;
@@ -262,7 +263,7 @@ extern "C" int b200_conv_igemm(const b200_conv_args* a, void* ws, size_t ws_byte
   if (r) return r;
 
   ConvK k;
-  k.out = a->out;
+  k.out = static_cast<float*>(a->out);
   k.bias = a->bias;
   k.emb = a->emb;
   k.residual = a->residual;

@@ -41,6 +41,7 @@ constexpr int kStripSmem = kSS * kStripBytes + kSB * kBTile + 1024 + 256 + 2 * 5
 struct StripK {
   float* out;
   uint16_t* out_bf;  // optional dense bf16 copy [M][128] of out
+  int out_is_bf;     // out itself holds bf16
   const float* bias;
   const float* bias2;
   const float* emb;
@@ -332,12 +333,31 @@ conv_strip_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
           }
         }
         tmem_ld_wait();
+        if (!a.out_is_bf) {
 #pragma unroll
-        for (int j = 0; j < 32; ++j) {
-          if (mm[j] >= 0) {
-            const float v = __uint_as_float(r[j]) + add[j];
-            a.out[static_cast<size_t>(mm[j]) * a.out_ld + co] = a.round_out ? round_tf32(v) : v;
-            if (a.out_bf) a.out_bf[static_cast<size_t>(mm[j]) * 128 + co] = bf16_bits(v);
+          for (int j = 0; j < 32; ++j) {
+            if (mm[j] >= 0) {
+              const float v = __uint_as_float(r[j]) + add[j];
+              a.out[static_cast<size_t>(mm[j]) * a.out_ld + co] = a.round_out ? round_tf32(v) : v;
+            }
+          }
+        }
+        uint16_t* ob = a.out_is_bf ? reinterpret_cast<uint16_t*>(a.out) : a.out_bf;
+        if (ob) {
+          // bf16 stores: neighbouring lanes (channels c, c+1) trade one value per position pair so that every lane
+          // stores a 4 B word {c, c+1} — even lanes for position j, odd lanes for j+1 — instead of 2 B per lane:
+          // half the store instructions, whole 32 B sectors per pixel
+          const int obld = a.out_is_bf ? a.out_ld : 128;
+          const int odd = lane & 1;
+#pragma unroll
+          for (int j = 0; j < 32; j += 2) {
+            const float v0 = __uint_as_float(r[j]) + add[j], v1 = __uint_as_float(r[j + 1]) + add[j + 1];
+            const float got = __shfl_xor_sync(0xffffffffu, odd ? v0 : v1, 1);
+            const float lo = odd ? got : v0, hi = odd ? v1 : got;
+            uint32_t wrd;
+            asm("cvt.rn.bf16x2.f32 %0, %1, %2;" : "=r"(wrd) : "f"(hi), "f"(lo));
+            const int m = odd ? mm[j + 1] : mm[j];
+            if (m >= 0) *reinterpret_cast<uint32_t*>(ob + static_cast<size_t>(m) * obld + (co & ~1)) = wrd;
           }
         }
       }
@@ -439,7 +459,8 @@ int conv_strip_launch(const b200_conv_args* a, void* stream) {
   }
 
   StripK k;
-  k.out = a->out;
+  k.out = static_cast<float*>(a->out);
+  k.out_is_bf = a->out_dtype == 1;
   k.out_bf = static_cast<uint16_t*>(a->out_bf16);
   k.bias = a->bias;
   k.bias2 = a->bias2;

@@ -32,6 +32,7 @@ struct GnSrc {
   const float* x2;
   int ld1, ld2;
   int N, HW, C1, C;  // C = C1 + C2
+  int bf;            // x / x2 hold bf16 (ld in elements); fused kernels only
 };
 
 __device__ __forceinline__ float4 ld_src(const GnSrc& s, size_t pix, int c) {
@@ -50,6 +51,16 @@ __device__ __forceinline__ float dsilu_f(float u) {
 __device__ __forceinline__ void cp_async16(void* smem_dst, const void* gsrc) {
   asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(
                    static_cast<uint32_t>(__cvta_generic_to_shared(smem_dst))), "l"(gsrc) : "memory");
+}
+__device__ __forceinline__ void cp_async8(void* smem_dst, const void* gsrc) {
+  asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(
+                   static_cast<uint32_t>(__cvta_generic_to_shared(smem_dst))), "l"(gsrc) : "memory");
+}
+// a 16 B smem slot whose first 8 bytes hold 4 bf16 (as cp_async8 left them) -> 4 floats
+__device__ __forceinline__ float4 slot_bf16(const float4* slot) {
+  const uint2 r = *reinterpret_cast<const uint2*>(slot);
+  return make_float4(__uint_as_float(r.x << 16), __uint_as_float(r.x & 0xffff0000u), __uint_as_float(r.y << 16),
+                     __uint_as_float(r.y & 0xffff0000u));
 }
 __device__ __forceinline__ void cp_async_wait_all() {
   asm volatile("cp.async.commit_group;\n\tcp.async.wait_group 0;" ::: "memory");
@@ -93,18 +104,32 @@ gn_fwd_fused_kernel(GnSrc s, float* __restrict__ stats, const float* __restrict_
     src = s.x2 + (c - s.C1);
     ld = s.ld2;
   }
-  src += static_cast<size_t>(n) * s.HW * ld;
   if (tid < 16) red[tid] = 0.f;
-  for (int idx = tid; idx < total; idx += kGnThreads) cp_async16(&gn_smem[idx], src + static_cast<size_t>(idx / L) * ld);
+  if (s.bf) {  // bf16 source: 8 B per lane into the first half of each 16 B slot, widened in place by the first pass
+    const uint16_t* sb = reinterpret_cast<const uint16_t*>(c < s.C1 ? s.x : s.x2) + (c < s.C1 ? c : c - s.C1) +
+                         static_cast<size_t>(n) * s.HW * ld;
+    for (int idx = tid; idx < total; idx += kGnThreads) cp_async8(&gn_smem[idx], sb + static_cast<size_t>(idx / L) * ld);
+  } else {
+    src += static_cast<size_t>(n) * s.HW * ld;
+    for (int idx = tid; idx < total; idx += kGnThreads) cp_async16(&gn_smem[idx], src + static_cast<size_t>(idx / L) * ld);
+  }
   cp_async_wait_all();
   __syncthreads();
   const bool pair = (cpg == 8);
   const bool leader = (lane < L) && (!pair || !(lane & 1));
   const float inv_cnt = 1.0f / static_cast<float>(s.HW * cpg);
   float sum = 0.f;
-  for (int idx = tid; idx < total; idx += kGnThreads) {
-    const float4 v = gn_smem[idx];
-    sum += (v.x + v.y) + (v.z + v.w);
+  if (s.bf) {
+    for (int idx = tid; idx < total; idx += kGnThreads) {  // own slots only: no sync needed before the next pass
+      const float4 v = slot_bf16(&gn_smem[idx]);
+      gn_smem[idx] = v;
+      sum += (v.x + v.y) + (v.z + v.w);
+    }
+  } else {
+    for (int idx = tid; idx < total; idx += kGnThreads) {
+      const float4 v = gn_smem[idx];
+      sum += (v.x + v.y) + (v.z + v.w);
+    }
   }
   sum = lane_group_sum<L>(sum, pair);
   if (leader) atomicAdd(&red[gl], sum);
@@ -160,7 +185,7 @@ gn_bwd_fused_kernel(GnSrc s, const float* __restrict__ stats, const float* __res
                     const float* __restrict__ beta, const float* __restrict__ dy, float* __restrict__ dx,
                     const float* __restrict__ add1, int add1_ld, const float* __restrict__ add2, int add2_ld, int add_c,
                     float* __restrict__ dgamma, float* __restrict__ dbeta, int silu, int round_dx,
-                    uint16_t* __restrict__ dxb, int dxb_c, GnColsum cs) {
+                    uint16_t* __restrict__ dxb, int dxb_c, GnColsum cs, int dy_bf) {
   extern __shared__ float4 gn_smem[];
   __shared__ float red[16];
   __shared__ float chan[2 * CS];
@@ -193,10 +218,16 @@ gn_bwd_fused_kernel(GnSrc s, const float* __restrict__ stats, const float* __res
   if (tid < 16) red[tid] = 0.f;
   if (tid < 2 * CS) chan[tid] = 0.f;
   if (tid < CS) csum[tid] = 0.f;
+  // bf16 sources (s.bf for x, dy_bf for dy): 8 B per lane into the first half of the 16 B slot, widened by phase 1
+  const uint16_t* srcb = reinterpret_cast<const uint16_t*>(c < s.C1 ? s.x : s.x2) + (c < s.C1 ? c : c - s.C1) +
+                         static_cast<size_t>(n) * s.HW * ld;
+  const uint16_t* dsrcb = reinterpret_cast<const uint16_t*>(dy) + row0 * s.C + c;
   for (int idx = tid; idx < total; idx += kGnThreads) {
     const size_t pix = idx / L;
-    cp_async16(&xs[idx], src + pix * ld);
-    cp_async16(&ds[idx], dsrc + pix * s.C);
+    if (s.bf) cp_async8(&xs[idx], srcb + pix * ld);
+    else cp_async16(&xs[idx], src + pix * ld);
+    if (dy_bf) cp_async8(&ds[idx], dsrcb + pix * s.C);
+    else cp_async16(&ds[idx], dsrc + pix * s.C);
   }
   cp_async_wait_all();
   __syncthreads();
@@ -209,8 +240,8 @@ gn_bwd_fused_kernel(GnSrc s, const float* __restrict__ stats, const float* __res
   float dg[4] = {0.f, 0.f, 0.f, 0.f}, db[4] = {0.f, 0.f, 0.f, 0.f};
   float s1 = 0.f, s2 = 0.f;
   for (int idx = tid; idx < total; idx += kGnThreads) {
-    const float4 v = xs[idx];
-    const float4 d = ds[idx];
+    const float4 v = s.bf ? slot_bf16(&xs[idx]) : xs[idx];
+    const float4 d = dy_bf ? slot_bf16(&ds[idx]) : ds[idx];
     const float xv[4] = {v.x, v.y, v.z, v.w};
     const float dv[4] = {d.x, d.y, d.z, d.w};
     float xh[4], du[4];
@@ -276,7 +307,7 @@ gn_bwd_fused_kernel(GnSrc s, const float* __restrict__ stats, const float* __res
     }
     if (dstb) *reinterpret_cast<uint2*>(dstb + pix * dxb_c) = pack_bf16x4(o);
     if (round_dx) o = round_tf32(o);
-    *reinterpret_cast<float4*>(dst + pix * s.C) = o;
+    if (dx) *reinterpret_cast<float4*>(dst + pix * s.C) = o;  // dx may be NULL when only the bf16 copy is wanted
     cacc.x += o.x; cacc.y += o.y; cacc.z += o.z; cacc.w += o.w;
   }
   // fused column sums of dx (bias gradient of the convolution that produced x, and the per-sample gradient of the
@@ -519,6 +550,8 @@ static int gn_src(const b200_gn_args* a, GnSrc* s) {
   s->HW = a->HW;
   s->C1 = a->C1;
   s->C = C;
+  if (a->x_dtype != 0 && a->x_dtype != 1) return fail_arg("gn: x_dtype must be 0 (fp32) or 1 (bf16)");
+  s->bf = a->x_dtype;
   return 0;
 }
 
@@ -597,6 +630,7 @@ extern "C" int b200_gn_fwd(const b200_gn_args* a, void* ws, size_t ws_bytes, voi
 #undef GN_FWD
     return after_launch("gn_fwd_fused_kernel");
   }
+  if (s.bf) return fail_arg("gn_fwd: a bf16 input needs the shared-memory-resident kernel (HW too large)");
   if (int r = check_cuda(cudaMemsetAsync(a->stats, 0, static_cast<size_t>(s.N) * 64 * sizeof(float), st), "gn_fwd memset")) return r;
   const int chunks = gn_chunks(s.N, s.HW);
   const int ppc = (s.HW + chunks - 1) / chunks;
@@ -614,7 +648,9 @@ extern "C" int b200_gn_bwd(const b200_gn_bwd_args* b, void* ws, size_t ws_bytes,
   if (!b) return fail_arg("gn_bwd: null args");
   GnSrc s;
   if (int r = gn_src(&b->fwd, &s)) return r;
-  if (!b->dy || !b->dx || !b->dgamma || !b->dbeta) return fail_arg("gn_bwd: null pointer");
+  if (!b->dy || !b->dgamma || !b->dbeta) return fail_arg("gn_bwd: null pointer");
+  if (!b->dx && !b->dx_bf16) return fail_arg("gn_bwd: neither dx nor dx_bf16 given");
+  if (b->dy_dtype != 0 && b->dy_dtype != 1) return fail_arg("gn_bwd: dy_dtype must be 0 (fp32) or 1 (bf16)");
   if (int r = gn_init()) return r;
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   const int add_c = b->add_c ? b->add_c : s.C;
@@ -634,7 +670,7 @@ extern "C" int b200_gn_bwd(const b200_gn_bwd_args* b, void* ws, size_t ws_bytes,
 #define GN_BWD(CS, TH)                                                                                                  \
   gn_bwd_fused_kernel<CS, TH><<<grid, TH, smem, st>>>(s, b->fwd.stats, b->fwd.gamma, b->fwd.beta, b->dy, b->dx, b->add1, \
                                                       b->add1_ld, b->add2, b->add2_ld, add_c, b->dgamma, b->dbeta,       \
-                                                      b->fwd.silu, b->round_dx, dxb, dxb_c, csm)
+                                                      b->fwd.silu, b->round_dx, dxb, dxb_c, csm, b->dy_dtype)
     if (cs == 8) GN_BWD(8, 256);
     else if (cs == 32 && th == 256) GN_BWD(32, 256);
     else if (cs == 32) GN_BWD(32, 512);
@@ -643,6 +679,8 @@ extern "C" int b200_gn_bwd(const b200_gn_bwd_args* b, void* ws, size_t ws_bytes,
 #undef GN_BWD
     return after_launch("gn_bwd_fused_kernel");
   }
+  if (s.bf || b->dy_dtype || !b->dx)
+    return fail_arg("gn_bwd: bf16 inputs / a bf16-only dx need the shared-memory-resident kernel (HW too large)");
   const size_t need = static_cast<size_t>(s.N) * 64 * sizeof(float);
   if (!ws || ws_bytes < need) return fail_arg("gn_bwd: workspace of N*64 floats required for the streaming path");
   float* red = static_cast<float*>(ws);

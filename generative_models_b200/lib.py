@@ -21,7 +21,7 @@ class ConvArgs(C.Structure):
         ("R", C.c_int), ("S", C.c_int), ("stride", C.c_int), ("pad", C.c_int),
         ("mode", C.c_int), ("w_cout", C.c_int), ("w_cin", C.c_int), ("n_off", C.c_int),
         ("out_ld", C.c_int), ("emb_ld", C.c_int), ("res_ld", C.c_int),
-        ("x_ld", C.c_int), ("x2_ld", C.c_int), ("round_out", C.c_int),
+        ("x_ld", C.c_int), ("x2_ld", C.c_int), ("round_out", C.c_int), ("out_dtype", C.c_int),
         ("skip_x", _f32p), ("skip_x2", _f32p), ("skip_w", _f32p), ("bias2", _f32p),
         ("skip_c1", C.c_int), ("skip_c2", C.c_int), ("skip_x_ld", C.c_int), ("skip_x2_ld", C.c_int),
         ("op_dtype", C.c_int), ("out_bf16", _f32p),
@@ -43,7 +43,7 @@ class GnArgs(C.Structure):
         ("x", _f32p), ("x2", _f32p), ("stats", _f32p), ("gamma", _f32p), ("beta", _f32p), ("y", _f32p),
         ("N", C.c_int), ("HW", C.c_int), ("C1", C.c_int), ("C2", C.c_int),
         ("x_ld", C.c_int), ("x2_ld", C.c_int),
-        ("eps", C.c_float), ("silu", C.c_int), ("round_tf32", C.c_int), ("y_dtype", C.c_int),
+        ("eps", C.c_float), ("silu", C.c_int), ("round_tf32", C.c_int), ("y_dtype", C.c_int), ("x_dtype", C.c_int),
     ]
 
 
@@ -53,7 +53,7 @@ class GnBwdArgs(C.Structure):
         ("add1_ld", C.c_int), ("add2_ld", C.c_int), ("add_c", C.c_int),
         ("dgamma", _f32p), ("dbeta", _f32p), ("round_dx", C.c_int), ("dx_bf16", _f32p), ("dx_bf16_c", C.c_int),
         ("colsum_per_sample", _f32p), ("colsum_ps_ld", C.c_int), ("colsum_total1", _f32p), ("colsum_total2", _f32p),
-        ("colsum_c", C.c_int),
+        ("colsum_c", C.c_int), ("dy_dtype", C.c_int),
     ]
 
 

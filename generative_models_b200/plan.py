@@ -106,6 +106,10 @@ class UNetPlan:
         assert S % 4 == 0, "image side must be divisible by 4 (two stride-2 levels)"
         self.bf16 = bool(bf16)
         self.fuse_colsum = True
+        # bf16 STORAGE of the tensors only GroupNorm reads (h1, the dgrad outputs): kernels and tests exist, but the
+        # narrower accesses (8 B cp.async in GroupNorm) measured slower than the bytes they save; off by default
+        import os
+        self.bfs = self.bf16 and os.environ.get("B200_BF16_STORE", "0") == "1"
         if self.bf16:
             store.ensure_bf16()
         self.store = store
@@ -166,7 +170,7 @@ class UNetPlan:
         return s
 
     def _conv(self, x, x2, wname, out, H, Ho, R, stride, pad, C1, C2, bias=True, emb=None, residual=None,
-              res_ld=128, x_ld=0, x2_ld=0, round_out=1, bf=False, out_bf=None):
+              res_ld=128, x_ld=0, x2_ld=0, round_out=1, bf=False, out_bf=None, out_dtype=0):
         if out_bf is not None:
             out.bf16_copy = out_bf
         a = lib.ConvArgs(x=_p(x), x2=_p(x2), w=(self._wbf if bf else self._wtc)(wname + ".weight"), out=_p(out),
@@ -174,7 +178,7 @@ class UNetPlan:
                          residual=residual, N=self.B, H=H, W=H, C1=C1, C2=C2, Ho=Ho, Wo=Ho, R=R, S=R, stride=stride,
                          pad=pad, mode=0, w_cout=128, w_cin=C1 + C2, n_off=0, out_ld=128, emb_ld=12 * self.Cc,
                          res_ld=res_ld, x_ld=x_ld, x2_ld=x2_ld, round_out=round_out, op_dtype=1 if bf else 0,
-                         out_bf16=_p(out_bf))
+                         out_bf16=_p(out_bf), out_dtype=out_dtype)
         return Op("b200_conv_igemm", a)
 
     def _rel(self, t):
@@ -188,14 +192,14 @@ class UNetPlan:
         t.bf16_copy = self._get_bf(self.pool, rows, 128)
         ops.append(Op("b200_cast_bf16", lib.CastArgs(src=_p(t), dst=_p(t.bf16_copy), rows=rows, cols=128, src_ld=0)))
 
-    def _dgrad(self, dy, wname, out, H, R, pad, w_cin, n_off, out_ld, residual=None, res_ld=0, bf=False):
+    def _dgrad(self, dy, wname, out, H, R, pad, w_cin, n_off, out_ld, residual=None, res_ld=0, bf=False, out_dtype=0):
         """dy: _Grad with 128 channels; writes 128 input channels [n_off, n_off+128) of `out`.
         bf: read the dense bf16 copy dy.bf and the bf16 weight shadow."""
         a = lib.ConvArgs(x=_p(dy.bf) if bf else dy.ptr(), x2=None, w=(self._wbf if bf else self._wtc)(wname + ".weight"),
-                         out=_p(out, n_off), bias=None, emb=None,
+                         out=C.c_void_p(out.data_ptr() + 2 * n_off) if out_dtype else _p(out, n_off), bias=None, emb=None,
                          residual=residual, N=self.B, H=H, W=H, C1=128, C2=0, Ho=H, Wo=H, R=R, S=R, stride=1, pad=pad,
                          mode=1, w_cout=128, w_cin=w_cin, n_off=n_off, out_ld=out_ld, emb_ld=0, res_ld=res_ld,
-                         x_ld=128 if bf else dy.ld, x2_ld=0, round_out=1, op_dtype=1 if bf else 0)
+                         x_ld=128 if bf else dy.ld, x2_ld=0, round_out=1, op_dtype=1 if bf else 0, out_dtype=out_dtype)
         return Op("b200_conv_igemm", a)
 
     def _wgrad(self, x, x2, dy, wname, H, Ho, R, stride, pad, C1, C2, bf=False):
@@ -204,10 +208,10 @@ class UNetPlan:
                           x2_ld=0, dy_ld=128 if bf else dy.ld, op_dtype=1 if bf else 0)
         return Op("b200_conv_wgrad", a)
 
-    def _gn(self, x, x2, gname, y, HW, C2, stats, silu=1, tf32=1, bf=False):
+    def _gn(self, x, x2, gname, y, HW, C2, stats, silu=1, tf32=1, bf=False, x_bf=False):
         return lib.GnArgs(x=_p(x), x2=_p(x2), stats=_p(stats), gamma=self._w(gname + ".weight"),
                           beta=self._w(gname + ".bias"), y=_p(y), N=self.B, HW=HW, C1=128, C2=C2, x_ld=0, x2_ld=0,
-                          eps=GN_EPS, silu=silu, round_tf32=tf32, y_dtype=1 if bf else 0)
+                          eps=GN_EPS, silu=silu, round_tf32=tf32, y_dtype=1 if bf else 0, x_dtype=1 if x_bf else 0)
 
     def _ensure_bf(self, ops, g, HW):
         """bf16 mode: make sure the 128-channel gradient slice `g` has its dense bf16 copy (producers that are not a
@@ -259,13 +263,15 @@ class UNetPlan:
         a1 = self._get_bf(pool, B, HW, Cin) if bf else pool.get(B, HW, Cin)
         g1 = self._gn(x, x2, name + ".in_layers.0", a1, HW, C2, st1, bf=bf)
         ops.append(Op("b200_gn_fwd", g1))
-        h1 = pool.get(B, HW, 128)
-        # h1 feeds only the GroupNorm (never a tensor-core operand), so it keeps its full fp32 mantissa
+        # h1 feeds only the GroupNorm (never a tensor-core operand): full fp32 mantissa in tf32 mode, bf16 storage in
+        # bf16 mode (like the reference's autocast conv output)
+        bfs = self.bfs
+        h1 = self._get_bf(pool, B, HW, 128) if bfs else pool.get(B, HW, 128)
         ops.append(self._conv(a1, None, name + ".in_layers.2", h1, H, H, 3, 1, 1, Cin, 0,
-                              emb=_p(self.embout, k * 128), round_out=0, bf=bf))
+                              emb=_p(self.embout, k * 128), round_out=0, bf=bf, out_dtype=1 if bfs else 0))
         pool.release(a1)
         a2 = self._get_bf(pool, B, HW, 128) if bf else pool.get(B, HW, 128)
-        g2 = self._gn(h1, None, name + ".out_layers.0", a2, HW, 0, st2, bf=bf)
+        g2 = self._gn(h1, None, name + ".out_layers.0", a2, HW, 0, st2, bf=bf, x_bf=bfs)
         ops.append(Op("b200_gn_fwd", g2))
         pool.release(h1)
         skip = None
@@ -384,14 +390,17 @@ class UNetPlan:
         run_ops(self.head_ops[1 if to_out2 else 0:][:1], stream_ptr)
 
     # ------------------------------------------------------------------ backward
-    def _gn_bwd(self, ops, g_fwd, dy, dx, gname, add1=None, add2=None, add_c=0, dx_bf=None):
+    def _gn_bwd(self, ops, g_fwd, dy, dx, gname, add1=None, add2=None, add_c=0, dx_bf=None, dy_bf=False):
         """dx_bf: storage for the bf16 copy of dx[:, :128] (bf16 mode: the dY operand of the conv that produced x)."""
         a = lib.GnBwdArgs(fwd=g_fwd, dy=_p(dy), dx=_p(dx), add1=add1.ptr() if add1 else None,
                           add2=add2.ptr() if add2 else None, add1_ld=add1.ld if add1 else 0,
                           add2_ld=add2.ld if add2 else 0, add_c=add_c, dgamma=self._g(gname + ".weight"),
                           dbeta=self._g(gname + ".bias"), round_dx=1, dx_bf16=_p(dx_bf),
-                          dx_bf16_c=128 if dx_bf is not None else 0)
+                          dx_bf16_c=128 if dx_bf is not None else 0, dy_dtype=1 if dy_bf else 0)
         ops.append(Op("b200_gn_bwd", a, ws=self.gn_ws))
+        if dx is None:  # bf16-only output
+            dx_bf.producer_gn = a
+            return
         dx.producer_gn = a
         if dx_bf is not None:
             dx.bf16_copy = dx_bf
@@ -402,6 +411,7 @@ class UNetPlan:
             g.colsum_per_sample, g.colsum_ps_ld, g.colsum_total1, g.colsum_total2 = per_sample, ps_ld, total1, total2
             g.colsum_c = 128
             return
+        assert dy.t is not dy.bf, "a bf16-only gradient has no fp32 tensor for the stand-alone colsum kernel"
         a = lib.ColsumArgs(dy=dy.ptr(), per_sample=per_sample, total1=total1, total2=total2, N=self.B, HW=HW, ld=dy.ld,
                            ps_ld=ps_ld)
         ops.append(Op("b200_colsum", a))
@@ -423,20 +433,24 @@ class UNetPlan:
         self._colsum(ops, dOut, HW, total1=self._g(name + ".out_layers.3.bias"),
                      total2=self._g(name + ".skip_connection.bias") if has_skip else None)
         ops.append(self._wgrad(r["a2"], None, dOut, name + ".out_layers.3", H, H, 3, 1, 1, 128, 0, bf=bf))
-        da2 = gp.get(B, HW, 128)
-        ops.append(self._dgrad(dOut, name + ".out_layers.3", da2, H, 3, 1, 128, 0, 128, bf=bf))
-        dh1 = gp.get(B, HW, 128)
+        # bf16 mode: the dgrad outputs (read only by the GroupNorm backward) and dh1 (read only by conv1's dgrad /
+        # wgrad; its column sums are fused into the GroupNorm backward) are stored as bf16 only
+        bfs = self.bfs
+        da2 = self._get_bf(gp, B, HW, 128) if bfs else gp.get(B, HW, 128)
+        ops.append(self._dgrad(dOut, name + ".out_layers.3", da2, H, 3, 1, 128, 0, 128, bf=bf, out_dtype=1 if bfs else 0))
+        dh1 = None if bf else gp.get(B, HW, 128)
         dh1_bf = self._get_bf(gp, B, HW, 128) if bf else None
-        self._gn_bwd(ops, r["g2"], da2, dh1, name + ".out_layers.0", dx_bf=dh1_bf)
+        self._gn_bwd(ops, r["g2"], da2, dh1, name + ".out_layers.0", dx_bf=dh1_bf, dy_bf=bfs)
         gp.release(da2)
         # emb_out broadcast add (simple_unet.py:183-184) and conv1 bias
-        dh1g = _Grad(dh1)
+        dh1g = _Grad(dh1_bf, 0, 128, bf=dh1_bf) if bf else _Grad(dh1)
         self._colsum(ops, dh1g, HW, per_sample=_p(self.d_embout, r["k"] * 128), ps_ld=12 * self.Cc,
                      total1=self._g(name + ".in_layers.2.bias"))
         ops.append(self._wgrad(r["a1"], None, dh1g, name + ".in_layers.2", H, H, 3, 1, 1, Cin, 0, bf=bf))
-        da1 = gp.get(B, HW, Cin)
+        da1 = self._get_bf(gp, B, HW, Cin) if bfs else gp.get(B, HW, Cin)
         for n_off in range(0, Cin, 128):
-            ops.append(self._dgrad(dh1g, name + ".in_layers.2", da1, H, 3, 1, Cin, n_off, Cin, bf=bf))
+            ops.append(self._dgrad(dh1g, name + ".in_layers.2", da1, H, 3, 1, Cin, n_off, Cin, bf=bf,
+                                   out_dtype=1 if bfs else 0))
         gp.release(dh1)
         gp.release(dh1_bf)
         dsk = None
@@ -454,7 +468,8 @@ class UNetPlan:
         dx = (self.pool_dcat if has_skip else gp).get(B, HW, Cin)
         # the first 128 channels of dx are the output gradient of whatever produced x: give it its bf16 copy here
         dx_bf = self._get_bf(self.bfpool, B, HW, 128) if bf else None
-        self._gn_bwd(ops, r["g1"], da1, dx, name + ".in_layers.0", add1=add1, add2=extra, add_c=add_c, dx_bf=dx_bf)
+        self._gn_bwd(ops, r["g1"], da1, dx, name + ".in_layers.0", add1=add1, add2=extra, add_c=add_c, dx_bf=dx_bf,
+                     dy_bf=bfs)
         gp.release(da1)
         gp.release(dsk)
         return dx

@@ -43,7 +43,7 @@ typedef struct {
   const void* x;   /* fp32, or bf16 when op_dtype == 1 */
   const void* x2;  /* NULL when C2 == 0 */
   const void* w;   /* same element type as x */
-  float* out;
+  void* out;
   const float* bias;     /* [128] or NULL */
   const float* emb;      /* [N][emb_ld] or NULL */
   const float* residual; /* [M][res_ld] or NULL */
@@ -56,6 +56,7 @@ typedef struct {
   int out_ld, emb_ld, res_ld;
   int x_ld, x2_ld;       /* pixel stride (floats) of x / x2; 0 = dense (C1 / C2) */
   int round_out;         /* store the result rounded to TF32 (it feeds another tensor-core operand) */
+  int out_dtype;         /* 0 = out is fp32; 1 = out holds bf16 (out_ld in elements; strip-kernel layers only) */
   /* fused skip segment (stride-1 layers): out += Conv1x1(cat(skip_x, skip_x2), skip_w) + bias2, accumulated on the
    * tensor cores as extra K-chunks.  skip_w is [128][skip_c1+skip_c2]; with the 128x128 identity it is the residual
    * add of ResBlock.forward (simple_unet.py:186), with skip_connection.weight it is the 1x1 skip conv (:177). */
@@ -114,6 +115,7 @@ typedef struct {
   int silu;
   int round_tf32;
   int y_dtype;     /* 0 = fp32 (optionally TF32-rounded), 1 = bf16 (the operand of a bf16 convolution) */
+  int x_dtype;     /* 0 = fp32, 1 = x / x2 hold bf16 (x_ld in elements; shared-memory-resident kernels only) */
 } b200_gn_args;
 int b200_gn_fwd(const b200_gn_args* a, void* ws, size_t ws_bytes, void* stream);
 
@@ -142,6 +144,7 @@ typedef struct {
   float* colsum_total1;
   float* colsum_total2;
   int colsum_c;
+  int dy_dtype; /* 0 = fp32, 1 = dy holds bf16.  dx may be NULL when only dx_bf16 (and the column sums) are wanted. */
 } b200_gn_bwd_args;
 int b200_gn_bwd(const b200_gn_bwd_args* a, void* ws, size_t ws_bytes, void* stream);
 

@@ -273,3 +273,71 @@ def test_bf16_sampler_step_vs_reference_fixture(built_lib, golden):
         assert far < 0.03, (k, far)
         if k > 0:
             assert rel(z_ours, f["zs"][k]) < 2e-2, k
+
+
+@pytest.mark.parametrize("N,HW,C2", [(3, 784, 0), (2, 196, 128), (4, 49, 0)])
+def test_gn_bf16_inputs(lib, N, HW, C2):
+    """x_dtype / dy_dtype = 1: bf16 sources give exactly what the fp32 kernels give on the same (bf16-representable)
+    values; a NULL dx writes only the bf16 copy and the fused column sums."""
+    g = torch.Generator().manual_seed(HW + C2 + 1)
+    Cc = 128 + C2
+    x = bf(rn(g, N, HW, Cc) * 2 + 0.5).to(DEV)
+    dy = bf(rn(g, N, HW, Cc)).to(DEV)
+    x1, x2 = x[..., :128].contiguous(), (x[..., 128:].contiguous() if C2 else None)
+    x1b, x2b = x1.bfloat16(), (x2.bfloat16() if C2 else None)
+    dyb = dy.bfloat16()
+    gd, bd = (1 + 0.2 * rn(g, Cc)).to(DEV), (0.1 * rn(g, Cc)).to(DEV)
+    res = {}
+    for mode in (0, 1):
+        stats = torch.zeros(N, 64, device=DEV)
+        y = torch.empty(N, HW, Cc, device=DEV)
+        a = lib.GnArgs(x=ptr(x1b if mode else x1), x2=ptr(x2b if mode else x2), stats=ptr(stats), gamma=ptr(gd),
+                       beta=ptr(bd), y=ptr(y), N=N, HW=HW, C1=128, C2=C2, x_ld=0, x2_ld=0, eps=1e-5, silu=1, round_tf32=0,
+                       y_dtype=0, x_dtype=mode)
+        lib.call("b200_gn_fwd", a, stream())
+        dx = torch.empty(N, HW, Cc, device=DEV)
+        dxb = torch.zeros(N, HW, 128, dtype=torch.bfloat16, device=DEV)
+        dgam, dbet = torch.zeros(Cc, device=DEV), torch.zeros(Cc, device=DEV)
+        tot, per = torch.zeros(128, device=DEV), torch.zeros(N, 128, device=DEV)
+        b = lib.GnBwdArgs(fwd=a, dy=ptr(dyb if mode else dy), dx=ptr(dx) if mode == 0 else None, add1=None, add2=None,
+                          add1_ld=0, add2_ld=0, add_c=0, dgamma=ptr(dgam), dbeta=ptr(dbet), round_dx=0, dx_bf16=ptr(dxb),
+                          dx_bf16_c=128, colsum_per_sample=ptr(per), colsum_ps_ld=128, colsum_total1=ptr(tot),
+                          colsum_total2=None, colsum_c=128, dy_dtype=mode)
+        lib.call("b200_gn_bwd", b, stream())
+        res[mode] = (y.cpu(), stats.cpu(), dxb.float().cpu(), dgam.cpu(), dbet.cpu(), tot.cpu(), per.cpu(), dx.cpu())
+    for i, (u, v) in enumerate(zip(res[0][:7], res[1][:7])):
+        # same values, same arithmetic: only the atomics' order differs (the bf16 copy may flip one ulp on a few elements)
+        assert rel(v, u) < (2 ** -7 if i == 2 else 2e-5), i
+    # fused column sums against the fp32 dx of the fp32 run
+    dx0 = res[0][7][..., :128]
+    assert rel(res[0][5], dx0.sum((0, 1))) < 1e-4 and rel(res[0][6], dx0.sum(1)) < 1e-4
+
+
+def test_bf16_conv_bf16_output(lib):
+    """out_dtype = 1: the strip epilogue stores bf16 (fprop with emb, and dgrad into a 256-wide buffer at n_off)."""
+    g = torch.Generator().manual_seed(9)
+    N, H = 4, 14
+    x, w = bf(rn(g, N, 128, H, H)), bf(rn(g, 128, 128, 3, 3) * 0.03)
+    bias, emb = rn(g, 128), rn(g, N, 128)
+    ref = F.conv2d(x, w, bias=bias, padding=1) + emb[:, :, None, None]
+    xh, wk = dev_bf(nhwc(x)), dev_bf(w_khwc(w))
+    out = torch.zeros(N, H, H, 128, dtype=torch.bfloat16, device=DEV)
+    bd, ed = bias.to(DEV), emb.to(DEV)
+    a = lib.ConvArgs(x=ptr(xh), x2=None, w=ptr(wk), out=ptr(out), bias=ptr(bd), emb=ptr(ed), residual=None, N=N, H=H, W=H,
+                     C1=128, C2=0, Ho=H, Wo=H, R=3, S=3, stride=1, pad=1, mode=0, w_cout=128, w_cin=128, n_off=0, out_ld=128,
+                     emb_ld=128, res_ld=128, op_dtype=1, out_dtype=1)
+    lib.call("b200_conv_igemm", a, stream())
+    got = out.float().permute(0, 3, 1, 2).cpu()
+    assert rel(got, ref) < 2 ** -8
+    w2 = bf(rn(g, 128, 256, 3, 3) * 0.03)
+    dy = bf(rn(g, N, 128, H, H))
+    ref2 = torch.nn.grad.conv2d_input((N, 256, H, H), w2, dy, padding=1)
+    dyh, w2k = dev_bf(nhwc(dy)), dev_bf(w_khwc(w2))
+    out2 = torch.zeros(N, H, H, 256, dtype=torch.bfloat16, device=DEV)
+    import ctypes as C
+    for n_off in (0, 128):
+        a = lib.ConvArgs(x=ptr(dyh), x2=None, w=ptr(w2k), out=C.c_void_p(out2.data_ptr() + 2 * n_off), bias=None, emb=None,
+                         residual=None, N=N, H=H, W=H, C1=128, C2=0, Ho=H, Wo=H, R=3, S=3, stride=1, pad=1, mode=1,
+                         w_cout=128, w_cin=256, n_off=n_off, out_ld=256, emb_ld=0, res_ld=0, op_dtype=1, out_dtype=1)
+        lib.call("b200_conv_igemm", a, stream())
+    assert rel(out2.float().permute(0, 3, 1, 2).cpu(), ref2) < 2 ** -8
