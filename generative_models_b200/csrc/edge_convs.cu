@@ -95,7 +95,7 @@ conv_in_bwd_kernel(const float* __restrict__ x, const float* __restrict__ dy, fl
 }
 
 // ------------------------------------------------------------------------------------------------ conv_out forward
-// out[pix] = b + sum_{tap,c} h[pix+tap][c] * w[tap][c].  One CTA per image (HW <= 1024): every input row is read
+// out[pix] = b + sum_{tap,c} h[pix+tap][c] * w[tap][c].  One CTA per image (HW <= 4096): every input row is read
 // once, its 9 per-tap dot products are parked in smem, then each output pixel gathers its 9 partials.
 __global__ void __launch_bounds__(256)
 conv_out_fwd_kernel(const float* __restrict__ h, const float* __restrict__ w, const float* __restrict__ bias,
@@ -228,8 +228,14 @@ extern "C" int b200_conv_out_fwd(const b200_conv_out_args* a, void* ws, size_t w
   (void)ws; (void)ws_bytes;
   if (!a || !a->h || !a->w || !a->bias || !a->out) return fail_arg("conv_out_fwd: null pointer");
   const int HW = a->H * a->W;
-  if (HW > 1024) return fail_arg("conv_out_fwd: H*W must be <= 1024");
+  if (HW > 4096) return fail_arg("conv_out_fwd: H*W must be <= 4096");
   const size_t smem = static_cast<size_t>(HW) * 9 * sizeof(float);
+  static bool fwd_attr_set = false;
+  if (!fwd_attr_set) {
+    cudaError_t e = cudaFuncSetAttribute(conv_out_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 4096 * 9 * 4);
+    if (e != cudaSuccess) return check_cuda(e, "cudaFuncSetAttribute(conv_out_fwd)");
+    fwd_attr_set = true;
+  }
   conv_out_fwd_kernel<<<a->N, 256, smem, static_cast<cudaStream_t>(stream)>>>(a->h, a->w, a->bias, a->out, a->H, a->W);
   return after_launch("conv_out_fwd_kernel");
 }
@@ -238,11 +244,11 @@ extern "C" int b200_conv_out_bwd(const b200_conv_out_args* a, void* ws, size_t w
   (void)ws; (void)ws_bytes;
   if (!a || !a->h || !a->w || !a->dout || !a->dh || !a->dw || !a->db) return fail_arg("conv_out_bwd: null pointer");
   const int HW = a->H * a->W;
-  if (HW > 1024) return fail_arg("conv_out_bwd: H*W must be <= 1024");
+  if (HW > 4096) return fail_arg("conv_out_bwd: H*W must be <= 4096");
   const size_t smem = (static_cast<size_t>((HW + 3) & ~3) + 8 * 9 * 128) * sizeof(float);
   static bool attr_set = false;
   if (!attr_set) {
-    cudaError_t e = cudaFuncSetAttribute(conv_out_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 48 * 1024);
+    cudaError_t e = cudaFuncSetAttribute(conv_out_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (4096 + 8 * 9 * 128) * 4);
     if (e != cudaSuccess) return check_cuda(e, "cudaFuncSetAttribute(conv_out_bwd)");
     attr_set = true;
   }

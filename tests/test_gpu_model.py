@@ -279,3 +279,40 @@ def test_loss_curve_tracks_oracle_over_many_steps(built_lib):
     assert max(r["first5_rel_dev"]) < 2e-3, r["first5_rel_dev"]
     assert r["windowed_rel_dev_max"] < 0.2, r["windowed_rel_dev"]
     assert r["ours_first_last"][1] < 0.25 * r["ours_first_last"][0]
+
+
+@pytest.mark.parametrize("S,prec", [(32, "tf32"), (32, "bf16"), (64, "tf32")])
+def test_other_image_sizes_vs_oracle(built_lib, S, prec):
+    """pad32 (the reference's G.pad32 option, 32x32) and the 64x64 spatial size of BASELINE.json configs[4]: forward
+    and every parameter gradient of a linear loss against oracle autograd.  64x64 takes the streaming GroupNorm path
+    and the im2col conv kernel (strips need W <= 56 at this tile size)."""
+    from generative_models_b200.plan import UNetPlan
+    m, sd0 = make_model(built_lib, mean_type="eps", precision=prec)
+    g = torch.Generator().manual_seed(S)
+    B = 2
+    z = torch.randn(B, 1, S, S, generator=g)
+    logsnr = torch.tensor([1.5, -3.0])
+    y = torch.tensor([7, -1])
+    r = torch.randn(B, 1, S, S, generator=g)
+    sd = {k: v.clone().requires_grad_(True) for k, v in sd0.items()}
+    out_ref = O.unet_forward(sd, z, logsnr, guide=y)
+    (out_ref * r).sum().backward()
+    p = UNetPlan(m.store, B, S, train=True, bf16=(prec == "bf16"))
+    p.z_in.copy_(z.reshape(B, -1))
+    p.t.copy_(logsnr)
+    p.guide.copy_(y)
+    st = m._stream()
+    m.store.grad.zero_()
+    p.forward(st)
+    p.dout.copy_(r.reshape(B, -1))
+    p.backward(st)
+    net_tol, grad_tol = (NET_TOL, GRAD_TOL) if prec == "tf32" else (5e-3, 2.5e-2)
+    assert rms_rel(p.out.cpu().view(B, 1, S, S), out_ref.detach()) < net_tol
+    worst = ("", 0.0)
+    for k, prm in m.net.named_parameters():
+        if sd[k].grad is None:
+            continue
+        e = rel(prm.grad.cpu(), sd[k].grad)
+        if e > worst[1]:
+            worst = (k, e)
+    assert worst[1] < grad_tol, worst
