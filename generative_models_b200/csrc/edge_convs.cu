@@ -10,40 +10,55 @@
 namespace b200 {
 
 // ------------------------------------------------------------------------------------------------ conv_in forward
-// out[n,y,x,c] = b[c] + sum_{kh,kw} x[n,y+kh-1,x+kw-1] * w[c][kh][kw];  one thread = one pixel x 4 channels.
+// out[n,y,x,c] = b[c] + sum_{kh,kw} x[n,y+kh-1,x+kw-1] * w[c][kh][kw].
+// One warp = one image row; lane = 4 output channels with its 36 weights in registers.  The 3x3 input window slides
+// along the row in registers (3 broadcast loads per pixel), so a pixel costs ~50 instructions for a 512 B store and no
+// integer division: the kernel is bound by the HBM write (the per-element version spent its time on index math).
 __global__ void __launch_bounds__(256)
 conv_in_fwd_kernel(const float* __restrict__ x, const float* __restrict__ w, const float* __restrict__ bias,
                    float* __restrict__ out, int N, int H, int W, int round_out) {
-  __shared__ float sw[9][128];
-  __shared__ float sb[128];
-  for (int i = threadIdx.x; i < 9 * 128; i += blockDim.x) sw[i % 9][i / 9] = w[i];  // w is [c][tap]
-  if (threadIdx.x < 128) sb[threadIdx.x] = bias[threadIdx.x];
-  __syncthreads();
-  const size_t total = static_cast<size_t>(N) * H * W * 32;
-  for (size_t i = blockIdx.x * static_cast<size_t>(blockDim.x) + threadIdx.x; i < total;
-       i += static_cast<size_t>(gridDim.x) * blockDim.x) {
-    const size_t pix = i >> 5;
-    const int c = static_cast<int>(i & 31) * 4;
-    const int n = static_cast<int>(pix / (H * W));
-    const int rem = static_cast<int>(pix - static_cast<size_t>(n) * H * W);
-    const int y = rem / W, xx = rem - y * W;
-    float4 acc = make_float4(sb[c], sb[c + 1], sb[c + 2], sb[c + 3]);
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int c = lane * 4;
+  float wv[4][9];
+#pragma unroll
+  for (int j = 0; j < 4; ++j)
+#pragma unroll
+    for (int t = 0; t < 9; ++t) wv[j][t] = w[(c + j) * 9 + t];  // w is [c][tap]
+  const float4 b4 = *reinterpret_cast<const float4*>(bias + c);
+  const int rows = N * H;
+  for (int row = blockIdx.x * 8 + warp; row < rows; row += gridDim.x * 8) {
+    const int n = row / H, y = row - n * H;
     const float* img = x + static_cast<size_t>(n) * H * W;
+    const float* r0 = (y > 0) ? img + (y - 1) * W : nullptr;
+    const float* r1 = img + y * W;
+    const float* r2 = (y + 1 < H) ? img + (y + 1) * W : nullptr;
+    float a[3][3];  // a[kh][kw]: input columns x-1, x, x+1
+    a[0][0] = a[1][0] = a[2][0] = 0.f;
+    a[0][1] = r0 ? __ldg(r0) : 0.f;
+    a[1][1] = __ldg(r1);
+    a[2][1] = r2 ? __ldg(r2) : 0.f;
+    float* orow = out + static_cast<size_t>(row) * W * 128 + c;
+    for (int xx = 0; xx < W; ++xx) {
+      const bool in = xx + 1 < W;
+      a[0][2] = (in && r0) ? __ldg(r0 + xx + 1) : 0.f;
+      a[1][2] = in ? __ldg(r1 + xx + 1) : 0.f;
+      a[2][2] = (in && r2) ? __ldg(r2 + xx + 1) : 0.f;
+      float acc[4] = {b4.x, b4.y, b4.z, b4.w};
 #pragma unroll
-    for (int kh = 0; kh < 3; ++kh) {
-      const int yy = y + kh - 1;
-      if (yy < 0 || yy >= H) continue;
+      for (int kh = 0; kh < 3; ++kh)
 #pragma unroll
-      for (int kw = 0; kw < 3; ++kw) {
-        const int xw = xx + kw - 1;
-        if (xw < 0 || xw >= W) continue;
-        const float v = img[yy * W + xw];
-        const float4 wv = *reinterpret_cast<const float4*>(&sw[kh * 3 + kw][c]);
-        acc.x += v * wv.x; acc.y += v * wv.y; acc.z += v * wv.z; acc.w += v * wv.w;
+        for (int kw = 0; kw < 3; ++kw)
+#pragma unroll
+          for (int j = 0; j < 4; ++j) acc[j] += a[kh][kw] * wv[j][kh * 3 + kw];
+      float4 o = make_float4(acc[0], acc[1], acc[2], acc[3]);
+      if (round_out) o = round_tf32(o);
+      *reinterpret_cast<float4*>(orow + static_cast<size_t>(xx) * 128) = o;
+#pragma unroll
+      for (int kh = 0; kh < 3; ++kh) {
+        a[kh][0] = a[kh][1];
+        a[kh][1] = a[kh][2];
       }
     }
-    if (round_out) acc = round_tf32(acc);
-    *reinterpret_cast<float4*>(out + pix * 128 + c) = acc;
   }
 }
 
@@ -107,20 +122,43 @@ conv_out_fwd_kernel(const float* __restrict__ h, const float* __restrict__ w, co
   float4 wv[9];
 #pragma unroll
   for (int t = 0; t < 9; ++t) wv[t] = *reinterpret_cast<const float4*>(w + t * 128 + lane * 4);
-  for (int p = warp; p < HW; p += 8) {
-    const float4 v = *reinterpret_cast<const float4*>(h + (static_cast<size_t>(n) * HW + p) * 128 + lane * 4);
-    float d[9];
+  // Reduction of the 9 per-tap dot products over the 32 lanes by value-splitting butterflies: at every step a lane
+  // keeps half of its values and trades the other half with its partner (5 + 3 + 2 + 1 + 1 = 12 shuffles per pixel
+  // instead of 9 x 5).  After the steps lane L holds tap (b1 + 2 b2) + 3 b3 + 5 b4 (b_k = bit k of L), pads excluded.
+  const bool b4 = lane & 16, b3 = lane & 8, b2 = lane & 4, b1 = lane & 2;
+  const int jj = (b1 ? 1 : 0) + (b2 ? 2 : 0), j5 = jj + (b3 ? 3 : 0), tap = j5 + (b4 ? 5 : 0);
+  const bool writer = !(lane & 1) && jj < 3 && j5 < 5 && tap < 9;
+  const float* hn = h + static_cast<size_t>(n) * HW * 128 + lane * 4;
+  for (int p = warp; p < HW; p += 16) {  // two pixels per iteration: two independent 512 B loads in flight per warp
+    const int p2 = p + 8;
+    const bool has2 = p2 < HW;
+    const float4 va = *reinterpret_cast<const float4*>(hn + static_cast<size_t>(p) * 128);
+    const float4 vb = has2 ? *reinterpret_cast<const float4*>(hn + static_cast<size_t>(p2) * 128) : make_float4(0.f, 0.f, 0.f, 0.f);
 #pragma unroll
-    for (int t = 0; t < 9; ++t) d[t] = v.x * wv[t].x + v.y * wv[t].y + v.z * wv[t].z + v.w * wv[t].w;
+    for (int half = 0; half < 2; ++half) {
+      const float4 v = half ? vb : va;
+      float d[10];
 #pragma unroll
-    for (int o = 16; o > 0; o >>= 1)
+      for (int t = 0; t < 9; ++t) d[t] = v.x * wv[t].x + v.y * wv[t].y + v.z * wv[t].z + v.w * wv[t].w;
+      d[9] = 0.f;
+      float u[6];
 #pragma unroll
-      for (int t = 0; t < 9; ++t) d[t] += __shfl_xor_sync(0xffffffffu, d[t], o);
-    if (lane < 9) {
-      float sel = d[0];
+      for (int i = 0; i < 5; ++i)
+        u[i] = (b4 ? d[5 + i] : d[i]) + __shfl_xor_sync(0xffffffffu, b4 ? d[i] : d[5 + i], 16);
+      u[5] = 0.f;
+      float q[4];
 #pragma unroll
-      for (int t = 1; t < 9; ++t) sel = (lane == t) ? d[t] : sel;
-      part[p * 9 + lane] = sel;
+      for (int i = 0; i < 3; ++i)
+        q[i] = (b3 ? u[3 + i] : u[i]) + __shfl_xor_sync(0xffffffffu, b3 ? u[i] : u[3 + i], 8);
+      q[3] = 0.f;
+      float z2[2];
+#pragma unroll
+      for (int i = 0; i < 2; ++i)
+        z2[i] = (b2 ? q[2 + i] : q[i]) + __shfl_xor_sync(0xffffffffu, b2 ? q[i] : q[2 + i], 4);
+      float z = (b1 ? z2[1] : z2[0]) + __shfl_xor_sync(0xffffffffu, b1 ? z2[0] : z2[1], 2);
+      z += __shfl_xor_sync(0xffffffffu, z, 1);
+      const int pp = half ? p2 : p;
+      if (writer && (half == 0 || has2)) part[pp * 9 + tap] = z;
     }
   }
   __syncthreads();
@@ -203,8 +241,7 @@ using namespace b200;
 extern "C" int b200_conv_in_fwd(const b200_conv_in_args* a, void* ws, size_t ws_bytes, void* stream) {
   (void)ws; (void)ws_bytes;
   if (!a || !a->x || !a->w || !a->bias || !a->out) return fail_arg("conv_in_fwd: null pointer");
-  const size_t total = static_cast<size_t>(a->N) * a->H * a->W * 32;
-  size_t blocks = (total + 255) / 256;
+  size_t blocks = (static_cast<size_t>(a->N) * a->H + 7) / 8;  // one warp per image row
   if (blocks > 148 * 8) blocks = 148 * 8;
   conv_in_fwd_kernel<<<static_cast<int>(blocks), 256, 0, static_cast<cudaStream_t>(stream)>>>(a->x, a->w, a->bias, a->out,
                                                                                               a->N, a->H, a->W, a->round_out);
