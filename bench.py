@@ -371,6 +371,20 @@ def run_ours(args, rank, world, local_rank):
                 "activation_bytes": bound2.plan.activation_bytes()}
         if prof2:
             tot2 = sum(d["ms"] for d in prof2.values())
+            bms = sum(d["ms"] for k, d in prof2.items() if k.startswith("conv_strip_kernel<bf16>"))
+            bfl = sum(d["flops"] for k, d in prof2.items() if k.startswith("conv_strip_kernel<bf16>"))
+            bn = sum(d["launches"] for k, d in prof2.items() if k.startswith("conv_strip_kernel<bf16>"))
+            try:
+                pk = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+                peak_bf, src = pk.get("bf16_tflops_sustained") or pk.get("bf16_tflops"), "MEASURED_PEAKS.json bf16 sustained (kernel timed inside a long step)"
+            except Exception:
+                peak_bf, src = 1391.9, "fallback: the pool's sustained cuBLAS bf16 figure"
+            if bms > 0 and peak_bf:
+                bf16["roofline"] = {"kernel": "conv_strip_kernel<bf16> (all its fprop + dgrad launches of one train step)",
+                                    "bound": "tensor", "achieved": bfl / (bms / 1e3) / 1e12, "peak": peak_bf,
+                                    "unit": "TFLOP/s", "frac": bfl / (bms / 1e3) / 1e12 / peak_bf, "traffic": None,
+                                    "peak_source": src, "launches": bn, "avg_launch_us": bms / bn * 1e3,
+                                    "share_of_step": bms / tot2}
             bf16["breakdown"] = {k: {"ms": round(d["ms"], 4), "launches": d["launches"], "share": round(d["ms"] / tot2, 4),
                                      **({"tflops": round(d["flops"] / (d["ms"] / 1e3) / 1e12, 1)} if d["flops"] else {})}
                                  for k, d in sorted(prof2.items(), key=lambda kv: -kv[1]["ms"])[:10]}
