@@ -49,6 +49,8 @@ class ClockSampler:
         self.proc = None
 
     def start(self):
+        if self.idx < 0:
+            return
         try:
             self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
                                           "-lms", "100", "-i", str(self.idx)], stdout=subprocess.PIPE,
@@ -278,6 +280,10 @@ def run_ours(args, rank, world, local_rank):
     host = [(x.pin_memory(), y.pin_memory()) for x, y in host]
     devb = [(x.to(dev), y.to(dev)) for x, y in host]
     W, K = max(args.warmup, 3), args.steps
+    # nvidia-smi attaches to every GPU when it starts, which stalls kernel launches on all of them for tens of ms: only
+    # rank 0 samples (its own GPU), and it starts before the warm-up so that the start-up cost is outside the timed region
+    clocks = ClockSampler(local_rank if rank == 0 else -1)
+    clocks.start()
     for i in range(max(W, 8)):  # extra untimed steps beyond W: graph capture + clock ramp
         x, y = devb[i % nb]
         model.train_step(x, y.clone())
@@ -287,9 +293,6 @@ def run_ours(args, rank, world, local_rank):
     bound.enqueue_fwd_bwd()
     bound.enqueue_adam()
     launches_per_step = lib.launch_count() - l0
-    clocks = ClockSampler(local_rank)
-    clocks.start()
-    time.sleep(0.3)
     barrier()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     t_wall0 = time.time()
