@@ -48,6 +48,18 @@ __device__ __forceinline__ float dsilu_f(float u) {
   const float sg = sigmoid_f(u);
   return sg * (1.0f + u * (1.0f - sg));
 }
+// One-MUFU sigmoid for the bf16 paths: 0.5 tanh(u/2) + 0.5 with tanh.approx (abs error ~2.5e-4, an eighth of a bf16
+// ulp of the values it produces); the fp32 paths keep the ex2 + rcp form (1e-6).
+__device__ __forceinline__ float sigmoid_fast(float u) {
+  float t;
+  asm("tanh.approx.f32 %0, %1;" : "=f"(t) : "f"(0.5f * u));
+  return fmaf(0.5f, t, 0.5f);
+}
+__device__ __forceinline__ float silu_fast(float u) { return u * sigmoid_fast(u); }
+__device__ __forceinline__ float dsilu_fast(float u) {
+  const float sg = sigmoid_fast(u);
+  return sg * (1.0f + u * (1.0f - sg));
+}
 __device__ __forceinline__ void cp_async16(void* smem_dst, const void* gsrc) {
   asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(
                    static_cast<uint32_t>(__cvta_generic_to_shared(smem_dst))), "l"(gsrc) : "memory");
@@ -161,7 +173,11 @@ gn_fwd_fused_kernel(GnSrc s, float* __restrict__ stats, const float* __restrict_
     o.z = (v.z - mean) * sc.z + be.z;
     o.w = (v.w - mean) * sc.w + be.w;
     if (silu) {
-      o.x = silu_f(o.x); o.y = silu_f(o.y); o.z = silu_f(o.z); o.w = silu_f(o.w);
+      if (tf32 == 2) {  // bf16 output: the one-MUFU sigmoid is far inside the output rounding
+        o.x = silu_fast(o.x); o.y = silu_fast(o.y); o.z = silu_fast(o.z); o.w = silu_fast(o.w);
+      } else {
+        o.x = silu_f(o.x); o.y = silu_f(o.y); o.z = silu_f(o.z); o.w = silu_f(o.w);
+      }
     }
     if (tf32 == 2) {
       *reinterpret_cast<uint2*>(dstb + static_cast<size_t>(idx / L) * s.C) = pack_bf16x4(o);
@@ -319,6 +335,239 @@ gn_bwd_fused_kernel(GnSrc s, const float* __restrict__ stats, const float* __res
     if (lane < L) {
 #pragma unroll
       for (int j = 0; j < 4; ++j) atomicAdd(&csum[l * 4 + j], ca[j]);
+    }
+    __syncthreads();
+    if (tid < CS) {
+      const float v = csum[tid];
+      if (cs.per_sample) atomicAdd(&cs.per_sample[static_cast<size_t>(n) * cs.ps_ld + c0 + tid], v);
+      if (cs.total1) atomicAdd(&cs.total1[c0 + tid], v);
+      if (cs.total2) atomicAdd(&cs.total2[c0 + tid], v);
+    }
+  }
+}
+
+// ---------------------------------------------------------------------------------------------------- bf16 sources
+// Variants for bf16 x and / or dy (bf16 storage of the tensors only GroupNorm reads).  The slice is staged in shared
+// memory in its RAW element type with plain 16 B cp.async chunks (8 bf16 channels each; loader and consumer mappings
+// differ, a block barrier separates them) and every pass widens on the fly; nothing is written back to shared memory
+// — the backward recomputes xhat and du in its second phase (2 extra MUFU ops per element) instead of parking them —
+// so a bf16 slice costs half the footprint: 4 CTAs/SM in the backward when both sources are bf16, 3 when one is.
+__device__ __forceinline__ float4 widen_bf16x4(uint2 r) {
+  return make_float4(__uint_as_float(r.x << 16), __uint_as_float(r.x & 0xffff0000u), __uint_as_float(r.y << 16),
+                     __uint_as_float(r.y & 0xffff0000u));
+}
+// stage the [HW][CS] slice of channels [c0, c0+CS) of sample n into smem `dst` (raw, EB bytes per element)
+template <int CS, int EB, int T>
+__device__ __forceinline__ void gn_stage(uint8_t* dst, const void* base, int ld, int HW, int tid) {
+  constexpr int CPR = CS * EB / 16;  // 16 B chunks per pixel row of the slice
+  const uint8_t* b = static_cast<const uint8_t*>(base);
+  const int total = HW * CPR;
+  for (int i = tid; i < total; i += T) {
+    const int pix = i / CPR, ch = i - pix * CPR;
+    cp_async16(dst + static_cast<size_t>(i) * 16, b + (static_cast<size_t>(pix) * ld * EB + ch * 16));
+  }
+}
+template <int EB>
+__device__ __forceinline__ float4 gn_elem(const uint8_t* raw, int idx) {
+  if (EB == 4) return reinterpret_cast<const float4*>(raw)[idx];
+  return widen_bf16x4(reinterpret_cast<const uint2*>(raw)[idx]);
+}
+
+template <int CS, int T>
+__global__ void __launch_bounds__(T)
+gn_fwd_bfx_kernel(GnSrc s, float* __restrict__ stats, const float* __restrict__ gamma, const float* __restrict__ beta,
+                  float* __restrict__ y, float eps, int silu, int tf32) {
+  extern __shared__ float4 gn_smem[];
+  __shared__ float red[16];
+  const uint8_t* raw = reinterpret_cast<const uint8_t*>(gn_smem);
+  constexpr int L = CS / 4;
+  const int slices = s.C / CS;
+  const int n = blockIdx.x / slices;
+  const int c0 = (blockIdx.x - n * slices) * CS;
+  const int cpg = s.C >> 5;
+  const int tid = threadIdx.x, lane = tid & 31, l = tid % L;
+  const int c = c0 + l * 4;
+  const int gl = (l * 4) / cpg;
+  const int total = s.HW * L;
+  const bool first = c0 < s.C1;
+  const int ld = first ? s.ld1 : s.ld2;
+  const uint16_t* base = reinterpret_cast<const uint16_t*>(first ? s.x : s.x2) + (first ? c0 : c0 - s.C1) +
+                         static_cast<size_t>(n) * s.HW * ld;
+  if (tid < 16) red[tid] = 0.f;
+  gn_stage<CS, 2, T>(reinterpret_cast<uint8_t*>(gn_smem), base, ld, s.HW, tid);
+  cp_async_wait_all();
+  __syncthreads();
+  const bool pair = (cpg == 8);
+  const bool leader = (lane < L) && (!pair || !(lane & 1));
+  const float inv_cnt = 1.0f / static_cast<float>(s.HW * cpg);
+  float sum = 0.f;
+  for (int idx = tid; idx < total; idx += T) {
+    const float4 v = gn_elem<2>(raw, idx);
+    sum += (v.x + v.y) + (v.z + v.w);
+  }
+  sum = lane_group_sum<L>(sum, pair);
+  if (leader) atomicAdd(&red[gl], sum);
+  __syncthreads();
+  const float mean = red[gl] * inv_cnt;
+  float sq = 0.f;
+  for (int idx = tid; idx < total; idx += T) {
+    const float4 v = gn_elem<2>(raw, idx);
+    const float a = v.x - mean, b = v.y - mean, cc = v.z - mean, d = v.w - mean;
+    sq += (a * a + b * b) + (cc * cc + d * d);
+  }
+  sq = lane_group_sum<L>(sq, pair);
+  if (leader) atomicAdd(&red[8 + gl], sq);
+  __syncthreads();
+  const float rstd = rsqrtf(red[8 + gl] * inv_cnt + eps);
+  if (tid < L && (!pair || !(tid & 1)))
+    *reinterpret_cast<float2*>(stats + (static_cast<size_t>(n) * 32 + c / cpg) * 2) = make_float2(mean, rstd);
+  const float4 ga = *reinterpret_cast<const float4*>(gamma + c);
+  const float4 be = *reinterpret_cast<const float4*>(beta + c);
+  const float4 sc = make_float4(rstd * ga.x, rstd * ga.y, rstd * ga.z, rstd * ga.w);
+  float* dst = y + static_cast<size_t>(n) * s.HW * s.C + c;
+  uint16_t* dstb = reinterpret_cast<uint16_t*>(y) + static_cast<size_t>(n) * s.HW * s.C + c;
+  for (int idx = tid; idx < total; idx += T) {
+    const float4 v = gn_elem<2>(raw, idx);
+    float4 o;
+    o.x = (v.x - mean) * sc.x + be.x;
+    o.y = (v.y - mean) * sc.y + be.y;
+    o.z = (v.z - mean) * sc.z + be.z;
+    o.w = (v.w - mean) * sc.w + be.w;
+    if (silu) {
+      o.x = silu_fast(o.x); o.y = silu_fast(o.y); o.z = silu_fast(o.z); o.w = silu_fast(o.w);
+    }
+    if (tf32 == 2) {
+      *reinterpret_cast<uint2*>(dstb + static_cast<size_t>(idx / L) * s.C) = pack_bf16x4(o);
+    } else {
+      if (tf32) o = round_tf32(o);
+      *reinterpret_cast<float4*>(dst + static_cast<size_t>(idx / L) * s.C) = o;
+    }
+  }
+}
+
+// XB / DB: bytes per element of x / dy (2 or 4; at least one is 2)
+template <int CS, int T, int XB, int DB>
+__global__ void __launch_bounds__(T, 1024 / T)
+gn_bwd_raw_kernel(GnSrc s, const float* __restrict__ stats, const float* __restrict__ gamma,
+                  const float* __restrict__ beta, const void* __restrict__ dy, float* __restrict__ dx,
+                  const float* __restrict__ add1, int add1_ld, const float* __restrict__ add2, int add2_ld, int add_c,
+                  float* __restrict__ dgamma, float* __restrict__ dbeta, int silu, int round_dx,
+                  uint16_t* __restrict__ dxb, int dxb_c, GnColsum cs) {
+  extern __shared__ float4 gn_smem[];
+  __shared__ float red[16];
+  __shared__ float chan[2 * CS];
+  __shared__ float csum[CS];
+  constexpr int L = CS / 4;
+  const int slices = s.C / CS;
+  const int n = blockIdx.x / slices;
+  const int c0 = (blockIdx.x - n * slices) * CS;
+  const int cpg = s.C >> 5;
+  const int tid = threadIdx.x, lane = tid & 31, l = tid % L;
+  const int c = c0 + l * 4;
+  const int gl = (l * 4) / cpg;
+  const int total = s.HW * L;
+  uint8_t* xraw = reinterpret_cast<uint8_t*>(gn_smem);
+  uint8_t* draw = xraw + static_cast<size_t>(s.HW) * CS * XB;
+  const bool first = c0 < s.C1;
+  const int ld = first ? s.ld1 : s.ld2;
+  const size_t row0 = static_cast<size_t>(n) * s.HW;
+  const uint8_t* xbase = reinterpret_cast<const uint8_t*>(first ? s.x : s.x2) +
+                         (static_cast<size_t>(first ? c0 : c0 - s.C1) + row0 * ld) * XB;
+  const uint8_t* dbase = static_cast<const uint8_t*>(dy) + (row0 * s.C + c0) * DB;
+  if (tid < 16) red[tid] = 0.f;
+  if (tid < 2 * CS) chan[tid] = 0.f;
+  if (tid < CS) csum[tid] = 0.f;
+  gn_stage<CS, XB, T>(xraw, xbase, ld, s.HW, tid);
+  gn_stage<CS, DB, T>(draw, dbase, s.C, s.HW, tid);
+  cp_async_wait_all();
+  __syncthreads();
+  const float2 st = *reinterpret_cast<const float2*>(stats + (static_cast<size_t>(n) * 32 + c / cpg) * 2);
+  const float mean = st.x, rstd = st.y;
+  const float4 ga4 = *reinterpret_cast<const float4*>(gamma + c);
+  const float4 be4 = *reinterpret_cast<const float4*>(beta + c);
+  const float ga[4] = {ga4.x, ga4.y, ga4.z, ga4.w};
+  const float be[4] = {be4.x, be4.y, be4.z, be4.w};
+  float dg[4] = {0.f, 0.f, 0.f, 0.f}, db[4] = {0.f, 0.f, 0.f, 0.f};
+  float s1 = 0.f, s2 = 0.f;
+  for (int idx = tid; idx < total; idx += T) {
+    const float4 v = gn_elem<XB>(xraw, idx);
+    const float4 d = gn_elem<DB>(draw, idx);
+    const float xv[4] = {v.x, v.y, v.z, v.w};
+    const float dv[4] = {d.x, d.y, d.z, d.w};
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const float xh = (xv[j] - mean) * rstd;
+      const float du = silu ? dv[j] * dsilu_fast(xh * ga[j] + be[j]) : dv[j];
+      dg[j] += du * xh;
+      db[j] += du;
+      const float dxh = du * ga[j];
+      s1 += dxh;
+      s2 += dxh * xh;
+    }
+  }
+  const bool pair = (cpg == 8);
+  s1 = lane_group_sum<L>(s1, pair);
+  s2 = lane_group_sum<L>(s2, pair);
+#pragma unroll
+  for (int j = 0; j < 4; ++j) {
+    dg[j] = lane_group_sum<L>(dg[j], false);
+    db[j] = lane_group_sum<L>(db[j], false);
+  }
+  if (lane < L) {
+    if (!pair || !(lane & 1)) {
+      atomicAdd(&red[gl], s1);
+      atomicAdd(&red[8 + gl], s2);
+    }
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      atomicAdd(&chan[l * 4 + j], dg[j]);
+      atomicAdd(&chan[CS + l * 4 + j], db[j]);
+    }
+  }
+  __syncthreads();
+  if (tid < CS) atomicAdd(&dgamma[c0 + tid], chan[tid]);
+  else if (tid < 2 * CS) atomicAdd(&dbeta[c0 + tid - CS], chan[tid]);
+  const float inv_cnt = 1.0f / static_cast<float>(s.HW * cpg);
+  const float m1 = red[gl] * inv_cnt, m2 = red[8 + gl] * inv_cnt;
+  const bool has_add = c < add_c;
+  const float* a1 = (has_add && add1) ? add1 + row0 * add1_ld + c : nullptr;
+  const float* a2 = (has_add && add2) ? add2 + row0 * add2_ld + c : nullptr;
+  float* dst = dx ? dx + row0 * s.C + c : nullptr;
+  uint16_t* dstb = (dxb && c < dxb_c) ? dxb + row0 * dxb_c + c : nullptr;
+  float cacc[4] = {0.f, 0.f, 0.f, 0.f};
+  for (int idx = tid; idx < total; idx += T) {
+    const size_t pix = idx / L;
+    const float4 v = gn_elem<XB>(xraw, idx);
+    const float4 d = gn_elem<DB>(draw, idx);
+    const float xv[4] = {v.x, v.y, v.z, v.w};
+    const float dv[4] = {d.x, d.y, d.z, d.w};
+    float ov[4];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {  // recomputed, not parked in smem
+      const float xh = (xv[j] - mean) * rstd;
+      const float du = silu ? dv[j] * dsilu_fast(xh * ga[j] + be[j]) : dv[j];
+      ov[j] = rstd * (du * ga[j] - m1 - xh * m2);
+    }
+    float4 o = make_float4(ov[0], ov[1], ov[2], ov[3]);
+    if (a1) {
+      const float4 a = __ldg(reinterpret_cast<const float4*>(a1 + pix * add1_ld));
+      o.x += a.x; o.y += a.y; o.z += a.z; o.w += a.w;
+    }
+    if (a2) {
+      const float4 a = __ldg(reinterpret_cast<const float4*>(a2 + pix * add2_ld));
+      o.x += a.x; o.y += a.y; o.z += a.z; o.w += a.w;
+    }
+    if (dstb) *reinterpret_cast<uint2*>(dstb + pix * dxb_c) = pack_bf16x4(o);
+    if (round_dx) o = round_tf32(o);
+    if (dst) *reinterpret_cast<float4*>(dst + pix * s.C) = o;
+    cacc[0] += o.x; cacc[1] += o.y; cacc[2] += o.z; cacc[3] += o.w;
+  }
+  if (cs.c > 0 && c0 < cs.c) {  // uniform per CTA
+#pragma unroll
+    for (int j = 0; j < 4; ++j) cacc[j] = lane_group_sum<L>(cacc[j], false);
+    if (lane < L) {
+#pragma unroll
+      for (int j = 0; j < 4; ++j) atomicAdd(&csum[l * 4 + j], cacc[j]);
     }
     __syncthreads();
     if (tid < CS) {
@@ -578,6 +827,14 @@ static int gn_init() {
   if (e == cudaSuccess) e = gn_optin(gn_bwd_fused_kernel<16, 256>, max_dyn);
   if (e == cudaSuccess) e = gn_optin(gn_bwd_fused_kernel<32, 512>, max_dyn);
   if (e == cudaSuccess) e = gn_optin(gn_bwd_fused_kernel<16, 512>, max_dyn);
+  if (e == cudaSuccess) e = gn_optin(gn_fwd_bfx_kernel<16, 256>, max_dyn);
+  if (e == cudaSuccess) e = gn_optin(gn_fwd_bfx_kernel<32, 256>, max_dyn);
+  if (e == cudaSuccess) e = gn_optin(gn_bwd_raw_kernel<16, 256, 2, 2>, max_dyn);
+  if (e == cudaSuccess) e = gn_optin(gn_bwd_raw_kernel<32, 256, 2, 2>, max_dyn);
+  if (e == cudaSuccess) e = gn_optin(gn_bwd_raw_kernel<16, 256, 4, 2>, max_dyn);
+  if (e == cudaSuccess) e = gn_optin(gn_bwd_raw_kernel<32, 256, 4, 2>, max_dyn);
+  if (e == cudaSuccess) e = gn_optin(gn_bwd_raw_kernel<16, 256, 2, 4>, max_dyn);
+  if (e == cudaSuccess) e = gn_optin(gn_bwd_raw_kernel<32, 256, 2, 4>, max_dyn);
   if (e == cudaSuccess) e = gn_optin(gn_fwd_fused_kernel<8, 256>, max_dyn);
   if (e == cudaSuccess) e = gn_optin(gn_bwd_fused_kernel<8, 256>, max_dyn);
   if (e != cudaSuccess) return check_cuda(e, "cudaFuncSetAttribute(gn fused)");
@@ -615,6 +872,17 @@ extern "C" int b200_gn_fwd(const b200_gn_args* a, void* ws, size_t ws_bytes, voi
   const int ymode = a->y_dtype == 1 ? 2 : (a->round_tf32 ? 1 : 0);
   if (int r = gn_init()) return r;
   cudaStream_t st = static_cast<cudaStream_t>(stream);
+  if (s.bf) {  // bf16 x: raw-staged kernel, 2 B per element of shared memory
+    const size_t b16 = static_cast<size_t>(s.HW) * 16 * 2;
+    if (g_gn_stream || s.C1 % 32 || b16 > static_cast<size_t>(g_gn_max_dyn))
+      return fail_arg("gn_fwd: a bf16 input needs the shared-memory-resident kernel (HW too large)");
+    const int cs = (2 * b16 <= 50 * 1024) ? 32 : 16;
+    const int grid = s.N * (s.C / cs);
+    const size_t smem = static_cast<size_t>(s.HW) * cs * 2;
+    if (cs == 32) gn_fwd_bfx_kernel<32, 256><<<grid, 256, smem, st>>>(s, a->stats, a->gamma, a->beta, static_cast<float*>(a->y), a->eps, a->silu, ymode);
+    else gn_fwd_bfx_kernel<16, 256><<<grid, 256, smem, st>>>(s, a->stats, a->gamma, a->beta, static_cast<float*>(a->y), a->eps, a->silu, ymode);
+    return after_launch("gn_fwd_bfx_kernel");
+  }
   const int cs = gn_slice(s, 1);
   if (cs) {
     const int grid = s.N * (s.C / cs);
@@ -662,6 +930,24 @@ extern "C" int b200_gn_bwd(const b200_gn_bwd_args* b, void* ws, size_t ws_bytes,
     if (b->colsum_c != 128) return fail_arg("gn_bwd: colsum_c must be 128");
     csm.c = 128;
   }
+  if (s.bf || b->dy_dtype) {  // raw-staged kernel: 2 or 4 B per element of x and dy in shared memory, recompute in phase 2
+    const int xb = s.bf ? 2 : 4, dbb = b->dy_dtype ? 2 : 4;
+    const size_t b16 = static_cast<size_t>(s.HW) * 16 * (xb + dbb);
+    if (g_gn_stream || s.C1 % 32 || b16 > static_cast<size_t>(g_gn_max_dyn))
+      return fail_arg("gn_bwd: bf16 inputs need the shared-memory-resident kernel (HW too large)");
+    const int cs = (2 * b16 <= 50 * 1024) ? 32 : 16;
+    const int grid = s.N * (s.C / cs);
+    const size_t smem = static_cast<size_t>(s.HW) * cs * (xb + dbb);
+#define GN_BWD_RAW(CS, XB, DB)                                                                                          \
+  gn_bwd_raw_kernel<CS, 256, XB, DB><<<grid, 256, smem, st>>>(s, b->fwd.stats, b->fwd.gamma, b->fwd.beta, b->dy, b->dx,  \
+                                                              b->add1, b->add1_ld, b->add2, b->add2_ld, add_c, b->dgamma, \
+                                                              b->dbeta, b->fwd.silu, b->round_dx, dxb, dxb_c, csm)
+    if (xb == 2 && dbb == 2) { if (cs == 32) GN_BWD_RAW(32, 2, 2); else GN_BWD_RAW(16, 2, 2); }
+    else if (xb == 4) { if (cs == 32) GN_BWD_RAW(32, 4, 2); else GN_BWD_RAW(16, 4, 2); }
+    else { if (cs == 32) GN_BWD_RAW(32, 2, 4); else GN_BWD_RAW(16, 2, 4); }
+#undef GN_BWD_RAW
+    return after_launch("gn_bwd_raw_kernel");
+  }
   const int cs = gn_slice(s, 2);
   if (cs) {
     const int grid = s.N * (s.C / cs);
@@ -670,7 +956,7 @@ extern "C" int b200_gn_bwd(const b200_gn_bwd_args* b, void* ws, size_t ws_bytes,
 #define GN_BWD(CS, TH)                                                                                                  \
   gn_bwd_fused_kernel<CS, TH><<<grid, TH, smem, st>>>(s, b->fwd.stats, b->fwd.gamma, b->fwd.beta, b->dy, b->dx, b->add1, \
                                                       b->add1_ld, b->add2, b->add2_ld, add_c, b->dgamma, b->dbeta,       \
-                                                      b->fwd.silu, b->round_dx, dxb, dxb_c, csm, b->dy_dtype)
+                                                      b->fwd.silu, b->round_dx, dxb, dxb_c, csm, 0)
     if (cs == 8) GN_BWD(8, 256);
     else if (cs == 32 && th == 256) GN_BWD(32, 256);
     else if (cs == 32) GN_BWD(32, 512);

@@ -106,10 +106,10 @@ class UNetPlan:
         assert S % 4 == 0, "image side must be divisible by 4 (two stride-2 levels)"
         self.bf16 = bool(bf16)
         self.fuse_colsum = True
-        # bf16 STORAGE of the tensors only GroupNorm reads (h1, the dgrad outputs): kernels and tests exist, but the
-        # narrower accesses (8 B cp.async in GroupNorm) measured slower than the bytes they save; off by default
+        # bf16 STORAGE of the tensors only GroupNorm reads (h1, the dgrad outputs), like the reference's autocast conv
+        # outputs: halves their HBM traffic (B200_BF16_STORE=0 keeps them fp32, for A/B measurements)
         import os
-        self.bfs = self.bf16 and os.environ.get("B200_BF16_STORE", "0") == "1"
+        self.bfs = self.bf16 and os.environ.get("B200_BF16_STORE", "1") == "1"
         if self.bf16:
             store.ensure_bf16()
         self.store = store

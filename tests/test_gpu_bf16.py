@@ -168,13 +168,15 @@ def test_gn_bf16_outputs(lib, N, HW, C2):
 
 
 # ------------------------------------------------------------------------------------------------ whole model, bf16 mode
-# precision='bf16' rounds the operands of the 24 ResBlock 3x3 convolutions to bf16 (8 mantissa bits instead of TF32's
-# 10): the stated bars are 4x the TF32 ones.  Measured on B200 (tools/bf16_check.py): raw net output vs the reference
-# fixture 2.9e-3 rms-relative / 3.3e-3 max-norm (TF32: 7.5e-4 / 9.9e-4); parameter gradients of a linear loss
-# worst 1.35e-2 max-norm, median 7.2e-3 (TF32: 2.7e-3 / 1.6e-3).
-BF16_NET_TOL = 5e-3       # rms-relative
-BF16_NET_TOL_MAX = 6e-3   # max-norm relative
-BF16_GRAD_TOL = 2.5e-2    # max-norm relative, worst of the 156 tensors
+# precision='bf16': every stride-1 convolution takes bf16 operands (8 mantissa bits instead of TF32's 10) and the tensors
+# only GroupNorm reads (conv1 outputs, dgrad outputs) are STORED as bf16, like the reference's autocast step.  The stated
+# bars are ~8x the TF32 ones.  Measured on B200 (tools/bf16_check.py): raw net output vs the reference fixture 4.7e-3
+# rms-relative / 5.5e-3 .. 6.3e-3 max-norm (TF32: 7.5e-4 / 1.0e-3); parameter gradients of a linear loss worst 2.1e-2
+# max-norm, median 1.2e-2 (TF32: 3.3e-3 / 1.6e-3).  With fp32 storage (B200_BF16_STORE=0) the figures are 2.9e-3 /
+# 3.3e-3 and 1.35e-2 / 7.2e-3.
+BF16_NET_TOL = 8e-3       # rms-relative
+BF16_NET_TOL_MAX = 1e-2   # max-norm relative
+BF16_GRAD_TOL = 4e-2      # max-norm relative, worst of the 156 tensors
 
 
 def rms_rel(a, b):

@@ -306,7 +306,7 @@ def test_other_image_sizes_vs_oracle(built_lib, S, prec):
     p.forward(st)
     p.dout.copy_(r.reshape(B, -1))
     p.backward(st)
-    net_tol, grad_tol = (NET_TOL, GRAD_TOL) if prec == "tf32" else (5e-3, 2.5e-2)
+    net_tol, grad_tol = (NET_TOL, GRAD_TOL) if prec == "tf32" else (8e-3, 4e-2)
     assert rms_rel(p.out.cpu().view(B, 1, S, S), out_ref.detach()) < net_tol
     worst = ("", 0.0)
     for k, prm in m.net.named_parameters():
