@@ -64,16 +64,6 @@ __device__ __forceinline__ void cp_async16(void* smem_dst, const void* gsrc) {
   asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(
                    static_cast<uint32_t>(__cvta_generic_to_shared(smem_dst))), "l"(gsrc) : "memory");
 }
-__device__ __forceinline__ void cp_async8(void* smem_dst, const void* gsrc) {
-  asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(
-                   static_cast<uint32_t>(__cvta_generic_to_shared(smem_dst))), "l"(gsrc) : "memory");
-}
-// a 16 B smem slot whose first 8 bytes hold 4 bf16 (as cp_async8 left them) -> 4 floats
-__device__ __forceinline__ float4 slot_bf16(const float4* slot) {
-  const uint2 r = *reinterpret_cast<const uint2*>(slot);
-  return make_float4(__uint_as_float(r.x << 16), __uint_as_float(r.x & 0xffff0000u), __uint_as_float(r.y << 16),
-                     __uint_as_float(r.y & 0xffff0000u));
-}
 __device__ __forceinline__ void cp_async_wait_all() {
   asm volatile("cp.async.commit_group;\n\tcp.async.wait_group 0;" ::: "memory");
 }
@@ -117,31 +107,17 @@ gn_fwd_fused_kernel(GnSrc s, float* __restrict__ stats, const float* __restrict_
     ld = s.ld2;
   }
   if (tid < 16) red[tid] = 0.f;
-  if (s.bf) {  // bf16 source: 8 B per lane into the first half of each 16 B slot, widened in place by the first pass
-    const uint16_t* sb = reinterpret_cast<const uint16_t*>(c < s.C1 ? s.x : s.x2) + (c < s.C1 ? c : c - s.C1) +
-                         static_cast<size_t>(n) * s.HW * ld;
-    for (int idx = tid; idx < total; idx += kGnThreads) cp_async8(&gn_smem[idx], sb + static_cast<size_t>(idx / L) * ld);
-  } else {
-    src += static_cast<size_t>(n) * s.HW * ld;
-    for (int idx = tid; idx < total; idx += kGnThreads) cp_async16(&gn_smem[idx], src + static_cast<size_t>(idx / L) * ld);
-  }
+  src += static_cast<size_t>(n) * s.HW * ld;
+  for (int idx = tid; idx < total; idx += kGnThreads) cp_async16(&gn_smem[idx], src + static_cast<size_t>(idx / L) * ld);
   cp_async_wait_all();
   __syncthreads();
   const bool pair = (cpg == 8);
   const bool leader = (lane < L) && (!pair || !(lane & 1));
   const float inv_cnt = 1.0f / static_cast<float>(s.HW * cpg);
   float sum = 0.f;
-  if (s.bf) {
-    for (int idx = tid; idx < total; idx += kGnThreads) {  // own slots only: no sync needed before the next pass
-      const float4 v = slot_bf16(&gn_smem[idx]);
-      gn_smem[idx] = v;
-      sum += (v.x + v.y) + (v.z + v.w);
-    }
-  } else {
-    for (int idx = tid; idx < total; idx += kGnThreads) {
-      const float4 v = gn_smem[idx];
-      sum += (v.x + v.y) + (v.z + v.w);
-    }
+  for (int idx = tid; idx < total; idx += kGnThreads) {
+    const float4 v = gn_smem[idx];
+    sum += (v.x + v.y) + (v.z + v.w);
   }
   sum = lane_group_sum<L>(sum, pair);
   if (leader) atomicAdd(&red[gl], sum);
@@ -201,7 +177,7 @@ gn_bwd_fused_kernel(GnSrc s, const float* __restrict__ stats, const float* __res
                     const float* __restrict__ beta, const float* __restrict__ dy, float* __restrict__ dx,
                     const float* __restrict__ add1, int add1_ld, const float* __restrict__ add2, int add2_ld, int add_c,
                     float* __restrict__ dgamma, float* __restrict__ dbeta, int silu, int round_dx,
-                    uint16_t* __restrict__ dxb, int dxb_c, GnColsum cs, int dy_bf) {
+                    uint16_t* __restrict__ dxb, int dxb_c, GnColsum cs) {
   extern __shared__ float4 gn_smem[];
   __shared__ float red[16];
   __shared__ float chan[2 * CS];
@@ -234,16 +210,10 @@ gn_bwd_fused_kernel(GnSrc s, const float* __restrict__ stats, const float* __res
   if (tid < 16) red[tid] = 0.f;
   if (tid < 2 * CS) chan[tid] = 0.f;
   if (tid < CS) csum[tid] = 0.f;
-  // bf16 sources (s.bf for x, dy_bf for dy): 8 B per lane into the first half of the 16 B slot, widened by phase 1
-  const uint16_t* srcb = reinterpret_cast<const uint16_t*>(c < s.C1 ? s.x : s.x2) + (c < s.C1 ? c : c - s.C1) +
-                         static_cast<size_t>(n) * s.HW * ld;
-  const uint16_t* dsrcb = reinterpret_cast<const uint16_t*>(dy) + row0 * s.C + c;
   for (int idx = tid; idx < total; idx += kGnThreads) {
     const size_t pix = idx / L;
-    if (s.bf) cp_async8(&xs[idx], srcb + pix * ld);
-    else cp_async16(&xs[idx], src + pix * ld);
-    if (dy_bf) cp_async8(&ds[idx], dsrcb + pix * s.C);
-    else cp_async16(&ds[idx], dsrc + pix * s.C);
+    cp_async16(&xs[idx], src + pix * ld);
+    cp_async16(&ds[idx], dsrc + pix * s.C);
   }
   cp_async_wait_all();
   __syncthreads();
@@ -256,8 +226,8 @@ gn_bwd_fused_kernel(GnSrc s, const float* __restrict__ stats, const float* __res
   float dg[4] = {0.f, 0.f, 0.f, 0.f}, db[4] = {0.f, 0.f, 0.f, 0.f};
   float s1 = 0.f, s2 = 0.f;
   for (int idx = tid; idx < total; idx += kGnThreads) {
-    const float4 v = s.bf ? slot_bf16(&xs[idx]) : xs[idx];
-    const float4 d = dy_bf ? slot_bf16(&ds[idx]) : ds[idx];
+    const float4 v = xs[idx];
+    const float4 d = ds[idx];
     const float xv[4] = {v.x, v.y, v.z, v.w};
     const float dv[4] = {d.x, d.y, d.z, d.w};
     float xh[4], du[4];
@@ -956,7 +926,7 @@ extern "C" int b200_gn_bwd(const b200_gn_bwd_args* b, void* ws, size_t ws_bytes,
 #define GN_BWD(CS, TH)                                                                                                  \
   gn_bwd_fused_kernel<CS, TH><<<grid, TH, smem, st>>>(s, b->fwd.stats, b->fwd.gamma, b->fwd.beta, b->dy, b->dx, b->add1, \
                                                       b->add1_ld, b->add2, b->add2_ld, add_c, b->dgamma, b->dbeta,       \
-                                                      b->fwd.silu, b->round_dx, dxb, dxb_c, csm, 0)
+                                                      b->fwd.silu, b->round_dx, dxb, dxb_c, csm)
     if (cs == 8) GN_BWD(8, 256);
     else if (cs == 32 && th == 256) GN_BWD(32, 256);
     else if (cs == 32) GN_BWD(32, 512);
