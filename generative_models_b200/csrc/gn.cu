@@ -41,7 +41,14 @@ __device__ __forceinline__ float4 ld_src(const GnSrc& s, size_t pix, int c) {
 }
 // SiLU with the hardware exp2 / reciprocal (2 MUFU ops, ~1e-6 relative): the IEEE expf + division sequence costs about
 // as many issue slots as the kernel's whole memory phase.
-__device__ __forceinline__ float sigmoid_f(float u) { return __frcp_rn(1.0f + __expf(-u)); }
+__device__ __forceinline__ float sigmoid_f(float u) {
+  // exactly two MUFU ops (ex2.approx, rcp.approx; ~2^-22 relative): __frcp_rn is the IEEE-rounded reciprocal, a MUFU
+  // plus a Newton/fix-up sequence that cost the forward a quarter of its time (68 -> 89 us at 28x28, C=128)
+  float e, r;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(e) : "f"(-1.4426950408889634f * u));
+  asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(1.0f + e));
+  return r;
+}
 __device__ __forceinline__ float silu_f(float u) { return u * sigmoid_f(u); }
 // d silu(u) / du
 __device__ __forceinline__ float dsilu_f(float u) {

@@ -63,7 +63,7 @@ def main():
             fa, ba, ba1 = [], [], []
             for x1, x2, y, dy, dx, add1, stats in sets:
                 f = lib.GnArgs(x=ptr(x1), x2=ptr(x2), stats=ptr(stats), gamma=ptr(gamma), beta=ptr(beta), y=ptr(y), N=N,
-                               HW=HW, C1=128, C2=C2, x_ld=0, x2_ld=0, eps=1e-5, silu=1, round_tf32=1)
+                               HW=HW, C1=128, C2=C2, x_ld=0, x2_ld=0, eps=1e-5, silu=int(os.environ.get("GN_SILU", 1)), round_tf32=1)
                 fa.append(f)
                 ba.append(lib.GnBwdArgs(fwd=f, dy=ptr(dy), dx=ptr(dx), add1=None, add2=None, add1_ld=0, add2_ld=0,
                                         add_c=Cc, dgamma=ptr(dg), dbeta=ptr(db), round_dx=1))
