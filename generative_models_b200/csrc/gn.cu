@@ -232,6 +232,7 @@ gn_bwd_fused_kernel(GnSrc s, const float* __restrict__ stats, const float* __res
   const float be[4] = {be4.x, be4.y, be4.z, be4.w};
   float dg[4] = {0.f, 0.f, 0.f, 0.f}, db[4] = {0.f, 0.f, 0.f, 0.f};
   float s1 = 0.f, s2 = 0.f;
+  const float nmr = -mean * rstd;
   for (int idx = tid; idx < total; idx += kGnThreads) {
     const float4 v = xs[idx];
     const float4 d = ds[idx];
@@ -240,16 +241,20 @@ gn_bwd_fused_kernel(GnSrc s, const float* __restrict__ stats, const float* __res
     float xh[4], du[4];
 #pragma unroll
     for (int j = 0; j < 4; ++j) {
-      xh[j] = (xv[j] - mean) * rstd;
-      du[j] = silu ? dv[j] * dsilu_f(xh[j] * ga[j] + be[j]) : dv[j];
+      xh[j] = fmaf(xv[j], rstd, nmr);
+      du[j] = silu ? dv[j] * dsilu_f(fmaf(xh[j], ga[j], be[j])) : dv[j];
       dg[j] += du[j] * xh[j];
       db[j] += du[j];
-      const float dxh = du[j] * ga[j];
-      s1 += dxh;
-      s2 += dxh * xh[j];
     }
     xs[idx] = make_float4(xh[0], xh[1], xh[2], xh[3]);  // own slot: re-read by this thread only
     ds[idx] = make_float4(du[0], du[1], du[2], du[3]);
+  }
+  // sum(du * gamma) and sum(du * gamma * xhat) over this thread's elements follow from its per-channel sums
+  // (gamma is constant along the pixels): three instructions per element less in the loop above
+#pragma unroll
+  for (int j = 0; j < 4; ++j) {
+    s1 = fmaf(ga[j], db[j], s1);
+    s2 = fmaf(ga[j], dg[j], s2);
   }
   const bool pair = (cpg == 8);
   s1 = lane_group_sum<L>(s1, pair);
@@ -281,15 +286,17 @@ gn_bwd_fused_kernel(GnSrc s, const float* __restrict__ stats, const float* __res
   float* dst = dx + row0 * s.C + c;
   uint16_t* dstb = (dxb && c < dxb_c) ? dxb + row0 * dxb_c + c : nullptr;  // bf16 copy of the first dxb_c channels
   float4 cacc = make_float4(0.f, 0.f, 0.f, 0.f);  // per-channel sum of dx over this sample's pixels (fused colsum)
+  const float k1 = -m1 * rstd, k2 = -m2 * rstd;
+  const float gr[4] = {ga[0] * rstd, ga[1] * rstd, ga[2] * rstd, ga[3] * rstd};
   for (int idx = tid; idx < total; idx += kGnThreads) {
     const size_t pix = idx / L;
     const float4 xh = xs[idx];
     const float4 du = ds[idx];
     float4 o;
-    o.x = rstd * (du.x * ga[0] - m1 - xh.x * m2);
-    o.y = rstd * (du.y * ga[1] - m1 - xh.y * m2);
-    o.z = rstd * (du.z * ga[2] - m1 - xh.z * m2);
-    o.w = rstd * (du.w * ga[3] - m1 - xh.w * m2);
+    o.x = fmaf(xh.x, k2, fmaf(du.x, gr[0], k1));  // rstd * (du * gamma - m1 - xhat * m2)
+    o.y = fmaf(xh.y, k2, fmaf(du.y, gr[1], k1));
+    o.z = fmaf(xh.z, k2, fmaf(du.z, gr[2], k1));
+    o.w = fmaf(xh.w, k2, fmaf(du.w, gr[3], k1));
     if (a1) {
       const float4 a = __ldg(reinterpret_cast<const float4*>(a1 + pix * add1_ld));
       o.x += a.x; o.y += a.y; o.z += a.z; o.w += a.w;
@@ -464,6 +471,7 @@ gn_bwd_raw_kernel(GnSrc s, const float* __restrict__ stats, const float* __restr
   const float4 be4 = *reinterpret_cast<const float4*>(beta + c);
   const float ga[4] = {ga4.x, ga4.y, ga4.z, ga4.w};
   const float be[4] = {be4.x, be4.y, be4.z, be4.w};
+  const float nmr = -mean * rstd;
   float dg[4] = {0.f, 0.f, 0.f, 0.f}, db[4] = {0.f, 0.f, 0.f, 0.f};
   float s1 = 0.f, s2 = 0.f;
   for (int idx = tid; idx < total; idx += T) {
@@ -473,14 +481,16 @@ gn_bwd_raw_kernel(GnSrc s, const float* __restrict__ stats, const float* __restr
     const float dv[4] = {d.x, d.y, d.z, d.w};
 #pragma unroll
     for (int j = 0; j < 4; ++j) {
-      const float xh = (xv[j] - mean) * rstd;
-      const float du = silu ? dv[j] * dsilu_fast(xh * ga[j] + be[j]) : dv[j];
+      const float xh = fmaf(xv[j], rstd, nmr);
+      const float du = silu ? dv[j] * dsilu_fast(fmaf(xh, ga[j], be[j])) : dv[j];
       dg[j] += du * xh;
       db[j] += du;
-      const float dxh = du * ga[j];
-      s1 += dxh;
-      s2 += dxh * xh;
     }
+  }
+#pragma unroll
+  for (int j = 0; j < 4; ++j) {  // gamma is constant along the pixels: the group sums follow from the channel sums
+    s1 = fmaf(ga[j], db[j], s1);
+    s2 = fmaf(ga[j], dg[j], s2);
   }
   const bool pair = (cpg == 8);
   s1 = lane_group_sum<L>(s1, pair);
@@ -511,6 +521,8 @@ gn_bwd_raw_kernel(GnSrc s, const float* __restrict__ stats, const float* __restr
   const float* a2 = (has_add && add2) ? add2 + row0 * add2_ld + c : nullptr;
   float* dst = dx ? dx + row0 * s.C + c : nullptr;
   uint16_t* dstb = (dxb && c < dxb_c) ? dxb + row0 * dxb_c + c : nullptr;
+  const float k1 = -m1 * rstd, k2 = -m2 * rstd;
+  const float gr[4] = {ga[0] * rstd, ga[1] * rstd, ga[2] * rstd, ga[3] * rstd};
   float cacc[4] = {0.f, 0.f, 0.f, 0.f};
   for (int idx = tid; idx < total; idx += T) {
     const size_t pix = idx / L;
@@ -521,9 +533,9 @@ gn_bwd_raw_kernel(GnSrc s, const float* __restrict__ stats, const float* __restr
     float ov[4];
 #pragma unroll
     for (int j = 0; j < 4; ++j) {  // recomputed, not parked in smem
-      const float xh = (xv[j] - mean) * rstd;
-      const float du = silu ? dv[j] * dsilu_fast(xh * ga[j] + be[j]) : dv[j];
-      ov[j] = rstd * (du * ga[j] - m1 - xh * m2);
+      const float xh = fmaf(xv[j], rstd, nmr);
+      const float du = silu ? dv[j] * dsilu_fast(fmaf(xh, ga[j], be[j])) : dv[j];
+      ov[j] = fmaf(xh, k2, fmaf(du, gr[j], k1));  // rstd * (du * gamma - m1 - xhat * m2)
     }
     float4 o = make_float4(ov[0], ov[1], ov[2], ov[3]);
     if (a1) {
