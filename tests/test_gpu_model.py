@@ -316,3 +316,61 @@ def test_other_image_sizes_vs_oracle(built_lib, S, prec):
         if e > worst[1]:
             worst = (k, e)
     assert worst[1] < grad_tol, worst
+
+
+def test_public_api_as_gms_main_drives_it(built_lib, tmp_path):
+    """The call sequence of gms/main.py:160-215 on the drop-in: train_step / loss under no_grad / evaluate(writer) /
+    sample(n, y) with and without labels / save + load_state_dict(strict=False) — shapes, dtypes, ranges, side effects."""
+    from generative_models_b200.model import DiffusionModelB200, default_G
+
+    class Writer:  # the SummaryWriter calls diffusion_model.py:89-111 / common.py:177-193 make
+        def __init__(self):
+            self.images, self.videos = {}, {}
+
+        def add_image(self, tag, img, epoch):
+            self.images[tag] = img
+
+        def add_video(self, tag, vid, epoch, fps=4):
+            self.videos[tag] = (vid, fps)
+
+    torch.manual_seed(0)
+    G = default_G(device=DEV, mean_type="eps", sampler="noisy", timesteps=6, logdir=tmp_path, bs=8)
+    m = DiffusionModelB200(G).to(G.device)
+    assert sum(p.numel() for p in m.parameters()) == 6_033_665
+    g = torch.Generator().manual_seed(0)
+    x = (torch.rand(8, 1, 28, 28, generator=g) * 2 - 1).to(DEV)
+    y = torch.randint(0, 10, (8,), generator=g).to(DEV)
+    m.train()
+    torch.manual_seed(5)
+    y_in = y.clone()
+    metrics = m.train_step(x, y_in)
+    assert set(metrics) == {"loss", "loss_scale"} and metrics["loss"].dim() == 0
+    assert torch.isfinite(metrics["loss"].detach().cpu()) and float(metrics["loss_scale"]) == 1.0
+    # the reference drops labels in place on the caller's tensor with the CPU generator (diffusion_model.py:67)
+    torch.manual_seed(5)
+    drop = torch.rand(8) < G.cf_drop_prob
+    assert torch.equal(y_in.cpu() == -1, drop)
+    m.eval()
+    with torch.no_grad():
+        loss, met = m.loss(x, y)
+    assert loss.dim() == 0 and set(met) == {"loss"} and torch.isfinite(loss)
+    w = Writer()
+    m.evaluate(w, x, y, 0)
+    assert w.images["samples"].shape == (1, 140, 140) and w.images["samples"].dtype == torch.uint8
+    for tag in ("sampling_process", "diffusion_model/eps", "diffusion_model/x"):
+        vid, fps = w.videos[tag]
+        assert vid.shape == (1, 6, 3, 140, 140) and vid.dtype == torch.uint8 and fps == 2
+    with torch.inference_mode():
+        s1 = m.sample(5, y=y[:5])
+        s2 = m.sample(5, y=-torch.ones_like(y[:5]))
+        s3 = m.sample(3)
+    for s_, n in ((s1, 5), (s2, 5), (s3, 3)):
+        assert s_.shape == (n, 1, 28, 28) and s_.dtype == torch.float32 and s_.device.type == "cuda"
+        assert torch.isfinite(s_).all() and s_.min() >= -1 and s_.max() <= 1  # last step returns the clipped x
+    m.save(tmp_path, x, y)
+    sd = torch.load(tmp_path / "model.pt", map_location=DEV)
+    assert len(sd) == 160 and all(k.startswith("net.") for k in sd)
+    m2 = DiffusionModelB200(default_G(device=DEV, mean_type="eps"))
+    missing = m2.load_state_dict(sd, strict=False)
+    assert not missing.missing_keys and not missing.unexpected_keys
+    assert torch.equal(m2.store.flat, m.store.flat)
