@@ -34,7 +34,7 @@ namespace b200 {
 constexpr int kSB = 6;                    // weight-tile ring
 constexpr int kSS = 2;                    // strip double buffer
 constexpr int kBTile = 16384;             // 128 x 128 B
-constexpr int kStripBytes = 48 * 1024;    // >= (256 + 2*Wp + 2 rounded up to whole rows) * 128 B for W <= 64
+constexpr int kStripBytes = 58 * 1024;    // >= (256 + 2*Wp + 2 rounded up to whole rows) * 128 B for W <= 64 (7 rows of 65)
 constexpr int kTileM = 256;               // positions per CTA tile (the N of one UMMA)
 constexpr int kStripSmem = kSS * kStripBytes + kSB * kBTile + 1024 + 256 + 2 * 512 * 4;
 

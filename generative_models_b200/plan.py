@@ -110,6 +110,10 @@ class UNetPlan:
         # outputs: halves their HBM traffic (B200_BF16_STORE=0 keeps them fp32, for A/B measurements)
         import os
         self.bfs = self.bf16 and os.environ.get("B200_BF16_STORE", "1") == "1"
+        if S * S > 2304:  # the raw-staged GroupNorm backward holds a 16-channel slice (6 B/element) in shared memory
+            self.bfs = False
+        # dh1 as bf16 only (no fp32 dx) needs the shared-memory-resident GroupNorm backward (16 channels x 8 B/pixel)
+        self.dh1_bf_only = self.bf16 and S * S * 128 <= 220 * 1024
         if self.bf16:
             store.ensure_bf16()
         self.store = store
@@ -438,12 +442,12 @@ class UNetPlan:
         bfs = self.bfs
         da2 = self._get_bf(gp, B, HW, 128) if bfs else gp.get(B, HW, 128)
         ops.append(self._dgrad(dOut, name + ".out_layers.3", da2, H, 3, 1, 128, 0, 128, bf=bf, out_dtype=1 if bfs else 0))
-        dh1 = None if bf else gp.get(B, HW, 128)
+        dh1 = None if self.dh1_bf_only else gp.get(B, HW, 128)
         dh1_bf = self._get_bf(gp, B, HW, 128) if bf else None
         self._gn_bwd(ops, r["g2"], da2, dh1, name + ".out_layers.0", dx_bf=dh1_bf, dy_bf=bfs)
         gp.release(da2)
         # emb_out broadcast add (simple_unet.py:183-184) and conv1 bias
-        dh1g = _Grad(dh1_bf, 0, 128, bf=dh1_bf) if bf else _Grad(dh1)
+        dh1g = _Grad(dh1_bf, 0, 128, bf=dh1_bf) if dh1 is None else _Grad(dh1)
         self._colsum(ops, dh1g, HW, per_sample=_p(self.d_embout, r["k"] * 128), ps_ld=12 * self.Cc,
                      total1=self._g(name + ".in_layers.2.bias"))
         ops.append(self._wgrad(r["a1"], None, dh1g, name + ".in_layers.2", H, H, 3, 1, 1, Cin, 0, bf=bf))
