@@ -180,7 +180,7 @@ def profile_ops(model, bound, kind):
     p = bound.plan
     if kind == "train":
         groups = [bound.zero_ops, bound.pre_ops, p.refresh_ops, p.embed_ops[0], p.body_ops, p.head_ops[:1],
-                  bound.loss_ops, p.bwd_ops, bound.adam_ops]
+                  bound.loss_ops, p.refreshT_ops, p.bwd_ops, bound.adam_ops]
     else:
         groups = [p.embed_ops[0], p.body_ops, p.head_ops[:1], bound.step_ops[False]]
     ops = [o for g in groups for o in g]
@@ -200,7 +200,8 @@ def profile_ops(model, bound, kind):
             from generative_models_b200 import lib as _lib
             strip = _lib.load().b200_conv_kernel_of(o.ref) == 1
             prec = "bf16" if o.args.op_dtype == 1 else "tf32"
-            name = (f"conv_strip_kernel<{prec}>" if strip else "conv_igemm_tf32_kernel") + ("[dgrad]" if o.args.mode == 1 else "[fprop]")
+            is_dgrad = o.args.mode == 1 or getattr(o, "tag", None) == "dgrad"
+            name = (f"conv_strip_kernel<{prec}>" if strip else "conv_igemm_tf32_kernel") + ("[dgrad]" if is_dgrad else "[fprop]")
         elif name == "b200_conv_wgrad":
             name = f"conv_wgrad_kernel<{'bf16' if o.args.op_dtype == 1 else 'tf32'}>"
         d = out.setdefault(name, {"ms": 0.0, "launches": 0, "flops": 0.0})

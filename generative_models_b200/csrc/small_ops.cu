@@ -405,6 +405,33 @@ extern "C" int b200_cast_bf16(const b200_cast_args* a, void* ws, size_t ws_bytes
   return after_launch("cast_bf16_kernel");
 }
 
+// one thread per output element; consecutive threads = consecutive co (coalesced stores; the strided reads hit L2)
+__global__ void __launch_bounds__(256) conv_weights_transpose_kernel(const float* __restrict__ src, void* __restrict__ dst,
+                                                                     const int4* __restrict__ table, int out_bf16) {
+  const int4 e = table[blockIdx.y];
+  const int off = e.x, T = e.y, Cin = e.z;
+  const int total = 128 * T * Cin;
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x) {
+    const int co = i & 127;
+    const int r = i >> 7;  // ci * T + t
+    const int ci = r / T, t = r - ci * T;
+    const float v = src[off + (co * T + (T - 1 - t)) * Cin + ci];
+    if (out_bf16) static_cast<uint16_t*>(dst)[off + i] = bf16_bits(v);
+    else static_cast<float*>(dst)[off + i] = round_tf32(v);
+  }
+}
+
+extern "C" int b200_conv_weights_transpose(const b200_wtranspose_args* a, void* ws, size_t ws_bytes, void* stream) {
+  (void)ws; (void)ws_bytes;
+  if (!a || !a->src || !a->dst || !a->table || a->n_weights <= 0 || a->max_elems <= 0)
+    return fail_arg("conv_weights_transpose: bad arguments");
+  int bx = (a->max_elems + 255) / 256;
+  if (bx > 64) bx = 64;
+  conv_weights_transpose_kernel<<<dim3(bx, a->n_weights), 256, 0, ST(stream)>>>(
+      a->src, a->dst, reinterpret_cast<const int4*>(a->table), a->out_dtype);
+  return after_launch("conv_weights_transpose_kernel");
+}
+
 extern "C" int b200_zero(const b200_zero_args* a, void* ws, size_t ws_bytes, void* stream) {
   (void)ws; (void)ws_bytes;
   if (!a || !a->ptr) return fail_arg("zero: null pointer");

@@ -137,6 +137,11 @@ class CastArgs(C.Structure):
     _fields_ = [("src", _f32p), ("dst", _f32p), ("rows", C.c_size_t), ("cols", C.c_int), ("src_ld", C.c_int)]
 
 
+class WTransposeArgs(C.Structure):
+    _fields_ = [("src", _f32p), ("dst", _f32p), ("table", _f32p), ("n_weights", C.c_int), ("max_elems", C.c_int),
+                ("out_dtype", C.c_int)]
+
+
 class ZeroArgs(C.Structure):
     _fields_ = [("ptr", _f32p), ("bytes", C.c_size_t)]
 
@@ -187,7 +192,7 @@ EXPORTS = [
     "b200_conv_in_fwd", "b200_conv_in_bwd", "b200_conv_out_fwd", "b200_conv_out_bwd",
     "b200_upsample2x", "b200_colsum",
     "b200_embed_prep", "b200_embed_combine", "b200_embed_combine_bwd",
-    "b200_linear", "b200_adam", "b200_zero", "b200_round_tf32", "b200_cast_bf16",
+    "b200_linear", "b200_adam", "b200_zero", "b200_round_tf32", "b200_cast_bf16", "b200_conv_weights_transpose",
 ]
 
 

@@ -30,10 +30,11 @@ def _p(t, off_floats=0):
 
 
 class Op:
-    __slots__ = ("fn", "ref", "args", "ws", "wsb", "name", "alg_scale")
+    __slots__ = ("fn", "ref", "args", "ws", "wsb", "name", "alg_scale", "tag")
 
     def __init__(self, name, args, ws=None):
         self.name = name
+        self.tag = None  # "dgrad" on backward-data launches (they run the forward kernel on transposed weights)
         self.alg_scale = 1.0  # algorithmic / executed work of this launch (bench.py's roofline accounting)
         self.fn = getattr(lib.load(), name)
         self.args = args  # keep the struct alive
@@ -198,7 +199,21 @@ class UNetPlan:
 
     def _dgrad(self, dy, wname, out, H, R, pad, w_cin, n_off, out_ld, residual=None, res_ld=0, bf=False, out_dtype=0):
         """dy: _Grad with 128 channels; writes 128 input channels [n_off, n_off+128) of `out`.
-        bf: read the dense bf16 copy dy.bf and the bf16 weight shadow."""
+        bf: read the dense bf16 copy dy.bf and the bf16 weight shadow.
+        Backward-data of a stride-1 'same' convolution is the forward convolution of dY with the transposed, tap-flipped
+        weights: with the [Cin][T][128] shadow (ParamStore.ensure_transposed) it runs the K-major forward path, which is
+        ~12 % faster than the MN-major weight operand of mode 1 (239 -> 211 us at 28x28, 128 channels)."""
+        if self.dgrad_T:
+            esz = 2 if bf else 4
+            wT = (self.store.bfT_ptr if bf else self.store.tcT_ptr)(wname + ".weight") + esz * n_off * R * R * 128
+            a = lib.ConvArgs(x=_p(dy.bf) if bf else dy.ptr(), x2=None, w=C.c_void_p(wT),
+                             out=C.c_void_p(out.data_ptr() + 2 * n_off) if out_dtype else _p(out, n_off), bias=None,
+                             emb=None, residual=residual, N=self.B, H=H, W=H, C1=128, C2=0, Ho=H, Wo=H, R=R, S=R, stride=1,
+                             pad=pad, mode=0, w_cout=128, w_cin=128, n_off=0, out_ld=out_ld, emb_ld=0, res_ld=res_ld,
+                             x_ld=128 if bf else dy.ld, x2_ld=0, round_out=1, op_dtype=1 if bf else 0, out_dtype=out_dtype)
+            op = Op("b200_conv_igemm", a)
+            op.tag = "dgrad"
+            return op
         a = lib.ConvArgs(x=_p(dy.bf) if bf else dy.ptr(), x2=None, w=(self._wbf if bf else self._wtc)(wname + ".weight"),
                          out=C.c_void_p(out.data_ptr() + 2 * n_off) if out_dtype else _p(out, n_off), bias=None, emb=None,
                          residual=residual, N=self.B, H=H, W=H, C1=128, C2=0, Ho=H, Wo=H, R=R, S=R, stride=1, pad=pad,
@@ -511,6 +526,18 @@ class UNetPlan:
         H0, H1, H2 = S, S // 2, S // 4
         sv = self.saved
         gp = self.gpool
+        import os
+        self.dgrad_T = os.environ.get("B200_DGRAD_T", "1") == "1"
+        self.refreshT_ops = []
+        if self.dgrad_T:
+            table = st.ensure_transposed(self.bf16)
+            self.refreshT_ops.append(Op("b200_conv_weights_transpose", lib.WTransposeArgs(
+                src=_p(st.flat), dst=_p(st.flat_tcT), table=_p(table), n_weights=table.shape[0], max_elems=st.wT_max,
+                out_dtype=0)))
+            if self.bf16:
+                self.refreshT_ops.append(Op("b200_conv_weights_transpose", lib.WTransposeArgs(
+                    src=_p(st.flat), dst=_p(st.flat_bfT), table=_p(table), n_weights=table.shape[0], max_elems=st.wT_max,
+                    out_dtype=1)))
         self.pool_dcat = _Pool(dev, recycle=False)  # concat gradients live until the Down path consumes their 2nd half
         self.bfpool = _Pool(dev, recycle=False)     # bf16 copies of block-output gradients (live across blocks)
         self.gn_ws = torch.zeros(B * 64, **f32)
@@ -591,6 +618,7 @@ class UNetPlan:
 
     def backward(self, stream_ptr):
         """Enqueue the reverse pass: reads self.dout, accumulates into store.grad (caller zeroes it once per step)."""
+        run_ops(self.refreshT_ops, stream_ptr)  # the weights have not changed since the forward's refresh
         run_ops(self.bwd_ops, stream_ptr)
 
     def activation_bytes(self):

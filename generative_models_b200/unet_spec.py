@@ -136,6 +136,27 @@ class ParamStore:
         if self.flat_bf is None:
             self.flat_bf = torch.zeros(self.numel, dtype=torch.bfloat16, device=self.device)
 
+    def ensure_transposed(self, bf16):
+        """Transposed, tap-flipped shadows of the conv weights ([Cin][T][128] at the weight's own offset): backward-data
+        runs through the forward kernel with them.  Returns the device table {off, T, Cin, 0} of the 128-output convs."""
+        if getattr(self, "flat_tcT", None) is None:
+            self.flat_tcT = torch.zeros(self.numel, dtype=torch.float32, device=self.device)
+            rows = []
+            for name, shape, kind in self.specs:
+                if kind == "conv_w" and shape[0] == 128 and shape[1] % 32 == 0:
+                    rows.append([self.offsets[name], shape[2] * shape[3], shape[1], 0])
+            self.wT_table = torch.tensor(rows, dtype=torch.int32, device=self.device)
+            self.wT_max = max(128 * r[1] * r[2] for r in rows)
+        if bf16 and getattr(self, "flat_bfT", None) is None:
+            self.flat_bfT = torch.zeros(self.numel, dtype=torch.bfloat16, device=self.device)
+        return self.wT_table
+
+    def tcT_ptr(self, name):
+        return self.flat_tcT.data_ptr() + 4 * self.offsets[name]
+
+    def bfT_ptr(self, name):
+        return self.flat_bfT.data_ptr() + 2 * self.offsets[name]
+
     def bf_ptr(self, name):
         return self.flat_bf.data_ptr() + 2 * self.offsets[name]
 

@@ -325,6 +325,21 @@ typedef struct {
 } b200_cast_args;
 int b200_cast_bf16(const b200_cast_args* a, void* ws, size_t ws_bytes, void* stream);
 
+/* Transposed, tap-flipped shadow of the convolution weights, so that backward-data runs through the forward kernel:
+ *   dst[off + (ci*T + t)*128 + co] = round(src[off + (co*T + (T-1-t))*Cin + ci])   for every listed weight
+ * (backward-data of a stride-1 'same' convolution == the forward convolution of dY with these weights; no reference
+ * counterpart — cuDNN picks its own dgrad algorithm).  table: n_weights rows of {off, T = R*S, Cin, 0} (int32, device
+ * memory), all weights have 128 output channels.  dst is fp32 rounded to TF32 (out_dtype 0) or bf16 (out_dtype 1). */
+typedef struct {
+  const float* src;
+  void* dst;
+  const int* table;
+  int n_weights;
+  int max_elems; /* largest 128*T*Cin in the table (sizes the grid) */
+  int out_dtype;
+} b200_wtranspose_args;
+int b200_conv_weights_transpose(const b200_wtranspose_args* a, void* ws, size_t ws_bytes, void* stream);
+
 /* cudaMemsetAsync(ptr, 0, bytes) on the stream (statistics / gradient arenas; replaces optimizer.zero_grad()). */
 typedef struct {
   void* ptr;

@@ -33,7 +33,7 @@ def test_ctypes_structs_match_header_field_order(built_lib):
               "b200_conv_out_args": built_lib.ConvOutArgs, "b200_resample_args": built_lib.ResampleArgs,
               "b200_colsum_args": built_lib.ColsumArgs, "b200_embed_args": built_lib.EmbedArgs,
               "b200_linear_args": built_lib.LinearArgs, "b200_zero_args": built_lib.ZeroArgs,
-              "b200_round_args": built_lib.RoundArgs, "b200_cast_args": built_lib.CastArgs,
+              "b200_round_args": built_lib.RoundArgs, "b200_cast_args": built_lib.CastArgs, "b200_wtranspose_args": built_lib.WTransposeArgs,
               "b200_adam_args": built_lib.AdamArgs}
     for m in re.finditer(r"typedef struct \{(.*?)\}\s*(b200_\w+);", hdr, re.S):
         body, name = m.group(1), m.group(2)
