@@ -137,42 +137,57 @@ conv_igemm_tf32_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_con
       tc_commit(tmem_full);
     }
   } else {
-    // ---------------- epilogue: TMEM -> registers -> (+bias +emb +residual) -> global
+    // ---------------- epilogue: TMEM -> registers -> smem (transpose) -> (+bias +emb +residual) -> global
+    // tcgen05.ld hands a thread one pixel ROW of the tile; writing (and reading the residual) from that layout touches
+    // 16 B per 512 B-strided row per lane — half-empty sectors on every access.  The pipeline's stage buffers are idle
+    // once the accumulator is complete, so each warp parks its 32 rows there (row pitch 132 floats: conflict-free
+    // float4 accesses) and then streams them out one row per instruction: 512 contiguous bytes per warp access for
+    // the output, the residual and the embedding row alike.
     const int quarter = warp & 3;  // TMEM lane quarter this warp may read
-    const int row = quarter * 32 + lane;
-    const int m = m0 + row;
     mbar_wait(tmem_full, 0);
     tc_fence_after();
-    const bool valid = m < a.M_total;
-    const int n = valid ? m / a.HoWo : 0;
-    float* orow = a.out + static_cast<size_t>(m) * a.out_ld;
-    const float* rrow = a.residual ? a.residual + static_cast<size_t>(m) * a.res_ld : nullptr;
-    const float* erow = a.emb ? a.emb + static_cast<size_t>(n) * a.emb_ld : nullptr;
+    constexpr int kPitch = 132;
+    float* stg = reinterpret_cast<float*>(smem) + quarter * 32 * kPitch;  // this warp's 32 rows
 #pragma unroll 1
     for (int cc = 0; cc < 4; ++cc) {
       uint32_t r[32];
       tmem_ld_32x32(tmem_base + (static_cast<uint32_t>(quarter * 32) << 16) + cc * 32, r);
       tmem_ld_wait();
-      if (valid) {
+      float* srow = stg + lane * kPitch + cc * 32;
 #pragma unroll
-        for (int j = 0; j < 32; j += 4) {
-          float4 v = make_float4(__uint_as_float(r[j]), __uint_as_float(r[j + 1]), __uint_as_float(r[j + 2]),
-                                 __uint_as_float(r[j + 3]));
-          const int c = cc * 32 + j;
-          if (a.bias) {
-            const float4 b = *reinterpret_cast<const float4*>(a.bias + c);
-            v.x += b.x; v.y += b.y; v.z += b.z; v.w += b.w;
-          }
-          if (erow) {
-            const float4 e = *reinterpret_cast<const float4*>(erow + c);
-            v.x += e.x; v.y += e.y; v.z += e.z; v.w += e.w;
-          }
-          if (rrow) {
-            const float4 e = *reinterpret_cast<const float4*>(rrow + c);
-            v.x += e.x; v.y += e.y; v.z += e.z; v.w += e.w;
-          }
+      for (int j = 0; j < 32; j += 4)
+        *reinterpret_cast<float4*>(srow + j) = make_float4(__uint_as_float(r[j]), __uint_as_float(r[j + 1]),
+                                                           __uint_as_float(r[j + 2]), __uint_as_float(r[j + 3]));
+    }
+    __syncwarp();
+    const int c = lane * 4;
+    float4 b4 = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (a.bias) b4 = *reinterpret_cast<const float4*>(a.bias + c);
+    const int m_first = m0 + quarter * 32;
+    const int nrows = min(32, a.M_total - m_first);
+#pragma unroll 1
+    for (int r0 = 0; r0 < nrows; r0 += 8) {  // batches of 8 rows: 8 (+8) independent 512 B loads in flight per warp
+      float4 add[8];
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        add[j] = b4;
+        const int m = min(m_first + r0 + j, a.M_total - 1);
+        if (a.residual) {
+          const float4 e = __ldg(reinterpret_cast<const float4*>(a.residual + static_cast<size_t>(m) * a.res_ld + c));
+          add[j].x += e.x; add[j].y += e.y; add[j].z += e.z; add[j].w += e.w;
+        }
+        if (a.emb) {
+          const float4 e = __ldg(reinterpret_cast<const float4*>(a.emb + static_cast<size_t>(m / a.HoWo) * a.emb_ld + c));
+          add[j].x += e.x; add[j].y += e.y; add[j].z += e.z; add[j].w += e.w;
+        }
+      }
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        if (r0 + j < nrows) {
+          float4 v = *reinterpret_cast<const float4*>(stg + (r0 + j) * kPitch + c);
+          v.x += add[j].x; v.y += add[j].y; v.z += add[j].z; v.w += add[j].w;
           if (a.round_out) v = round_tf32(v);
-          *reinterpret_cast<float4*>(orow + c) = v;
+          *reinterpret_cast<float4*>(a.out + static_cast<size_t>(m_first + r0 + j) * a.out_ld + c) = v;
         }
       }
     }

@@ -391,7 +391,12 @@ int conv_strip_applicable(const b200_conv_args* a) {
   // few tiles (small spatial levels at small batch): one 256-position tile per SM leaves the machine under-filled and
   // the im2col kernel (128-position tiles, 2 CTAs/SM) is faster there — measured crossover ~4 tiles per SM.
   // bf16 operands exist only in this kernel.
-  if (!a->skip_x && num_tiles < 4 * 148 && !flat && a->op_dtype == 0) return 0;
+  static int min_tiles = -1;  // developer knob B200_STRIP_MIN_TILES
+  if (min_tiles < 0) {
+    const char* e = getenv("B200_STRIP_MIN_TILES");
+    min_tiles = e ? atoi(e) : 4 * 148;
+  }
+  if (!a->skip_x && num_tiles < min_tiles && !flat && a->op_dtype == 0) return 0;
   return 1;
 }
 
