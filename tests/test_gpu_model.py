@@ -374,3 +374,58 @@ def test_public_api_as_gms_main_drives_it(built_lib, tmp_path):
     missing = m2.load_state_dict(sd, strict=False)
     assert not missing.missing_keys and not missing.unexpected_keys
     assert torch.equal(m2.store.flat, m.store.flat)
+
+
+@pytest.fixture(scope="module")
+def oracle_b512():
+    """oracle forward + autograd of a linear loss at BASELINE.json's full batch (512 images, some labels -1), once"""
+    B = 512
+    g = torch.Generator().manual_seed(5)
+    x = torch.rand(B, 1, 28, 28, generator=g) * 2 - 1
+    y = torch.randint(-1, 10, (B,), generator=g)
+    eps = torch.randn(B, 1, 28, 28, generator=g)
+    u = torch.rand(B, generator=g) * 0.8 + 0.1
+    r = torch.randn(B, 1, 28, 28, generator=g)
+    sd = {k: v.clone().requires_grad_(True) for k, v in O.random_state_dict(1).items()}
+    with torch.no_grad():
+        _, per, aux = O.training_loss(sd, x, y, eps, u, "eps")
+    (O.unet_forward(sd, aux["z"], aux["logsnr"], guide=y) * r).sum().backward()
+    return dict(x=x, y=y, eps=eps, u=u, r=r, out=aux["out"], per=per, grads={k: v.grad for k, v in sd.items()})
+
+
+@pytest.mark.parametrize("precision", ["tf32", "bf16"])
+def test_full_batch_512_vs_oracle(built_lib, oracle_b512, precision):
+    """configs[1] / configs[2] at their full size (512 images per GPU — the batch at which the plan picks the strip
+    kernels, the smem-resident GroupNorm and the one-CTA-per-SM wgrad grid): net output, per-sample loss and all 156
+    gradients of a linear loss against the oracle, and batch invariance (image i gives the same output in a batch of 6
+    as in the batch of 512)."""
+    from tests.test_gpu_bf16 import BF16_GRAD_TOL, BF16_NET_TOL, BF16_NET_TOL_MAX
+    net_tol, net_max, grad_tol = (NET_TOL, NET_TOL_RAND, GRAD_TOL) if precision == "tf32" else \
+        (BF16_NET_TOL, BF16_NET_TOL_MAX, BF16_GRAD_TOL)
+    o = oracle_b512
+    B = 512
+    m, _ = make_model(built_lib, mean_type="eps", precision=precision)
+    m.store.grad.zero_()
+    _, b = m.loss_and_grads(o["x"].to(DEV), o["y"].to(DEV), eps=o["eps"].to(DEV), u=o["u"].to(DEV))
+    ours = b.plan.out.cpu().view(B, 1, 28, 28)
+    assert rms_rel(ours, o["out"]) < net_tol and rel(ours, o["out"]) < net_max
+    assert rms_rel(b.loss_b.cpu(), o["per"]) < (3e-3 if precision == "tf32" else 3e-2)
+    m.store.grad.zero_()
+    st = m._stream()
+    b.plan.forward(st)
+    b.plan.dout.copy_(o["r"].reshape(B, -1))
+    b.plan.backward(st)
+    worst = ("", 0.0)
+    for k, p in m.net.named_parameters():
+        ref = o["grads"][k]
+        if ref is None:
+            assert p.grad.abs().max().item() == 0.0, k
+            continue
+        e = rel(p.grad.cpu(), ref)
+        if e > worst[1]:
+            worst = (k, e)
+    assert worst[1] < grad_tol, worst
+    # batch invariance: no kernel mixes samples, whatever tiling the batch size selects
+    _, b6 = m.loss_and_grads(o["x"][:6].to(DEV), o["y"][:6].to(DEV), eps=o["eps"][:6].to(DEV), u=o["u"][:6].to(DEV))
+    small = b6.plan.out.cpu().view(6, 1, 28, 28)
+    assert rms_rel(small, ours[:6]) < 2 * net_tol
