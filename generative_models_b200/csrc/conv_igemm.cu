@@ -147,17 +147,19 @@ conv_igemm_tf32_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_con
     mbar_wait(tmem_full, 0);
     tc_fence_after();
     constexpr int kPitch = 132;
-    float* stg = reinterpret_cast<float*>(smem) + quarter * 32 * kPitch;  // this warp's 32 rows
+    // this warp's 32 rows, addressed in the shared window (generic-pointer accesses compile to LD.E / ST.E)
+    const uint32_t stg = smem_u32(smem) + quarter * 32 * kPitch * 4;
 #pragma unroll 1
     for (int cc = 0; cc < 4; ++cc) {
       uint32_t r[32];
       tmem_ld_32x32(tmem_base + (static_cast<uint32_t>(quarter * 32) << 16) + cc * 32, r);
       tmem_ld_wait();
-      float* srow = stg + lane * kPitch + cc * 32;
+      const uint32_t srow = stg + (lane * kPitch + cc * 32) * 4;
 #pragma unroll
       for (int j = 0; j < 32; j += 4)
-        *reinterpret_cast<float4*>(srow + j) = make_float4(__uint_as_float(r[j]), __uint_as_float(r[j + 1]),
-                                                           __uint_as_float(r[j + 2]), __uint_as_float(r[j + 3]));
+        asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(srow + j * 4), "r"(r[j]), "r"(r[j + 1]),
+                     "r"(r[j + 2]), "r"(r[j + 3])
+                     : "memory");
     }
     __syncwarp();
     const int c = lane * 4;
@@ -184,7 +186,11 @@ conv_igemm_tf32_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_con
 #pragma unroll
       for (int j = 0; j < 8; ++j) {
         if (r0 + j < nrows) {
-          float4 v = *reinterpret_cast<const float4*>(stg + (r0 + j) * kPitch + c);
+          float4 v;
+          asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];"
+                       : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w)
+                       : "r"(stg + ((r0 + j) * kPitch + c) * 4)
+                       : "memory");
           v.x += add[j].x; v.y += add[j].y; v.z += add[j].z; v.w += add[j].w;
           if (a.round_out) v = round_tf32(v);
           *reinterpret_cast<float4*>(a.out + static_cast<size_t>(m_first + r0 + j) * a.out_ld + c) = v;

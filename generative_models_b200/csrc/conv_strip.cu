@@ -72,6 +72,23 @@ __device__ __forceinline__ int floor_div(int a, int b) {
 // BF16 = true:  bf16 operands, kind::f16, 64 channels per 128 B row — the byte geometry of every tile, strip, box and
 // descriptor step is identical (a K-step is 32 B either way), only the channel count per chunk doubles, so one
 // instruction does twice the FLOPs for the same shared-memory operand bytes.
+__device__ __forceinline__ int4 lds_int4(uint32_t saddr) {
+  int4 q;
+  asm volatile("ld.shared.v4.s32 {%0, %1, %2, %3}, [%4];" : "=r"(q.x), "=r"(q.y), "=r"(q.z), "=r"(q.w) : "r"(saddr));
+  return q;
+}
+__device__ __forceinline__ int lds_int(uint32_t saddr) {
+  int v;
+  asm volatile("ld.shared.s32 %0, [%1];" : "=r"(v) : "r"(saddr));
+  return v;
+}
+
+// *p = v when m >= 0, as one predicated store
+__device__ __forceinline__ void st_if_nonneg(float* p, float v, int m) {
+  asm volatile("{\n\t.reg .pred q;\n\tsetp.ge.s32 q, %2, 0;\n\t@q st.global.f32 [%0], %1;\n\t}" ::"l"(p), "f"(v), "r"(m)
+               : "memory");
+}
+
 template <bool BF16>
 __global__ void __launch_bounds__(320, 1)
 conv_strip_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmA2,
@@ -282,6 +299,9 @@ conv_strip_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
       // position -> (pixel row m, sample n) table of this tile (m = -1: halo position, nothing to store)
       int* tm = tab + as * 512;
       int* tn = tm + 256;
+      // the table is read through explicit shared-space loads: from the generic pointer the compiler emits LD.E
+      // (generic path, long-scoreboard latency) instead of LDS
+      const uint32_t tm_s = smem_u32(tm), tn_s = tm_s + 1024;
       {
         const int P = t * kTileM + et;
         int m, n;
@@ -299,6 +319,24 @@ conv_strip_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
         tn[et] = n;
       }
       asm volatile("bar.sync 1, 256;" ::: "memory");
+      // Residual rows are fetched one 32-position chunk AHEAD: chunk 0 before the wait for the accumulator (the MMAs of
+      // this tile are still running), chunk c+1 before the stores of chunk c — the loads' DRAM latency used to be
+      // exposed four times per tile.  The position table is re-read from shared memory instead of living in 32
+      // registers, which is what makes room for the second buffer under the 168-register cap.
+      const float* res_co = a.residual ? a.residual + co : nullptr;
+      float nxt[32];
+      auto fetch_residual = [&](int cb) {
+#pragma unroll
+        for (int j = 0; j < 32; j += 4) {
+          const int4 q = lds_int4(tm_s + (cb + j) * 4);
+          // unconditional (halo positions read row 0): predicates would serialise the loads
+          nxt[j] = __ldg(res_co + static_cast<size_t>(q.x < 0 ? 0 : q.x) * a.res_ld);
+          nxt[j + 1] = __ldg(res_co + static_cast<size_t>(q.y < 0 ? 0 : q.y) * a.res_ld);
+          nxt[j + 2] = __ldg(res_co + static_cast<size_t>(q.z < 0 ? 0 : q.z) * a.res_ld);
+          nxt[j + 3] = __ldg(res_co + static_cast<size_t>(q.w < 0 ? 0 : q.w) * a.res_ld);
+        }
+      };
+      if (res_co) fetch_residual(colhalf * 128);
       mbar_wait(&acc_full[as], (tc >> 1) & 1);
       tc_fence_after();
 #pragma unroll 1
@@ -306,22 +344,16 @@ conv_strip_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
         const int cb = colhalf * 128 + c4 * 32;  // first position column of this chunk
         uint32_t r[32];
         tmem_ld_32x32(tmem_base + (static_cast<uint32_t>(quarter * 32) << 16) + as * 256 + cb, r);
-        int mm[32];
-#pragma unroll
-        for (int j = 0; j < 32; j += 4) {
-          const int4 q = *reinterpret_cast<const int4*>(tm + cb + j);
-          mm[j] = q.x; mm[j + 1] = q.y; mm[j + 2] = q.z; mm[j + 3] = q.w;
-        }
         float add[32];
 #pragma unroll
         for (int j = 0; j < 32; ++j) add[j] = bias_v;
-        if (a.residual) {  // 32 independent loads in flight per thread
+        if (res_co) {
 #pragma unroll
-          for (int j = 0; j < 32; ++j)  // unconditional (halo positions read row 0): predicates would serialise them
-            add[j] += __ldg(a.residual + static_cast<size_t>(mm[j] < 0 ? 0 : mm[j]) * a.res_ld + co);
+          for (int j = 0; j < 32; ++j) add[j] += nxt[j];
+          if (c4 < 3) fetch_residual(cb + 32);
         }
         if (a.emb) {
-          const int n0 = tn[cb], n1 = tn[cb + 31];
+          const int n0 = lds_int(tn_s + cb * 4), n1 = lds_int(tn_s + (cb + 31) * 4);
           if (n0 == n1) {
             const float e = (n0 < a.N) ? __ldg(a.emb + static_cast<size_t>(n0) * a.emb_ld + co) : 0.f;
 #pragma unroll
@@ -329,16 +361,22 @@ conv_strip_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
           } else {
 #pragma unroll
             for (int j = 0; j < 32; ++j)
-              if (mm[j] >= 0) add[j] += __ldg(a.emb + static_cast<size_t>(tn[cb + j]) * a.emb_ld + co);
+              if (lds_int(tm_s + (cb + j) * 4) >= 0)
+                add[j] += __ldg(a.emb + static_cast<size_t>(lds_int(tn_s + (cb + j) * 4)) * a.emb_ld + co);
           }
         }
         tmem_ld_wait();
         if (!a.out_is_bf) {
 #pragma unroll
-          for (int j = 0; j < 32; ++j) {
-            if (mm[j] >= 0) {
-              const float v = __uint_as_float(r[j]) + add[j];
-              a.out[static_cast<size_t>(mm[j]) * a.out_ld + co] = a.round_out ? round_tf32(v) : v;
+          for (int j = 0; j < 32; j += 4) {
+            const int4 q = lds_int4(tm_s + (cb + j) * 4);
+            const int mq[4] = {q.x, q.y, q.z, q.w};
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+              // predicated store (a branch per position costs more than the store)
+              const float v = __uint_as_float(r[j + i]) + add[j + i];
+              st_if_nonneg(a.out + static_cast<size_t>(mq[i] < 0 ? 0 : mq[i]) * a.out_ld + co,
+                           a.round_out ? round_tf32(v) : v, mq[i]);
             }
           }
         }
@@ -356,8 +394,9 @@ conv_strip_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
             const float lo = odd ? got : v0, hi = odd ? v1 : got;
             uint32_t wrd;
             asm("cvt.rn.bf16x2.f32 %0, %1, %2;" : "=r"(wrd) : "f"(hi), "f"(lo));
-            const int m = odd ? mm[j + 1] : mm[j];
-            if (m >= 0) *reinterpret_cast<uint32_t*>(ob + static_cast<size_t>(m) * obld + (co & ~1)) = wrd;
+            const int m = lds_int(tm_s + (cb + j + odd) * 4);
+            st_if_nonneg(reinterpret_cast<float*>(ob + static_cast<size_t>(m < 0 ? 0 : m) * obld + (co & ~1)),
+                         __uint_as_float(wrd), m);
           }
         }
       }
