@@ -239,6 +239,109 @@ linear_bwd_w_kernel(const float* __restrict__ dY, const float* __restrict__ X, f
   if (db && blockIdx.x == 0 && tx == 0 && n < N) atomicAdd(&db[n], bacc);
 }
 
+// The batched embedding projection (512 -> 13 x 128 at batch 512) is the one linear big enough to matter: 64x64 output
+// tiles, 4x4 outputs per thread, both operand tiles staged reduction-major in shared memory (16 FMAs per two LDS.128).
+// C[i][j] = sum_r A(i, r) * B(j, r).  ARC / BRC: the operand's reduction index is its contiguous one (row = output
+// index) — otherwise the output index is contiguous (row = reduction index).  I x J x R need not be tile multiples in
+// I (the batch); J and R are multiples of 64 / 16 (checked by the host).
+template <bool RC>
+__device__ __forceinline__ void lin_load_tile(float (*dst)[68], const float* __restrict__ src, int ld, int o0, int r0,
+                                              int o_lim, int act) {
+  const int t = threadIdx.x;
+  if (RC) {  // src[(o0 + o) * ld + r0 + r]: thread -> (o = t / 4, r = 4 * (t % 4)), stored transposed
+    const int o = t >> 2, r4 = (t & 3) * 4;
+    float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (o0 + o < o_lim) v = *reinterpret_cast<const float4*>(src + static_cast<size_t>(o0 + o) * ld + r0 + r4);
+    if (act) {
+      v.x = v.x / (1.0f + expf(-v.x)); v.y = v.y / (1.0f + expf(-v.y));
+      v.z = v.z / (1.0f + expf(-v.z)); v.w = v.w / (1.0f + expf(-v.w));
+    }
+    dst[r4][o] = v.x; dst[r4 + 1][o] = v.y; dst[r4 + 2][o] = v.z; dst[r4 + 3][o] = v.w;
+  } else {  // src[(r0 + r) * ld + o0 + o]: thread -> (r = t / 16, o = 4 * (t % 16)); rows past o_lim do not occur
+    const int r = t >> 4, o4 = (t & 15) * 4;
+    float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (r0 + r < o_lim) v = *reinterpret_cast<const float4*>(src + static_cast<size_t>(r0 + r) * ld + o0 + o4);
+    if (act) {
+      v.x = v.x / (1.0f + expf(-v.x)); v.y = v.y / (1.0f + expf(-v.y));
+      v.z = v.z / (1.0f + expf(-v.z)); v.w = v.w / (1.0f + expf(-v.w));
+    }
+    *reinterpret_cast<float4*>(&dst[r][o4]) = v;
+  }
+}
+// MODE 0: Y = act(X) W^T + b  (A = X rows m, RC; B = W rows n, RC; R = K)
+// MODE 1: dX = dY W (* silu'(X))  (A = dY rows m, RC over n; B = W[n][k], output-contiguous; R = N)
+// MODE 2: dW += dY^T act(X), db += colsum(dY)  (A = dY[m][n], B = X[m][k], both output-contiguous; R = M)
+template <int MODE>
+__global__ void __launch_bounds__(256)
+linear_tile_kernel(const float* __restrict__ A, const float* __restrict__ B, const float* __restrict__ aux,
+                   float* __restrict__ Cout, float* __restrict__ db, int M, int N, int K, int act) {
+  __shared__ __align__(16) float sa[16][68], sb[16][68];
+  const int i0 = blockIdx.y * 64, j0 = blockIdx.x * 64;
+  const int ty = threadIdx.x >> 4, tx = threadIdx.x & 15;
+  const int R = MODE == 0 ? K : (MODE == 1 ? N : M);
+  float acc[4][4] = {};
+  float bacc[4] = {0.f, 0.f, 0.f, 0.f};
+  for (int r0 = 0; r0 < R; r0 += 16) {
+    if (MODE == 0) {
+      lin_load_tile<true>(sa, A, K, i0, r0, M, act);
+      lin_load_tile<true>(sb, B, K, j0, r0, N, 0);
+    } else if (MODE == 1) {
+      lin_load_tile<true>(sa, A, N, i0, r0, M, 0);
+      lin_load_tile<false>(sb, B, K, j0, r0, N, 0);
+    } else {
+      lin_load_tile<false>(sa, A, N, i0, r0, M, 0);
+      lin_load_tile<false>(sb, B, K, j0, r0, M, act);
+    }
+    __syncthreads();
+#pragma unroll
+    for (int r = 0; r < 16; ++r) {
+      const float4 a4 = *reinterpret_cast<const float4*>(&sa[r][ty * 4]);
+      const float4 b4 = *reinterpret_cast<const float4*>(&sb[r][tx * 4]);
+      const float av[4] = {a4.x, a4.y, a4.z, a4.w}, bv[4] = {b4.x, b4.y, b4.z, b4.w};
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        if (MODE == 2) bacc[i] += av[i];
+#pragma unroll
+        for (int j = 0; j < 4; ++j) acc[i][j] = fmaf(av[i], bv[j], acc[i][j]);
+      }
+    }
+    __syncthreads();
+  }
+  const int ldc = MODE == 0 ? N : K;
+  const int i_lim = MODE == 2 ? N : M;
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    const int gi = i0 + ty * 4 + i;
+    if (gi >= i_lim) continue;
+    const int gj = j0 + tx * 4;
+    float4 o = make_float4(acc[i][0], acc[i][1], acc[i][2], acc[i][3]);
+    float* dst = Cout + static_cast<size_t>(gi) * ldc + gj;
+    if (MODE == 0) {
+      if (aux) {
+        const float4 b = *reinterpret_cast<const float4*>(aux + gj);
+        o.x += b.x; o.y += b.y; o.z += b.z; o.w += b.w;
+      }
+      *reinterpret_cast<float4*>(dst) = o;
+    } else if (MODE == 1) {
+      if (act) {
+        const float4 u = *reinterpret_cast<const float4*>(aux + static_cast<size_t>(gi) * K + gj);
+        const float uv[4] = {u.x, u.y, u.z, u.w};
+        float ov[4] = {o.x, o.y, o.z, o.w};
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          const float sg = 1.0f / (1.0f + expf(-uv[j]));
+          ov[j] *= sg * (1.0f + uv[j] * (1.0f - sg));
+        }
+        o = make_float4(ov[0], ov[1], ov[2], ov[3]);
+      }
+      *reinterpret_cast<float4*>(dst) = o;
+    } else {
+      atomicAdd(dst, o.x); atomicAdd(dst + 1, o.y); atomicAdd(dst + 2, o.z); atomicAdd(dst + 3, o.w);
+      if (db && blockIdx.x == 0 && tx == 0) atomicAdd(&db[gi], bacc[i]);
+    }
+  }
+}
+
 // ---------------------------------------------------------------------------------------------- Adam
 // torch.optim.Adam (defaults: amsgrad=False, weight_decay=0), one pass over the flat buffers.  g is scaled by
 // grad_scale first (1/world_size after the allreduce-sum, and/or 1/loss_scale).
@@ -349,16 +452,31 @@ extern "C" int b200_linear(const b200_linear_args* a, void* ws, size_t ws_bytes,
   (void)ws; (void)ws_bytes;
   if (!a || !a->W) return fail_arg("linear: null pointer");
   const int M = a->M, N = a->N, K = a->K;
+  // the 64x64-tile kernel where it gets at least 64 CTAs (batch-512 embedding MLPs); the 16x16 one otherwise
+  const int out_tiles = a->mode == 0 ? (N / 64) * ((M + 63) / 64) : a->mode == 1 ? (K / 64) * ((M + 63) / 64) : (K / 64) * (N / 64);
+  const bool big = (N % 64 == 0) && (K % 64 == 0) && out_tiles >= 64;
   if (a->mode == 0) {
     if (!a->X || !a->Y) return fail_arg("linear fwd: null pointer");
+    if (big) {
+      linear_tile_kernel<0><<<dim3(N / 64, (M + 63) / 64), 256, 0, ST(stream)>>>(a->X, a->W, a->bias, a->Y, nullptr, M, N, K, a->act);
+      return after_launch("linear_tile_kernel<fwd>");
+    }
     linear_fwd_kernel<<<dim3((N + 15) / 16, (M + 15) / 16), 256, 0, ST(stream)>>>(a->X, a->W, a->bias, a->Y, M, N, K, a->act);
     return after_launch("linear_fwd_kernel");
   } else if (a->mode == 1) {
     if (!a->dY || !a->dX || (a->act && !a->X)) return fail_arg("linear bwd_x: null pointer");
+    if (big) {
+      linear_tile_kernel<1><<<dim3(K / 64, (M + 63) / 64), 256, 0, ST(stream)>>>(a->dY, a->W, a->X, a->dX, nullptr, M, N, K, a->act);
+      return after_launch("linear_tile_kernel<bwd_x>");
+    }
     linear_bwd_x_kernel<<<dim3((K + 15) / 16, (M + 15) / 16), 256, 0, ST(stream)>>>(a->dY, a->W, a->X, a->dX, M, N, K, a->act);
     return after_launch("linear_bwd_x_kernel");
   } else if (a->mode == 2) {
     if (!a->dY || !a->X || !a->dW) return fail_arg("linear bwd_w: null pointer");
+    if (big) {
+      linear_tile_kernel<2><<<dim3(K / 64, N / 64), 256, 0, ST(stream)>>>(a->dY, a->X, nullptr, a->dW, a->db, M, N, K, a->act);
+      return after_launch("linear_tile_kernel<bwd_w>");
+    }
     linear_bwd_w_kernel<<<dim3((K + 15) / 16, (N + 15) / 16), 256, 0, ST(stream)>>>(a->dY, a->X, a->dW, a->db, M, N, K, a->act);
     return after_launch("linear_bwd_w_kernel");
   }

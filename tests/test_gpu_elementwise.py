@@ -146,3 +146,36 @@ def test_adam_matches_torch(lib):
                          grad_scale=0.5, step_dev=ptr(step), step=0)
         lib.call("b200_adam", a, stream())
         assert (p.cpu() - ref.detach()).abs().max().item() < 2e-6
+
+
+@pytest.mark.parametrize("M,N,K", [(6, 128, 512), (3, 512, 128), (512, 1664, 512), (500, 512, 128), (512, 512, 512)])
+@pytest.mark.parametrize("act", [0, 1])
+def test_linear_fwd_bwd_vs_torch(lib, M, N, K, act):
+    """b200_linear (the embedding MLPs: simple_unet.py:33-37 time_embed, :119-121 emb_layers) in its three modes against
+    torch fp32 on the CPU: Y = silu?(X) W^T + b, dX = dY W (* silu'(X)), dW += dY^T silu?(X), db += colsum(dY).  The
+    batch-512 shapes take the 64x64-tile kernel (500 = a ragged last tile), the small ones the 16x16 one.  fp32 FMAs
+    in a different summation order: 1e-5 relative."""
+    g = torch.Generator().manual_seed(M * 7 + N + act)
+    X = torch.randn(M, K, generator=g)
+    W = torch.randn(N, K, generator=g) / K ** 0.5
+    b = torch.randn(N, generator=g)
+    dY = torch.randn(M, N, generator=g)
+    Xr = X.clone().requires_grad_(True)
+    Wr = W.clone().requires_grad_(True)
+    br = b.clone().requires_grad_(True)
+    Yr = torch.nn.functional.linear(torch.nn.functional.silu(Xr) if act else Xr, Wr, br)
+    Yr.backward(dY)
+    d = {k: v.to(DEV) for k, v in dict(X=X, W=W, b=b, dY=dY).items()}
+    Y = torch.empty(M, N, device=DEV)
+    dX = torch.empty(M, K, device=DEV)
+    dW = torch.zeros(N, K, device=DEV)
+    db = torch.zeros(N, device=DEV)
+    base = dict(X=ptr(d["X"]), W=ptr(d["W"]), bias=ptr(d["b"]), Y=ptr(Y), dY=ptr(d["dY"]), dX=ptr(dX), dW=ptr(dW),
+                db=ptr(db), M=M, N=N, K=K, act=act)
+    for mode in (0, 1, 2):
+        lib.call("b200_linear", lib.LinearArgs(mode=mode, **base), stream())
+    torch.cuda.synchronize()
+    assert rel(Y.cpu(), Yr.detach()) < 1e-5
+    assert rel(dX.cpu(), Xr.grad) < 1e-5
+    assert rel(dW.cpu(), Wr.grad) < 1e-5
+    assert rel(db.cpu(), br.grad) < 1e-5
