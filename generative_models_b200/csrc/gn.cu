@@ -116,6 +116,8 @@ gn_fwd_fused_kernel(GnSrc s, float* __restrict__ stats, const float* __restrict_
   if (tid < 16) red[tid] = 0.f;
   src += static_cast<size_t>(n) * s.HW * ld;
   for (int idx = tid; idx < total; idx += kGnThreads) cp_async16(&gn_smem[idx], src + static_cast<size_t>(idx / L) * ld);
+  const float4 ga = __ldg(reinterpret_cast<const float4*>(gamma + c));  // in flight with the slice
+  const float4 be = __ldg(reinterpret_cast<const float4*>(beta + c));
   cp_async_wait_all();
   __syncthreads();
   const bool pair = (cpg == 8);
@@ -142,8 +144,6 @@ gn_fwd_fused_kernel(GnSrc s, float* __restrict__ stats, const float* __restrict_
   const float rstd = rsqrtf(red[8 + gl] * inv_cnt + eps);
   if (tid < L && (!pair || !(tid & 1)))
     *reinterpret_cast<float2*>(stats + (static_cast<size_t>(n) * 32 + c / cpg) * 2) = make_float2(mean, rstd);
-  const float4 ga = *reinterpret_cast<const float4*>(gamma + c);
-  const float4 be = *reinterpret_cast<const float4*>(beta + c);
   const float4 sc = make_float4(rstd * ga.x, rstd * ga.y, rstd * ga.z, rstd * ga.w);
   // tf32: 0 = plain fp32, 1 = fp32 rounded to TF32, 2 = bf16 (y then holds 2-byte elements)
   float* dst = y + static_cast<size_t>(n) * s.HW * s.C + c;
@@ -222,12 +222,21 @@ gn_bwd_fused_kernel(GnSrc s, const float* __restrict__ stats, const float* __res
     cp_async16(&xs[idx], src + pix * ld);
     cp_async16(&ds[idx], dsrc + pix * s.C);
   }
+  // the rows of the add tensors that phase 2 will read are pulled into L2 now (its loads were the top stall)
+  if (c0 < add_c) {
+    for (int pix = tid; pix < s.HW; pix += kGnThreads) {
+      if (add1) asm volatile("prefetch.global.L2 [%0];" ::"l"(add1 + (row0 + pix) * add1_ld + c0));
+      if (add2) asm volatile("prefetch.global.L2 [%0];" ::"l"(add2 + (row0 + pix) * add2_ld + c0));
+    }
+  }
+  // statistics and affine parameters are requested while the slice is still in flight (after the wait their
+  // latency was fully exposed: 11 % of the stall samples)
+  const float2 st = __ldg(reinterpret_cast<const float2*>(stats + (static_cast<size_t>(n) * 32 + c / cpg) * 2));
+  const float4 ga4 = __ldg(reinterpret_cast<const float4*>(gamma + c));
+  const float4 be4 = __ldg(reinterpret_cast<const float4*>(beta + c));
   cp_async_wait_all();
   __syncthreads();
-  const float2 st = *reinterpret_cast<const float2*>(stats + (static_cast<size_t>(n) * 32 + c / cpg) * 2);
   const float mean = st.x, rstd = st.y;
-  const float4 ga4 = *reinterpret_cast<const float4*>(gamma + c);
-  const float4 be4 = *reinterpret_cast<const float4*>(beta + c);
   const float ga[4] = {ga4.x, ga4.y, ga4.z, ga4.w};
   const float be[4] = {be4.x, be4.y, be4.z, be4.w};
   float dg[4] = {0.f, 0.f, 0.f, 0.f}, db[4] = {0.f, 0.f, 0.f, 0.f};
@@ -379,6 +388,8 @@ gn_fwd_bfx_kernel(GnSrc s, float* __restrict__ stats, const float* __restrict__ 
                          static_cast<size_t>(n) * s.HW * ld;
   if (tid < 16) red[tid] = 0.f;
   gn_stage<CS, 2, T>(reinterpret_cast<uint8_t*>(gn_smem), base, ld, s.HW, tid);
+  const float4 ga = __ldg(reinterpret_cast<const float4*>(gamma + c));  // in flight with the slice
+  const float4 be = __ldg(reinterpret_cast<const float4*>(beta + c));
   cp_async_wait_all();
   __syncthreads();
   const bool pair = (cpg == 8);
@@ -405,8 +416,6 @@ gn_fwd_bfx_kernel(GnSrc s, float* __restrict__ stats, const float* __restrict__ 
   const float rstd = rsqrtf(red[8 + gl] * inv_cnt + eps);
   if (tid < L && (!pair || !(tid & 1)))
     *reinterpret_cast<float2*>(stats + (static_cast<size_t>(n) * 32 + c / cpg) * 2) = make_float2(mean, rstd);
-  const float4 ga = *reinterpret_cast<const float4*>(gamma + c);
-  const float4 be = *reinterpret_cast<const float4*>(beta + c);
   const float4 sc = make_float4(rstd * ga.x, rstd * ga.y, rstd * ga.z, rstd * ga.w);
   float* dst = y + static_cast<size_t>(n) * s.HW * s.C + c;
   uint16_t* dstb = reinterpret_cast<uint16_t*>(y) + static_cast<size_t>(n) * s.HW * s.C + c;
@@ -463,12 +472,19 @@ gn_bwd_raw_kernel(GnSrc s, const float* __restrict__ stats, const float* __restr
   if (tid < CS) csum[tid] = 0.f;
   gn_stage<CS, XB, T>(xraw, xbase, ld, s.HW, tid);
   gn_stage<CS, DB, T>(draw, dbase, s.C, s.HW, tid);
+  if (c0 < add_c) {  // add-tensor rows of phase 2 into L2 now
+    for (int pix = tid; pix < s.HW; pix += T) {
+      if (add1) asm volatile("prefetch.global.L2 [%0];" ::"l"(add1 + (row0 + pix) * add1_ld + c0));
+      if (add2) asm volatile("prefetch.global.L2 [%0];" ::"l"(add2 + (row0 + pix) * add2_ld + c0));
+    }
+  }
+  // statistics / affine parameters requested while the slice is in flight
+  const float2 st = __ldg(reinterpret_cast<const float2*>(stats + (static_cast<size_t>(n) * 32 + c / cpg) * 2));
+  const float4 ga4 = __ldg(reinterpret_cast<const float4*>(gamma + c));
+  const float4 be4 = __ldg(reinterpret_cast<const float4*>(beta + c));
   cp_async_wait_all();
   __syncthreads();
-  const float2 st = *reinterpret_cast<const float2*>(stats + (static_cast<size_t>(n) * 32 + c / cpg) * 2);
   const float mean = st.x, rstd = st.y;
-  const float4 ga4 = *reinterpret_cast<const float4*>(gamma + c);
-  const float4 be4 = *reinterpret_cast<const float4*>(beta + c);
   const float ga[4] = {ga4.x, ga4.y, ga4.z, ga4.w};
   const float be[4] = {be4.x, be4.y, be4.z, be4.w};
   const float nmr = -mean * rstd;
