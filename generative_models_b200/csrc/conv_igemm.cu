@@ -144,6 +144,16 @@ conv_igemm_tf32_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_con
     // float4 accesses) and then streams them out one row per instruction: 512 contiguous bytes per warp access for
     // the output, the residual and the embedding row alike.
     const int quarter = warp & 3;  // TMEM lane quarter this warp may read
+    if (a.residual) {
+      // these warps idle through the main loop: pull the 32 residual rows this warp will add into L2 meanwhile, so the
+      // epilogue's loads see L2 latency (the residual add cost 26 us on a 66 us 14x14 layer)
+      const int m = m0 + quarter * 32 + lane;
+      if (m < a.M_total) {
+        const float* rp = a.residual + static_cast<size_t>(m) * a.res_ld;
+#pragma unroll
+        for (int k = 0; k < 4; ++k) asm volatile("prefetch.global.L2 [%0];" ::"l"(rp + k * 32));
+      }
+    }
     mbar_wait(tmem_full, 0);
     tc_fence_after();
     constexpr int kPitch = 132;
