@@ -65,33 +65,54 @@ conv_in_fwd_kernel(const float* __restrict__ x, const float* __restrict__ w, con
 // ------------------------------------------------------------------------------------------------ conv_in backward
 // dw[c][tap] += sum_pix dy[pix][c] * x[pix + tap];  db[c] += sum_pix dy[pix][c].  grid (chunks, N), block 256:
 // thread = (pixel row r = tid/32, channel quad tid%32); 40 register accumulators, smem reduce over the 8 pixel rows.
+// The image is staged zero-padded in shared memory (no bounds tests, no global loads in the tap loop) and the dy rows
+// of FOUR pixels are requested before any of them is used: the kernel reads 205 MB and was bound by one exposed load
+// latency per pixel (112 us; 31 us is the HBM time).
 __global__ void __launch_bounds__(256)
 conv_in_bwd_kernel(const float* __restrict__ x, const float* __restrict__ dy, float* __restrict__ dw,
                    float* __restrict__ db, int H, int W, int pix_per_chunk) {
   __shared__ float sh[8][32][41];
+  extern __shared__ float simg[];  // (H + 2) x (W + 2), zero border
   const int n = blockIdx.y;
   const int q = threadIdx.x & 31, r = threadIdx.x >> 5;
-  const int HW = H * W;
+  const int HW = H * W, Wp = W + 2;
   const float* img = x + static_cast<size_t>(n) * HW;
+  for (int i = threadIdx.x; i < (H + 2) * Wp; i += 256) {
+    const int yy = i / Wp - 1, xx = i - (yy + 1) * Wp - 1;
+    simg[i] = (yy >= 0 && yy < H && xx >= 0 && xx < W) ? img[yy * W + xx] : 0.f;
+  }
+  __syncthreads();
   float acc[10][4];
 #pragma unroll
   for (int t = 0; t < 10; ++t)
 #pragma unroll
     for (int j = 0; j < 4; ++j) acc[t][j] = 0.f;
   const int p0 = blockIdx.x * pix_per_chunk, p1 = min(p0 + pix_per_chunk, HW);
-  for (int p = p0 + r; p < p1; p += 8) {
-    const float4 d = *reinterpret_cast<const float4*>(dy + (static_cast<size_t>(n) * HW + p) * 128 + q * 4);
-    const int y = p / W, xx = p - y * W;
+  const float* dyn = dy + static_cast<size_t>(n) * HW * 128 + q * 4;
+  for (int p = p0 + r; p < p1; p += 32) {
+    float4 d[4];
 #pragma unroll
-    for (int kh = 0; kh < 3; ++kh)
+    for (int u = 0; u < 4; ++u) {
+      const int pp = p + 8 * u;
+      d[u] = pp < p1 ? __ldg(reinterpret_cast<const float4*>(dyn + static_cast<size_t>(pp) * 128))
+                     : make_float4(0.f, 0.f, 0.f, 0.f);
+    }
 #pragma unroll
-      for (int kw = 0; kw < 3; ++kw) {
-        const int yy = y + kh - 1, xw = xx + kw - 1;
-        const float v = (yy >= 0 && yy < H && xw >= 0 && xw < W) ? img[yy * W + xw] : 0.f;
-        acc[kh * 3 + kw][0] += d.x * v; acc[kh * 3 + kw][1] += d.y * v;
-        acc[kh * 3 + kw][2] += d.z * v; acc[kh * 3 + kw][3] += d.w * v;
-      }
-    acc[9][0] += d.x; acc[9][1] += d.y; acc[9][2] += d.z; acc[9][3] += d.w;
+    for (int u = 0; u < 4; ++u) {
+      const int pp = p + 8 * u;
+      if (pp >= p1) break;
+      const int y = pp / W, xx = pp - y * W;
+      const float* sp = simg + y * Wp + xx;  // padded (y, xx) = tap (0, 0)
+#pragma unroll
+      for (int kh = 0; kh < 3; ++kh)
+#pragma unroll
+        for (int kw = 0; kw < 3; ++kw) {
+          const float v = sp[kh * Wp + kw];
+          acc[kh * 3 + kw][0] += d[u].x * v; acc[kh * 3 + kw][1] += d[u].y * v;
+          acc[kh * 3 + kw][2] += d[u].z * v; acc[kh * 3 + kw][3] += d[u].w * v;
+        }
+      acc[9][0] += d[u].x; acc[9][1] += d[u].y; acc[9][2] += d[u].z; acc[9][3] += d[u].w;
+    }
   }
 #pragma unroll
   for (int t = 0; t < 10; ++t)
@@ -129,14 +150,15 @@ conv_out_fwd_kernel(const float* __restrict__ h, const float* __restrict__ w, co
   const int jj = (b1 ? 1 : 0) + (b2 ? 2 : 0), j5 = jj + (b3 ? 3 : 0), tap = j5 + (b4 ? 5 : 0);
   const bool writer = !(lane & 1) && jj < 3 && j5 < 5 && tap < 9;
   const float* hn = h + static_cast<size_t>(n) * HW * 128 + lane * 4;
-  for (int p = warp; p < HW; p += 16) {  // two pixels per iteration: two independent 512 B loads in flight per warp
-    const int p2 = p + 8;
-    const bool has2 = p2 < HW;
-    const float4 va = *reinterpret_cast<const float4*>(hn + static_cast<size_t>(p) * 128);
-    const float4 vb = has2 ? *reinterpret_cast<const float4*>(hn + static_cast<size_t>(p2) * 128) : make_float4(0.f, 0.f, 0.f, 0.f);
+  for (int p = warp; p < HW; p += 32) {  // four pixels per iteration: four independent 512 B loads in flight per warp
+    float4 vv[4];
 #pragma unroll
-    for (int half = 0; half < 2; ++half) {
-      const float4 v = half ? vb : va;
+    for (int u = 0; u < 4; ++u)
+      vv[u] = (p + 8 * u < HW) ? __ldg(reinterpret_cast<const float4*>(hn + static_cast<size_t>(p + 8 * u) * 128))
+                               : make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+    for (int half = 0; half < 4; ++half) {
+      const float4 v = vv[half];
       float d[10];
 #pragma unroll
       for (int t = 0; t < 9; ++t) d[t] = v.x * wv[t].x + v.y * wv[t].y + v.z * wv[t].z + v.w * wv[t].w;
@@ -157,8 +179,8 @@ conv_out_fwd_kernel(const float* __restrict__ h, const float* __restrict__ w, co
         z2[i] = (b2 ? q[2 + i] : q[i]) + __shfl_xor_sync(0xffffffffu, b2 ? q[i] : q[2 + i], 4);
       float z = (b1 ? z2[1] : z2[0]) + __shfl_xor_sync(0xffffffffu, b1 ? z2[0] : z2[1], 2);
       z += __shfl_xor_sync(0xffffffffu, z, 1);
-      const int pp = half ? p2 : p;
-      if (writer && (half == 0 || has2)) part[pp * 9 + tap] = z;
+      const int pp = p + 8 * half;
+      if (writer && pp < HW) part[pp * 9 + tap] = z;
     }
   }
   __syncthreads();
@@ -183,16 +205,19 @@ conv_out_fwd_kernel(const float* __restrict__ h, const float* __restrict__ w, co
 __global__ void __launch_bounds__(256)
 conv_out_bwd_kernel(const float* __restrict__ h, const float* __restrict__ w, const float* __restrict__ dout,
                     float* __restrict__ dh, float* __restrict__ dw, float* __restrict__ db, int H, int W, int round_dh) {
-  extern __shared__ float sm[];  // [HW] dout, then [8][9][128] dw partials
+  extern __shared__ float sm[];  // [(H+2)(W+2)] zero-padded dout, then [8][9][128] dw partials
   const int n = blockIdx.x;
-  const int HW = H * W;
+  const int HW = H * W, Wp = W + 2;
+  const int padded = (H + 2) * Wp;
   float* sd = sm;
-  float* sdw = sm + ((HW + 3) & ~3);
+  float* sdw = sm + ((padded + 3) & ~3);
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   float bsum = 0.f;
-  for (int p = threadIdx.x; p < HW; p += blockDim.x) {
-    const float v = dout[static_cast<size_t>(n) * HW + p];
-    sd[p] = v;
+  for (int i = threadIdx.x; i < padded; i += blockDim.x) {
+    const int yy = i / Wp - 1, xx = i - (yy + 1) * Wp - 1;
+    float v = 0.f;
+    if (yy >= 0 && yy < H && xx >= 0 && xx < W) v = dout[static_cast<size_t>(n) * HW + yy * W + xx];
+    sd[i] = v;
     bsum += v;
   }
   __syncthreads();
@@ -202,23 +227,33 @@ conv_out_bwd_kernel(const float* __restrict__ h, const float* __restrict__ w, co
     wv[t] = *reinterpret_cast<const float4*>(w + t * 128 + lane * 4);
     aw[t] = make_float4(0.f, 0.f, 0.f, 0.f);
   }
-  for (int p = warp; p < HW; p += 8) {
-    const size_t off = (static_cast<size_t>(n) * HW + p) * 128 + lane * 4;
-    const float4 v = *reinterpret_cast<const float4*>(h + off);
-    const int y = p / W, xx = p - y * W;
-    float4 g = make_float4(0.f, 0.f, 0.f, 0.f);
+  const size_t base = static_cast<size_t>(n) * HW * 128 + lane * 4;
+  for (int p = warp; p < HW; p += 32) {  // four pixels per trip, their 512 B rows of h requested together
+    float4 vv[4];
 #pragma unroll
-    for (int kh = 0; kh < 3; ++kh)
+    for (int u = 0; u < 4; ++u)
+      vv[u] = (p + 8 * u < HW) ? __ldg(reinterpret_cast<const float4*>(h + base + static_cast<size_t>(p + 8 * u) * 128))
+                               : make_float4(0.f, 0.f, 0.f, 0.f);
 #pragma unroll
-      for (int kw = 0; kw < 3; ++kw) {
-        const int yy = y - kh + 1, xw = xx - kw + 1;
-        const float d = (yy >= 0 && yy < H && xw >= 0 && xw < W) ? sd[yy * W + xw] : 0.f;
-        const int t = kh * 3 + kw;
-        g.x += d * wv[t].x; g.y += d * wv[t].y; g.z += d * wv[t].z; g.w += d * wv[t].w;
-        aw[t].x += d * v.x; aw[t].y += d * v.y; aw[t].z += d * v.z; aw[t].w += d * v.w;
-      }
-    if (round_dh) g = round_tf32(g);
-    *reinterpret_cast<float4*>(dh + off) = g;
+    for (int u = 0; u < 4; ++u) {
+      const int pp = p + 8 * u;
+      if (pp >= HW) break;
+      const float4 v = vv[u];
+      const int y = pp / W, xx = pp - y * W;
+      const float* sp = sd + (y + 2) * Wp + xx + 2;  // padded position of (y + 1, xx + 1): tap (kh, kw) reads sp[-kh*Wp - kw]
+      float4 g = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+      for (int kh = 0; kh < 3; ++kh)
+#pragma unroll
+        for (int kw = 0; kw < 3; ++kw) {
+          const float d = sp[-kh * Wp - kw];
+          const int t = kh * 3 + kw;
+          g.x += d * wv[t].x; g.y += d * wv[t].y; g.z += d * wv[t].z; g.w += d * wv[t].w;
+          aw[t].x += d * v.x; aw[t].y += d * v.y; aw[t].z += d * v.z; aw[t].w += d * v.w;
+        }
+      if (round_dh) g = round_tf32(g);
+      *reinterpret_cast<float4*>(dh + base + static_cast<size_t>(pp) * 128) = g;
+    }
   }
 #pragma unroll
   for (int t = 0; t < 9; ++t) *reinterpret_cast<float4*>(sdw + (warp * 9 + t) * 128 + lane * 4) = aw[t];
@@ -256,8 +291,16 @@ extern "C" int b200_conv_in_bwd(const b200_conv_in_args* a, void* ws, size_t ws_
   if (chunks > (HW + 63) / 64) chunks = (HW + 63) / 64;
   if (chunks < 1) chunks = 1;
   const int ppc = (HW + chunks - 1) / chunks;
-  conv_in_bwd_kernel<<<dim3(chunks, a->N), 256, 0, static_cast<cudaStream_t>(stream)>>>(a->x, a->dy, a->dw, a->db, a->H,
-                                                                                        a->W, ppc);
+  const size_t img_smem = static_cast<size_t>(a->H + 2) * (a->W + 2) * sizeof(float);
+  if (img_smem > 64 * 1024) return fail_arg("conv_in_bwd: image too large for the shared-memory copy");
+  static bool in_bwd_attr = false;
+  if (!in_bwd_attr) {
+    cudaError_t e = cudaFuncSetAttribute(conv_in_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024);
+    if (e != cudaSuccess) return check_cuda(e, "cudaFuncSetAttribute(conv_in_bwd)");
+    in_bwd_attr = true;
+  }
+  conv_in_bwd_kernel<<<dim3(chunks, a->N), 256, img_smem, static_cast<cudaStream_t>(stream)>>>(a->x, a->dy, a->dw, a->db,
+                                                                                               a->H, a->W, ppc);
   return after_launch("conv_in_bwd_kernel");
 }
 
@@ -281,11 +324,11 @@ extern "C" int b200_conv_out_bwd(const b200_conv_out_args* a, void* ws, size_t w
   (void)ws; (void)ws_bytes;
   if (!a || !a->h || !a->w || !a->dout || !a->dh || !a->dw || !a->db) return fail_arg("conv_out_bwd: null pointer");
   const int HW = a->H * a->W;
-  if (HW > 4096) return fail_arg("conv_out_bwd: H*W must be <= 4096");
-  const size_t smem = (static_cast<size_t>((HW + 3) & ~3) + 8 * 9 * 128) * sizeof(float);
+  if (HW > 4096 || a->H > 64 || a->W > 64) return fail_arg("conv_out_bwd: H and W must be <= 64");
+  const size_t smem = (static_cast<size_t>(((a->H + 2) * (a->W + 2) + 3) & ~3) + 8 * 9 * 128) * sizeof(float);
   static bool attr_set = false;
   if (!attr_set) {
-    cudaError_t e = cudaFuncSetAttribute(conv_out_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (4096 + 8 * 9 * 128) * 4);
+    cudaError_t e = cudaFuncSetAttribute(conv_out_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (66 * 66 + 4 + 8 * 9 * 128) * 4);
     if (e != cudaSuccess) return check_cuda(e, "cudaFuncSetAttribute(conv_out_bwd)");
     attr_set = true;
   }
