@@ -245,26 +245,30 @@ linear_bwd_w_kernel(const float* __restrict__ dY, const float* __restrict__ X, f
 // index) — otherwise the output index is contiguous (row = reduction index).  I x J x R need not be tile multiples in
 // I (the batch); J and R are multiples of 64 / 16 (checked by the host).
 template <bool RC>
-__device__ __forceinline__ void lin_load_tile(float (*dst)[68], const float* __restrict__ src, int ld, int o0, int r0,
-                                              int o_lim, int act) {
+__device__ __forceinline__ float4 lin_fetch(const float* __restrict__ src, int ld, int o0, int r0, int o_lim, int act) {
   const int t = threadIdx.x;
-  if (RC) {  // src[(o0 + o) * ld + r0 + r]: thread -> (o = t / 4, r = 4 * (t % 4)), stored transposed
+  float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+  if (RC) {  // src[(o0 + o) * ld + r0 + r]: thread -> (o = t / 4, r = 4 * (t % 4))
     const int o = t >> 2, r4 = (t & 3) * 4;
-    float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
-    if (o0 + o < o_lim) v = *reinterpret_cast<const float4*>(src + static_cast<size_t>(o0 + o) * ld + r0 + r4);
-    if (act) {
-      v.x = v.x / (1.0f + expf(-v.x)); v.y = v.y / (1.0f + expf(-v.y));
-      v.z = v.z / (1.0f + expf(-v.z)); v.w = v.w / (1.0f + expf(-v.w));
-    }
-    dst[r4][o] = v.x; dst[r4 + 1][o] = v.y; dst[r4 + 2][o] = v.z; dst[r4 + 3][o] = v.w;
-  } else {  // src[(r0 + r) * ld + o0 + o]: thread -> (r = t / 16, o = 4 * (t % 16)); rows past o_lim do not occur
+    if (o0 + o < o_lim) v = __ldg(reinterpret_cast<const float4*>(src + static_cast<size_t>(o0 + o) * ld + r0 + r4));
+  } else {  // src[(r0 + r) * ld + o0 + o]: thread -> (r = t / 16, o = 4 * (t % 16)); o_lim bounds the reduction rows
     const int r = t >> 4, o4 = (t & 15) * 4;
-    float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
-    if (r0 + r < o_lim) v = *reinterpret_cast<const float4*>(src + static_cast<size_t>(r0 + r) * ld + o0 + o4);
-    if (act) {
-      v.x = v.x / (1.0f + expf(-v.x)); v.y = v.y / (1.0f + expf(-v.y));
-      v.z = v.z / (1.0f + expf(-v.z)); v.w = v.w / (1.0f + expf(-v.w));
-    }
+    if (r0 + r < o_lim) v = __ldg(reinterpret_cast<const float4*>(src + static_cast<size_t>(r0 + r) * ld + o0 + o4));
+  }
+  if (act) {
+    v.x = v.x / (1.0f + expf(-v.x)); v.y = v.y / (1.0f + expf(-v.y));
+    v.z = v.z / (1.0f + expf(-v.z)); v.w = v.w / (1.0f + expf(-v.w));
+  }
+  return v;
+}
+template <bool RC>
+__device__ __forceinline__ void lin_put(float (*dst)[68], float4 v) {
+  const int t = threadIdx.x;
+  if (RC) {  // stored transposed: reduction-major
+    const int o = t >> 2, r4 = (t & 3) * 4;
+    dst[r4][o] = v.x; dst[r4 + 1][o] = v.y; dst[r4 + 2][o] = v.z; dst[r4 + 3][o] = v.w;
+  } else {
+    const int r = t >> 4, o4 = (t & 15) * 4;
     *reinterpret_cast<float4*>(&dst[r][o4]) = v;
   }
 }
@@ -281,17 +285,26 @@ linear_tile_kernel(const float* __restrict__ A, const float* __restrict__ B, con
   const int R = MODE == 0 ? K : (MODE == 1 ? N : M);
   float acc[4][4] = {};
   float bacc[4] = {0.f, 0.f, 0.f, 0.f};
-  for (int r0 = 0; r0 < R; r0 += 16) {
+  // global -> register fetch of tile r0 + 16 is issued before the FMAs on tile r0 (its latency was exposed once per
+  // 16-deep step)
+  auto fetch = [&](int r0, float4& fa, float4& fb) {
     if (MODE == 0) {
-      lin_load_tile<true>(sa, A, K, i0, r0, M, act);
-      lin_load_tile<true>(sb, B, K, j0, r0, N, 0);
+      fa = lin_fetch<true>(A, K, i0, r0, M, act);
+      fb = lin_fetch<true>(B, K, j0, r0, N, 0);
     } else if (MODE == 1) {
-      lin_load_tile<true>(sa, A, N, i0, r0, M, 0);
-      lin_load_tile<false>(sb, B, K, j0, r0, N, 0);
+      fa = lin_fetch<true>(A, N, i0, r0, M, 0);
+      fb = lin_fetch<false>(B, K, j0, r0, N, 0);
     } else {
-      lin_load_tile<false>(sa, A, N, i0, r0, M, 0);
-      lin_load_tile<false>(sb, B, K, j0, r0, M, act);
+      fa = lin_fetch<false>(A, N, i0, r0, M, 0);
+      fb = lin_fetch<false>(B, K, j0, r0, M, act);
     }
+  };
+  float4 fa, fb;
+  fetch(0, fa, fb);
+  for (int r0 = 0; r0 < R; r0 += 16) {
+    lin_put<MODE != 2>(sa, fa);
+    lin_put<MODE == 0>(sb, fb);
+    if (r0 + 16 < R) fetch(r0 + 16, fa, fb);
     __syncthreads();
 #pragma unroll
     for (int r = 0; r < 16; ++r) {
@@ -452,9 +465,15 @@ extern "C" int b200_linear(const b200_linear_args* a, void* ws, size_t ws_bytes,
   (void)ws; (void)ws_bytes;
   if (!a || !a->W) return fail_arg("linear: null pointer");
   const int M = a->M, N = a->N, K = a->K;
-  // the 64x64-tile kernel where it gets at least 64 CTAs (batch-512 embedding MLPs); the 16x16 one otherwise
+  // the 64x64-tile kernel where it gets at least 32 CTAs (batch-512 embedding MLPs; measured 64: 0.343 ms for the 13
+  // linears of a step, 32: 0.328, 16: 0.369); the 16x16 one otherwise
   const int out_tiles = a->mode == 0 ? (N / 64) * ((M + 63) / 64) : a->mode == 1 ? (K / 64) * ((M + 63) / 64) : (K / 64) * (N / 64);
-  const bool big = (N % 64 == 0) && (K % 64 == 0) && out_tiles >= 64;
+  static int min_tiles = -1;  // developer knob B200_LIN_MIN_TILES
+  if (min_tiles < 0) {
+    const char* e = getenv("B200_LIN_MIN_TILES");
+    min_tiles = e ? atoi(e) : 32;
+  }
+  const bool big = (N % 64 == 0) && (K % 64 == 0) && out_tiles >= min_tiles;
   if (a->mode == 0) {
     if (!a->X || !a->Y) return fail_arg("linear fwd: null pointer");
     if (big) {
