@@ -429,3 +429,32 @@ def test_full_batch_512_vs_oracle(built_lib, oracle_b512, precision):
     _, b6 = m.loss_and_grads(o["x"][:6].to(DEV), o["y"][:6].to(DEV), eps=o["eps"][:6].to(DEV), u=o["u"][:6].to(DEV))
     small = b6.plan.out.cpu().view(6, 1, 28, 28)
     assert rms_rel(small, ours[:6]) < 2 * net_tol
+
+
+@pytest.mark.parametrize("precision", ["tf32", "bf16"])
+@pytest.mark.parametrize("B", [1, 5, 33])
+def test_ragged_batch_sizes_vs_oracle(built_lib, B, precision):
+    """batch sizes that fill none of the tiles evenly (1, 5, 33 images: partial 128- and 256-position tiles, a ragged
+    64-row linear tile, GroupNorm grids of a few CTAs): loss, net output and the gradient norm against the oracle."""
+    from tests.test_gpu_bf16 import BF16_NET_TOL
+    g = torch.Generator().manual_seed(100 + B)
+    x = torch.rand(B, 1, 28, 28, generator=g) * 2 - 1
+    y = torch.randint(-1, 10, (B,), generator=g)
+    eps = torch.randn(B, 1, 28, 28, generator=g)
+    u = torch.rand(B, generator=g) * 0.8 + 0.1
+    m, sd0 = make_model(built_lib, mean_type="eps", precision=precision)
+    sd = {k: v.clone().requires_grad_(True) for k, v in sd0.items()}
+    loss, per, aux = O.training_loss(sd, x, y, eps, u, "eps")
+    m.store.grad.zero_()
+    l2, b = m.loss_and_grads(x.to(DEV), y.to(DEV), eps=eps.to(DEV), u=u.to(DEV))
+    ours = b.plan.out.cpu().view(B, 1, 28, 28)
+    tol = NET_TOL if precision == "tf32" else BF16_NET_TOL
+    assert rms_rel(ours, aux["out"].detach()) < tol
+    assert abs(float(l2) - loss.item()) / loss.item() < (3e-3 if precision == "tf32" else 3e-2)
+    assert torch.isfinite(m.store.grad).all()
+    out = m.train_step(x.to(DEV), y.to(DEV), eps=eps.to(DEV), u=u.to(DEV))
+    assert torch.isfinite(out["loss"]).item()
+    # and a few sampler steps at this batch (guided: the doubled cond/uncond batch of 2B)
+    m2, _ = make_model(built_lib, mean_type="eps", precision=precision, timesteps=4, sampler="noisy")
+    z = m2.sample(B, y=torch.randint(0, 10, (B,), device=DEV))
+    assert z.shape == (B, 1, 28, 28) and torch.isfinite(z).all()
