@@ -39,7 +39,19 @@ struct ConvK {
   int n_off;
   int out_ld, emb_ld, res_ld;
   int round_out;
+  // mode 2 (backward-data of a stride-2 3x3/pad-1 conv): CTA (tile, class) = (blockIdx.x >> 2, blockIdx.x & 3) runs a
+  // small R x S forward conv over dY (R = 1 + class/2, S = 1 + class%2) whose result row m = (n, i, j) lands on pixel
+  // (2i + class/2, 2j + class%2) of the twice-as-large dX.  The four classes of a tile are neighbours in launch order:
+  // one class alone touches 512 B of every KB of dX, i.e. half of the DRAM channels (measured 1.1 TB/s).
+  int sub;
 };
+
+// output / residual row of GEMM row m
+__device__ __forceinline__ size_t out_row(int sub, int sub_a, int sub_b, int Wo, int m) {
+  if (!sub) return static_cast<size_t>(m);
+  const int g = m / Wo, j = m - g * Wo;  // g = n * Ho + i
+  return static_cast<size_t>(2 * g + sub_a) * (2 * Wo) + 2 * j + sub_b;
+}
 
 __global__ void __launch_bounds__(192)
 conv_igemm_tf32_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmA2,
@@ -74,8 +86,11 @@ conv_igemm_tf32_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_con
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
 
-  const int m0 = blockIdx.x * 128;
-  const int num_it = a.R * a.S * a.chunks;
+  const int cls = a.sub ? (blockIdx.x & 3) : 0;
+  const int sub_a = cls >> 1, sub_b = cls & 1;
+  const int R = a.sub ? 1 + sub_a : a.R, S = a.sub ? 1 + sub_b : a.S;
+  const int m0 = (a.sub ? (blockIdx.x >> 2) : blockIdx.x) * 128;
+  const int num_it = R * S * a.chunks;
 
   if (warp == 0) {
     if (lane == 0) {
@@ -92,7 +107,7 @@ conv_igemm_tf32_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_con
         const uint32_t ph = (it / kStages) & 1;
         mbar_wait(&empty[s], ph ^ 1);
         mbar_expect_tx(&full[s], kStageBytes);
-        const int kh = tap / a.S, kw = tap - kh * a.S;
+        const int kh = tap / S, kw = tap - kh * S;
         uint8_t* sA = smem + s * kStageBytes;
         uint8_t* sB = sA + kTileBytes;
         if (ch < a.chunks1)
@@ -101,9 +116,11 @@ conv_igemm_tf32_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_con
           tma_load_im2col_4d(sA, &tmA2, &full[s], (ch - a.chunks1) * 32, w_base, h_base, n, (uint16_t)kw,
                              (uint16_t)kh);
         if (a.mode == 0) {
-          tma_load_2d(sB, &tmB, &full[s], tap * a.w_rowlen_tap + ch * 32, 0);
+          // mode 2, per axis: dX[2i+1] = dY[i] w[2] + dY[i+1] w[0], dX[2i] = dY[i] w[1]; shadow tap = 8 - original tap
+          const int wt = a.sub ? 8 - ((sub_a ? 2 - 2 * kh : 1) * 3 + (sub_b ? 2 - 2 * kw : 1)) : tap;
+          tma_load_2d(sB, &tmB, &full[s], wt * a.w_rowlen_tap + ch * 32, 0);
         } else {
-          const int wtap = (a.R - 1 - kh) * a.S + (a.S - 1 - kw);
+          const int wtap = (R - 1 - kh) * S + (S - 1 - kw);
 #pragma unroll
           for (int j = 0; j < 4; ++j)
             tma_load_2d(sB + j * 4096, &tmB, &full[s], wtap * a.w_rowlen_tap + a.n_off + j * 32, ch * 32);
@@ -149,7 +166,7 @@ conv_igemm_tf32_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_con
       // epilogue's loads see L2 latency (the residual add cost 26 us on a 66 us 14x14 layer)
       const int m = m0 + quarter * 32 + lane;
       if (m < a.M_total) {
-        const float* rp = a.residual + static_cast<size_t>(m) * a.res_ld;
+        const float* rp = a.residual + out_row(a.sub, sub_a, sub_b, a.Wo, m) * a.res_ld;
 #pragma unroll
         for (int k = 0; k < 4; ++k) asm volatile("prefetch.global.L2 [%0];" ::"l"(rp + k * 32));
       }
@@ -185,7 +202,7 @@ conv_igemm_tf32_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_con
         add[j] = b4;
         const int m = min(m_first + r0 + j, a.M_total - 1);
         if (a.residual) {
-          const float4 e = __ldg(reinterpret_cast<const float4*>(a.residual + static_cast<size_t>(m) * a.res_ld + c));
+          const float4 e = __ldg(reinterpret_cast<const float4*>(a.residual + out_row(a.sub, sub_a, sub_b, a.Wo, m) * a.res_ld + c));
           add[j].x += e.x; add[j].y += e.y; add[j].z += e.z; add[j].w += e.w;
         }
         if (a.emb) {
@@ -203,7 +220,7 @@ conv_igemm_tf32_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_con
                        : "memory");
           v.x += add[j].x; v.y += add[j].y; v.z += add[j].z; v.w += add[j].w;
           if (a.round_out) v = round_tf32(v);
-          *reinterpret_cast<float4*>(a.out + static_cast<size_t>(m_first + r0 + j) * a.out_ld + c) = v;
+          *reinterpret_cast<float4*>(a.out + out_row(a.sub, sub_a, sub_b, a.Wo, m_first + r0 + j) * a.out_ld + c) = v;
         }
       }
     }
@@ -240,6 +257,54 @@ extern "C" int b200_conv_kernel_of(const b200_conv_args* a) {
   return (strip_enabled() && strip_shape(a) && conv_strip_applicable(a)) ? 1 : 0;
 }
 
+// mode 2: backward-data of a stride-2 3x3/pad-1 convolution WITHOUT zero-stuffing dY.  x = dY [N, H, W, 128],
+// w = the transposed, tap-flipped weight shadow [128 ci][9][128 co] that b200_conv_weights_transpose writes,
+// out = dX [N, 2H, 2W, 128] (+ residual in the same layout).  dX[2i+a, 2j+b] only receives the filter taps whose parity
+// matches: (a, b) = (0, 0): tap (1, 1); (0, 1): (1, 0) and (1, 2); (1, 0): (0, 1) and (2, 1); (1, 1): the four corners
+// — nine taps in all instead of the 36 tap evaluations of the zero-stuffed stride-1 formulation.  Each parity class is
+// a 1x1 / 1x2 / 2x1 / 2x2 forward conv over dY (far-edge OOB = zero) whose rows scatter to the class's pixels of dX;
+// one launch, the four classes of a 128-row tile in neighbouring CTAs.
+static int conv_dgrad_stride2(const b200_conv_args* a, void* stream) {
+  if (a->R != 3 || a->S != 3 || a->pad != 1 || a->stride != 2) return fail_arg("conv_igemm mode 2: 3x3 / pad 1 / stride 2 only");
+  if (a->C1 != 128 || a->C2 != 0 || a->w_cout != 128 || a->w_cin != 128)
+    return fail_arg("conv_igemm mode 2: dY and dX have 128 channels, w is the [128][9][128] transposed shadow");
+  if (a->Ho != 2 * a->H || a->Wo != 2 * a->W) return fail_arg("conv_igemm mode 2: out must be twice the size of dY");
+  if (a->bias || a->emb || a->skip_x || a->out_dtype || a->op_dtype || a->out_bf16)
+    return fail_arg("conv_igemm mode 2: plain fp32 output (+ residual) only");
+  if (a->out_ld % 4 || (a->residual && a->res_ld % 4)) return fail_arg("conv_igemm: leading dimensions must be multiples of 4 floats");
+  CUtensorMap tmA, tmB;
+  int r = get_tmap_im2col(a->x, a->N, a->H, a->W, 128, a->x_ld ? a->x_ld : 128, 0, 0, 1, 32, 128, 4, 0, &tmA);
+  if (r) return r;
+  r = get_tmap_2d(a->w, 128, 9 * 128, 9 * 128, 32, 128, 4, 0, &tmB);
+  if (r) return r;
+  static bool attr_set = false;
+  if (!attr_set) {
+    cudaError_t e = cudaFuncSetAttribute(conv_igemm_tf32_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kConvSmem);
+    if (e != cudaSuccess) return check_cuda(e, "cudaFuncSetAttribute(conv_igemm)");
+    attr_set = true;
+  }
+  ConvK k = {};
+  k.out = static_cast<float*>(a->out);
+  k.residual = a->residual;
+  k.M_total = a->N * a->H * a->W;
+  k.HoWo = a->H * a->W;
+  k.Wo = a->W;
+  k.stride = 1;
+  k.pad_eff = 0;
+  k.R = k.S = 2;  // per class in the kernel
+  k.chunks1 = k.chunks = 4;
+  k.mode = 0;
+  k.w_rowlen_tap = 128;
+  k.out_ld = a->out_ld;
+  k.res_ld = a->res_ld;
+  k.round_out = a->round_out;
+  k.sub = 1;
+  const int grid = 4 * ((k.M_total + 127) / 128);
+  conv_igemm_tf32_kernel<<<grid, 192, kConvSmem, static_cast<cudaStream_t>(stream)>>>(tmA, tmA, tmB, k);
+  if (int rc = after_launch("conv_igemm_tf32_kernel")) return rc;
+  return 0;
+}
+
 extern "C" int b200_conv_igemm(const b200_conv_args* a, void* ws, size_t ws_bytes, void* stream) {
   (void)ws;
   (void)ws_bytes;
@@ -247,7 +312,8 @@ extern "C" int b200_conv_igemm(const b200_conv_args* a, void* ws, size_t ws_byte
   if (a->C1 <= 0 || a->C1 % 32 || a->C2 < 0 || a->C2 % 32) return fail_arg("conv_igemm: C1/C2 must be multiples of 32");
   if (a->C2 > 0 && !a->x2) return fail_arg("conv_igemm: C2 > 0 needs x2");
   if (a->R != a->S || (a->R != 1 && a->R != 3)) return fail_arg("conv_igemm: only 1x1 and 3x3 filters");
-  if (a->mode != 0 && a->mode != 1) return fail_arg("conv_igemm: mode must be 0 (fprop) or 1 (dgrad)");
+  if (a->mode == 2) return conv_dgrad_stride2(a, stream);
+  if (a->mode != 0 && a->mode != 1) return fail_arg("conv_igemm: mode must be 0 (fprop), 1 (dgrad) or 2 (stride-2 dgrad)");
   if (a->op_dtype != 0 && a->op_dtype != 1) return fail_arg("conv_igemm: op_dtype must be 0 (fp32/TF32) or 1 (bf16)");
   if (a->out_ld % 4 || (a->residual && a->res_ld % 4) || (a->emb && a->emb_ld % 4))
     return fail_arg("conv_igemm: leading dimensions must be multiples of 4 floats");
@@ -314,6 +380,7 @@ extern "C" int b200_conv_igemm(const b200_conv_args* a, void* ws, size_t ws_byte
   k.emb_ld = a->emb_ld;
   k.res_ld = a->res_ld;
   k.round_out = a->round_out;
+  k.sub = 0;
 
   static bool attr_set = false;
   if (!attr_set) {

@@ -36,6 +36,9 @@ unsigned long long b200_launch_count(void);
  *                                 (+ bias[co]) (+ emb[n, co]) (+ residual[m, co]),      m = (n, p, q)
  *   mode 1 (dgrad, stride 1): x is dY [N,H,W,Cout]; out[m, ci] for ci in [n_off, n_off+128) =
  *                                 sum_{kh,kw,co} dY[n, h+pad-kh, w+pad-kw, co] * w[co, kh, kw, ci]  (+ residual[m, ci])
+ *   mode 2 (dgrad, stride 2, 3x3 pad 1): x is dY [N,H,W,128], w is the transposed tap-flipped shadow [128 ci][9][128 co]
+ *                                 written by b200_conv_weights_transpose, out = dX [N,2H,2W,128] (Ho = 2H, Wo = 2W)
+ *                                 (+ residual, same layout); one launch, CTA = (128-row tile of dY, output-pixel parity class)
  * x may be a virtual channel concat of two tensors (x: C1 channels, x2: C2 channels), reference torch.cat at
  * simple_unet.py:150.  C1, C2 multiples of 32; Cout (fprop) must be 128; N-tile is 128 columns per launch.
  */
@@ -50,7 +53,7 @@ typedef struct {
   int N, H, W, C1, C2;   /* geometry of the tensor the im2col walks (x) */
   int Ho, Wo;            /* output spatial size */
   int R, S, stride, pad; /* filter of the ORIGINAL convolution */
-  int mode;              /* 0 fprop, 1 dgrad */
+  int mode;              /* 0 fprop, 1 dgrad (stride 1), 2 dgrad of a stride-2 3x3 conv over the transposed shadow */
   int w_cout, w_cin;     /* weight tensor is [w_cout][R*S*w_cin] */
   int n_off;             /* dgrad only: first input channel produced by this launch */
   int out_ld, emb_ld, res_ld;

@@ -134,6 +134,33 @@ def test_strided_dgrad_via_zero_stuffing(lib, H):
     assert rel(got, ref) < TF32_TOL
 
 
+@pytest.mark.parametrize("with_res", [0, 1])
+@pytest.mark.parametrize("N,H", [(3, 28), (5, 14), (2, 32), (1, 6)])
+def test_strided_dgrad_parity_classes(lib, N, H, with_res):
+    """Downsample conv backward-data without zero-stuffing (mode 2): four parity-class launches over dY with the
+    transposed, tap-flipped weight shadow; against torch.nn.grad.conv2d_input (+ a residual in dX's layout)."""
+    g = torch.Generator().manual_seed(7 * H + N)
+    Ho = H // 2
+    dy = rn(g, N, 128, Ho, Ho)
+    w = rn(g, 128, 128, 3, 3) * 0.03
+    res = rn(g, N, 128, H, H) if with_res else None
+    ref = torch.nn.grad.conv2d_input((N, 128, H, H), w, dy, stride=2, padding=1)
+    if with_res:
+        ref = ref + res
+    dyh = nhwc(dy).to(DEV)
+    # shadow[ci][t][co] = w[co][T-1-t][ci]  (what b200_conv_weights_transpose writes)
+    shadow = w_khwc(w).reshape(128, 9, 128).flip(1).permute(2, 1, 0).contiguous().to(DEV)
+    out = torch.full((N, H, H, 128), float("nan"), device=DEV)
+    resh = nhwc(res).to(DEV) if with_res else None
+    a = lib.ConvArgs(x=ptr(dyh), x2=None, w=ptr(shadow), out=ptr(out), bias=None, emb=None, residual=ptr(resh), N=N, H=Ho,
+                     W=Ho, C1=128, C2=0, Ho=H, Wo=H, R=3, S=3, stride=2, pad=1, mode=2, w_cout=128, w_cin=128, n_off=0,
+                     out_ld=128, emb_ld=0, res_ld=128)
+    lib.call("b200_conv_igemm", a, stream())
+    got = out.permute(0, 3, 1, 2).cpu()
+    assert torch.isfinite(got).all()
+    assert rel(got, ref) < TF32_TOL
+
+
 @pytest.mark.parametrize("N,H,Cin,R,stride,pad,ks", [(8, 28, 128, 3, 1, 1, 0), (8, 28, 128, 3, 1, 1, 1),
                                                     (8, 28, 128, 3, 2, 1, 0), (4, 14, 256, 1, 1, 0, 0),
                                                     (4, 14, 256, 3, 1, 1, 0), (3, 7, 128, 3, 1, 1, 0),
