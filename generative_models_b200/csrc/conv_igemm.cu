@@ -27,6 +27,7 @@ constexpr int kConvSmem = kStages * kStageBytes + 1024 /*align slack*/ + 256 /*b
 
 struct ConvK {
   float* out;
+  uint16_t* out_bf;  // optional dense bf16 copy [M][128] of out (fprop)
   const float* bias;
   const float* emb;
   const float* residual;
@@ -221,6 +222,7 @@ conv_igemm_tf32_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_con
           v.x += add[j].x; v.y += add[j].y; v.z += add[j].z; v.w += add[j].w;
           if (a.round_out) v = round_tf32(v);
           *reinterpret_cast<float4*>(a.out + out_row(a.sub, sub_a, sub_b, a.Wo, m_first + r0 + j) * a.out_ld + c) = v;
+          if (a.out_bf) *reinterpret_cast<uint2*>(a.out_bf + static_cast<size_t>(m_first + r0 + j) * 128 + c) = pack_bf16x4(v);
         }
       }
     }
@@ -344,7 +346,7 @@ extern "C" int b200_conv_igemm(const b200_conv_args* a, void* ws, size_t ws_byte
   }
   if (a->skip_x) return fail_arg("conv_igemm: the fused skip segment needs a stride-1 3x3/pad-1 or 1x1/pad-0 layer");
   if (a->out_dtype != 0) return fail_arg("conv_igemm: a bf16 out needs a stride-1 3x3/pad-1 or 1x1/pad-0 layer (strip kernel)");
-  if (a->out_bf16) return fail_arg("conv_igemm: out_bf16 needs a stride-1 3x3/pad-1 or 1x1/pad-0 layer (strip kernel)");
+  if (a->out_bf16 && a->mode != 0) return fail_arg("conv_igemm: out_bf16 is an fprop output");
   if (a->op_dtype != 0) return fail_arg("conv_igemm: bf16 operands need a stride-1 3x3/pad-1 or 1x1/pad-0 layer (strip kernel)");
   CUtensorMap tmA, tmA2, tmB;
   int r = get_tmap_im2col(a->x, a->N, a->H, a->W, a->C1, a->x_ld ? a->x_ld : a->C1, lower, upper, a->stride, 32, 128, 4, 0, &tmA);
@@ -361,6 +363,7 @@ extern "C" int b200_conv_igemm(const b200_conv_args* a, void* ws, size_t ws_byte
 
   ConvK k;
   k.out = static_cast<float*>(a->out);
+  k.out_bf = static_cast<uint16_t*>(a->out_bf16);
   k.bias = a->bias;
   k.emb = a->emb;
   k.residual = a->residual;

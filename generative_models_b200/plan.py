@@ -341,15 +341,13 @@ class UNetPlan:
         d1 = self._rb_fwd(ops, "down.seq.1", d0, None, H0)
         d2 = self._rb_fwd(ops, "down.seq.2", d1, None, H0)
         d3 = pool.get(B, H1 * H1, 128)
-        ops.append(self._conv(d2, None, "down.seq.3.conv", d3, H0, H1, 3, 2, 1, 128, 0))
-        if bf:
-            self._cast_copy(ops, d3, B * H1 * H1)
+        ops.append(self._conv(d2, None, "down.seq.3.conv", d3, H0, H1, 3, 2, 1, 128, 0,
+                              out_bf=self._get_bf(pool, B, H1 * H1, 128) if bf else None))
         d4 = self._rb_fwd(ops, "down.seq.4", d3, None, H1)
         d5 = self._rb_fwd(ops, "down.seq.5", d4, None, H1)
         d6 = pool.get(B, H2 * H2, 128)
-        ops.append(self._conv(d5, None, "down.seq.6.conv", d6, H1, H2, 3, 2, 1, 128, 0))
-        if bf:
-            self._cast_copy(ops, d6, B * H2 * H2)
+        ops.append(self._conv(d5, None, "down.seq.6.conv", d6, H1, H2, 3, 2, 1, 128, 0,
+                              out_bf=self._get_bf(pool, B, H2 * H2, 128) if bf else None))
         # ---- turn (simple_unet.py:36,68)
         t = self._rb_fwd(ops, "turn", d6, None, H2)
         # ---- Up (simple_unet.py:125-152): block i consumes cat([h, cache.pop()])
@@ -527,6 +525,9 @@ class UNetPlan:
                                residual=residual.ptr() if residual else None, res_ld=residual.ld if residual else 0, bf=bf))
         if stride == 2:
             ops[-1].alg_scale = 0.25  # 3/4 of the zero-stuffed rows are zeros
+            if self.bf16 and self.dgrad_T:  # the ResBlock below reads dx as a bf16 dY operand: no cast pass
+                dx.bf16_copy = self._get_bf(self.bfpool, B, H * H, 128)
+                ops[-1].args.out_bf16 = _p(dx.bf16_copy)
         gp.release(zs)
         return dx
 

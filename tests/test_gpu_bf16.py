@@ -343,3 +343,23 @@ def test_bf16_conv_bf16_output(lib):
                          w_cout=128, w_cin=256, n_off=n_off, out_ld=256, emb_ld=0, res_ld=0, op_dtype=1, out_dtype=1)
         lib.call("b200_conv_igemm", a, stream())
     assert rel(out2.float().permute(0, 3, 1, 2).cpu(), ref2) < 2 ** -8
+
+
+@pytest.mark.parametrize("N,H,stride", [(3, 28, 2), (2, 14, 2), (2, 7, 1)])
+def test_im2col_conv_bf16_copy(lib, N, H, stride):
+    """out_bf16 on the layers the im2col kernel takes (the stride-2 Downsample convs, small stride-1 levels): the dense
+    bf16 copy equals the fp32 output rounded to bf16."""
+    g = torch.Generator().manual_seed(H + stride)
+    x = rn(g, N, 128, H, H)
+    w = rn(g, 128, 128, 3, 3) * 0.03
+    Ho = (H + 2 - 3) // stride + 1
+    xh, wk = nhwc(x).to(DEV), w_khwc(w).to(DEV)
+    out = torch.full((N, Ho, Ho, 128), float("nan"), device=DEV)
+    outb = torch.zeros(N, Ho, Ho, 128, dtype=torch.bfloat16, device=DEV)
+    a = lib.ConvArgs(x=ptr(xh), x2=None, w=ptr(wk), out=ptr(out), bias=None, emb=None, residual=None, N=N, H=H, W=H,
+                     C1=128, C2=0, Ho=Ho, Wo=Ho, R=3, S=3, stride=stride, pad=1, mode=0, w_cout=128, w_cin=128, n_off=0,
+                     out_ld=128, emb_ld=0, res_ld=0, out_bf16=ptr(outb))
+    lib.call("b200_conv_igemm", a, stream())
+    ref = F.conv2d(x, w, stride=stride, padding=1)
+    assert rel(out.permute(0, 3, 1, 2).cpu(), ref) < 2e-3
+    assert torch.equal(outb, out.to(torch.bfloat16))
