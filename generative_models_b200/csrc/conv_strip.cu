@@ -16,6 +16,8 @@
 //     of a 128x128x8 one (measured issue rate 480 -> 680 TFLOP/s);
 //   * persistent CTAs (one per SM), TMEM accumulators double-buffered (2 x 256 columns) so the epilogue of tile i
 //     overlaps the MMAs of tile i+1; epilogue thread = output channel, so a warp stores 128 contiguous bytes per pixel;
+//   * two-phase tiling: whole waves of 256-position tiles, then the remaining positions split evenly over the CTAs in
+//     one wave of smaller tiles (N of the UMMA = tail_n, a multiple of 16) instead of a last wave at full cost;
 //   * optional fused "skip" K-segment (extra 1-tap chunks over a second tensor pair: identity = residual add on the
 //     tensor cores, or the ResBlock's 1x1 skip conv).
 //   1x1 convolutions use the same kernel in "flat" mode (positions = pixels, one 256-row box per chunk).
@@ -29,14 +31,17 @@
 
 #include <stdlib.h>
 
+#include <mutex>
+
 namespace b200 {
 
-constexpr int kSB = 6;                    // weight-tile ring
+constexpr int kSBMax = 10;                // weight-tile ring: as deep as the strips leave room for (6 at W = 64, 8 at 28/14, 9 at 7)
 constexpr int kSS = 2;                    // strip double buffer
 constexpr int kBTile = 16384;             // 128 x 128 B
 constexpr int kStripBytes = 58 * 1024;    // >= (256 + 2*Wp + 2 rounded up to whole rows) * 128 B for W <= 64 (7 rows of 65)
 constexpr int kTileM = 256;               // positions per CTA tile (the N of one UMMA)
-constexpr int kStripSmem = kSS * kStripBytes + kSB * kBTile + 1024 + 256 + 2 * 512 * 4;
+constexpr int kStripTail = 256 + 2 * 512 * 4;  // barriers + the two position tables
+constexpr int kStripSmem = 232448;             // the whole 227 KB opt-in maximum; strips first, the ring takes the rest
 
 struct StripK {
   float* out;
@@ -50,6 +55,8 @@ struct StripK {
   int flat;        // 1: positions are pixels (1x1 conv), strip = 256 rows of a 2-D map
   int P_total;     // number of positions
   int num_tiles;
+  int full_tiles;  // tiles [0, full_tiles) hold kTileM positions; the rest ("tail wave") hold tail_n each
+  int tail_n;      // positions per tail tile (multiple of 16, <= kTileM)
   int taps;        // 9 or 1
   int chunks1, chunks;
   int skip_chunks1, skip_chunks;  // fused 1x1 "skip" segment over a second pair of tensors (0 = none)
@@ -59,6 +66,11 @@ struct StripK {
   int out_ld, emb_ld, res_ld;
   int round_out;
   int strip_rows;  // image rows per strip (non-flat)
+  int rb;          // image rows per box of the multi-row strip maps (0: single-row boxes only)
+  int rb2;         // rows per box of the second, smaller multi-row maps (0: none)
+  int sb;          // weight-tile ring depth
+  int strip_alloc; // bytes between the two strip buffers (1 KB multiple)
+  int cl;          // launched as 2-CTA clusters: each weight tile is fetched once per pair (half by each CTA, multicast)
   int dbg;         // developer knobs (B200_STRIP_DBG): 1 = skip TMA loads (timing of the MMA issue path only)
 };
 
@@ -66,6 +78,25 @@ __device__ __forceinline__ int floor_div(int a, int b) {
   int q = a / b;
   if ((a % b) != 0 && ((a < 0) != (b < 0))) --q;
   return q;
+}
+
+// Two-phase tiling: whole waves of kTileM-position tiles, then ONE last wave whose remaining positions are split evenly
+// over the CTAs in tail_n-position tiles (a multiple of 16, the UMMA N granularity) — with uniform 256-position tiles
+// the last wave is on the critical path at full cost however few CTAs have a tile in it (28x28 at batch 512: 11.36
+// waves cost 12; 14x14: 3.04 cost 4).
+struct TileGeom {
+  int p0, n;
+};
+__device__ __forceinline__ TileGeom tile_geom(const StripK& a, int t) {
+  TileGeom g;
+  if (t < a.full_tiles) {
+    g.p0 = t * kTileM;
+    g.n = kTileM;
+  } else {
+    g.p0 = a.full_tiles * kTileM + (t - a.full_tiles) * a.tail_n;
+    g.n = a.tail_n;
+  }
+  return g;
 }
 
 // BF16 = false: fp32 operands in smem, kind::tf32, 32 channels per 128 B row.
@@ -94,17 +125,19 @@ __global__ void __launch_bounds__(320, 1)
 conv_strip_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmA2,
                        const __grid_constant__ CUtensorMap tmB, const __grid_constant__ CUtensorMap tmS,
                        const __grid_constant__ CUtensorMap tmS2, const __grid_constant__ CUtensorMap tmW2,
+                       const __grid_constant__ CUtensorMap tmAm, const __grid_constant__ CUtensorMap tmA2m,
+                       const __grid_constant__ CUtensorMap tmAs, const __grid_constant__ CUtensorMap tmA2s,
                        const StripK a) {
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   uint8_t* strip0 = smem;
-  uint8_t* bring = smem + kSS * kStripBytes;
-  uint64_t* bars = reinterpret_cast<uint64_t*>(bring + kSB * kBTile);
-  uint64_t* s_full = bars;             // [kSS]
-  uint64_t* s_empty = s_full + kSS;    // [kSS]
-  uint64_t* b_full = s_empty + kSS;    // [kSB]
-  uint64_t* b_empty = b_full + kSB;    // [kSB]
-  uint64_t* acc_full = b_empty + kSB;  // [2]
+  uint8_t* bring = smem + kSS * a.strip_alloc;
+  uint64_t* bars = reinterpret_cast<uint64_t*>(bring + a.sb * kBTile);
+  uint64_t* s_full = bars;                // [kSS]
+  uint64_t* s_empty = s_full + kSS;       // [kSS]
+  uint64_t* b_full = s_empty + kSS;       // [kSBMax]
+  uint64_t* b_empty = b_full + kSBMax;    // [kSBMax]
+  uint64_t* acc_full = b_empty + kSBMax;  // [2]
   uint64_t* acc_empty = acc_full + 2;  // [2]
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(acc_empty + 2);
   int* tab = reinterpret_cast<int*>(bars + 32);  // 256 B past the barriers, 16 B-aligned: [2 acc stages][m[256], n[256]]
@@ -116,6 +149,14 @@ conv_strip_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
     tma_prefetch_desc(&tmA);
     tma_prefetch_desc(&tmA2);
     tma_prefetch_desc(&tmB);
+    if (a.rb) {
+      tma_prefetch_desc(&tmAm);
+      tma_prefetch_desc(&tmA2m);
+    }
+    if (a.rb2) {
+      tma_prefetch_desc(&tmAs);
+      tma_prefetch_desc(&tmA2s);
+    }
     if (a.skip_chunks) {
       tma_prefetch_desc(&tmS);
       tma_prefetch_desc(&tmS2);
@@ -125,9 +166,9 @@ conv_strip_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
       mbar_init(&s_full[s], 1);
       mbar_init(&s_empty[s], 1);
     }
-    for (int s = 0; s < kSB; ++s) {
+    for (int s = 0; s < a.sb; ++s) {
       mbar_init(&b_full[s], 1);
-      mbar_init(&b_empty[s], 1);
+      mbar_init(&b_empty[s], a.cl ? 2 : 1);  // cluster: a slot is free when BOTH CTAs' MMAs have read it
     }
     for (int s = 0; s < 2; ++s) {
       mbar_init(&acc_full[s], 1);
@@ -141,11 +182,11 @@ conv_strip_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
   }
   tc_fence_before();
   __syncthreads();
+  if (a.cl) cluster_sync_all();  // the peer's barriers exist before anything is multicast at them
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
 
   constexpr int CK = BF16 ? 64 : 32;  // channels per K-chunk (one 128 B smem row)
-  const int strip_bytes = a.flat ? kTileM * 128 : a.strip_rows * a.Wp * 128;
   const int CH = a.chunks + a.skip_chunks;  // K-chunks (32 channels each) per tile: main conv, then the skip segment
 
   if (warp == 0) {
@@ -154,7 +195,7 @@ conv_strip_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
       // Order of issue: strip(0); then per chunk: weight taps 0..3, strip(next chunk), weight taps 4..8 — the next
       // strip is requested ~1.5 chunks of MMA time before it is needed, and never blocks the weight stream (its buffer
       // was released by the chunk before the one in flight).
-      uint32_t bc = 0;
+      uint32_t bs = 0, bph = 1;  // ring slot and the parity its "empty" barrier is awaited with
       const int tiles_mine = (a.num_tiles - static_cast<int>(blockIdx.x) + static_cast<int>(gridDim.x) - 1) / static_cast<int>(gridDim.x);
       const int total_chunks = tiles_mine * CH;
       auto load_strip = [&](int q) {  // q = running chunk index of this CTA
@@ -166,28 +207,47 @@ conv_strip_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
           mbar_arrive(&s_full[ss]);
           return;
         }
-        mbar_expect_tx(&s_full[ss], strip_bytes);
-        uint8_t* sdst = strip0 + ss * kStripBytes;
+        const TileGeom tg = tile_geom(a, t);
+        // image rows this tile's strip spans (a.strip_rows for a full tile)
+        const int rows = a.flat ? 0 : 3 + (tg.n + a.Wp) / a.Wp;
+        mbar_expect_tx(&s_full[ss], a.flat ? kTileM * 128 : rows * a.Wp * 128);
+        uint8_t* sdst = strip0 + ss * a.strip_alloc;
         const CUtensorMap* m;
+        const CUtensorMap* mm = nullptr;  // the same tensor in boxes of a.rb image rows
+        const CUtensorMap* ms = nullptr;  // ... and of a.rb2 rows
         int c0;
         if (ch < a.chunks) {
           m = (ch < a.chunks1) ? &tmA : &tmA2;
+          if (a.rb) mm = (ch < a.chunks1) ? &tmAm : &tmA2m;
+          if (a.rb2) ms = (ch < a.chunks1) ? &tmAs : &tmA2s;
           c0 = ((ch < a.chunks1) ? ch : ch - a.chunks1) * CK;
         } else {
           const int sk = ch - a.chunks;
           m = (sk < a.skip_chunks1) ? &tmS : &tmS2;
           c0 = ((sk < a.skip_chunks1) ? sk : sk - a.skip_chunks1) * CK;
         }
-        const int p0 = t * kTileM;
+        const int p0 = tg.p0;
         if (a.flat) {
           tma_load_2d(sdst, m, &s_full[ss], c0, p0);
         } else {
           const int g0 = floor_div(p0 - a.Wp - 1, a.Wp);  // first padded row of the strip
-          for (int r = 0; r < a.strip_rows; ++r) {
+          // One box per image row, or per a.rb rows where they stay inside one image (its trailing zero row, which is
+          // the next image's row -1, may be the last of them): the cost of a strip is per TMA instruction, not per byte
+          // (7x7: 32 one-KB boxes per chunk).
+          for (int r = 0; r < rows;) {
             const int g = g0 + r;
             const int n = floor_div(g, a.Hp);
             const int hh = g - n * a.Hp - 1;  // -1 = the shared zero row (OOB -> zeros)
-            tma_load_4d(sdst + r * a.Wp * 128, m, &s_full[ss], c0, -1, hh, n);
+            if (mm && r + a.rb <= rows && hh + a.rb - 1 <= a.H) {
+              tma_load_4d(sdst + r * a.Wp * 128, mm, &s_full[ss], c0, -1, hh, n);
+              r += a.rb;
+            } else if (ms && r + a.rb2 <= rows && hh + a.rb2 - 1 <= a.H) {
+              tma_load_4d(sdst + r * a.Wp * 128, ms, &s_full[ss], c0, -1, hh, n);
+              r += a.rb2;
+            } else {
+              tma_load_4d(sdst + r * a.Wp * 128, m, &s_full[ss], c0, -1, hh, n);
+              r += 1;
+            }
           }
         }
       };
@@ -197,10 +257,9 @@ conv_strip_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
         const bool is_skip = ch >= a.chunks;
         const int ntaps = is_skip ? 1 : a.taps;
         const int split = ntaps > 4 ? 4 : 0;
-        for (int tap = 0; tap < ntaps; ++tap, ++bc) {
+        for (int tap = 0; tap < ntaps; ++tap, bs = (bs + 1 == static_cast<uint32_t>(a.sb)) ? (bph ^= 1, 0u) : bs + 1) {
           if (tap == split && q + 1 < total_chunks) load_strip(q + 1);
-          const uint32_t bs = bc % kSB;
-          mbar_wait(&b_empty[bs], ((bc / kSB) & 1) ^ 1);
+          mbar_wait(&b_empty[bs], bph);
           if (a.dbg & 1) {
             mbar_arrive(&b_full[bs]);
             continue;
@@ -216,6 +275,10 @@ conv_strip_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
               for (int jj = 0; jj < 128 / CK; ++jj)
                 tma_load_2d(sB + jj * (CK * 128), &tmW2, &b_full[bs], jj * CK, sk * CK);
             }
+          } else if (a.cl) {
+            // this CTA's half (64 output channels) of the tile, delivered to both CTAs of the pair
+            const int half = static_cast<int>(cluster_ctarank());
+            tma_load_2d_mc(sB + half * (kBTile / 2), &tmB, &b_full[bs], tap * a.w_rowlen_tap + ch * CK, half * 64, 3);
           } else if (a.mode == 0) {
             tma_load_2d(sB, &tmB, &b_full[bs], tap * a.w_rowlen_tap + ch * CK, 0);
           } else {
@@ -234,13 +297,15 @@ conv_strip_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
       // A = weight tile (K-major for fprop, MN-major for dgrad), B = the shifted strip view (K-major, N = 256 rows).
       // One N=256 instruction reads 4 KB of A + 8 KB of B for twice the FLOPs of a 128x128x8 one: SS-mode TF32 is
       // bound by smem operand bandwidth (measured: 480 -> 680 TFLOP/s issue rate), hence this orientation.
-      const uint32_t idesc = make_idesc(BF16 ? 1u : 2u, 128u, 256u, a.mode == 0 ? 0u : 1u, 0u);
-      uint32_t sc = 0, bc = 0, tc = 0;
+      const uint32_t idesc_full = make_idesc(BF16 ? 1u : 2u, 128u, 256u, a.mode == 0 ? 0u : 1u, 0u);
+      const uint32_t idesc_tail = make_idesc(BF16 ? 1u : 2u, 128u, static_cast<uint32_t>(a.tail_n), a.mode == 0 ? 0u : 1u, 0u);
+      uint32_t sc = 0, bs = 0, bph = 0, tc = 0;
       for (int t = blockIdx.x; t < a.num_tiles; t += gridDim.x, ++tc) {
         const uint32_t as = tc & 1;
         mbar_wait(&acc_empty[as], ((tc >> 1) & 1) ^ 1);
         tc_fence_after();
-        const int p0 = t * kTileM;
+        const int p0 = tile_geom(a, t).p0;
+        const uint32_t idesc = t < a.full_tiles ? idesc_full : idesc_tail;
         const int g0 = a.flat ? 0 : floor_div(p0 - a.Wp - 1, a.Wp);
         const int row0 = a.flat ? 0 : p0 - g0 * a.Wp;  // strip row of position p0 (centre tap)
         const uint32_t d_tmem = tmem_base + as * 256;
@@ -248,12 +313,11 @@ conv_strip_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
           const uint32_t ss = sc % kSS;
           mbar_wait(&s_full[ss], (sc / kSS) & 1);
           tc_fence_after();
-          const uint32_t strip_addr = smem_u32(strip0 + ss * kStripBytes);
+          const uint32_t strip_addr = smem_u32(strip0 + ss * a.strip_alloc);
           const bool is_skip = ch >= a.chunks;
           const int ntaps = is_skip ? 1 : a.taps;
-          for (int tap = 0; tap < ntaps; ++tap, ++bc) {
-            const uint32_t bs = bc % kSB;
-            mbar_wait(&b_full[bs], (bc / kSB) & 1);
+          for (int tap = 0; tap < ntaps; ++tap, bs = (bs + 1 == static_cast<uint32_t>(a.sb)) ? (bph ^= 1, 0u) : bs + 1) {
+            mbar_wait(&b_full[bs], bph);
             tc_fence_after();
             const uint32_t w_base = smem_u32(bring + bs * kBTile);
             int shift = 0;
@@ -275,7 +339,8 @@ conv_strip_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
               if (BF16) mma_f16_ss(d_tmem, adesc, bdesc, idesc, (ch | tap | k) != 0 ? 1u : 0u);
               else mma_tf32_ss(d_tmem, adesc, bdesc, idesc, (ch | tap | k) != 0 ? 1u : 0u);
             }
-            tc_commit(&b_empty[bs]);
+            if (a.cl) tc_commit_mc(&b_empty[bs], 3);
+            else tc_commit(&b_empty[bs]);
           }
           tc_commit(&s_empty[ss]);
         }
@@ -302,10 +367,16 @@ conv_strip_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
       // the table is read through explicit shared-space loads: from the generic pointer the compiler emits LD.E
       // (generic path, long-scoreboard latency) instead of LDS
       const uint32_t tm_s = smem_u32(tm), tn_s = tm_s + 1024;
+      int tile_n;
       {
-        const int P = t * kTileM + et;
+        const TileGeom tg = tile_geom(a, t);
+        tile_n = tg.n;
+        const int P = tg.p0 + et;
         int m, n;
-        if (a.flat) {
+        if (et >= tg.n) {  // past the end of a tail tile: the next tile owns the position
+          m = -1;
+          n = a.N;
+        } else if (a.flat) {
           m = P < a.P_total ? P : -1;
           n = P / (a.H * a.W);
         } else {
@@ -342,6 +413,7 @@ conv_strip_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
 #pragma unroll 1
       for (int c4 = 0; c4 < 4; ++c4) {
         const int cb = colhalf * 128 + c4 * 32;  // first position column of this chunk
+        if (cb >= tile_n) break;                 // tail tile: no positions left (the TMEM columns were not written)
         uint32_t r[32];
         tmem_ld_32x32(tmem_base + (static_cast<uint32_t>(quarter * 32) << 16) + as * 256 + cb, r);
         float add[32];
@@ -406,6 +478,7 @@ conv_strip_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
   }
   tc_fence_before();
   __syncthreads();
+  if (a.cl) cluster_sync_all();  // no CTA leaves while its peer may still signal its barriers
   if (warp == 1) {
     tc_fence_after();
     tmem_dealloc(tmem_base, 512);
@@ -415,6 +488,107 @@ conv_strip_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
 }  // namespace b200
 
 using namespace b200;
+
+namespace {
+
+// Two-phase tiling of P positions over `ctas` persistent CTAs (see tile_geom).
+void split_tiles(int P, int ctas, bool tail, int* full_tiles, int* tail_n, int* num_tiles) {
+  if (tail) {
+    *full_tiles = (P / (kTileM * ctas)) * ctas;
+    const int rest = P - *full_tiles * kTileM;
+    int tn = (((rest + ctas - 1) / ctas) + 15) & ~15;
+    tn = tn < 16 ? 16 : (tn > kTileM ? kTileM : tn);
+    *tail_n = tn;
+    *num_tiles = *full_tiles + (rest + tn - 1) / tn;
+  } else {
+    *full_tiles = (P + kTileM - 1) / kTileM;
+    *tail_n = kTileM;
+    *num_tiles = *full_tiles;
+  }
+}
+
+bool tail_split_on() {
+  static int v = -1;  // developer knob B200_STRIP_TAIL=0: uniform 256-position tiles
+  if (v < 0) {
+    const char* e = getenv("B200_STRIP_TAIL");
+    v = e ? atoi(e) : 1;
+  }
+  return v != 0;
+}
+
+int num_sms_cached() {
+  static int n = 0;
+  if (!n) {
+    int dev = 0;
+    cudaGetDevice(&dev);
+    if (cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || n <= 0) n = 148;
+  }
+  return n;
+}
+
+// Rows per box of the two multi-row strip maps: a strip costs per TMA instruction (~90 ns each on the producer's
+// critical path), so the launch walks its own tiles once per (N, H, W) and keeps the pair (rb, rb2) that covers the
+// strips of this geometry with the fewest boxes.  A box may not leave its image (one trailing zero row allowed), which
+// is why the best size depends on how H + 1 and the strip height divide.  B200_STRIP_RB=0 turns the boxes off,
+// B200_STRIP_RB=r forces a single level of r rows.
+void pick_strip_boxes(int N, int H, int W, int* rb_out, int* rb2_out) {
+  static int knob = -2;
+  if (knob == -2) {
+    const char* e = getenv("B200_STRIP_RB");
+    knob = e ? atoi(e) : -1;
+  }
+  const int Wp = W + 1, Hp = H + 1;
+  const int cap = 256 / Wp < Hp ? 256 / Wp : Hp;  // TMA box dimensions are <= 256 elements
+  *rb_out = *rb2_out = 0;
+  if (knob == 0 || cap < 2) return;
+  if (knob > 0) {
+    *rb_out = knob <= cap ? knob : 0;
+    return;
+  }
+  struct Memo {
+    int N, H, W, rb, rb2;
+  };
+  static Memo memo[64];
+  static int memo_n = 0;
+  static std::mutex mu;
+  std::lock_guard<std::mutex> lock(mu);
+  for (int i = 0; i < memo_n; ++i)
+    if (memo[i].N == N && memo[i].H == H && memo[i].W == W) {
+      *rb_out = memo[i].rb;
+      *rb2_out = memo[i].rb2;
+      return;
+    }
+  int full_tiles, tail_n, num_tiles;
+  split_tiles(N * Hp * Wp, num_sms_cached(), tail_split_on(), &full_tiles, &tail_n, &num_tiles);
+  const int step = num_tiles > 1024 ? num_tiles / 1024 : 1;  // a sample of the tiles is enough
+  long best = -1;
+  for (int r1 = 2; r1 <= cap; ++r1)
+    for (int r2 = 0; r2 < r1; r2 = r2 ? r2 + 1 : 2) {
+      long boxes = 0;
+      for (int t = 0; t < num_tiles; t += step) {
+        const int p0 = t < full_tiles ? t * kTileM : full_tiles * kTileM + (t - full_tiles) * tail_n;
+        const int n = t < full_tiles ? kTileM : tail_n;
+        const int q = p0 - Wp - 1;
+        const int g0 = q >= 0 ? q / Wp : -((-q + Wp - 1) / Wp);
+        const int rows = 3 + (n + Wp) / Wp;
+        for (int r = 0; r < rows; ++boxes) {
+          const int g = g0 + r;
+          const int hh = ((g % Hp) + Hp) % Hp - 1;
+          if (r + r1 <= rows && hh + r1 - 1 <= H) r += r1;
+          else if (r2 && r + r2 <= rows && hh + r2 - 1 <= H) r += r2;
+          else r += 1;
+        }
+      }
+      if (best < 0 || boxes < best) {
+        best = boxes;
+        *rb_out = r1;
+        *rb2_out = r2;
+      }
+    }
+  if (memo_n < 64) memo[memo_n++] = {N, H, W, *rb_out, *rb2_out};
+}
+
+}  // namespace
 
 // Called by b200_conv_igemm for stride-1 3x3/pad-1 and 1x1/pad-0 layers.  Returns -100 when the geometry does not fit
 // the strip buffers (caller falls back to the im2col kernel).
@@ -435,7 +609,10 @@ int conv_strip_applicable(const b200_conv_args* a) {
     const char* e = getenv("B200_STRIP_MIN_TILES");
     min_tiles = e ? atoi(e) : 4 * 148;
   }
-  if (!a->skip_x && num_tiles < min_tiles && !flat && a->op_dtype == 0) return 0;
+  // with a residual operand the crossover sits lower: the strip epilogue prefetches the residual rows one chunk ahead
+  // (+3 us at 14x14, batch 512: 92 us), the im2col kernel's does not (+33 us: 107 us)
+  const int need = a->residual ? min_tiles / 2 : min_tiles;
+  if (!a->skip_x && num_tiles < need && !flat && a->op_dtype == 0) return 0;
   return 1;
 }
 
@@ -452,8 +629,10 @@ int conv_strip_launch(const b200_conv_args* a, void* stream) {
 
   if (a->out_bf16 && a->mode != 0) return fail_arg("conv_igemm: out_bf16 is an fprop output");
 
-  CUtensorMap tmA, tmA2, tmB;
+  CUtensorMap tmA, tmA2, tmB, tmAm = {}, tmA2m = {}, tmAs = {}, tmA2s = {};
   int r;
+  int rb = 0, rb2 = 0;
+  if (!flat) pick_strip_boxes(a->N, a->H, a->W, &rb, &rb2);
   const long long M = static_cast<long long>(a->N) * a->H * a->W;
   if (flat) {
     r = get_tmap_2d(a->x, M, a->C1, a->x_ld ? a->x_ld : a->C1, CK, 256, eb, 0, &tmA);
@@ -473,9 +652,31 @@ int conv_strip_launch(const b200_conv_args* a, void* stream) {
     } else {
       tmA2 = tmA;
     }
+    tmAm = tmAs = tmA;
+    tmA2m = tmA2s = tmA2;
+    for (int lvl = 0; lvl < 2; ++lvl) {
+      const int rows_box = lvl ? rb2 : rb;
+      if (!rows_box) continue;
+      CUtensorMap* m1 = lvl ? &tmAs : &tmAm;
+      CUtensorMap* m2 = lvl ? &tmA2s : &tmA2m;
+      r = get_tmap_rows4d(a->x, a->N, a->H, a->W, a->C1, a->x_ld ? a->x_ld : a->C1, CK, Wp, m1, eb, rows_box);
+      if (r) return r;
+      *m2 = *m1;
+      if (a->C2 > 0) {
+        r = get_tmap_rows4d(a->x2, a->N, a->H, a->W, a->C2, a->x2_ld ? a->x2_ld : a->C2, CK, Wp, m2, eb, rows_box);
+        if (r) return r;
+      }
+    }
   }
   const uint64_t wcols = static_cast<uint64_t>(a->R) * a->S * a->w_cin;
-  r = get_tmap_2d(a->w, a->w_cout, wcols, wcols, CK, a->mode == 0 ? 128 : CK, eb, (a->mode == 1 && !bf) ? 1 : 0, &tmB);
+  // 2-CTA clusters sharing the weight stream (fprop orientation, no skip segment)
+  static int cluster_on = -1;  // developer knob B200_STRIP_CLUSTER
+  if (cluster_on < 0) {
+    const char* e = getenv("B200_STRIP_CLUSTER");
+    cluster_on = e ? atoi(e) : 0;
+  }
+  const int cl = (cluster_on && a->mode == 0 && !a->skip_x) ? 1 : 0;
+  r = get_tmap_2d(a->w, a->w_cout, wcols, wcols, CK, a->mode == 0 ? (cl ? 64 : 128) : CK, eb, (a->mode == 1 && !bf) ? 1 : 0, &tmB);
   if (r) return r;
   // fused skip segment: a 1x1 convolution over (skip_x | skip_x2) with weights skip_w [128][skip_c1 + skip_c2],
   // accumulated into the same TMEM tile as extra K-chunks (identity weights = a residual add on the tensor cores,
@@ -513,7 +714,6 @@ int conv_strip_launch(const b200_conv_args* a, void* stream) {
   k.N = a->N; k.H = a->H; k.W = a->W; k.Wp = Wp; k.Hp = Hp;
   k.flat = flat;
   k.P_total = flat ? static_cast<int>(M) : a->N * Hp * Wp;
-  k.num_tiles = (k.P_total + kTileM - 1) / kTileM;
   k.taps = a->R * a->S;
   k.chunks1 = a->C1 / CK;
   k.chunks = Cin / CK;
@@ -525,6 +725,20 @@ int conv_strip_launch(const b200_conv_args* a, void* stream) {
   k.out_ld = a->out_ld; k.emb_ld = a->emb_ld; k.res_ld = a->res_ld;
   k.round_out = a->round_out;
   k.strip_rows = strip_rows;
+  k.rb = rb;
+  k.rb2 = rb2;
+  k.strip_alloc = ((flat ? kTileM * 128 : strip_rows * Wp * 128) + 1023) & ~1023;
+  {
+    static int sb_cap = -1;  // developer knob B200_STRIP_RING
+    if (sb_cap < 0) {
+      const char* e = getenv("B200_STRIP_RING");
+      sb_cap = e ? atoi(e) : kSBMax;
+    }
+    int sb = (kStripSmem - 1024 - kStripTail - kSS * k.strip_alloc) / kBTile;
+    sb = sb > kSBMax ? kSBMax : sb;
+    k.sb = sb > sb_cap ? sb_cap : sb;
+    if (k.sb < 2) return fail_arg("conv_strip: no room for the weight ring");
+  }
 
   static int dbg = -1;
   if (dbg < 0) {
@@ -544,11 +758,34 @@ int conv_strip_launch(const b200_conv_args* a, void* stream) {
     cudaDeviceGetAttribute(&num_sms, cudaDevAttrMultiProcessorCount, dev);
     attr_set = true;
   }
+  // whole waves of 256-position tiles, then the remainder split evenly over the CTAs (see tile_geom)
+  split_tiles(k.P_total, num_sms, tail_split_on(), &k.full_tiles, &k.tail_n, &k.num_tiles);
+  k.cl = cl && (num_sms % 2 == 0);
+  if (k.cl && (k.num_tiles & 1)) ++k.num_tiles;  // both CTAs of a pair walk the same number of weight tiles: the extra
+                                                 // tile lies past the last position (zero-filled loads, nothing stored)
   const int grid = k.num_tiles < num_sms ? k.num_tiles : num_sms;
+  if (k.cl) {
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(grid);
+    cfg.blockDim = dim3(320);
+    cfg.dynamicSmemBytes = kStripSmem;
+    cfg.stream = static_cast<cudaStream_t>(stream);
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeClusterDimension;
+    at[0].val.clusterDim.x = 2;
+    at[0].val.clusterDim.y = 1;
+    at[0].val.clusterDim.z = 1;
+    cfg.attrs = at;
+    cfg.numAttrs = 1;
+    cudaError_t e = bf ? cudaLaunchKernelEx(&cfg, conv_strip_kernel<true>, tmA, tmA2, tmB, tmS, tmS2, tmW2, tmAm, tmA2m, tmAs, tmA2s, k)
+                       : cudaLaunchKernelEx(&cfg, conv_strip_kernel<false>, tmA, tmA2, tmB, tmS, tmS2, tmW2, tmAm, tmA2m, tmAs, tmA2s, k);
+    if (e != cudaSuccess) return check_cuda(e, "cudaLaunchKernelEx(conv_strip, cluster 2)");
+    return after_launch(bf ? "conv_strip_kernel<bf16>" : "conv_strip_kernel<tf32>");
+  }
   if (bf) {
-    conv_strip_kernel<true><<<grid, 320, kStripSmem, static_cast<cudaStream_t>(stream)>>>(tmA, tmA2, tmB, tmS, tmS2, tmW2, k);
+    conv_strip_kernel<true><<<grid, 320, kStripSmem, static_cast<cudaStream_t>(stream)>>>(tmA, tmA2, tmB, tmS, tmS2, tmW2, tmAm, tmA2m, tmAs, tmA2s, k);
     return after_launch("conv_strip_kernel<bf16>");
   }
-  conv_strip_kernel<false><<<grid, 320, kStripSmem, static_cast<cudaStream_t>(stream)>>>(tmA, tmA2, tmB, tmS, tmS2, tmW2, k);
+  conv_strip_kernel<false><<<grid, 320, kStripSmem, static_cast<cudaStream_t>(stream)>>>(tmA, tmA2, tmB, tmS, tmS2, tmW2, tmAm, tmA2m, tmAs, tmA2s, k);
   return after_launch("conv_strip_kernel<tf32>");
 }

@@ -110,10 +110,10 @@ int get_tmap_im2col(const void* base, int N, int H, int W, int C, int ld, int lo
 }
 
 int get_tmap_rows4d(const void* base, int N, int H, int W, int C, int ld, uint32_t box_c, uint32_t box_w, CUtensorMap* out,
-                    int elem_bytes) {
+                    int elem_bytes, uint32_t box_h) {
   TmapKey k = {{reinterpret_cast<uint64_t>(base), (static_cast<uint64_t>(N) << 32) | static_cast<uint32_t>(C),
                 (static_cast<uint64_t>(H) << 32) | static_cast<uint32_t>(W), static_cast<uint64_t>(ld),
-                (static_cast<uint64_t>(box_c) << 32) | box_w, static_cast<uint64_t>(elem_bytes), 0, 44}};
+                (static_cast<uint64_t>(box_c) << 32) | box_w, static_cast<uint64_t>(elem_bytes), box_h, 44}};
   std::lock_guard<std::mutex> lock(g_mu);
   auto it = g_cache.find(k);
   if (it != g_cache.end()) {
@@ -124,7 +124,7 @@ int get_tmap_rows4d(const void* base, int N, int H, int W, int C, int ld, uint32
   cuuint64_t dims[4] = {(cuuint64_t)C, (cuuint64_t)W, (cuuint64_t)H, (cuuint64_t)N};
   const uint64_t eb4 = static_cast<uint64_t>(elem_bytes);
   cuuint64_t strides[3] = {(uint64_t)ld * eb4, (uint64_t)W * ld * eb4, (uint64_t)H * W * ld * eb4};
-  cuuint32_t box[4] = {box_c, box_w, 1, 1};
+  cuuint32_t box[4] = {box_c, box_w, box_h, 1};  // box_h > 1: several image rows of the strip raster per instruction
   cuuint32_t estr[4] = {1, 1, 1, 1};
   CUtensorMap m;
   CUresult r = g_encode_tiled(&m, dtype_of(elem_bytes), 4, const_cast<void*>(base), dims, strides, box, estr,

@@ -58,6 +58,6 @@ int get_tmap_im2col(const void* base, int N, int H, int W, int C, int ld, int lo
 // NHWC [N][H][W][C] plain tiled 4-D map {C, W, H, N}: box = box_c channels x box_w pixels of ONE image row
 // (out-of-range w / h / n coordinates are zero-filled: the convolution halo).
 int get_tmap_rows4d(const void* base, int N, int H, int W, int C, int ld, uint32_t box_c, uint32_t box_w, CUtensorMap* out,
-                    int elem_bytes = 4);
+                    int elem_bytes = 4, uint32_t box_h = 1);
 
 }  // namespace b200
