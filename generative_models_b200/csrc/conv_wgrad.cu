@@ -14,6 +14,8 @@
 #include "host_common.h"
 #include "ptx.cuh"
 
+#include <stdlib.h>
+
 #include "../../include/b200ddpm.h"
 
 namespace b200 {
@@ -32,6 +34,7 @@ struct WgradK {
   int taps;   // filter taps handled by one CTA: S (one filter row)
   int C1, Cin;
   int steps_total, steps_per_slice;
+  int dy3d;   // tmDY is the 3-D channel-block view: the whole dY tile is one TMA instruction
 };
 
 __device__ __forceinline__ void red_add_v4(float* p, float a, float b, float c, float d) {
@@ -104,7 +107,13 @@ conv_wgrad_kernel(const __grid_constant__ CUtensorMap tmDY, const __grid_constan
         const int q = rem - p * a.Wo;
         uint8_t* sA = smem + s * stage_bytes;
 #pragma unroll
-        for (int j = 0; j < NB; ++j) tma_load_2d(sA + j * BOXB, &tmDY, &full[s], j * CB, pix0);
+        for (int j = 0; j < NB; ++j) {
+          if (a.dy3d) {  // all channel blocks of the dY tile in one instruction (tmDY is the 3-D block view)
+            tma_load_3d(sA, &tmDY, &full[s], 0, pix0, 0);
+            break;
+          }
+          tma_load_2d(sA + j * BOXB, &tmDY, &full[s], j * CB, pix0);
+        }
         for (int kw = 0; kw < a.taps; ++kw) {
           uint8_t* sB = sA + (1 + kw) * kWgTileBytes;
 #pragma unroll
@@ -213,7 +222,13 @@ extern "C" int b200_conv_wgrad(const b200_wgrad_args* a, void* ws, size_t ws_byt
   const int eb = bf ? 2 : 4, sw32 = bf ? 0 : 1;
   const uint32_t cb = bf ? 64 : 32, pixs = bf ? kWgPixBf : kWgPix;
   CUtensorMap tmDY, tmX, tmX2;
-  int r = get_tmap_2d(a->dy, M_total, 128, a->dy_ld ? a->dy_ld : 128, cb, pixs, eb, sw32, &tmDY);
+  static int dy3d = -1;  // developer knob B200_WGRAD_DY3D=0: one 2-D box per channel block of the dY tile
+  if (dy3d < 0) {
+    const char* e = getenv("B200_WGRAD_DY3D");
+    dy3d = e ? atoi(e) : 1;
+  }
+  int r = dy3d ? get_tmap_blocks3d(a->dy, M_total, a->dy_ld ? a->dy_ld : 128, cb, pixs, 128 / cb, eb, sw32, &tmDY)
+               : get_tmap_2d(a->dy, M_total, 128, a->dy_ld ? a->dy_ld : 128, cb, pixs, eb, sw32, &tmDY);
   if (r) return r;
   r = get_tmap_im2col(a->x, a->N, a->H, a->W, a->C1, a->x_ld ? a->x_ld : a->C1, lower, upper, a->stride, cb, pixs, eb, sw32, &tmX);
   if (r) return r;
@@ -227,6 +242,7 @@ extern "C" int b200_conv_wgrad(const b200_wgrad_args* a, void* ws, size_t ws_byt
   const int tiles = a->R * (Cin / 128);  // one CTA per (filter row, 128-channel ci block, pixel slice)
   WgradK k;
   k.dw = a->dw;
+  k.dy3d = dy3d;
   k.M_total = M_total;
   k.HoWo = a->Ho * a->Wo;
   k.Wo = a->Wo;

@@ -72,6 +72,39 @@ int get_tmap_2d(const void* base, uint64_t rows, uint64_t cols, uint64_t ld_elem
   return 0;
 }
 
+// A [rows][nblocks * box_cols] matrix as {box_cols, rows, nblocks}: ONE box {box_cols, box_rows, nblocks} lands in shared
+// memory as nblocks consecutive [box_rows][128 B] sub-tiles — the layout of nblocks separate 2-D boxes, in one instruction.
+int get_tmap_blocks3d(const void* base, uint64_t rows, uint64_t ld_elems, uint32_t box_cols, uint32_t box_rows,
+                      uint32_t nblocks, int elem_bytes, int swizzle32, CUtensorMap* out) {
+  TmapKey k = {{reinterpret_cast<uint64_t>(base), rows, nblocks, ld_elems,
+                (static_cast<uint64_t>(box_cols) << 32) | box_rows, static_cast<uint64_t>(elem_bytes), 3, static_cast<uint64_t>(swizzle32)}};
+  std::lock_guard<std::mutex> lock(g_mu);
+  auto it = g_cache.find(k);
+  if (it != g_cache.end()) {
+    *out = it->second;
+    return 0;
+  }
+  if (int r = load_driver_fns()) return r;
+  const uint64_t eb = static_cast<uint64_t>(elem_bytes);
+  cuuint64_t dims[3] = {box_cols, rows, nblocks};
+  cuuint64_t strides[2] = {ld_elems * eb, box_cols * eb};
+  cuuint32_t box[3] = {box_cols, box_rows, nblocks};
+  cuuint32_t estr[3] = {1, 1, 1};
+  CUtensorMap m;
+  CUresult r = g_encode_tiled(&m, dtype_of(elem_bytes), 3, const_cast<void*>(base), dims, strides, box, estr,
+                              CU_TENSOR_MAP_INTERLEAVE_NONE,
+                              swizzle32 ? CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B : CU_TENSOR_MAP_SWIZZLE_128B,
+                              CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) {
+    snprintf(g_last_error, sizeof(g_last_error), "cuTensorMapEncodeTiled(3d blocks) failed (CUresult %d) rows=%llu",
+             static_cast<int>(r), (unsigned long long)rows);
+    return -2;
+  }
+  g_cache.emplace(k, m);
+  *out = m;
+  return 0;
+}
+
 int get_tmap_im2col(const void* base, int N, int H, int W, int C, int ld, int lower, int upper, int stride, uint32_t box_c,
                     uint32_t box_pix, int elem_bytes, int swizzle32, CUtensorMap* out) {
   TmapKey k = {{reinterpret_cast<uint64_t>(base),
