@@ -68,7 +68,8 @@ struct StripK {
   int strip_rows;  // image rows per strip (non-flat)
   int rb;          // image rows per box of the multi-row strip maps (0: single-row boxes only)
   int rb2;         // rows per box of the second, smaller multi-row maps (0: none)
-  int sb;          // weight-tile ring depth
+  int wpair;       // ring slots hold TWO filter taps (32 KB), fetched by one 3-D TMA instruction (tmB = {ci, co, tap})
+  int sb;          // weight-tile ring depth (slots)
   int strip_alloc; // bytes between the two strip buffers (1 KB multiple)
   int cl;          // launched as 2-CTA clusters: each weight tile is fetched once per pair (half by each CTA, multicast)
   int dbg;         // developer knobs (B200_STRIP_DBG): 1 = skip TMA loads (timing of the MMA issue path only)
@@ -132,7 +133,8 @@ conv_strip_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   uint8_t* strip0 = smem;
   uint8_t* bring = smem + kSS * a.strip_alloc;
-  uint64_t* bars = reinterpret_cast<uint64_t*>(bring + a.sb * kBTile);
+  const int slot_bytes = a.wpair ? 2 * kBTile : kBTile;
+  uint64_t* bars = reinterpret_cast<uint64_t*>(bring + a.sb * slot_bytes);
   uint64_t* s_full = bars;                // [kSS]
   uint64_t* s_empty = s_full + kSS;       // [kSS]
   uint64_t* b_full = s_empty + kSS;       // [kSBMax]
@@ -257,16 +259,20 @@ conv_strip_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
         const bool is_skip = ch >= a.chunks;
         const int ntaps = is_skip ? 1 : a.taps;
         const int split = ntaps > 4 ? 4 : 0;
-        for (int tap = 0; tap < ntaps; ++tap, bs = (bs + 1 == static_cast<uint32_t>(a.sb)) ? (bph ^= 1, 0u) : bs + 1) {
+        const int tstep = a.wpair ? 2 : 1;
+        for (int tap = 0; tap < ntaps; tap += tstep, bs = (bs + 1 == static_cast<uint32_t>(a.sb)) ? (bph ^= 1, 0u) : bs + 1) {
           if (tap == split && q + 1 < total_chunks) load_strip(q + 1);
           mbar_wait(&b_empty[bs], bph);
           if (a.dbg & 1) {
             mbar_arrive(&b_full[bs]);
             continue;
           }
-          mbar_expect_tx(&b_full[bs], kBTile);
-          uint8_t* sB = bring + bs * kBTile;
-          if (is_skip) {
+          mbar_expect_tx(&b_full[bs], slot_bytes);
+          uint8_t* sB = bring + bs * slot_bytes;
+          if (a.wpair) {
+            // taps (tap, tap + 1) of this channel chunk in one instruction; past the last tap the box is zero-filled
+            tma_load_3d(sB, &tmB, &b_full[bs], ch * CK, 0, tap);
+          } else if (is_skip) {
             const int sk = ch - a.chunks;
             if (a.mode == 0) {
               tma_load_2d(sB, &tmW2, &b_full[bs], sk * CK, 0);
@@ -316,28 +322,32 @@ conv_strip_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
           const uint32_t strip_addr = smem_u32(strip0 + ss * a.strip_alloc);
           const bool is_skip = ch >= a.chunks;
           const int ntaps = is_skip ? 1 : a.taps;
-          for (int tap = 0; tap < ntaps; ++tap, bs = (bs + 1 == static_cast<uint32_t>(a.sb)) ? (bph ^= 1, 0u) : bs + 1) {
+          const int tstep = a.wpair ? 2 : 1;
+          for (int tap0 = 0; tap0 < ntaps; tap0 += tstep, bs = (bs + 1 == static_cast<uint32_t>(a.sb)) ? (bph ^= 1, 0u) : bs + 1) {
             mbar_wait(&b_full[bs], bph);
             tc_fence_after();
-            const uint32_t w_base = smem_u32(bring + bs * kBTile);
-            int shift = 0;
-            if (ntaps == 9) {
-              const int kh = tap / 3, kw = tap - kh * 3;
-              shift = (kh - 1) * a.Wp + (kw - 1);
-            }
-            // strip view: start address only 128 B-aligned.  The 128B-swizzle XOR uses absolute smem address bits
-            // [7,10) (as TMA's does), so row-shifted views need no descriptor base offset (verified on B200).
-            const uint32_t x_base = strip_addr + static_cast<uint32_t>(row0 + shift) * 128u;
+            for (int tt = 0; tt < tstep && tap0 + tt < ntaps; ++tt) {
+              const int tap = tap0 + tt;
+              const uint32_t w_base = smem_u32(bring + bs * slot_bytes + tt * kBTile);
+              int shift = 0;
+              if (ntaps == 9) {
+                const int kh = tap / 3, kw = tap - kh * 3;
+                shift = (kh - 1) * a.Wp + (kw - 1);
+              }
+              // strip view: start address only 128 B-aligned.  The 128B-swizzle XOR uses absolute smem address bits
+              // [7,10) (as TMA's does), so row-shifted views need no descriptor base offset (verified on B200).
+              const uint32_t x_base = strip_addr + static_cast<uint32_t>(row0 + shift) * 128u;
 #pragma unroll
-            for (int k = 0; k < 4; ++k) {
-              // MN-major A (dgrad): TF32 = 32 B-atom layout, 4 boxes of 32 ci; bf16 = plain SWIZZLE_128B, 2 boxes of
-              // 64 ci (LBO = box pitch, SBO = pitch of the 8-row K groups)
-              const uint64_t adesc = (a.mode == 0) ? make_smem_desc_sw128(w_base + k * 32, 16, 1024)
-                                     : BF16        ? make_smem_desc_sw128(w_base + k * 2048, 8192, 1024, 2)
-                                                   : make_smem_desc_sw128(w_base + k * 1024, 4096, 512, 1);
-              const uint64_t bdesc = make_smem_desc_sw128(x_base + k * 32, 16, 1024);
-              if (BF16) mma_f16_ss(d_tmem, adesc, bdesc, idesc, (ch | tap | k) != 0 ? 1u : 0u);
-              else mma_tf32_ss(d_tmem, adesc, bdesc, idesc, (ch | tap | k) != 0 ? 1u : 0u);
+              for (int k = 0; k < 4; ++k) {
+                // MN-major A (dgrad): TF32 = 32 B-atom layout, 4 boxes of 32 ci; bf16 = plain SWIZZLE_128B, 2 boxes of
+                // 64 ci (LBO = box pitch, SBO = pitch of the 8-row K groups)
+                const uint64_t adesc = (a.mode == 0) ? make_smem_desc_sw128(w_base + k * 32, 16, 1024)
+                                       : BF16        ? make_smem_desc_sw128(w_base + k * 2048, 8192, 1024, 2)
+                                                     : make_smem_desc_sw128(w_base + k * 1024, 4096, 512, 1);
+                const uint64_t bdesc = make_smem_desc_sw128(x_base + k * 32, 16, 1024);
+                if (BF16) mma_f16_ss(d_tmem, adesc, bdesc, idesc, (ch | tap | k) != 0 ? 1u : 0u);
+                else mma_tf32_ss(d_tmem, adesc, bdesc, idesc, (ch | tap | k) != 0 ? 1u : 0u);
+              }
             }
             if (a.cl) tc_commit_mc(&b_empty[bs], 3);
             else tc_commit(&b_empty[bs]);
@@ -602,12 +612,14 @@ int conv_strip_applicable(const b200_conv_args* a) {
   const long long positions = flat ? static_cast<long long>(a->N) * a->H * a->W : static_cast<long long>(a->N) * Hp * Wp;
   const long long num_tiles = (positions + kTileM - 1) / kTileM;
   // few tiles (small spatial levels at small batch): one 256-position tile per SM leaves the machine under-filled and
-  // the im2col kernel (128-position tiles, 2 CTAs/SM) is faster there — measured crossover ~4 tiles per SM.
+  // the im2col kernel (128-position tiles, 2 CTAs/SM) is faster there — measured crossover ~2 tiles per SM (it was ~4
+  // before the strip rows and filter taps were fetched in multi-row / two-tap TMA boxes: at batch 512 the 14x14 layers
+  // now take 72 us here against 74 us there, the 7x7 layers 25 us on either).
   // bf16 operands exist only in this kernel.
   static int min_tiles = -1;  // developer knob B200_STRIP_MIN_TILES
   if (min_tiles < 0) {
     const char* e = getenv("B200_STRIP_MIN_TILES");
-    min_tiles = e ? atoi(e) : 4 * 148;
+    min_tiles = e ? atoi(e) : 2 * 148;
   }
   // with a residual operand the crossover sits lower: the strip epilogue prefetches the residual rows one chunk ahead
   // (+3 us at 14x14, batch 512: 92 us), the im2col kernel's does not (+33 us: 107 us)
@@ -676,7 +688,17 @@ int conv_strip_launch(const b200_conv_args* a, void* stream) {
     cluster_on = e ? atoi(e) : 0;
   }
   const int cl = (cluster_on && a->mode == 0 && !a->skip_x) ? 1 : 0;
-  r = get_tmap_2d(a->w, a->w_cout, wcols, wcols, CK, a->mode == 0 ? (cl ? 64 : 128) : CK, eb, (a->mode == 1 && !bf) ? 1 : 0, &tmB);
+  // 3x3 fprop orientation: two filter taps per ring slot and per TMA instruction
+  static int wpair_on = -1;  // developer knob B200_STRIP_WPAIR=0: one tap per slot
+  if (wpair_on < 0) {
+    const char* e = getenv("B200_STRIP_WPAIR");
+    wpair_on = e ? atoi(e) : 1;
+  }
+  const int wpair = (wpair_on && a->mode == 0 && !a->skip_x && !cl && a->R * a->S == 9 && a->w_cout == 128) ? 1 : 0;
+  if (wpair)
+    r = get_tmap_3d(a->w, a->w_cin, a->w_cout, 9, wcols * eb, static_cast<uint64_t>(a->w_cin) * eb, CK, 128, 2, eb, 0, &tmB);
+  else
+    r = get_tmap_2d(a->w, a->w_cout, wcols, wcols, CK, a->mode == 0 ? (cl ? 64 : 128) : CK, eb, (a->mode == 1 && !bf) ? 1 : 0, &tmB);
   if (r) return r;
   // fused skip segment: a 1x1 convolution over (skip_x | skip_x2) with weights skip_w [128][skip_c1 + skip_c2],
   // accumulated into the same TMEM tile as extra K-chunks (identity weights = a residual add on the tensor cores,
@@ -734,7 +756,8 @@ int conv_strip_launch(const b200_conv_args* a, void* stream) {
       const char* e = getenv("B200_STRIP_RING");
       sb_cap = e ? atoi(e) : kSBMax;
     }
-    int sb = (kStripSmem - 1024 - kStripTail - kSS * k.strip_alloc) / kBTile;
+    k.wpair = wpair;
+    int sb = (kStripSmem - 1024 - kStripTail - kSS * k.strip_alloc) / (wpair ? 2 * kBTile : kBTile);
     sb = sb > kSBMax ? kSBMax : sb;
     k.sb = sb > sb_cap ? sb_cap : sb;
     if (k.sb < 2) return fail_arg("conv_strip: no room for the weight ring");

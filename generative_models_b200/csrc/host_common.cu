@@ -72,12 +72,13 @@ int get_tmap_2d(const void* base, uint64_t rows, uint64_t cols, uint64_t ld_elem
   return 0;
 }
 
-// A [rows][nblocks * box_cols] matrix as {box_cols, rows, nblocks}: ONE box {box_cols, box_rows, nblocks} lands in shared
-// memory as nblocks consecutive [box_rows][128 B] sub-tiles — the layout of nblocks separate 2-D boxes, in one instruction.
-int get_tmap_blocks3d(const void* base, uint64_t rows, uint64_t ld_elems, uint32_t box_cols, uint32_t box_rows,
-                      uint32_t nblocks, int elem_bytes, int swizzle32, CUtensorMap* out) {
-  TmapKey k = {{reinterpret_cast<uint64_t>(base), rows, nblocks, ld_elems,
-                (static_cast<uint64_t>(box_cols) << 32) | box_rows, static_cast<uint64_t>(elem_bytes), 3, static_cast<uint64_t>(swizzle32)}};
+// Generic 3-D tiled map {d0 (contiguous), d1, d2} with byte strides s1, s2 (multiples of 16; s2 may be smaller than s1:
+// the outer box dimension then walks column blocks of a row-major matrix) and box {b0, b1, b2}.
+int get_tmap_3d(const void* base, uint64_t d0, uint64_t d1, uint64_t d2, uint64_t s1, uint64_t s2, uint32_t b0, uint32_t b1,
+                uint32_t b2, int elem_bytes, int swizzle32, CUtensorMap* out) {
+  TmapKey k = {{reinterpret_cast<uint64_t>(base), (d0 << 32) | d1, (d2 << 40) | s1, s2,
+                (static_cast<uint64_t>(b0) << 32) | (static_cast<uint64_t>(b1) << 16) | b2, static_cast<uint64_t>(elem_bytes), 3,
+                static_cast<uint64_t>(swizzle32)}};
   std::lock_guard<std::mutex> lock(g_mu);
   auto it = g_cache.find(k);
   if (it != g_cache.end()) {
@@ -85,10 +86,9 @@ int get_tmap_blocks3d(const void* base, uint64_t rows, uint64_t ld_elems, uint32
     return 0;
   }
   if (int r = load_driver_fns()) return r;
-  const uint64_t eb = static_cast<uint64_t>(elem_bytes);
-  cuuint64_t dims[3] = {box_cols, rows, nblocks};
-  cuuint64_t strides[2] = {ld_elems * eb, box_cols * eb};
-  cuuint32_t box[3] = {box_cols, box_rows, nblocks};
+  cuuint64_t dims[3] = {d0, d1, d2};
+  cuuint64_t strides[2] = {s1, s2};
+  cuuint32_t box[3] = {b0, b1, b2};
   cuuint32_t estr[3] = {1, 1, 1};
   CUtensorMap m;
   CUresult r = g_encode_tiled(&m, dtype_of(elem_bytes), 3, const_cast<void*>(base), dims, strides, box, estr,
@@ -96,13 +96,22 @@ int get_tmap_blocks3d(const void* base, uint64_t rows, uint64_t ld_elems, uint32
                               swizzle32 ? CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B : CU_TENSOR_MAP_SWIZZLE_128B,
                               CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   if (r != CUDA_SUCCESS) {
-    snprintf(g_last_error, sizeof(g_last_error), "cuTensorMapEncodeTiled(3d blocks) failed (CUresult %d) rows=%llu",
-             static_cast<int>(r), (unsigned long long)rows);
+    snprintf(g_last_error, sizeof(g_last_error), "cuTensorMapEncodeTiled(3d) failed (CUresult %d) dims=%llu,%llu,%llu",
+             static_cast<int>(r), (unsigned long long)d0, (unsigned long long)d1, (unsigned long long)d2);
     return -2;
   }
   g_cache.emplace(k, m);
   *out = m;
   return 0;
+}
+
+// A [rows][nblocks * box_cols] matrix as {box_cols, rows, nblocks}: ONE box {box_cols, box_rows, nblocks} lands in shared
+// memory as nblocks consecutive [box_rows][128 B] sub-tiles — the layout of nblocks separate 2-D boxes, in one instruction.
+int get_tmap_blocks3d(const void* base, uint64_t rows, uint64_t ld_elems, uint32_t box_cols, uint32_t box_rows,
+                      uint32_t nblocks, int elem_bytes, int swizzle32, CUtensorMap* out) {
+  const uint64_t eb = static_cast<uint64_t>(elem_bytes);
+  return get_tmap_3d(base, box_cols, rows, nblocks, ld_elems * eb, box_cols * eb, box_cols, box_rows, nblocks, elem_bytes,
+                     swizzle32, out);
 }
 
 int get_tmap_im2col(const void* base, int N, int H, int W, int C, int ld, int lower, int upper, int stride, uint32_t box_c,

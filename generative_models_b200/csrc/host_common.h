@@ -57,6 +57,8 @@ int get_tmap_im2col(const void* base, int N, int H, int W, int C, int ld, int lo
 
 // NHWC [N][H][W][C] plain tiled 4-D map {C, W, H, N}: box = box_c channels x box_w pixels of ONE image row
 // (out-of-range w / h / n coordinates are zero-filled: the convolution halo).
+int get_tmap_3d(const void* base, uint64_t d0, uint64_t d1, uint64_t d2, uint64_t s1, uint64_t s2, uint32_t b0, uint32_t b1,
+                uint32_t b2, int elem_bytes, int swizzle32, CUtensorMap* out);
 int get_tmap_blocks3d(const void* base, uint64_t rows, uint64_t ld_elems, uint32_t box_cols, uint32_t box_rows,
                       uint32_t nblocks, int elem_bytes, int swizzle32, CUtensorMap* out);
 int get_tmap_rows4d(const void* base, int N, int H, int W, int C, int ld, uint32_t box_c, uint32_t box_w, CUtensorMap* out,

@@ -151,7 +151,13 @@ class DiffusionModelB200(nn.Module):
         convolutions needs no loss scaling, so `loss_scale` is reported as 1."""
         if y is not None:
             # same CPU-generator draw and in-place edit of the caller's y as diffusion_model.py:67
-            y[torch.rand(y.shape[0]) < self.G.cf_drop_prob] = -1
+            drop = torch.rand(y.shape[0]) < self.G.cf_drop_prob
+            if y.is_cuda:
+                # y[drop] = -1 on a device tensor goes through nonzero(), a stream synchronisation every step; the
+                # masked fill of a (pinned, asynchronously copied) mask writes the same elements without one
+                y.masked_fill_(drop.pin_memory().to(y.device, non_blocking=True), -1)
+            else:
+                y[drop] = -1
         b = self._plan(x.shape[0], "train")
         b.stage_inputs(x, y, eps, u)
         world = torch.distributed.get_world_size() if torch.distributed.is_initialized() else 1
@@ -162,6 +168,8 @@ class DiffusionModelB200(nn.Module):
             b.enqueue_fwd_bwd()
         # the one collective of the path: sum of the flat fp32 gradient over NVLink; no-op at world 1
         dist.allreduce_flat_grad(self.store.grad)
+        # (fwd+bwd and Adam stay two graphs also at world 1: captured as ONE graph the step measured slower, 22.4 vs
+        # 20.0 ms, its launch costing ~4 ms of host time against 0.01 ms for the fwd+bwd graph alone)
         if self.use_graph:
             b.run_graphed(b.enqueue_adam, "adam")
         else:

@@ -381,3 +381,22 @@ def test_conv_dgrad_fused_residual(lib):
                      skip_w=ptr(eye), bias2=None, skip_c1=128, skip_c2=0, skip_x_ld=256, skip_x2_ld=0)
     lib.call("b200_conv_igemm", a, stream())
     assert rel(out.permute(0, 3, 1, 2).cpu(), ref) < TF32_TOL
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("knobs", [{"B200_STRIP_CLUSTER": "1"}, {"B200_STRIP_TAIL": "0", "B200_STRIP_RB": "0", "B200_STRIP_WPAIR": "0"},
+                                   {"B200_STRIP_RB": "4", "B200_STRIP_RING": "3"}, {"B200_WGRAD_DY3D": "0"}])
+def test_conv_parity_under_developer_knobs(knobs):
+    """The strip / wgrad kernels' alternative paths (2-CTA cluster weight multicast; uniform tiles, single-row strip boxes
+    and one-tap weight slots; a forced box height and a shallow ring; four 2-D dY boxes) give the same results: the knobs
+    are read once per process, so the fprop / dgrad / wgrad parity tests are re-run in a child process with them set."""
+    import os
+    import subprocess
+    import sys
+
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    env = dict(os.environ, **knobs)
+    r = subprocess.run([sys.executable, "-m", "pytest", os.path.join(root, "tests", "test_gpu_convs.py"), "-m", "gpu", "-x", "-q",
+                        "-k", "test_conv_fprop or test_conv_dgrad or test_conv_wgrad or test_strided_dgrad_via"],
+                       cwd=root, env=env, capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
