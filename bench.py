@@ -433,11 +433,12 @@ def run_ours(args, rank, world, local_rank):
     achieved = conv_fl / (conv_ms / 1e3) / 1e12
     roofline = {
         "kernel": strip_name + " (all its fprop + dgrad launches of one train step; the top kernel of "
-                  "profiles/r01_launches_summary.md)", "bound": "tensor",
+                  "profiles/r01e_launches_summary_tf32.md)", "bound": "tensor",
         "achieved": achieved, "peak": tf32_live, "unit": "TFLOP/s", "frac": achieved / tf32_live,
         # dram__bytes_read.sum + dram__bytes_write.sum of one captured launch (28x28 128->128 3x3 fprop, batch 512):
-        # profiles/r01_ncu_full_summary.md; algorithmic bytes of that launch = 205.5 MB in + 205.5 MB out + 0.6 MB weights
-        "traffic": 363.5e6, "traffic_launch": "fprop 3x3 128->128 @28x28, N=512 (algorithmic 411.6e6 B)",
+        # profiles/r01e_ncu_full_summary.md (206.5 MB read + 156.5 MB written; the write-back of the tail sits in L2 when
+        # the kernel ends); algorithmic bytes of that launch = 205.5 MB in + 205.5 MB out + 0.6 MB weights
+        "traffic": 363.0e6, "traffic_launch": "fprop 3x3 128->128 @28x28, N=512 (algorithmic 411.6e6 B)",
         "peak_source": "cuBLAS TF32 8192^3 measured live in this run (MEASURED_PEAKS.json has no TF32 figure; its bf16 "
                        f"burst is {peaks.get('bf16_tflops')} TFLOP/s, i.e. nominal TF32 = half = "
                        f"{(peaks.get('bf16_tflops') or 0) / 2:.1f})",
