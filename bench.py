@@ -156,7 +156,7 @@ def run_reference(args, rank):
         "sampling": {"value": 4.0 / (sps * args.sample_steps), "unit": "img/s", "n": 4, "timesteps": args.sample_steps,
                      "extrapolated_from_steps": 3, "guided": False},
     }
-    print(json.dumps(line), flush=True)
+    print(json.dumps(line), file=RESULT_OUT, flush=True)
     return 0
 
 
@@ -476,13 +476,27 @@ def run_ours(args, rank, world, local_rank):
         "breakdown": breakdown,
         "activation_bytes": bound.plan.activation_bytes(),
     }
-    print(json.dumps(line), flush=True)
+    print(json.dumps(line), file=RESULT_OUT, flush=True)
     if world > 1:
         dist.destroy_process_group()
     return 0
 
 
+RESULT_OUT = sys.stdout
+
+
+def keep_stdout_for_the_result():
+    """stdout carries the ONE JSON line and nothing else: fd 1 is pointed at stderr for the rest of the process (NCCL
+    prints its version banner to stdout from C), and the result goes to a private duplicate of the original stdout."""
+    global RESULT_OUT
+    sys.stdout.flush()
+    saved = os.dup(1)
+    os.dup2(2, 1)
+    RESULT_OUT = os.fdopen(saved, "w")
+
+
 def main():
+    keep_stdout_for_the_result()
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=20)
@@ -503,7 +517,7 @@ def main():
         # convenience: re-launch under torchrun, one rank per GPU
         cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={args.gpus}",
                "--master-addr", "127.0.0.1", "--master-port", "29511", os.path.abspath(__file__)] + sys.argv[1:]
-        return subprocess.call(cmd)
+        return subprocess.call(cmd, stdout=RESULT_OUT)
     return run_ours(args, rank, world, local_rank)
 
 
