@@ -71,6 +71,7 @@ struct StripK {
   int wpair;       // ring slots hold TWO filter taps (32 KB), fetched by one 3-D TMA instruction (tmB = {ci, co, tap})
   int sb;          // weight-tile ring depth (slots)
   int strip_alloc; // bytes between the two strip buffers (1 KB multiple)
+  int split;       // filter tap before whose weight load the next chunk's strip is requested
   int cl;          // launched as 2-CTA clusters: each weight tile is fetched once per pair (half by each CTA, multicast)
   int dbg;         // developer knobs (B200_STRIP_DBG): 1 = skip TMA loads (timing of the MMA issue path only)
 };
@@ -194,9 +195,11 @@ conv_strip_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
   if (warp == 0) {
     if (lane == 0) {
       // ---------------------------------------------------------------- TMA producer
-      // Order of issue: strip(0); then per chunk: weight taps 0..3, strip(next chunk), weight taps 4..8 — the next
-      // strip is requested ~1.5 chunks of MMA time before it is needed, and never blocks the weight stream (its buffer
-      // was released by the chunk before the one in flight).
+      // Order of issue: strip(0); then per chunk: weight taps 0..5, strip(next chunk), weight taps 6..8.  The request
+      // has to wait for the MMAs of the chunk before the one in flight to release the buffer, and the weight stream
+      // stands still meanwhile: asked for early (before tap 0 / 2) the ring drains and the kernel loses 7-18 %; before
+      // tap 6 or 8 the buffer is free by the time the producer (one ring ahead of the MMAs) gets there (28x28:
+      // 194.5 us with tap 4, 190.7 with 6 or 8).
       uint32_t bs = 0, bph = 1;  // ring slot and the parity its "empty" barrier is awaited with
       const int tiles_mine = (a.num_tiles - static_cast<int>(blockIdx.x) + static_cast<int>(gridDim.x) - 1) / static_cast<int>(gridDim.x);
       const int total_chunks = tiles_mine * CH;
@@ -258,7 +261,7 @@ conv_strip_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
         const int ch = q % CH;
         const bool is_skip = ch >= a.chunks;
         const int ntaps = is_skip ? 1 : a.taps;
-        const int split = ntaps > 4 ? 4 : 0;
+        const int split = ntaps > 4 ? a.split : 0;
         const int tstep = a.wpair ? 2 : 1;
         for (int tap = 0; tap < ntaps; tap += tstep, bs = (bs + 1 == static_cast<uint32_t>(a.sb)) ? (bph ^= 1, 0u) : bs + 1) {
           if (tap == split && q + 1 < total_chunks) load_strip(q + 1);
@@ -748,6 +751,14 @@ int conv_strip_launch(const b200_conv_args* a, void* stream) {
   k.round_out = a->round_out;
   k.strip_rows = strip_rows;
   k.rb = rb;
+  {
+    static int split = -1;  // developer knob B200_STRIP_SPLIT (even: the two-tap slots step by 2)
+    if (split < 0) {
+      const char* e = getenv("B200_STRIP_SPLIT");
+      split = e ? atoi(e) : 6;
+    }
+    k.split = split;
+  }
   k.rb2 = rb2;
   k.strip_alloc = ((flat ? kTileM * 128 : strip_rows * Wp * 128) + 1023) & ~1023;
   {
