@@ -43,12 +43,33 @@ def run_smoke():
             return O.unet_forward(sd0, z, l, guide=ys)
 
     rz, rx, re = O.sample_loop(net, init, 2, sampler="noisy", mean_type="eps", cond_w=None, noises=noises)
-    # the first step sits at logsnr = -20 where x^ = 2.2e4 * (z - eps^) is clipped: a 1e-3 net difference can flip a
-    # pixel between -1 and +1, so the bar is the FRACTION of pixels further than 5e-3 from the oracle, not the max norm
+    # Free-running: the first step sits at logsnr = -20 where x^ = 2.2e4 * (z - eps^) is clipped, so a 1e-3 net
+    # difference flips a pixel between -1 and +1 and the second (last) step carries every flip on through the UNet's
+    # receptive field.  With 2 x 784 pixels that fraction is a coarse, chaotic number (1-4 % from run to run: the
+    # GroupNorm / loss reductions use atomics, and stored activations are rounded to TF32, which turns a 1e-7
+    # reordering difference into a 5e-4 one now and then) — it only guards against a grossly wrong sampler.
     ez = ((zs.cpu() - rz).abs() > 5e-3).double().mean().item()
-    assert ez < 0.03, ez
+    assert ez < 0.10, ez
+    # The parity bar proper is teacher-forced, like tests/test_gpu_model.py: every single step from the ORACLE's z_t with
+    # the same noise; pixel-fraction bar at logsnr = -20, max-norm bar on the well-conditioned last step.
+    T = 2
+    b = m._plan(2, "sample")
+    e1 = 0.0
+    for k in range(T):
+        z_t = init if k == 0 else rz[k - 1]
+        b.begin_sampling(z_t.to(dev), ys.to(dev), None)
+        b.step_dev.fill_(T - 1 - k)
+        b.noise.copy_(noises[k].to(dev).reshape(2, -1))
+        b.enqueue_sampler_step(draw_noise=False)
+        z_ours = b.plan.z_in.cpu().view(2, 1, 28, 28)
+        if k == 0:
+            f0 = ((z_ours - rz[k]).abs() > 5e-3).double().mean().item()
+            assert f0 < 0.02, f0
+        else:
+            e1 = ((z_ours - rz[k]).abs().max() / rz[k].abs().max()).item()
+            assert e1 < 5e-3, e1
     torch.cuda.synchronize()
     launched = lib.launch_count() - n0
     assert launched > 100, launched
-    print(f"smoke ok: loss {loss:.6f} (oracle {ref_loss.item():.6f}), grad relerr {e:.2e}, sample pixels >5e-3 off: {ez:.2%}, "
+    print(f"smoke ok: loss {loss:.6f} (oracle {ref_loss.item():.6f}), grad relerr {e:.2e}, sample pixels >5e-3 off: {ez:.2%} free-running / {f0:.2%} first step teacher-forced, last step relerr {e1:.2e}, "
           f"{launched} kernels launched from {lib.LIB_PATH}")
