@@ -433,7 +433,7 @@ def run_ours(args, rank, world, local_rank):
     achieved = conv_fl / (conv_ms / 1e3) / 1e12
     roofline = {
         "kernel": strip_name + " (all its fprop + dgrad launches of one train step; the top kernel of "
-                  "profiles/r01e_launches_summary_tf32.md)", "bound": "tensor",
+                  "profiles/r01f_launches_summary_bench_tf32.md, the ncu launch list of this command: 45.7 % of a step there)", "bound": "tensor",
         "achieved": achieved, "peak": tf32_live, "unit": "TFLOP/s", "frac": achieved / tf32_live,
         # dram__bytes_read.sum + dram__bytes_write.sum of one captured launch (28x28 128->128 3x3 fprop, batch 512):
         # profiles/r01e_ncu_full_summary.md (206.5 MB read + 156.5 MB written; the write-back of the tail sits in L2 when
