@@ -94,67 +94,70 @@ def synthetic_batch(B, seed, size=28):
 
 
 # ----------------------------------------------------------------------------------------------- reference arm (CPU)
-def cpu_reference_rate(sample_B, steps, warmup, threads):
-    """The reference algorithm (oracle/ddpm_oracle.py, pinned to the reference's own outputs) on the host cores:
-    one train step = loss fwd + autograd bwd + torch.optim.Adam, like diffusion_model.py:63-74 on CPU."""
-    from oracle import ddpm_oracle as O
-    torch.set_num_threads(threads)
-    sd = {k: v.clone().requires_grad_(True) for k, v in O.random_state_dict(1).items()}
-    params = list(sd.values())
-    opt = torch.optim.Adam(params, lr=3e-4)
-    times = []
-    for it in range(warmup + steps):
-        x, y = synthetic_batch(sample_B, it)
-        t0 = time.perf_counter()
-        opt.zero_grad()
-        eps = torch.randn(x.shape)
-        u = torch.rand(sample_B)
-        loss, _, _ = O.training_loss(sd, x, y, eps, u, "eps")
-        loss.backward()
-        opt.step()
-        dt = time.perf_counter() - t0
-        if it >= warmup:
-            times.append(dt)
-    return sample_B * len(times) / sum(times), sum(times) / len(times)
+def workload_string(args, precision=None):
+    precision = precision or args.precision
+    return (f"DDPM UNet C=128 1x28x28, train step, batch {args.batch}/GPU "
+            + ("fp32/TF32 (configs[1])" if precision == "tf32" else "bf16 ResBlock convs (configs[2])")
+            + f" + {args.sample_steps}-step ancestral sampling of {args.sample_n} img/GPU")
 
 
-def cpu_reference_sampling_rate(n, steps, threads):
-    from oracle import ddpm_oracle as O
-    torch.set_num_threads(threads)
-    sd = O.random_state_dict(1)
-    y = torch.arange(n) % 10
-    init = torch.randn(n, 1, 28, 28)
-    noises = [torch.randn(n, 1, 28, 28) for _ in range(steps)]
+def run_cpu_reference(steps, warmup, bs, sample_n, sample_steps, timesteps, timeout=1500):
+    """The UNMODIFIED reference (baseline/_ref, installed by tools/vendor_reference.sh) through gms.main's own
+    construction path, on the host cores, in a child process that cannot see the GPU (so torch.cuda.amp is inert, as on
+    a CPU-only machine): oracle/cpu_reference_bench.py.  Returns its JSON, or {"error": ...}."""
+    env = dict(os.environ, CUDA_VISIBLE_DEVICES="")
+    for k in ("RANK", "WORLD_SIZE", "LOCAL_RANK", "MASTER_ADDR", "MASTER_PORT"):
+        env.pop(k, None)
+    cmd = [sys.executable, os.path.join(ROOT, "oracle", "cpu_reference_bench.py"), "--steps", str(steps), "--warmup",
+           str(warmup), "--bs", str(bs), "--sample-n", str(sample_n), "--sample-steps", str(sample_steps),
+           "--timesteps", str(timesteps)]
+    try:
+        r = subprocess.run(cmd, env=env, stdout=subprocess.PIPE, stderr=subprocess.PIPE, text=True, timeout=timeout)
+        lines = [ln for ln in r.stdout.splitlines() if ln.startswith("{")]
+        if r.returncode != 0 or not lines:
+            return {"error": (r.stderr or r.stdout)[-400:]}
+        return json.loads(lines[-1])
+    except Exception as e:  # noqa: BLE001
+        return {"error": repr(e)[:400]}
 
-    def net(z, l, uncond):
-        with torch.no_grad():
-            return O.unet_forward(sd, z, l, guide=y)
 
-    t0 = time.perf_counter()
-    O.sample_loop(net, init, steps, sampler="noisy", mean_type="eps", cond_w=None, noises=noises)
-    dt = time.perf_counter() - t0
-    return dt / steps  # seconds per sampler step for n images
+def cpu_sample_string(res, bs):
+    t, s = res["train"], res.get("sampling")
+    out = (f"unmodified reference (gms.main load_model_and_data + the train loop's inner body, main.py:205-215) on CPU, "
+           f"{t['steps']} train_step calls at batch {bs} (BASELINE.json configs[0]), {res['threads']} torch threads, "
+           f"{res.get('cpu', '')}, torch {res.get('torch', '')}")
+    if s:
+        out += (f"; sampling: {s['measured_steps']} ancestral steps of {s['n']} images extrapolated to "
+                f"{s['extrapolated_to_steps']}")
+    return out
 
 
 def run_reference(args, rank):
+    """`--impl reference`: the reference's own CPU implementation of the path on the box's host cores, on configs[0]'s
+    batch (64) as a bounded sample of this arm's workload."""
     if rank != 0:
         return 0
-    threads = os.cpu_count() or 1
-    sample_B = args.cpu_batch
-    rate, s_per_step = cpu_reference_rate(sample_B, max(1, args.steps), max(1, min(args.warmup, 1)), threads)
-    sps = cpu_reference_sampling_rate(4, 3, threads)
+    res = run_cpu_reference(max(1, args.steps), max(1, min(args.warmup, 5)), args.cpu_batch, 16, args.cpu_sample_steps,
+                            args.sample_steps)
+    if "error" in res:
+        print(json.dumps({"impl": "reference", "unavailable": "cpu reference failed: " + res["error"][-200:].replace("\n", " ")}),
+              file=RESULT_OUT, flush=True)
+        return 0
+    rate, sps = res["train"]["img_s"], res["train"]["s_per_step"]
+    smp = res.get("sampling") or {}
     line = {
         "impl": "reference", "metric": METRIC, "value": rate, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
-        "warmup": args.warmup, "ms_per_step": s_per_step * 1e3, "higher_is_better": True, "scaling": "weak",
+        "warmup": args.warmup, "ms_per_step": sps * 1e3, "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": {"workload": f"DDPM UNet C=128 1x28x28, train step, batch {args.batch}/GPU fp32/TF32 (configs[1])",
-                   "mean_type": "eps", "sampler": "noisy", "timesteps": args.sample_steps},
-        "cpu_baseline": {"value": rate, "unit": UNIT, "cores": threads, "kind": "port",
-                         "sample": f"{args.steps} train steps (fwd+bwd+Adam) of {sample_B} images, torch CPU fp32, "
-                                   f"oracle/ddpm_oracle.py (restatement pinned to reference-generated fixtures)"},
-        "e2e": {"value": rate, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
-        "sampling": {"value": 4.0 / (sps * args.sample_steps), "unit": "img/s", "n": 4, "timesteps": args.sample_steps,
-                     "extrapolated_from_steps": 3, "guided": False},
+        "config": {"workload": workload_string(args), "mean_type": "eps", "sampler": "noisy", "timesteps": args.sample_steps,
+                   "bounded_sample": f"batch {args.cpu_batch} per step on the host CPU (configs[0]'s batch) instead of {args.batch}"},
+        "cpu_baseline": {"value": rate, "unit": UNIT, "cores": res["threads"], "kind": "reference",
+                         "sample": cpu_sample_string(res, args.cpu_batch)},
+        "e2e": {"value": rate, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0,
+                "sampling": {"unguided_img_s": (smp.get("unguided") or {}).get("img_s_1000_steps"),
+                             "guided_img_s": (smp.get("guided") or {}).get("img_s_1000_steps"), "n": smp.get("n"),
+                             "T": smp.get("extrapolated_to_steps"), "measured_steps": smp.get("measured_steps")}},
+        "last_loss": res["train"]["last_loss"],
     }
     print(json.dumps(line), file=RESULT_OUT, flush=True)
     return 0
@@ -182,7 +185,7 @@ def profile_ops(model, bound, kind):
         groups = [bound.zero_ops, bound.pre_ops, p.refresh_ops, p.embed_ops[0], p.body_ops, p.head_ops[:1],
                   bound.loss_ops, p.refreshT_ops, p.bwd_ops, bound.adam_ops]
     else:
-        groups = [p.embed_ops[0], p.body_ops, p.head_ops[:1], bound.step_ops[False]]
+        groups = [p.embed_ops[0], p.body_ops, p.head_ops[:1], bound._step_ops(None)[0]]
     ops = [o for g in groups for o in g]
     st = torch.cuda.current_stream()
     sp = model._stream()
@@ -233,6 +236,33 @@ def measure_tf32_peak():
         torch.backends.cuda.matmul.allow_tf32 = old
 
 
+class _NullWriter:
+    """SummaryWriter stand-in for timing evaluate() (tensorboard's video encoder is not what is measured)."""
+
+    def add_image(self, *a, **k):
+        pass
+
+    def add_video(self, *a, **k):
+        pass
+
+
+def run_gpu_torch_baseline(batch, variants="ref_amp_fp16,tf32,bf16", steps=5, sample_steps=5):
+    """tools/gpu_torch_baseline.py in a child process: the unmodified reference in torch eager on this GPU."""
+    cmd = [sys.executable, os.path.join(ROOT, "tools", "gpu_torch_baseline.py"), "--batch", str(batch), "--steps", str(steps),
+           "--warmup", "2", "--sample-n", str(batch), "--sample-steps", str(sample_steps), "--variants", variants]
+    env = dict(os.environ)
+    for k in ("RANK", "WORLD_SIZE", "LOCAL_RANK", "MASTER_ADDR", "MASTER_PORT"):
+        env.pop(k, None)
+    try:
+        r = subprocess.run(cmd, env=env, stdout=subprocess.PIPE, stderr=subprocess.PIPE, text=True, timeout=600)
+        lines = [ln for ln in r.stdout.splitlines() if ln.startswith("{")]
+        if r.returncode != 0 or not lines:
+            return {"error": (r.stderr or r.stdout)[-300:]}
+        return json.loads(lines[-1])
+    except Exception as e:  # noqa: BLE001
+        return {"error": repr(e)[:300]}
+
+
 def run_ours(args, rank, world, local_rank):
     import torch.distributed as dist
     torch.cuda.set_device(local_rank)
@@ -244,11 +274,13 @@ def run_ours(args, rank, world, local_rank):
         ge.build()
     if world > 1:
         dist.barrier()
+    from generative_models_b200 import dist as bdist
     from generative_models_b200 import lib
     from generative_models_b200.model import DiffusionModelB200, default_G
 
     B = args.batch
     torch.manual_seed(0)
+
     def make_model(precision):
         torch.manual_seed(0)
         G = default_G(device=dev, mean_type="eps", sampler="noisy", timesteps=args.sample_steps, bs=B, graph=1,
@@ -268,12 +300,15 @@ def run_ours(args, rank, world, local_rank):
             dist.barrier()
         torch.cuda.synchronize()
 
-    def max_over_ranks(ms):
+    def over_ranks(ms, op):
         if world > 1:
             t = torch.tensor([ms], device=dev, dtype=torch.float64)
-            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            dist.all_reduce(t, op=op)
             return t.item()
         return ms
+
+    def max_over_ranks(ms):
+        return over_ranks(ms, dist.ReduceOp.MAX)
 
     # ---- device-resident leg: batches already in HBM
     nb = 4
@@ -319,10 +354,12 @@ def run_ours(args, rank, world, local_rank):
     e1.record()
     barrier()
     t_wall1 = time.time()
-    ms = max_over_ranks(e0.elapsed_time(e1))
+    ms_local = e0.elapsed_time(e1)
+    ms = max_over_ranks(ms_local)
+    ms_min = over_ranks(ms_local, dist.ReduceOp.MIN)
     value = B * world * K / (ms / 1e3)
 
-    # ---- end-to-end leg: pinned host batches in, loss out, every step
+    # ---- end-to-end leg: pinned host batches in, loss out, every step (what gms/main.py:205-215 does per batch)
     barrier()
     e0.record()
     last = 0.0
@@ -338,18 +375,39 @@ def run_ours(args, rank, world, local_rank):
     clocks.stop()
     e2e_value = B * world * K / (ms_e2e / 1e3)
 
-    # ---- sampling leg: fused ancestral loop, sharded by batch, no communication
+    # ---- the collective alone (world > 1): the two gradient buckets, back to back, CUDA events, max over ranks
+    allreduce_ms = None
+    if world > 1:
+        st = model.store
+        for _ in range(3):
+            bdist.allreduce_flat_grad(st.grad[st.bucket_split:])
+            bdist.allreduce_flat_grad(st.grad[:st.bucket_split])
+        barrier()
+        e0.record()
+        for _ in range(10):
+            bdist.allreduce_flat_grad(st.grad[st.bucket_split:])
+            bdist.allreduce_flat_grad(st.grad[:st.bucket_split])
+        e1.record()
+        barrier()
+        allreduce_ms = max_over_ranks(e0.elapsed_time(e1)) / 10
+
+    # ---- sampling legs: fused ancestral loop, sharded by batch, no communication
     n, T = args.sample_n, args.sample_steps
 
+    def warm_sampler(mdl, n_, guided):
+        labels = (torch.arange(n_, device=dev) % 10)
+        init = torch.randn(n_, 1, 28, 28, device=dev)
+        bs = mdl._plan(n_, "sample_g" if guided else "sample")  # warm-up: 3 steps of the real plan (eager, capture, replay)
+        bs.begin_sampling(init, labels, torch.ones(n_, device=dev) if guided else None)
+        for _ in range(min(3, T)):
+            bs.run_graphed(bs.enqueue_sampler_step, ("sampler_step", None))
+        return init, labels
+
     def time_sampling(mdl):
+        """Unguided (the evaluate() path: one net eval per step), z_T already on the device."""
         if T <= 0 or n <= 0:
             return None
-        labels = (torch.arange(n, device=dev) % 10)
-        init = torch.randn(n, 1, 28, 28, device=dev)
-        bs = mdl._plan(n, "sample")  # warm-up: 3 steps of the real plan (eager, capture, replay)
-        bs.begin_sampling(init, labels, None)
-        for _ in range(min(3, T)):
-            bs.run_graphed(bs.enqueue_sampler_step, "sampler_step")
+        init, labels = warm_sampler(mdl, n, False)
         barrier()
         e0.record()
         z = mdl._sample_loop(init, labels, None)[0]
@@ -357,10 +415,52 @@ def run_ours(args, rank, world, local_rank):
         barrier()
         ms_s = max_over_ranks(e0.elapsed_time(e1))
         return {"value": n * world / (ms_s / 1e3), "unit": "img/s", "n_per_gpu": n, "timesteps": T, "guided": False,
-                "seconds": ms_s / 1e3, "tensor_tflops": n * world * T * FWD_FLOP_PER_IMG / (ms_s / 1e3) / 1e12,
+                "seconds": ms_s / 1e3, "tensor_tflops": n * T * FWD_FLOP_PER_IMG / (ms_s / 1e3) / 1e12,
                 "finite": bool(torch.isfinite(z).all().item())}
 
+    def time_sample_api(mdl, n_):
+        """The public call gms/main.py:120 makes — model.sample(n, y): classifier-free guidance, two net evaluations
+        per step as ONE 2n-row forward — with the D2H read of the result inside the timed region."""
+        if T <= 0 or n_ <= 0:
+            return None
+        _, labels = warm_sampler(mdl, n_, True)
+        barrier()
+        t0 = time.perf_counter()
+        e0.record()
+        out = mdl.sample(n_, labels).cpu()
+        e1.record()
+        barrier()
+        wall = time.perf_counter() - t0
+        ms_s = max_over_ranks(e0.elapsed_time(e1))
+        return {"img_s": n_ * world / (ms_s / 1e3), "seconds": ms_s / 1e3, "wall_seconds": wall, "n": n_ * world, "T": T,
+                "guided": True, "net_evals_per_step": 2, "ms_per_step": ms_s / T, "d2h_bytes": out.numel() * 4,
+                "tensor_tflops": 2 * n_ * T * FWD_FLOP_PER_IMG / (ms_s / 1e3) / 1e12,
+                "finite": bool(torch.isfinite(out).all().item())}
+
     samp = time_sampling(model)
+    samp_api = time_sample_api(model, n) if args.sample_api else None
+
+    # small-n sampling (launch-bound): the calls gms.main makes by default — sample(16, y) of configs[0], evaluate()'s 25
+    small = None
+    if rank == 0 and args.small_n and T > 0:
+        small = {}
+        sbound = model._plan(16, "sample_g")
+        l0 = lib.launch_count()
+        warm_sampler(model, 16, True)
+        small["launches_per_guided_step"] = (lib.launch_count() - l0) // 3
+        r = time_sample_api(model, 16) if world == 1 else None
+        if r:
+            small["sample16_guided"] = {"ms_per_step": r["ms_per_step"], "seconds": r["seconds"], "wall_seconds": r["wall_seconds"]}
+        if world == 1:
+            warm_sampler(model, 25, False)
+            model.evaluate(_NullWriter(), None, None, 0)  # capture the u8-history graph
+            torch.cuda.synchronize()
+            t0 = time.perf_counter()
+            model.evaluate(_NullWriter(), None, None, 0)
+            torch.cuda.synchronize()
+            dt = time.perf_counter() - t0
+            small["evaluate25"] = {"ms_per_step": dt / T * 1e3, "wall_seconds": dt, "history": "3 x uint8 [T,25,1,28,28] written by the step kernel"}
+        del sbound
 
     # ---- BASELINE.json configs[2]: the same step with bf16 tensor-core operands in the ResBlock convolutions
     # (reported beside the headline, which stays the fp32/TF32 parity configuration)
@@ -381,7 +481,7 @@ def run_ours(args, rank, world, local_rank):
         ms_b = max_over_ranks(e0.elapsed_time(e1))
         bound2 = m2._plan(B, "train")
         prof2 = profile_ops(m2, bound2, "train") if rank == 0 else None
-        prof2 = profile_ops(m2, bound2, "train") if rank == 0 else None
+        prof2 = profile_ops(m2, bound2, "train") if rank == 0 else None  # second pass: warm
         sb = time_sampling(m2)
         bf16 = {"config": "configs[2]: ResBlock 3x3 convs with bf16 operands / fp32 accumulate, everything else fp32/TF32; "
                           f"batch {B}/GPU",
@@ -432,8 +532,8 @@ def run_ours(args, rank, world, local_rank):
     tf32_live = measure_tf32_peak()
     achieved = conv_fl / (conv_ms / 1e3) / 1e12
     roofline = {
-        "kernel": strip_name + " (all its fprop + dgrad launches of one train step; the top kernel of "
-                  "profiles/r01f_launches_summary_bench_tf32.md, the ncu launch list of this command: 45.7 % of a step there)", "bound": "tensor",
+        "kernel": strip_name + " (all its fprop + dgrad launches of one train step; the top kernel of the ncu launch "
+                  "list of this command under profiles/)", "bound": "tensor",
         "achieved": achieved, "peak": tf32_live, "unit": "TFLOP/s", "frac": achieved / tf32_live,
         # dram__bytes_read.sum + dram__bytes_write.sum of one captured launch (28x28 128->128 3x3 fprop, batch 512):
         # profiles/r01e_ncu_full_summary.md (206.5 MB read + 156.5 MB written; the write-back of the tail sits in L2 when
@@ -447,34 +547,51 @@ def run_ours(args, rank, world, local_rank):
     breakdown = {k: {"ms": round(d["ms"], 4), "launches": d["launches"], "share": round(d["ms"] / total_ms, 4),
                      **({"tflops": round(d["flops"] / (d["ms"] / 1e3) / 1e12, 1)} if d["flops"] else {})}
                  for k, d in sorted(prof.items(), key=lambda kv: -kv[1]["ms"])}
+    act_bytes = bound.plan.activation_bytes()
+    del model, bound
+    torch.cuda.empty_cache()
 
-    threads = os.cpu_count() or 1
-    cpu_rate, cpu_s = cpu_reference_rate(args.cpu_batch, 2, 1, threads)
+    # ---- comparison arms measured beside it: the unmodified reference on the host cores (bounded sample) and, on this
+    # same GPU, in torch eager (cuDNN / cuBLAS)
+    cpu = run_cpu_reference(args.cpu_steps, 1, args.cpu_batch, 16, min(args.cpu_sample_steps, 6), T) if world == 1 else None
+    if cpu and "error" not in cpu:
+        cpu_baseline = {"value": cpu["train"]["img_s"], "unit": UNIT, "cores": cpu["threads"], "kind": "reference",
+                        "sample": cpu_sample_string(cpu, args.cpu_batch),
+                        "sampling_img_s_unguided": ((cpu.get("sampling") or {}).get("unguided") or {}).get("img_s_1000_steps"),
+                        "sampling_img_s_guided": ((cpu.get("sampling") or {}).get("guided") or {}).get("img_s_1000_steps")}
+    else:
+        cpu_baseline = {"value": None, "unit": UNIT, "cores": os.cpu_count(), "kind": "reference",
+                        "sample": "not run" if world > 1 else "failed: " + (cpu or {}).get("error", "")[-200:]}
+    gpu_base = run_gpu_torch_baseline(B) if (world == 1 and args.gpu_baseline) else None
+
     line = {
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": K, "warmup": W, "settle_steps": settle_steps,
         "ms_per_step": ms / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": args.precision,
         "data": "synthetic",
-        "config": {"workload": f"DDPM UNet C=128 1x28x28, train step, batch {B}/GPU "
-                               + ("fp32/TF32 (configs[1])" if args.precision == "tf32" else "bf16 ResBlock convs (configs[2])") + " + "
-                               f"{T}-step ancestral sampling of {n} img/GPU",
+        "config": {"workload": workload_string(args),
                    "global_batch": B * world, "mean_type": "eps", "sampler": "noisy", "timesteps": T,
                    "parallelism": f"dp{world}", "cuda_graph": True,
                    "l2": "per-step working set (~22 MB/img of activations) >> 126 MB L2; no flush needed",
                    "settle": "1.5 s of untimed steps after the W warm-up steps, before each timed region"},
         "clocks": clocks.summary(t_wall0, t_wall2),
         "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": B * (784 * 4 + 8), "d2h_bytes_per_step": 4,
-                "ms_per_step": ms_e2e / K, "last_loss": last},
+                "ms_per_step": ms_e2e / K, "last_loss": last,
+                # the other half of BASELINE.json's metric, through the public model.sample(n, y) with the result read back
+                "sampling": samp_api,
+                "sampling_unguided_img_s": samp["value"] if samp else None},
         "gpu_launches": launches_per_step * K,
         "gpu_launches_per_step": launches_per_step,
+        "ms_per_step_min_over_ranks": ms_min / K,
+        "allreduce_ms": allreduce_ms,
         "tensor_tflops": value * TRAIN_FLOP_PER_IMG / 1e12 / world,
         "roofline": roofline,
-        "cpu_baseline": {"value": cpu_rate, "unit": UNIT, "cores": threads, "kind": "port",
-                         "sample": f"2 train steps (fwd+bwd+Adam) of {args.cpu_batch} images with oracle/ddpm_oracle.py "
-                                   "on torch CPU fp32"},
+        "cpu_baseline": cpu_baseline,
+        "gpu_torch_baseline": gpu_base,
         "sampling": samp,
+        "sampling_small_n": small,
         "bf16": bf16,
         "breakdown": breakdown,
-        "activation_bytes": bound.plan.activation_bytes(),
+        "activation_bytes": act_bytes,
     }
     print(json.dumps(line), file=RESULT_OUT, flush=True)
     if world > 1:
@@ -505,7 +622,12 @@ def main():
     ap.add_argument("--batch", type=int, default=512, help="images per GPU per train step")
     ap.add_argument("--sample-n", type=int, default=512, help="images per GPU in the sampling leg")
     ap.add_argument("--sample-steps", type=int, default=1000)
-    ap.add_argument("--cpu-batch", type=int, default=16, help="bounded CPU sample: images per CPU train step")
+    ap.add_argument("--cpu-batch", type=int, default=64, help="CPU reference arm: images per train step (configs[0]: 64)")
+    ap.add_argument("--cpu-steps", type=int, default=6, help="cpu_baseline leg of the GPU arm: timed reference train steps")
+    ap.add_argument("--cpu-sample-steps", type=int, default=50, help="CPU reference arm: ancestral steps timed (extrapolated to --sample-steps)")
+    ap.add_argument("--sample-api", type=int, default=1, help="time model.sample(n, y) (guided, D2H of the result) for e2e.sampling")
+    ap.add_argument("--small-n", type=int, default=1, help="time sample(16, y) and evaluate() (n=25) at full T")
+    ap.add_argument("--gpu-baseline", type=int, default=1, help="also time the unmodified reference in torch eager on this GPU")
     ap.add_argument("--precision", default="tf32", choices=["tf32", "bf16"],
                     help="tensor-core operand type of the ResBlock convs (tf32 = configs[1], the headline)")
     ap.add_argument("--bf16-leg", type=int, default=1, help="also time the bf16 configuration (configs[2]) beside the headline")

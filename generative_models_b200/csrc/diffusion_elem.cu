@@ -150,11 +150,28 @@ struct SampK {
   const float* sched;   // [T][2] = (logsnr_t, logsnr_s) per loop index i
   const int* step_dev;  // device loop index (graph replay) or NULL
   float* z_next;
-  float* x_hist;  // optional [n*D]
+  float* z_dup;   // optional second copy of z_next (the unconditional half of a 2n-row guided batch)
+  float* x_hist;  // optional [n*D], or [hist_T][n*D] when hist_T > 0 (row hist_T-1-step)
   float* e_hist;
+  float* z_hist;
+  uint8_t* z_u8;  // optional uint8 histories [hist_T][n*D] of ((v + 1) * 127.5).clamp(0, 255) (evaluate()'s proc)
+  uint8_t* x_u8;
+  uint8_t* e_u8;
+  int hist_T;
   int n, D, step, mean_type, sampler;
 };
 
+// diffusion_model.py:91-92 proc(): ((v + 1) * 127.5).clamp(0, 255).to(torch.uint8) (float -> uint8 truncates)
+__device__ __forceinline__ uint32_t proc_u8(float v) {
+  const float t = fminf(fmaxf(mulr(addr(v, 1.0f), 127.5f), 0.0f), 255.0f);
+  return static_cast<uint32_t>(static_cast<int>(t)) & 0xffu;
+}
+__device__ __forceinline__ uint32_t proc_u8x4(const float* v) {
+  return proc_u8(v[0]) | (proc_u8(v[1]) << 8) | (proc_u8(v[2]) << 16) | (proc_u8(v[3]) << 24);
+}
+
+// 16 B per thread and tensor: z, out_c (, out_u), noise in; z_next (, z_dup, x_hist, e_hist) out.  16 B/px algorithmic
+// for the plain ancestral step (z, out, noise in; z out).
 __global__ void __launch_bounds__(256) sampler_step_kernel(SampK a) {
   const int step = a.step_dev ? *a.step_dev : a.step;
   const float lt = a.sched[2 * step], ls = a.sched[2 * step + 1];
@@ -169,30 +186,55 @@ __global__ void __launch_bounds__(256) sampler_step_kernel(SampK a) {
   const float k_x = mulr(omr, alpha_s);
   const float stdv = sqrtf(mulr(omr, sigmoid_t(-lt)));
   const bool last = (step == 0);
-  const size_t total = static_cast<size_t>(a.n) * a.D;
+  const int D4 = a.D >> 2;
+  const size_t total = static_cast<size_t>(a.n) * D4;
   for (size_t i = blockIdx.x * static_cast<size_t>(blockDim.x) + threadIdx.x; i < total;
        i += static_cast<size_t>(gridDim.x) * blockDim.x) {
-    const float zv = a.z[i];
-    float xc = clip1(xhat_from_out(c, a.mean_type, zv, a.out_c[i]));
-    float ec = eps_from_x(c, zv, xc);
-    if (a.out_u) {  // _cf_guidance, gaussian_diffusion.py:174-187
-      const float xu = clip1(xhat_from_out(c, a.mean_type, zv, a.out_u[i]));
-      const float eu = eps_from_x(c, zv, xu);
-      const float w = a.cond_w[i / a.D];
-      const float e = addr(mulr(addr(1.0f, w), ec), mulr(-w, eu));
-      xc = clip1(mulr(c.A, subr(zv, mulr(e, c.Bc))));
-      ec = eps_from_x(c, zv, xc);
+    const float4 z4 = reinterpret_cast<const float4*>(a.z)[i];
+    const float4 o4 = reinterpret_cast<const float4*>(a.out_c)[i];
+    float4 u4 = make_float4(0.f, 0.f, 0.f, 0.f), n4 = u4;
+    float w = 0.f;
+    if (a.out_u) {
+      u4 = reinterpret_cast<const float4*>(a.out_u)[i];
+      w = a.cond_w[i / D4];
     }
-    float zs;
-    if (a.sampler == 1) {
-      const float mean = addr(mulr(k_z, zv), mulr(k_x, xc));
-      zs = addr(mean, mulr(stdv, a.noise[i]));
-    } else {
-      zs = addr(mulr(alpha_s, xc), mulr(sigma_s, ec));
+    if (a.sampler == 1) n4 = reinterpret_cast<const float4*>(a.noise)[i];
+    const float zv[4] = {z4.x, z4.y, z4.z, z4.w}, ov[4] = {o4.x, o4.y, o4.z, o4.w};
+    const float uv[4] = {u4.x, u4.y, u4.z, u4.w}, nv[4] = {n4.x, n4.y, n4.z, n4.w};
+    float zo[4], xo[4], eo[4];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      float xc = clip1(xhat_from_out(c, a.mean_type, zv[j], ov[j]));
+      float ec = eps_from_x(c, zv[j], xc);
+      if (a.out_u) {  // _cf_guidance, gaussian_diffusion.py:174-187
+        const float xu = clip1(xhat_from_out(c, a.mean_type, zv[j], uv[j]));
+        const float eu = eps_from_x(c, zv[j], xu);
+        const float e = addr(mulr(addr(1.0f, w), ec), mulr(-w, eu));
+        xc = clip1(mulr(c.A, subr(zv[j], mulr(e, c.Bc))));
+        ec = eps_from_x(c, zv[j], xc);
+      }
+      float zs;
+      if (a.sampler == 1) {
+        const float mean = addr(mulr(k_z, zv[j]), mulr(k_x, xc));
+        zs = addr(mean, mulr(stdv, nv[j]));
+      } else {
+        zs = addr(mulr(alpha_s, xc), mulr(sigma_s, ec));
+      }
+      zo[j] = last ? xc : zs;
+      xo[j] = xc;
+      eo[j] = ec;
     }
-    a.z_next[i] = last ? xc : zs;
-    if (a.x_hist) a.x_hist[i] = xc;
-    if (a.e_hist) a.e_hist[i] = ec;
+    const float4 zq = make_float4(zo[0], zo[1], zo[2], zo[3]);
+    reinterpret_cast<float4*>(a.z_next)[i] = zq;
+    if (a.z_dup) reinterpret_cast<float4*>(a.z_dup)[i] = zq;
+    // histories: row k = T-1-step of a [T][n*D] tensor (gaussian_diffusion.py:293-296 stacks in loop order)
+    const size_t h = a.hist_T > 0 ? static_cast<size_t>(a.hist_T - 1 - step) * total + i : i;
+    if (a.z_hist) reinterpret_cast<float4*>(a.z_hist)[h] = zq;
+    if (a.x_hist) reinterpret_cast<float4*>(a.x_hist)[h] = make_float4(xo[0], xo[1], xo[2], xo[3]);
+    if (a.e_hist) reinterpret_cast<float4*>(a.e_hist)[h] = make_float4(eo[0], eo[1], eo[2], eo[3]);
+    if (a.z_u8) reinterpret_cast<uint32_t*>(a.z_u8)[h] = proc_u8x4(zo);
+    if (a.x_u8) reinterpret_cast<uint32_t*>(a.x_u8)[h] = proc_u8x4(xo);
+    if (a.e_u8) reinterpret_cast<uint32_t*>(a.e_u8)[h] = proc_u8x4(eo);
   }
 }
 
@@ -244,11 +286,16 @@ extern "C" int b200_sampler_step(const b200_sampler_step_args* a, void* ws, size
   if (a->sampler == 1 && !a->noise) return fail_arg("sampler_step: the noisy sampler needs noise");
   if (a->sampler != 0 && a->sampler != 1) return fail_arg("sampler_step: sampler must be 0 (ddim) or 1 (noisy)");
   if (a->mean_type < 0 || a->mean_type > 2) return fail_arg("sampler_step: bad mean_type");
+  if (a->D % 4) return fail_arg("sampler_step: D must be a multiple of 4");
+  if ((a->z_u8 || a->x_u8 || a->e_u8) && a->hist_T <= 0) return fail_arg("sampler_step: uint8 histories need hist_T");
+  if (a->hist_T > 0 && !a->step_dev && (a->step < 0 || a->step >= a->hist_T)) return fail_arg("sampler_step: step outside the history");
   SampK k;
   k.z = a->z; k.out_c = a->out_c; k.out_u = a->out_u; k.cond_w = a->cond_w; k.noise = a->noise; k.sched = a->sched;
-  k.step_dev = a->step_dev; k.z_next = a->z_next; k.x_hist = a->x_hist; k.e_hist = a->e_hist;
+  k.step_dev = a->step_dev; k.z_next = a->z_next; k.z_dup = a->z_dup; k.z_hist = a->z_hist; k.hist_T = a->hist_T;
+  k.z_u8 = static_cast<uint8_t*>(a->z_u8); k.x_u8 = static_cast<uint8_t*>(a->x_u8); k.e_u8 = static_cast<uint8_t*>(a->e_u8);
+  k.x_hist = a->x_hist; k.e_hist = a->e_hist;
   k.n = a->n; k.D = a->D; k.step = a->step; k.mean_type = a->mean_type; k.sampler = a->sampler;
-  const size_t total = static_cast<size_t>(a->n) * a->D;
+  const size_t total = static_cast<size_t>(a->n) * (a->D / 4);
   sampler_step_kernel<<<ew_grid1(total), 256, 0, static_cast<cudaStream_t>(stream)>>>(k);
   return after_launch("sampler_step_kernel");
 }

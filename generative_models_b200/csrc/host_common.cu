@@ -188,13 +188,25 @@ extern "C" {
 
 int b200_abi_version(void) { return B200_ABI_VERSION; }
 
+// Validates the device; does NOT change the caller's current device (the process model is one process per GPU: the
+// per-process caches of function attributes and the SM count assume every launch of this process targets one device,
+// so a second, different device is refused instead of silently mis-launching).
 int b200_init(int device) {
-  cudaError_t e = cudaSetDevice(device);
-  if (e != cudaSuccess) return b200::check_cuda(e, "cudaSetDevice");
+  static int bound_device = -1;
   cudaDeviceProp prop;
-  e = cudaGetDeviceProperties(&prop, device);
+  cudaError_t e = cudaGetDeviceProperties(&prop, device);
   if (e != cudaSuccess) return b200::check_cuda(e, "cudaGetDeviceProperties");
   if (prop.major != 10) return b200::fail_arg("libb200ddpm.so requires a compute-capability 10.x (Blackwell) device");
+  if (bound_device >= 0 && bound_device != device)
+    return b200::fail_arg("libb200ddpm.so is bound to one device per process (one process per GPU); b200_init was "
+                          "called with a second device");
+  int cur = -1;
+  e = cudaGetDevice(&cur);
+  if (e != cudaSuccess) return b200::check_cuda(e, "cudaGetDevice");
+  if (cur != device)
+    return b200::fail_arg("b200_init: the calling thread's current CUDA device differs from the requested one "
+                          "(call torch.cuda.set_device first)");
+  bound_device = device;
   return 0;
 }
 

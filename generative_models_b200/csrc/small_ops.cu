@@ -360,8 +360,13 @@ linear_tile_kernel(const float* __restrict__ A, const float* __restrict__ B, con
 // grad_scale first (1/world_size after the allreduce-sum, and/or 1/loss_scale).
 __global__ void __launch_bounds__(256)
 adam_kernel(float* __restrict__ p, const float* __restrict__ g, float* __restrict__ m, float* __restrict__ v, size_t n,
-            float lr, float beta1, float beta2, float eps, float grad_scale, const int* __restrict__ step_dev, int step) {
+            float lr, float beta1, float beta2, float eps, float grad_scale, const int* __restrict__ step_dev, int step,
+            const float* __restrict__ hparams_dev) {
   const int t = step_dev ? *step_dev : step;
+  if (hparams_dev) {
+    lr = hparams_dev[0];
+    grad_scale = hparams_dev[1];
+  }
   const float bc1 = 1.0f - powf(beta1, static_cast<float>(t));
   const float bc2 = 1.0f - powf(beta2, static_cast<float>(t));
   const float step_size = lr / bc1;
@@ -506,7 +511,7 @@ extern "C" int b200_adam(const b200_adam_args* a, void* ws, size_t ws_bytes, voi
   (void)ws; (void)ws_bytes;
   if (!a || !a->p || !a->g || !a->m || !a->v) return fail_arg("adam: null pointer");
   adam_kernel<<<ew_grid2(a->n), 256, 0, ST(stream)>>>(a->p, a->g, a->m, a->v, a->n, a->lr, a->beta1, a->beta2, a->eps,
-                                                      a->grad_scale, a->step_dev, a->step);
+                                                      a->grad_scale, a->step_dev, a->step, a->hparams_dev);
   if (int r = after_launch("adam_kernel")) return r;
   return 0;
 }

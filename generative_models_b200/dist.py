@@ -35,13 +35,21 @@ def shard_range(n, rank, world):
     return lo, lo + base + (1 if rank < rem else 0)
 
 
-def allreduce_flat_grad(flat_grad):
-    """The training path's only collective: in-place sum of the flat gradient bucket over all ranks.
-    Returns the factor the optimiser must scale the summed gradient by (1/world)."""
+def allreduce_flat_grad(flat_grad, async_op=False):
+    """The training path's only collective: in-place sum of (a bucket of) the flat gradient buffer over all ranks.
+    async_op=True returns the Work handle (NCCL: the collective runs on the process group's own stream, ordered
+    after everything enqueued so far on the current stream; `.wait()` makes the current stream wait for it), so a
+    bucket can be reduced while later kernels of the backward still run.  Returns None at world size 1.
+    The optimiser scales the summed gradient by 1/world (folded into the fused Adam)."""
     if not dist.is_initialized() or dist.get_world_size() == 1:
-        return 1.0
-    dist.all_reduce(flat_grad, op=dist.ReduceOp.SUM)
-    return 1.0 / dist.get_world_size()
+        return None
+    work = dist.all_reduce(flat_grad, op=dist.ReduceOp.SUM, async_op=async_op)
+    return work if async_op else None
+
+
+def nccl_in_graph():
+    """Opt-in (B200_NCCL_GRAPH=1): capture the gradient allreduce inside the step's CUDA graph."""
+    return os.environ.get("B200_NCCL_GRAPH", "0") == "1"
 
 
 def broadcast_params(flat_params, src=0):

@@ -74,6 +74,7 @@ class SamplerStepArgs(C.Structure):
         ("z", _f32p), ("out_c", _f32p), ("out_u", _f32p), ("cond_w", _f32p), ("noise", _f32p), ("sched", _f32p),
         ("step_dev", _f32p), ("z_next", _f32p), ("x_hist", _f32p), ("e_hist", _f32p),
         ("n", C.c_int), ("D", C.c_int), ("step", C.c_int), ("mean_type", C.c_int), ("sampler", C.c_int),
+        ("z_dup", _f32p), ("z_hist", _f32p), ("hist_T", C.c_int), ("z_u8", _f32p), ("x_u8", _f32p), ("e_u8", _f32p),
     ]
 
 
@@ -125,7 +126,7 @@ class AdamArgs(C.Structure):
     _fields_ = [
         ("p", _f32p), ("g", _f32p), ("m", _f32p), ("v", _f32p), ("n", C.c_size_t),
         ("lr", C.c_float), ("beta1", C.c_float), ("beta2", C.c_float), ("eps", C.c_float), ("grad_scale", C.c_float),
-        ("step_dev", _f32p), ("step", C.c_int),
+        ("step_dev", _f32p), ("step", C.c_int), ("hparams_dev", _f32p),
     ]
 
 
@@ -168,7 +169,7 @@ def load():
     lib.b200_last_error.restype = C.c_char_p
     lib.b200_launch_count.restype = C.c_ulonglong
     lib.b200_init.argtypes = [C.c_int]
-    if lib.b200_abi_version() != 4:
+    if lib.b200_abi_version() != 5:
         raise B200Error("libb200ddpm.so ABI version mismatch")
     for name in EXPORTS:
         fn = getattr(lib, name)  # AttributeError if the symbol is missing

@@ -60,6 +60,10 @@ class DiffusionModelB200(nn.Module):
     # 'bf16': the ResBlock 3x3 convolutions (87 % of the FLOPs) take bf16 operands with fp32 accumulation — the
     # counterpart of the reference's torch.autocast step (diffusion_model.py:66) — everything else as in 'tf32'.
     DG.precision = "tf32"
+    # 1: draw the classifier-free label-drop mask on the device inside the captured step (no CPU RNG, no mask H2D;
+    # the caller's y is left untouched).  0 (default) mirrors diffusion_model.py:67 bit for bit: CPU generator draw,
+    # in-place edit of the caller's y.
+    DG.device_label_drop = 0
 
     def __init__(self, G):
         super().__init__()
@@ -81,6 +85,9 @@ class DiffusionModelB200(nn.Module):
             raise NotImplementedError("dropout != 0 is not on the DDPM hot path (reference default is 0.0)")
         if Path(G.teacher_path) != Path("."):
             raise NotImplementedError("progressive distillation (teacher_path) is out of scope (SURVEY.md §8f)")
+        if torch.cuda.current_device() != dev.index:
+            raise lib.B200Error(f"one process per GPU: make {dev} the current device (torch.cuda.set_device) before "
+                                "constructing DiffusionModelB200")
         rc = lib.load().b200_init(dev.index)
         if rc != 0:
             raise lib.B200Error(f"b200_init failed: {lib.load().b200_last_error().decode()}")
@@ -91,10 +98,47 @@ class DiffusionModelB200(nn.Module):
         self.optimizer = None  # the fused flat Adam below replaces torch.optim.Adam (diffusion_model.py:56)
         self.store.ensure_adam_state()
         self.adam_step = torch.zeros(1, dtype=torch.int32, device=dev)
+        # {lr, grad_scale} live in device memory: the captured step graph reads them, so a learning-rate change (or a
+        # scheduler) never forces a re-capture
+        self.hparams = torch.tensor([float(G.lr), 1.0], dtype=torch.float32, device=dev)
+        self._hparams_host = (float(G.lr), 1.0)
+        self._loss_scale = torch.tensor(1.0)
         self._plans = {}
         self._tables = {}
         self._train_graphs = {}
         self.use_graph = bool(G.get("graph", 1))
+        self.device_label_drop = bool(int(G.get("device_label_drop", 0)))
+        # ring of pinned slots for the CPU-drawn label-drop mask (slot reuse waits on the event of its last H2D copy)
+        self._drop_slots, self._drop_i = [], 0
+        # data-parallel replicas start from rank 0's weights whatever each rank's RNG state was
+        dist.broadcast_params(self.store.flat)
+
+    def load_state_dict(self, state_dict, strict=True, assign=False):
+        out = super().load_state_dict(state_dict, strict=strict)
+        dist.broadcast_params(self.store.flat)
+        return out
+
+    def set_hparams(self, lr, grad_scale):
+        """lr / gradient scale of the fused Adam; written to the device only when they change."""
+        if (lr, grad_scale) != self._hparams_host:
+            self._hparams_host = (lr, grad_scale)
+            self.hparams.copy_(torch.tensor([lr, grad_scale], dtype=torch.float32), non_blocking=False)
+
+    def _drop_mask_to_device(self, drop, device):
+        """Asynchronous H2D of the CPU-drawn label-drop mask through a small ring of pinned slots."""
+        n = drop.shape[0]
+        if not self._drop_slots or self._drop_slots[0][0].shape[0] != n:
+            self._drop_slots = [(torch.empty(n, dtype=torch.bool).pin_memory(), torch.cuda.Event()) for _ in range(4)]
+            self._drop_used = [False] * 4
+        i = self._drop_i = (self._drop_i + 1) % 4
+        buf, ev = self._drop_slots[i]
+        if self._drop_used[i]:
+            ev.synchronize()
+        buf.copy_(drop)
+        d = buf.to(device, non_blocking=True)
+        ev.record(torch.cuda.current_stream(self.device))
+        self._drop_used[i] = True
+        return d
 
     # ------------------------------------------------------------------ plumbing
     def _stream(self):
@@ -117,7 +161,8 @@ class DiffusionModelB200(nn.Module):
         return self._tables[T]
 
     def _plan(self, B, kind):
-        """kind: 'train' | 'loss' | 'sample'.  At most two plans per kind are kept (activations are large)."""
+        """kind: 'train' | 'loss' | 'sample' | 'sample_g' (guided: 2B rows).  At most two plans per kind are kept
+        (activations are large)."""
         key = (kind, B, self.size, int(self.G.timesteps))
         p = self._plans.get(key)
         if p is not None:
@@ -148,33 +193,50 @@ class DiffusionModelB200(nn.Module):
 
     def train_step(self, x, y, eps=None, u=None):
         """diffusion_model.py:63-74: class-label drop, loss, backward, Adam.  fp32 storage with TF32 tensor-core
-        convolutions needs no loss scaling, so `loss_scale` is reported as 1."""
-        if y is not None:
+        convolutions needs no loss scaling, so `loss_scale` is reported as 1.
+        Everything after the copy of (x, y) into the plan's static buffers — the eps / u draws (torch's own Philox
+        stream, captured), the log-SNR schedule, q_sample, UNet forward, loss, backward, Adam — is ONE CUDA graph at
+        world size 1; with a process group the flat-gradient allreduce sits between two graphs, its Up-path half
+        overlapped with the Down-path backward (`_Bound.enqueue_fwd_bwd`)."""
+        b = self._plan(x.shape[0], "train")
+        dev_drop = self.device_label_drop and y is not None
+        if y is not None and not dev_drop:
             # same CPU-generator draw and in-place edit of the caller's y as diffusion_model.py:67
             drop = torch.rand(y.shape[0]) < self.G.cf_drop_prob
             if y.is_cuda:
                 # y[drop] = -1 on a device tensor goes through nonzero(), a stream synchronisation every step; the
                 # masked fill of a (pinned, asynchronously copied) mask writes the same elements without one
-                y.masked_fill_(drop.pin_memory().to(y.device, non_blocking=True), -1)
+                y.masked_fill_(self._drop_mask_to_device(drop, y.device), -1)
             else:
                 y[drop] = -1
-        b = self._plan(x.shape[0], "train")
-        b.stage_inputs(x, y, eps, u)
+        b.copy_batch(x, y)
         world = torch.distributed.get_world_size() if torch.distributed.is_initialized() else 1
-        b.set_adam(float(self.G.lr), 1.0 / world)
-        if self.use_graph:
-            b.run_graphed(b.enqueue_fwd_bwd, "fwd_bwd")
+        self.set_hparams(float(self.G.lr), 1.0 / world)
+        key = (eps is None, u is None, dev_drop)
+        if eps is not None:
+            b.eps.copy_(eps.reshape(b.B, -1))
+        if u is not None:
+            b.u.copy_(u)
+        graphed = (lambda fn, k: b.run_graphed(fn, k)) if self.use_graph else (lambda fn, k: fn())
+        if world == 1:
+            graphed(lambda: (b.enqueue_stage(*key), b.enqueue_fwd_bwd(), b.enqueue_adam()), ("step",) + key)
+        elif dist.nccl_in_graph():
+            # opt-in (B200_NCCL_GRAPH=1): the two allreduce buckets captured inside the one step graph
+            graphed(lambda: (b.enqueue_stage(*key), b.enqueue_fwd_bwd(allreduce="captured"), b.enqueue_adam()),
+                    ("step_dp",) + key)
         else:
-            b.enqueue_fwd_bwd()
-        # the one collective of the path: sum of the flat fp32 gradient over NVLink (SURVEY.md §8e); no-op at world 1
-        dist.allreduce_flat_grad(self.store.grad)
-        # (fwd+bwd and Adam stay two graphs also at world 1: captured as ONE graph the step measured slower, 22.4 vs
-        # 20.0 ms, its launch costing ~4 ms of host time against 0.01 ms for the fwd+bwd graph alone)
-        if self.use_graph:
-            b.run_graphed(b.enqueue_adam, "adam")
-        else:
-            b.enqueue_adam()
-        return {"loss": b.loss_mean[0].clone(), "loss_scale": torch.tensor(1.0)}
+            # the one collective of the path: sum of the flat fp32 gradient over NVLink (SURVEY.md §8e), as two
+            # buckets.  The Up-path half (complete once the backward has walked the out head and the Up blocks) is
+            # reduced on NCCL's stream while the Down-path backward still runs; the rest follows the backward.
+            st = self.store
+            graphed(lambda: (b.enqueue_stage(*key), b.enqueue_fwd_bwd(part="up")), ("fwd_bwd_up",) + key)
+            w1 = dist.allreduce_flat_grad(st.grad[st.bucket_split:], async_op=True)
+            graphed(lambda: b.enqueue_fwd_bwd(part="down"), "bwd_down")
+            dist.allreduce_flat_grad(st.grad[:st.bucket_split])
+            if w1 is not None:
+                w1.wait()
+            graphed(b.enqueue_adam, "adam")
+        return {"loss": b.loss_mean[0].clone(), "loss_scale": self._loss_scale}
 
     def loss_and_grads(self, x, y, eps=None, u=None):
         """loss + backward without the optimiser step (parity tests: compare store.grad views with autograd)."""
@@ -184,31 +246,27 @@ class DiffusionModelB200(nn.Module):
         return b.loss_mean[0].clone(), b
 
     # ------------------------------------------------------------------ sampling
-    def _sample_loop(self, init_z, y, cond_w, keep_history=False, noises=None):
+    def _sample_loop(self, init_z, y, cond_w, history=None, noises=None):
         """gaussian_diffusion.py:245-296 as T replays of one fused step:
-        UNet(z, logsnr_t | y) [+ UNet(z, logsnr_t | uncond)] → randn → b200_sampler_step (x/eps reconstruction,
-        guidance, posterior update, `where(i == 0, x, z_s)`) → device loop index -= 1."""
+        UNet(z, logsnr_t | y ‖ uncond) → randn → b200_sampler_step (x/eps reconstruction, guidance, posterior update,
+        `where(i == 0, x, z_s)`, optional trajectory rows) → device loop index -= 1.
+        With guidance the conditional and the unconditional evaluation (:174-178) are ONE 2n-row forward: rows [0, n)
+        carry the labels, rows [n, 2n) the same z with guide = -1.
+        history: None | "f32" | "u8" — the three [T, n, 1, S, S] stacks (:293-296), written by the step kernel itself."""
         n = init_z.shape[0]
         T = int(self.G.timesteps)
-        b = self._plan(n, "sample")
-        b.begin_sampling(init_z, y, cond_w)
-        hist = None
-        if keep_history:
-            hist = [torch.empty(T, n, 1, self.size, self.size, device=self.device) for _ in range(3)]
+        b = self._plan(n, "sample_g" if cond_w is not None else "sample")
+        hist = b.begin_sampling(init_z, y, cond_w, history)
         noisy = SAMPLERS[self.G.sampler] == 1
         for k in range(T):
             if noises is not None and noisy:
                 b.noise.copy_(noises[k].reshape(n, -1))
                 b.enqueue_sampler_step(draw_noise=False)
             elif self.use_graph:
-                b.run_graphed(b.enqueue_sampler_step, "sampler_step")
+                b.run_graphed(b.enqueue_sampler_step, ("sampler_step", history))
             else:
                 b.enqueue_sampler_step()
-            if hist is not None:
-                hist[0][k].view(n, -1).copy_(b.plan.z_in)
-                hist[1][k].view(n, -1).copy_(b.x_hist)
-                hist[2][k].view(n, -1).copy_(b.e_hist)
-        z = b.plan.z_in.view(n, 1, self.size, self.size).clone()
+        z = b.plan.z_in[:n].view(n, 1, self.size, self.size).clone()
         return z, hist
 
     def sample(self, n, y=None):
@@ -225,25 +283,27 @@ class DiffusionModelB200(nn.Module):
             z, _ = self._sample_loop(noise, y, cond_w)
             return z
 
-    def sample_trajectory(self, init_z, y=None, cond_w=None, noises=None):
-        """The three [T, n, 1, S, S] histories (z, x, eps) GaussianDiffusion.sample returns (gaussian_diffusion.py:293-296)."""
+    def sample_trajectory(self, init_z, y=None, cond_w=None, noises=None, history="f32"):
+        """The three [T, n, 1, S, S] histories (z, x, eps) GaussianDiffusion.sample returns (gaussian_diffusion.py:293-296);
+        history="u8": already passed through evaluate()'s proc() (uint8)."""
         with torch.no_grad():
-            _, hist = self._sample_loop(init_z, y, cond_w, keep_history=True, noises=noises)
-            return hist
+            _, hist = self._sample_loop(init_z, y, cond_w, history=history, noises=noises)
+            return [h.clone() for h in hist]
 
     def evaluate(self, writer, x, y, epoch):
-        """diffusion_model.py:89-111: 25 class-conditional, unguided samples from seed 0; grid + three grid-videos."""
-        def proc(t):
-            t = ((t + 1) * 127.5).clamp(0, 255).to(torch.uint8).cpu()
-            if self.G.pad32:
-                t = t[..., 2:-2, 2:-2]
-            return t
-
+        """diffusion_model.py:89-111: 25 class-conditional samples from seed 0 (guided only when G.sample_cond_w is
+        set, gaussian_diffusion.py:257); grid + three grid-videos.  proc() — ((t+1)*127.5).clamp(0,255).uint8 — is
+        fused into the sampler step: the trajectories leave the device as uint8, 1 B/px."""
         torch.manual_seed(0)
         noise = torch.randn((25, 1, self.size, self.size), device=self.device)
         labels = torch.arange(25, dtype=torch.long, device=self.device) % 10
-        zs, xs, eps = self.sample_trajectory(noise, y=labels, cond_w=None)
-        zs, xs, eps = proc(zs), proc(xs), proc(eps)
+        scw = float(self.G.sample_cond_w)
+        cond_w = None if scw == -1.0 else torch.full((25,), scw, device=self.device)
+        with torch.no_grad():
+            _, hist = self._sample_loop(noise, labels, cond_w, history="u8")
+        zs, xs, eps = (h.cpu() for h in hist)
+        if self.G.pad32:
+            zs, xs, eps = (t[..., 2:-2, 2:-2] for t in (zs, xs, eps))
         _write_grid(writer, "samples", zs[-1], epoch)
         _write_gridvid(writer, "sampling_process", zs, epoch)
         _write_gridvid(writer, "diffusion_model/eps", eps, epoch)
@@ -285,29 +345,20 @@ class _Bound:
         f32 = dict(dtype=torch.float32, device=dev)
         self.graphs = {}
         mt = MEAN_TYPES[G.mean_type]
-        if kind == "sample":
+        if kind in ("sample", "sample_g"):
             T = int(G.timesteps)
+            self.guided = kind == "sample_g"
+            rows = 2 * B if self.guided else B  # guided: conditional rows, then the same z with guide = -1
             self.sched = model._table(T)
             self.step_dev = torch.zeros(1, dtype=torch.int32, device=dev)
-            self.plan = UNetPlan(model.store, B, S, train=False, sched=self.sched, step_dev=self.step_dev,
+            self.plan = UNetPlan(model.store, rows, S, train=False, sched=self.sched, step_dev=self.step_dev,
                                  bf16=model.bf16)
             self.noise = torch.zeros(B, D, **f32)
             self.cond_w = torch.zeros(B, **f32)
-            self.x_hist = torch.zeros(B, D, **f32)
-            self.e_hist = torch.zeros(B, D, **f32)
-            self.guided = False
             self.T = T
-            p = self.plan
-
-            def step_args(guided):
-                return lib.SamplerStepArgs(z=_p(p.z_in), out_c=_p(p.out), out_u=_p(p.out2) if guided else None,
-                                           cond_w=_p(self.cond_w) if guided else None, noise=_p(self.noise),
-                                           sched=_p(self.sched), step_dev=_p(self.step_dev), z_next=_p(p.z_in),
-                                           x_hist=_p(self.x_hist), e_hist=_p(self.e_hist), n=B, D=D, step=0,
-                                           mean_type=mt, sampler=SAMPLERS[G.sampler])
-            self.step_ops = {g: [Op("b200_sampler_step", step_args(g)),
-                                 Op("b200_step_advance", lib.StepAdvanceArgs(step_dev=_p(self.step_dev)))]
-                             for g in (False, True)}
+            self.hist = {}
+            self.history = None
+            self.mt = mt
             return
         self.plan = UNetPlan(model.store, B, S, train=(kind == "train"), bf16=model.bf16)
         p = self.plan
@@ -328,75 +379,137 @@ class _Bound:
             self.zero_ops = [Op("b200_zero", lib.ZeroArgs(ptr=_p(st.grad), bytes=st.numel * 4))]
             self.adam_args = lib.AdamArgs(p=_p(st.flat), g=_p(st.grad), m=_p(st.exp_avg), v=_p(st.exp_avg_sq),
                                           n=st.numel, lr=3e-4, beta1=0.9, beta2=0.999, eps=1e-8, grad_scale=1.0,
-                                          step_dev=_p(model.adam_step), step=0)
+                                          step_dev=_p(model.adam_step), step=0, hparams_dev=_p(model.hparams))
             self.adam_ops = [Op("b200_int_increment", lib.StepAdvanceArgs(step_dev=_p(model.adam_step))),
                              Op("b200_adam", self.adam_args)]
 
     # ---- inputs
-    def stage_inputs(self, x, y, eps, u):
-        """Copy the batch into the plan's static buffers and draw eps / u in the reference's order
-        (gaussian_diffusion.py:83 randn(x.shape) first, :94 rand(B) second) from the device's default generator."""
+    def copy_batch(self, x, y):
+        """(x, y) -> the plan's static buffers (the only per-step work outside the captured step besides the replay)."""
         B = self.B
         assert x.shape[0] == B and x.dtype in (torch.float32, torch.float64)
-        self.x.copy_(x.reshape(B, -1))
-        if eps is None:
-            self.eps.normal_()
-        else:
-            self.eps.copy_(eps.reshape(B, -1))
-        if u is None:
-            self.u.uniform_()
-        else:
-            self.u.copy_(u)
-        # logsnr via the reference's torch expression (diffusion_utils.py:198-201): bit-identical per sample
-        self.plan.t.copy_(logsnr_schedule_cosine(self.u))
+        self.x.copy_(x.reshape(B, -1), non_blocking=True)
         if y is None:
             self.plan.guide.fill_(-1)
         else:
-            self.plan.guide.copy_(y)
+            self.plan.guide.copy_(y, non_blocking=True)
 
-    def set_adam(self, lr, grad_scale):
-        if self.adam_args.lr != lr or self.adam_args.grad_scale != grad_scale:
-            self.adam_args.lr = lr
-            self.adam_args.grad_scale = grad_scale
-            self.graphs.pop("adam", None)  # kernel parameters are baked into a captured graph
+    def enqueue_stage(self, draw_eps=True, draw_u=True, dev_drop=False):
+        """The random draws in the reference's order (gaussian_diffusion.py:83 randn(x.shape) first, :94 rand(B)
+        second) from the device's default generator, then the log-SNR per sample.  Capturable: torch registers the
+        Philox offset with the graph, replays continue the generator's stream exactly like eager draws."""
+        if dev_drop:
+            # classifier-free label drop (diffusion_model.py:67) with a device draw; ahead of eps/u so that those keep
+            # their order relative to each other
+            self.plan.guide.masked_fill_(torch.rand(self.B, device=self.x.device) < float(self.m.G.cf_drop_prob), -1)
+        if draw_eps:
+            self.eps.normal_()
+        if draw_u:
+            self.u.uniform_()
+        # logsnr via the reference's torch expression (diffusion_utils.py:198-201): bit-identical per sample
+        self.plan.t.copy_(logsnr_schedule_cosine(self.u))
+
+    def stage_inputs(self, x, y, eps, u):
+        """Eager form: copy the batch, inject or draw eps / u, derive logsnr."""
+        self.copy_batch(x, y)
+        if eps is not None:
+            self.eps.copy_(eps.reshape(self.B, -1))
+        if u is not None:
+            self.u.copy_(u)
+        self.enqueue_stage(eps is None, u is None)
 
     # ---- enqueue
-    def enqueue_fwd_bwd(self):
+    def enqueue_fwd_bwd(self, part=None, allreduce=None):
+        """part: None = whole step; "up" = everything up to the point where the out/Up gradients are final;
+        "down" = the rest of the backward.  allreduce="captured": issue the two bucket allreduces from inside
+        (only when the whole step is being captured with NCCL in the graph)."""
         st = self.m._stream()
-        run_ops(self.zero_ops, st)
-        run_ops(self.pre_ops, st)
-        self.plan.forward(st)
-        run_ops(self.loss_ops, st)
-        self.plan.backward(st)
+        if part in (None, "up"):
+            run_ops(self.zero_ops, st)
+            run_ops(self.pre_ops, st)
+            self.plan.forward(st)
+            run_ops(self.loss_ops, st)
+        if allreduce == "captured":
+            store = self.m.store
+            self.plan.backward(st, "up")
+            w1 = dist.allreduce_flat_grad(store.grad[store.bucket_split:], async_op=True)
+            self.plan.backward(st, "down")
+            dist.allreduce_flat_grad(store.grad[:store.bucket_split])
+            if w1 is not None:
+                w1.wait()
+        else:
+            self.plan.backward(st, part)
 
     def enqueue_adam(self):
         run_ops(self.adam_ops, self.m._stream())
 
-    def begin_sampling(self, init_z, y, cond_w):
+    def _step_ops(self, history):
+        """b200_sampler_step + the loop-index decrement for one history mode (argument structs are built once)."""
+        key = ("ops", history)
+        if key not in self.hist:
+            p, B, D, T = self.plan, self.B, self.plan.S * self.plan.S, self.T
+            dev = self.noise.device
+            h = None
+            if history == "f32":
+                h = [torch.empty(T, B, 1, p.S, p.S, dtype=torch.float32, device=dev) for _ in range(3)]
+            elif history == "u8":
+                h = [torch.empty(T, B, 1, p.S, p.S, dtype=torch.uint8, device=dev) for _ in range(3)]
+            elif history == "last":  # single-row x / eps of the most recent step only (teacher-forced parity tests)
+                h = [None] + [torch.empty(B, 1, p.S, p.S, dtype=torch.float32, device=dev) for _ in range(2)]
+            elif history is not None:
+                raise ValueError(history)
+            f, u = (h if history in ("f32", "last") else [None] * 3), (h if history == "u8" else [None] * 3)
+            a = lib.SamplerStepArgs(z=_p(p.z_in), out_c=_p(p.out), out_u=_p(p.out, B * D) if self.guided else None,
+                                    cond_w=_p(self.cond_w) if self.guided else None, noise=_p(self.noise),
+                                    sched=_p(self.sched), step_dev=_p(self.step_dev), z_next=_p(p.z_in),
+                                    z_dup=_p(p.z_in, B * D) if self.guided else None,
+                                    x_hist=_p(f[1]), e_hist=_p(f[2]), z_hist=_p(f[0]), hist_T=T if history in ("f32", "u8") else 0,
+                                    z_u8=_p(u[0]), x_u8=_p(u[1]), e_u8=_p(u[2]), n=B, D=D, step=0,
+                                    mean_type=self.mt, sampler=SAMPLERS[self.m.G.sampler])
+            self.hist[key] = ([Op("b200_sampler_step", a),
+                               Op("b200_step_advance", lib.StepAdvanceArgs(step_dev=_p(self.step_dev)))], h)
+        return self.hist[key]
+
+    def begin_sampling(self, init_z, y, cond_w, history=None):
+        """Load z_T, the labels and the guidance weights; returns the history tensors of this mode (or None).  They
+        are owned by the plan (the captured step writes into them) and are overwritten by the next trajectory."""
         B = self.B
-        self.plan.z_in.copy_(init_z.reshape(B, -1))
+        assert (cond_w is not None) == self.guided
+        p = self.plan
+        p.z_in[:B].copy_(init_z.reshape(B, -1))
         if y is None:
-            self.plan.guide.fill_(-1)
+            p.guide.fill_(-1)
         else:
-            self.plan.guide.copy_(y)
-        guided = cond_w is not None
-        if guided:
+            p.guide[:B].copy_(y)
+        if self.guided:
+            p.z_in[B:].copy_(p.z_in[:B])
+            p.guide[B:].fill_(-1)  # gaussian_diffusion.py:176: guide = -ones
             self.cond_w.copy_(cond_w)
-        if guided != self.guided:
-            self.guided = guided
-            self.graphs.pop("sampler_step", None)
-            self.graphs.pop(("warm", "sampler_step"), None)
+        self.history = history
+        self.step_ops, hist = self._step_ops(history)
         self.step_dev.fill_(self.T - 1)
-        run_ops(self.plan.refresh_ops, self.m._stream())  # weights are fixed for the whole loop
+        run_ops(p.refresh_ops, self.m._stream())  # weights are fixed for the whole loop
+        return hist
+
+    def teacher_step(self, z_t, y, cond_w, index, noise=None):
+        """One sampler step at loop index `index` from a supplied z_t (and noise): returns (x_pred, eps_pred, z_next)
+        as [n, 1, S, S] tensors.  Parity tests drive every step of a reference trajectory through this."""
+        n, S = self.B, self.plan.S
+        hist = self.begin_sampling(z_t, y, cond_w, history="last")
+        self.step_dev.fill_(index)
+        if noise is not None:
+            self.noise.copy_(noise.reshape(n, -1))
+        else:
+            self.noise.zero_()
+        self.enqueue_sampler_step(draw_noise=False)
+        return hist[1].clone(), hist[2].clone(), self.plan.z_in[:n].view(n, 1, S, S).clone()
 
     def enqueue_sampler_step(self, draw_noise=True):
         st = self.m._stream()
-        self.plan.forward(st, refresh=False)  # conditional eval → plan.out
-        if self.guided:
-            self.plan.forward(st, uncond=True, to_out2=True, refresh=False)  # gaussian_diffusion.py:174-178
+        self.plan.forward(st, refresh=False)  # rows [0, B): conditional, rows [B, 2B) (guided): unconditional
         if draw_noise and SAMPLERS[self.m.G.sampler] == 1:
             self.noise.normal_()  # drawn after the net evals, like gaussian_diffusion.py:241
-        run_ops(self.step_ops[self.guided], st)
+        run_ops(self.step_ops, st)
 
     # ---- CUDA graphs
     def run_graphed(self, fn, key):

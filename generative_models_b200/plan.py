@@ -133,9 +133,6 @@ class UNetPlan:
         self.out = torch.zeros(B, S * S, **f32)
         self.out2 = torch.zeros(B, S * S, **f32)
         self.sched, self.step_dev = sched, step_dev
-        self.freqs = torch.exp(
-            -torch.log(torch.tensor(float(MAX_TIMESTEPS))) * torch.arange(0, 32, dtype=torch.float32) / 32
-        ).to(dev)
         import math
         # the reference evaluates exp(-math.log(max_period) * arange / half) in fp32 on the CPU (simple_unet.py:216-220)
         self.freqs = torch.exp(-math.log(MAX_TIMESTEPS) * torch.arange(0, 32, dtype=torch.float32) / 32).to(dev)
@@ -594,6 +591,9 @@ class UNetPlan:
         gp.release(dup0)
         dc0 = self._rb_bwd(ops, "up.seq.0.0", _Grad(dr0))
         gp.release(dr0)
+        # every gradient of out.* and up.* is final here (ParamStore.bucket_split): data-parallel training starts the
+        # allreduce of that bucket while the ops below (turn, Down, embeddings) still run
+        self.bwd_split = len(ops)
         # ---- turn, then Down reversed; each Down tensor also receives the tail of its concat consumer
         dd6 = self._rb_bwd(ops, "turn", half(dc0), extra=tail(dc0))
         dd5 = self._conv_bwd(ops, "down.seq.6.conv", sv["d5"], _Grad(dd6), H1, H2, 2, residual=tail(dc1))
@@ -633,10 +633,14 @@ class UNetPlan:
                                     dW=self._g(pre + ".0.weight"), db=self._g(pre + ".0.bias")))
         self.bwd_ops = ops
 
-    def backward(self, stream_ptr):
-        """Enqueue the reverse pass: reads self.dout, accumulates into store.grad (caller zeroes it once per step)."""
-        run_ops(self.refreshT_ops, stream_ptr)  # the weights have not changed since the forward's refresh
-        run_ops(self.bwd_ops, stream_ptr)
+    def backward(self, stream_ptr, part=None):
+        """Enqueue the reverse pass: reads self.dout, accumulates into store.grad (caller zeroes it once per step).
+        part: None = all of it; "up" = out head + Up blocks (ops [0, bwd_split)); "down" = the rest."""
+        if part in (None, "up"):
+            run_ops(self.refreshT_ops, stream_ptr)  # the weights have not changed since the forward's refresh
+        lo = self.bwd_split if part == "down" else 0
+        hi = self.bwd_split if part == "up" else len(self.bwd_ops)
+        run_ops(self.bwd_ops[lo:hi], stream_ptr)
 
     def activation_bytes(self):
         n = self.pool.bytes() + self.gpool.bytes()

@@ -101,6 +101,11 @@ class ParamStore:
             self.offsets[name] = off
             off = _align(off + math.prod(shape))
         self.numel = off
+        # data-parallel bucket boundary: [bucket_split, numel) holds every out.* / up.* tensor (registration order puts
+        # them last), whose gradients are complete before the backward reaches the turn block
+        self.bucket_split = min(o for n, o in self.offsets.items() if n.startswith(("up.", "out.")) and ".emb_layers." not in n)
+        assert all(o < self.bucket_split for n, o in self.offsets.items()
+                   if not n.startswith(("up.", "out.")) or ".emb_layers." in n)
         self.flat = torch.zeros(off, dtype=torch.float32, device=self.device)
         self.grad = torch.zeros(off, dtype=torch.float32, device=self.device)
         # TF32-rounded (round-to-nearest) shadow of `flat`: what the tensor-core convolutions read as their B operand

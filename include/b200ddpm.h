@@ -21,9 +21,11 @@
 extern "C" {
 #endif
 
-#define B200_ABI_VERSION 4
+#define B200_ABI_VERSION 5
 
 int b200_abi_version(void);
+/* validates `device` (compute capability 10.x, equal to the caller's current device); never changes the current
+ * device; one device per process (a second, different device is refused) */
 int b200_init(int device);
 const char* b200_last_error(void);
 /* number of kernels this library has launched since load (bench.py's gpu_launches). */
@@ -195,9 +197,19 @@ typedef struct {
   const float* sched;
   const int* step_dev;
   float* z_next;
-  float* x_hist;
-  float* e_hist;
-  int n, D, step, mean_type, sampler;
+  float* x_hist; /* optional: clipped x prediction of this step (evaluate()'s trajectories) */
+  float* e_hist; /* optional: eps prediction of this step */
+  int n, D, step, mean_type, sampler; /* D a multiple of 4 (16 B accesses) */
+  float* z_dup;  /* optional second copy of z_next: the unconditional rows of a 2n-row guided batch */
+  /* whole-trajectory histories (GaussianDiffusion.sample returns three [T, n, ...] stacks, gaussian_diffusion.py:293-296):
+   * with hist_T > 0, x_hist / e_hist / z_hist are [hist_T][n*D] and this step writes row hist_T-1-index.  The uint8
+   * variants hold DiffusionModel.evaluate's proc(): ((v + 1) * 127.5).clamp(0, 255).to(uint8) (diffusion_model.py:91-92),
+   * 1 B/px instead of a 4 B/px fp32 history converted afterwards. */
+  float* z_hist;
+  int hist_T;
+  void* z_u8;
+  void* x_u8;
+  void* e_u8;
 } b200_sampler_step_args;
 int b200_sampler_step(const b200_sampler_step_args* a, void* ws, size_t ws_bytes, void* stream);
 
@@ -360,6 +372,9 @@ typedef struct {
   float lr, beta1, beta2, eps, grad_scale;
   const int* step_dev;
   int step;
+  /* optional device-resident {lr, grad_scale} (2 floats): when given they override the two struct fields, so a
+   * captured CUDA graph follows a learning-rate schedule / a changed world size without being re-captured */
+  const float* hparams_dev;
 } b200_adam_args;
 int b200_adam(const b200_adam_args* a, void* ws, size_t ws_bytes, void* stream);
 

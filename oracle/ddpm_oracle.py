@@ -209,7 +209,7 @@ def sample_loop(net, init_z, num_steps, sampler="noisy", mean_type="eps", cond_w
     zs, xs, es = [], [], []
     n = init_z.shape[0]
     for k, i in enumerate(range(num_steps - 1, -1, -1)):
-        ti = torch.tensor(i)
+        ti = torch.tensor(i, device=init_z.device)  # gaussian_diffusion.py:288
         lt = logsnr_cosine((ti + 1.0) / num_steps)
         ls = logsnr_cosine(ti / num_steps)
         ltv = lt.expand(n)

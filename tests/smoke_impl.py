@@ -57,11 +57,7 @@ def run_smoke():
     e1 = 0.0
     for k in range(T):
         z_t = init if k == 0 else rz[k - 1]
-        b.begin_sampling(z_t.to(dev), ys.to(dev), None)
-        b.step_dev.fill_(T - 1 - k)
-        b.noise.copy_(noises[k].to(dev).reshape(2, -1))
-        b.enqueue_sampler_step(draw_noise=False)
-        z_ours = b.plan.z_in.cpu().view(2, 1, 28, 28)
+        z_ours = b.teacher_step(z_t.to(dev), ys.to(dev), None, T - 1 - k, noises[k].to(dev))[2].cpu()
         if k == 0:
             f0 = ((z_ours - rz[k]).abs() > 5e-3).double().mean().item()
             assert f0 < 0.02, f0

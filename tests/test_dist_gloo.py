@@ -61,8 +61,15 @@ def _worker(rank, world, port, q):
     for k, v in sd.items():
         if v.grad is not None:
             st.grad_view(k).copy_(v.grad)
-    scale = D.allreduce_flat_grad(st.grad)
-    assert scale == 1.0 / world
+    # the product's form (model.train_step): two buckets — [bucket_split, numel) = out.* / up.* first, asynchronously,
+    # then the rest — and the 1/world factor folded into Adam's grad_scale
+    assert 0 < st.bucket_split < st.numel
+    assert all((st.offsets[k] >= st.bucket_split) == (k.startswith(("up.", "out.")) and ".emb_layers." not in k)
+               for k in st.offsets)
+    w1 = D.allreduce_flat_grad(st.grad[st.bucket_split:], async_op=True)
+    assert D.allreduce_flat_grad(st.grad[:st.bucket_split]) is None
+    w1.wait()
+    scale = 1.0 / world
     if rank == 0:
         sdg = {k: v.clone().requires_grad_(True) for k, v in sd0.items()}
         gl, _, _ = O.training_loss(sdg, x, y, eps, u, "eps")

@@ -117,6 +117,55 @@ def test_sampler_step(lib, mean_type, sampler, guided, step):
     assert rel(eh, ec) < 2e-3
 
 
+def test_sampler_step_histories_and_fused_proc(lib):
+    """hist_T > 0: the step writes row T-1-index of the [T][n*D] stacks (gaussian_diffusion.py:293-296); the uint8 stacks
+    hold diffusion_model.py:91-92 proc() of the same values bit for bit; z_dup mirrors z_next (2n-row guided batch)."""
+    from generative_models_b200.schedule import sampler_table
+    g = torch.Generator().manual_seed(3)
+    n, D, T, step = 3, 784, 6, 2
+    z, out = torch.randn(n, D, generator=g).to(DEV), torch.randn(n, D, generator=g).to(DEV)
+    noise = torch.randn(n, D, generator=g).to(DEV)
+    sched = sampler_table(T, DEV)
+    zn, zd = torch.zeros(n, D, device=DEV), torch.zeros(n, D, device=DEV)
+    f32 = [torch.full((T, n, D), 7.0, device=DEV) for _ in range(3)]
+    u8 = [torch.full((T, n, D), 9, dtype=torch.uint8, device=DEV) for _ in range(3)]
+    a = lib.SamplerStepArgs(z=ptr(z), out_c=ptr(out), out_u=None, cond_w=None, noise=ptr(noise), sched=ptr(sched),
+                            step_dev=None, z_next=ptr(zn), z_dup=ptr(zd), z_hist=ptr(f32[0]), x_hist=ptr(f32[1]),
+                            e_hist=ptr(f32[2]), hist_T=T, z_u8=ptr(u8[0]), x_u8=ptr(u8[1]), e_u8=ptr(u8[2]), n=n, D=D,
+                            step=step, mean_type=0, sampler=1)
+    lib.call("b200_sampler_step", a, stream())
+    row = T - 1 - step
+    assert torch.equal(zd, zn) and torch.equal(f32[0][row], zn)
+    for h32, h8 in zip(f32, u8):
+        want = ((h32[row] + 1) * 127.5).clamp(0, 255).to(torch.uint8)
+        assert torch.equal(h8[row], want)
+        for r in range(T):
+            if r != row:
+                assert (h32[r] == 7.0).all() and (h8[r] == 9).all()
+    assert f32[1][row].abs().max() <= 1.0  # the clipped x prediction
+    a.step = T  # outside the history
+    assert lib.load().b200_sampler_step(__import__("ctypes").byref(a), None, 0, stream()) < 0
+
+
+def test_adam_reads_device_hparams(lib):
+    """hparams_dev = {lr, grad_scale} in device memory overrides the struct fields (a captured step graph follows an
+    lr schedule without re-capture)."""
+    g = torch.Generator().manual_seed(0)
+    n = 4096
+    p0, gr = torch.randn(n, generator=g), torch.randn(n, generator=g)
+    outs = []
+    for use_dev in (False, True):
+        p, m, v = p0.clone().to(DEV), torch.zeros(n, device=DEV), torch.zeros(n, device=DEV)
+        hp = torch.tensor([1e-2, 0.5], device=DEV)
+        a = lib.AdamArgs(p=ptr(p), g=ptr(gr.to(DEV)), m=ptr(m), v=ptr(v), n=n, lr=1e-2 if not use_dev else 123.0,
+                         beta1=0.9, beta2=0.999, eps=1e-8, grad_scale=0.5 if not use_dev else 77.0, step_dev=None, step=1,
+                         hparams_dev=ptr(hp) if use_dev else None)
+        lib.call("b200_adam", a, stream())
+        outs.append(p.cpu())
+    assert torch.equal(outs[0], outs[1])
+    assert (outs[0] - p0).abs().max() > 5e-3
+
+
 def test_step_advance_and_increment(lib):
     v = torch.tensor([5], dtype=torch.int32, device=DEV)
     lib.call("b200_step_advance", lib.StepAdvanceArgs(step_dev=ptr(v)), stream())

@@ -178,15 +178,12 @@ def test_sampler_vs_reference_fixture(built_lib, golden, tag, graph):
     # classifier-free guidance extrapolates e = (1+w) e_c - w e_u with w up to 4 (gaussian_diffusion.py:181): the TF32
     # net error is amplified up to (1+2w) = 9x before the x^ reconstruction, so the guided case gets a wider pixel budget
     far = 0.03 if cw is not None else 0.01
-    b = m._plan(n, "sample")
+    b = m._plan(n, "sample_g" if cw is not None else "sample")
     for k in range(T):
         z_t = f["init"] if k == 0 else f["zs"][k - 1]
-        b.begin_sampling(z_t.to(DEV), f["y"].to(DEV), cw)
-        b.step_dev.fill_(T - 1 - k)
-        if noises is not None:
-            b.noise.copy_(noises[k].reshape(n, -1))
-        b.enqueue_sampler_step(draw_noise=False)
-        x_ours, z_ours = b.x_hist.cpu().view(n, 1, 28, 28), b.plan.z_in.cpu().view(n, 1, 28, 28)
+        x_ours, _, z_ours = b.teacher_step(z_t.to(DEV), f["y"].to(DEV), cw, T - 1 - k,
+                                           noises[k] if noises is not None else None)
+        x_ours, z_ours = x_ours.cpu(), z_ours.cpu()
         assert frac_far(x_ours, f["xs"][k], 5e-3) < far, (tag, k)
         assert frac_far(z_ours, f["zs"][k], 5e-3) < far, (tag, k)
         if k > 0:  # away from logsnr = -20 the step is well conditioned: max-norm bar

@@ -44,7 +44,7 @@ def synthetic_mnist(n_train=8192, n_test=1024, seed=0):
     return load_mnist
 
 
-def install(reference_root, synthetic=False):
+def install(reference_root, synthetic=False, n_train=8192, n_test=1024):
     """Patch the registry (and optionally the data loader) of the reference's `gms.common`; returns the module."""
     if ROOT not in sys.path:
         sys.path.insert(0, ROOT)
@@ -77,21 +77,42 @@ def install(reference_root, synthetic=False):
 
     common.discover_models = discover_models
     if synthetic:
-        common.load_mnist = synthetic_mnist()
+        common.load_mnist = synthetic_mnist(n_train, n_test)
     return common
+
+
+def default_reference_root():
+    """baseline/_ref (the unmodified reference installed by tools/vendor_reference.sh; it travels to the GPU box), else
+    $GMS_ROOT, else /root/reference."""
+    vend = os.path.join(ROOT, "baseline", "_ref")
+    if os.path.isfile(os.path.join(vend, "gms", "main.py")):
+        return vend
+    return os.environ.get("GMS_ROOT", "/root/reference")
 
 
 def main():
     ap = argparse.ArgumentParser(description=__doc__, formatter_class=argparse.RawDescriptionHelpFormatter)
-    ap.add_argument("--reference-root", default=os.environ.get("GMS_ROOT", "/root/reference"))
+    ap.add_argument("--reference-root", default=default_reference_root())
     ap.add_argument("--synthetic-mnist", action="store_true")
+    ap.add_argument("--n-train", type=int, default=8192, help="size of the synthetic training set")
+    ap.add_argument("--n-test", type=int, default=1024)
+    ap.add_argument("--git-cwd", action="store_true",
+                    help="run from a fresh temp `git init` directory (gms/common.py:74-76 shells out to git rev-parse)")
     if "--" in sys.argv:
         k = sys.argv.index("--")
         own, rest = sys.argv[1:k], sys.argv[k + 1:]
     else:
         own, rest = sys.argv[1:], []
     a = ap.parse_args(own)
-    install(a.reference_root, a.synthetic_mnist)
+    if a.git_cwd:
+        import subprocess
+        import tempfile
+        tmp = tempfile.mkdtemp(prefix="gms_run_")
+        env = dict(os.environ, GIT_AUTHOR_NAME="x", GIT_AUTHOR_EMAIL="x@x", GIT_COMMITTER_NAME="x", GIT_COMMITTER_EMAIL="x@x")
+        subprocess.check_call(["git", "init", "-q", tmp])
+        subprocess.check_call(["git", "-C", tmp, "commit", "-q", "--allow-empty", "-m", "run"], env=env)
+        os.chdir(tmp)
+    install(a.reference_root, a.synthetic_mnist, a.n_train, a.n_test)
     sys.argv = ["gms.main"] + rest
     import runpy
 
