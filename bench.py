@@ -445,9 +445,10 @@ def run_ours(args, rank, world, local_rank):
     if rank == 0 and args.small_n and T > 0:
         small = {}
         sbound = model._plan(16, "sample_g")
-        l0 = lib.launch_count()
         warm_sampler(model, 16, True)
-        small["launches_per_guided_step"] = (lib.launch_count() - l0) // 3
+        l0 = lib.launch_count()
+        sbound.enqueue_sampler_step()  # one eager step: every kernel of a guided 2n-row step (replays are not counted)
+        small["launches_per_guided_step"] = lib.launch_count() - l0 + 1  # + torch's Philox normal_ for the step noise
         r = time_sample_api(model, 16) if world == 1 else None
         if r:
             small["sample16_guided"] = {"ms_per_step": r["ms_per_step"], "seconds": r["seconds"], "wall_seconds": r["wall_seconds"]}

@@ -48,23 +48,40 @@ __device__ __forceinline__ float eps_from_x(const Coef& c, float z, float x) {
 
 // ------------------------------------------------------------------------------------------------ q_sample
 // z = x * sqrt(sigmoid(l)) + sqrt(sigmoid(-l)) * eps      (12 B/px)
+// Each thread keeps kEwUnroll independent 16 B loads per tensor in flight (a grid-stride loop with one float4 per
+// iteration left the kernel latency-bound at n = 8192: 3.76 TB/s; the per-sample coefficients are recomputed per
+// float4, which costs nothing next to the memory time).
+constexpr int kEwUnroll = 4;
 __global__ void __launch_bounds__(256)
 q_sample_kernel(const float* __restrict__ x, const float* __restrict__ eps, const float* __restrict__ logsnr,
                 float* __restrict__ z, int B, int D4) {
   const size_t total = static_cast<size_t>(B) * D4;
-  for (size_t i = blockIdx.x * static_cast<size_t>(blockDim.x) + threadIdx.x; i < total;
-       i += static_cast<size_t>(gridDim.x) * blockDim.x) {
-    const int b = static_cast<int>(i / D4);
-    const float l = logsnr[b];
-    const float a = sqrtf(sigmoid_t(l)), s = sqrtf(sigmoid_t(-l));
-    const float4 xv = reinterpret_cast<const float4*>(x)[i];
-    const float4 ev = reinterpret_cast<const float4*>(eps)[i];
-    float4 o;
-    o.x = addr(mulr(xv.x, a), mulr(s, ev.x));
-    o.y = addr(mulr(xv.y, a), mulr(s, ev.y));
-    o.z = addr(mulr(xv.z, a), mulr(s, ev.z));
-    o.w = addr(mulr(xv.w, a), mulr(s, ev.w));
-    reinterpret_cast<float4*>(z)[i] = o;
+  const size_t stride = static_cast<size_t>(gridDim.x) * blockDim.x * kEwUnroll;
+  for (size_t base = static_cast<size_t>(blockIdx.x) * blockDim.x * kEwUnroll + threadIdx.x; base < total; base += stride) {
+    float4 xv[kEwUnroll], ev[kEwUnroll];
+    float lv[kEwUnroll];
+#pragma unroll
+    for (int u = 0; u < kEwUnroll; ++u) {
+      const size_t i = base + static_cast<size_t>(u) * blockDim.x;
+      if (i < total) {
+        xv[u] = __ldcs(reinterpret_cast<const float4*>(x) + i);
+        ev[u] = __ldcs(reinterpret_cast<const float4*>(eps) + i);
+        lv[u] = __ldg(logsnr + i / D4);
+      }
+    }
+#pragma unroll
+    for (int u = 0; u < kEwUnroll; ++u) {
+      const size_t i = base + static_cast<size_t>(u) * blockDim.x;
+      if (i < total) {
+        const float a = sqrtf(sigmoid_t(lv[u])), s = sqrtf(sigmoid_t(-lv[u]));
+        float4 o;
+        o.x = addr(mulr(xv[u].x, a), mulr(s, ev[u].x));
+        o.y = addr(mulr(xv[u].y, a), mulr(s, ev[u].y));
+        o.z = addr(mulr(xv[u].z, a), mulr(s, ev[u].z));
+        o.w = addr(mulr(xv[u].w, a), mulr(s, ev[u].w));
+        reinterpret_cast<float4*>(z)[i] = o;
+      }
+    }
   }
 }
 
@@ -87,27 +104,67 @@ __device__ __forceinline__ float block_sum(float v, float* sh) {
 }
 
 // One CTA per sample.  loss_b = max(mean (xc-x)^2, mean (ec-eps)^2); dout = d(grad_scale * loss_b)/d(out).
+// The sample (out, z, x, eps: 16 B accesses) is read ONCE and held in registers across the block reduction when it fits
+// (D <= 4 * 4 * 256 pixels; 28x28 .. 64x64 do): 20 B/px of HBM traffic, the algorithmic minimum.  Larger images re-read.
+constexpr int kLossV = 4;  // float4 chunks per thread and tensor held in registers
 __global__ void __launch_bounds__(256)
 loss_kernel(const float* __restrict__ out, const float* __restrict__ z, const float* __restrict__ x,
             const float* __restrict__ eps, const float* __restrict__ logsnr, float* __restrict__ loss_b,
-            float* __restrict__ mse2, float* __restrict__ dout, int D, int mean_type, float grad_scale) {
+            float* __restrict__ mse2, float* __restrict__ dout, int D, int mean_type, float grad_scale, int loss_type) {
   __shared__ float sh[32];
   const int b = blockIdx.x;
   const Coef c = make_coef(logsnr[b]);
   const size_t base = static_cast<size_t>(b) * D;
+  const int D4 = D >> 2;
+  const bool cached = D4 <= kLossV * 256;
+  const float4* o4 = reinterpret_cast<const float4*>(out + base);
+  const float4* z4 = reinterpret_cast<const float4*>(z + base);
+  const float4* x4 = reinterpret_cast<const float4*>(x + base);
+  const float4* e4 = reinterpret_cast<const float4*>(eps + base);
+  float4 ro[kLossV], rz[kLossV], rx[kLossV], re[kLossV];
   float sx = 0.f, se = 0.f;
-  for (int i = threadIdx.x; i < D; i += blockDim.x) {
-    const float zv = z[base + i];
-    const float xc = clip1(xhat_from_out(c, mean_type, zv, out[base + i]));
-    const float ec = eps_from_x(c, zv, xc);
-    const float dx = xc - x[base + i], de = ec - eps[base + i];
-    sx += dx * dx;
-    se += de * de;
+  if (cached) {
+#pragma unroll
+    for (int v = 0; v < kLossV; ++v) {
+      const int i = threadIdx.x + v * 256;
+      if (i < D4) {
+        ro[v] = __ldcs(o4 + i);
+        rz[v] = __ldcs(z4 + i);
+        rx[v] = __ldcs(x4 + i);
+        re[v] = __ldcs(e4 + i);
+      }
+    }
+#pragma unroll
+    for (int v = 0; v < kLossV; ++v) {
+      const int i = threadIdx.x + v * 256;
+      if (i < D4) {
+        const float ov[4] = {ro[v].x, ro[v].y, ro[v].z, ro[v].w}, zv[4] = {rz[v].x, rz[v].y, rz[v].z, rz[v].w};
+        const float xv[4] = {rx[v].x, rx[v].y, rx[v].z, rx[v].w}, ev[4] = {re[v].x, re[v].y, re[v].z, re[v].w};
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          const float xc = clip1(xhat_from_out(c, mean_type, zv[j], ov[j]));
+          const float ec = eps_from_x(c, zv[j], xc);
+          const float dx = xc - xv[j], de = ec - ev[j];
+          sx += dx * dx;
+          se += de * de;
+        }
+      }
+    }
+  } else {
+    for (int i = threadIdx.x; i < D; i += blockDim.x) {
+      const float zv = z[base + i];
+      const float xc = clip1(xhat_from_out(c, mean_type, zv, out[base + i]));
+      const float ec = eps_from_x(c, zv, xc);
+      const float dx = xc - x[base + i], de = ec - eps[base + i];
+      sx += dx * dx;
+      se += de * de;
+    }
   }
   const float x_mse = block_sum(sx, sh) / static_cast<float>(D);
   const float e_mse = block_sum(se, sh) / static_cast<float>(D);
   if (threadIdx.x == 0) {
-    loss_b[b] = fmaxf(x_mse, e_mse);
+    // 'snr_trunc' (gaussian_diffusion.py:166-168): max(x_mse, eps_mse); 'snr' (:169-170, distillation step1): eps_mse
+    loss_b[b] = loss_type == 1 ? e_mse : fmaxf(x_mse, e_mse);
     if (mse2) {
       mse2[2 * b] = x_mse;
       mse2[2 * b + 1] = e_mse;
@@ -115,19 +172,35 @@ loss_kernel(const float* __restrict__ out, const float* __restrict__ z, const fl
   }
   if (!dout) return;
   // torch.maximum backward: the larger branch gets the gradient, exact ties split it in half.
-  const float gx = (x_mse > e_mse) ? 1.f : ((x_mse == e_mse) ? 0.5f : 0.f);
+  const float gx = loss_type == 1 ? 0.f : ((x_mse > e_mse) ? 1.f : ((x_mse == e_mse) ? 0.5f : 0.f));
   const float ge = 1.f - gx;
   const float k = 2.0f * grad_scale / static_cast<float>(D);
   const float dxc_de = -(c.Ce * c.De);
   const float dxh_dout = (mean_type == 0) ? -(c.A * c.Bc) : ((mean_type == 1) ? 1.f : -c.sigma);
-  for (int i = threadIdx.x; i < D; i += blockDim.x) {
-    const float zv = z[base + i];
-    const float xh = xhat_from_out(c, mean_type, zv, out[base + i]);
+  auto grad1 = [&](float zv, float ov, float xv, float ev) {
+    const float xh = xhat_from_out(c, mean_type, zv, ov);
     const float xc = clip1(xh);
     const float ec = eps_from_x(c, zv, xc);
-    float g = k * (gx * (xc - x[base + i]) + ge * (ec - eps[base + i]) * dxc_de);
+    float g = k * (gx * (xc - xv) + ge * (ec - ev) * dxc_de);
     if (xh < -1.0f || xh > 1.0f) g = 0.f;  // clip backward is inclusive at +-1
-    dout[base + i] = g * dxh_dout;
+    return g * dxh_dout;
+  };
+  if (cached) {
+#pragma unroll
+    for (int v = 0; v < kLossV; ++v) {
+      const int i = threadIdx.x + v * 256;
+      if (i < D4) {
+        float4 g;
+        g.x = grad1(rz[v].x, ro[v].x, rx[v].x, re[v].x);
+        g.y = grad1(rz[v].y, ro[v].y, rx[v].y, re[v].y);
+        g.z = grad1(rz[v].z, ro[v].z, rx[v].z, re[v].z);
+        g.w = grad1(rz[v].w, ro[v].w, rx[v].w, re[v].w);
+        reinterpret_cast<float4*>(dout + base)[i] = g;
+      }
+    }
+  } else {
+    for (int i = threadIdx.x; i < D; i += blockDim.x)
+      dout[base + i] = grad1(z[base + i], out[base + i], x[base + i], eps[base + i]);
   }
 }
 
@@ -188,53 +261,68 @@ __global__ void __launch_bounds__(256) sampler_step_kernel(SampK a) {
   const bool last = (step == 0);
   const int D4 = a.D >> 2;
   const size_t total = static_cast<size_t>(a.n) * D4;
-  for (size_t i = blockIdx.x * static_cast<size_t>(blockDim.x) + threadIdx.x; i < total;
-       i += static_cast<size_t>(gridDim.x) * blockDim.x) {
-    const float4 z4 = reinterpret_cast<const float4*>(a.z)[i];
-    const float4 o4 = reinterpret_cast<const float4*>(a.out_c)[i];
-    float4 u4 = make_float4(0.f, 0.f, 0.f, 0.f), n4 = u4;
-    float w = 0.f;
-    if (a.out_u) {
-      u4 = reinterpret_cast<const float4*>(a.out_u)[i];
-      w = a.cond_w[i / D4];
-    }
-    if (a.sampler == 1) n4 = reinterpret_cast<const float4*>(a.noise)[i];
-    const float zv[4] = {z4.x, z4.y, z4.z, z4.w}, ov[4] = {o4.x, o4.y, o4.z, o4.w};
-    const float uv[4] = {u4.x, u4.y, u4.z, u4.w}, nv[4] = {n4.x, n4.y, n4.z, n4.w};
-    float zo[4], xo[4], eo[4];
+  const size_t stride = static_cast<size_t>(gridDim.x) * blockDim.x * 2;
+  for (size_t base = static_cast<size_t>(blockIdx.x) * blockDim.x * 2 + threadIdx.x; base < total; base += stride) {
+    // two independent float4 per tensor in flight per thread
+    float4 zq[2], oq[2], uq[2], nq[2];
+    float wq[2];
 #pragma unroll
-    for (int j = 0; j < 4; ++j) {
-      float xc = clip1(xhat_from_out(c, a.mean_type, zv[j], ov[j]));
-      float ec = eps_from_x(c, zv[j], xc);
-      if (a.out_u) {  // _cf_guidance, gaussian_diffusion.py:174-187
-        const float xu = clip1(xhat_from_out(c, a.mean_type, zv[j], uv[j]));
-        const float eu = eps_from_x(c, zv[j], xu);
-        const float e = addr(mulr(addr(1.0f, w), ec), mulr(-w, eu));
-        xc = clip1(mulr(c.A, subr(zv[j], mulr(e, c.Bc))));
-        ec = eps_from_x(c, zv[j], xc);
+    for (int u = 0; u < 2; ++u) {
+      const size_t i = base + static_cast<size_t>(u) * blockDim.x;
+      uq[u] = nq[u] = make_float4(0.f, 0.f, 0.f, 0.f);
+      wq[u] = 0.f;
+      if (i < total) {
+        zq[u] = reinterpret_cast<const float4*>(a.z)[i];
+        oq[u] = __ldcs(reinterpret_cast<const float4*>(a.out_c) + i);
+        if (a.out_u) {
+          uq[u] = __ldcs(reinterpret_cast<const float4*>(a.out_u) + i);
+          wq[u] = a.cond_w[i / D4];
+        }
+        if (a.sampler == 1) nq[u] = __ldcs(reinterpret_cast<const float4*>(a.noise) + i);
       }
-      float zs;
-      if (a.sampler == 1) {
-        const float mean = addr(mulr(k_z, zv[j]), mulr(k_x, xc));
-        zs = addr(mean, mulr(stdv, nv[j]));
-      } else {
-        zs = addr(mulr(alpha_s, xc), mulr(sigma_s, ec));
-      }
-      zo[j] = last ? xc : zs;
-      xo[j] = xc;
-      eo[j] = ec;
     }
-    const float4 zq = make_float4(zo[0], zo[1], zo[2], zo[3]);
-    reinterpret_cast<float4*>(a.z_next)[i] = zq;
-    if (a.z_dup) reinterpret_cast<float4*>(a.z_dup)[i] = zq;
-    // histories: row k = T-1-step of a [T][n*D] tensor (gaussian_diffusion.py:293-296 stacks in loop order)
-    const size_t h = a.hist_T > 0 ? static_cast<size_t>(a.hist_T - 1 - step) * total + i : i;
-    if (a.z_hist) reinterpret_cast<float4*>(a.z_hist)[h] = zq;
-    if (a.x_hist) reinterpret_cast<float4*>(a.x_hist)[h] = make_float4(xo[0], xo[1], xo[2], xo[3]);
-    if (a.e_hist) reinterpret_cast<float4*>(a.e_hist)[h] = make_float4(eo[0], eo[1], eo[2], eo[3]);
-    if (a.z_u8) reinterpret_cast<uint32_t*>(a.z_u8)[h] = proc_u8x4(zo);
-    if (a.x_u8) reinterpret_cast<uint32_t*>(a.x_u8)[h] = proc_u8x4(xo);
-    if (a.e_u8) reinterpret_cast<uint32_t*>(a.e_u8)[h] = proc_u8x4(eo);
+#pragma unroll
+    for (int u = 0; u < 2; ++u) {
+      const size_t i = base + static_cast<size_t>(u) * blockDim.x;
+      if (i >= total) continue;
+      const float w = wq[u];
+      const float zv[4] = {zq[u].x, zq[u].y, zq[u].z, zq[u].w}, ov[4] = {oq[u].x, oq[u].y, oq[u].z, oq[u].w};
+      const float uv[4] = {uq[u].x, uq[u].y, uq[u].z, uq[u].w}, nv[4] = {nq[u].x, nq[u].y, nq[u].z, nq[u].w};
+      float zo[4], xo[4], eo[4];
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        float xc = clip1(xhat_from_out(c, a.mean_type, zv[j], ov[j]));
+        float ec = eps_from_x(c, zv[j], xc);
+        if (a.out_u) {  // _cf_guidance, gaussian_diffusion.py:174-187
+          const float xu = clip1(xhat_from_out(c, a.mean_type, zv[j], uv[j]));
+          const float eu = eps_from_x(c, zv[j], xu);
+          const float e = addr(mulr(addr(1.0f, w), ec), mulr(-w, eu));
+          xc = clip1(mulr(c.A, subr(zv[j], mulr(e, c.Bc))));
+          ec = eps_from_x(c, zv[j], xc);
+        }
+        float zs;
+        if (a.sampler == 1) {
+          const float mean = addr(mulr(k_z, zv[j]), mulr(k_x, xc));
+          zs = addr(mean, mulr(stdv, nv[j]));
+        } else {
+          zs = addr(mulr(alpha_s, xc), mulr(sigma_s, ec));
+        }
+        zo[j] = last ? xc : zs;
+        xo[j] = xc;
+        eo[j] = ec;
+      }
+      const float4 zr = make_float4(zo[0], zo[1], zo[2], zo[3]);
+      reinterpret_cast<float4*>(a.z_next)[i] = zr;
+      if (a.z_dup) reinterpret_cast<float4*>(a.z_dup)[i] = zr;
+      // histories: row k = T-1-step of a [T][n*D] tensor (gaussian_diffusion.py:293-296 stacks in loop order)
+      const size_t h = a.hist_T > 0 ? static_cast<size_t>(a.hist_T - 1 - step) * total + i : i;
+      if (a.z_hist) reinterpret_cast<float4*>(a.z_hist)[h] = zr;
+      if (a.x_hist) reinterpret_cast<float4*>(a.x_hist)[h] = make_float4(xo[0], xo[1], xo[2], xo[3]);
+      if (a.e_hist) reinterpret_cast<float4*>(a.e_hist)[h] = make_float4(eo[0], eo[1], eo[2], eo[3]);
+      if (a.z_u8) reinterpret_cast<uint32_t*>(a.z_u8)[h] = proc_u8x4(zo);
+      if (a.x_u8) reinterpret_cast<uint32_t*>(a.x_u8)[h] = proc_u8x4(xo);
+      if (a.e_u8) reinterpret_cast<uint32_t*>(a.e_u8)[h] = proc_u8x4(eo);
+    }
   }
 }
 
@@ -244,8 +332,8 @@ __global__ void step_advance_kernel(int* step_dev) {
   if (threadIdx.x == 0 && blockIdx.x == 0) *step_dev -= 1;
 }
 
-static int ew_grid1(size_t total) {
-  size_t blocks = (total + 255) / 256;
+static int ew_grid1(size_t total, int per_thread = 1) {
+  size_t blocks = (total + 256 * per_thread - 1) / (256 * per_thread);
   const size_t cap = 148 * 8;
   return static_cast<int>(blocks < cap ? (blocks ? blocks : 1) : cap);
 }
@@ -259,7 +347,7 @@ extern "C" int b200_q_sample(const b200_q_sample_args* a, void* ws, size_t ws_by
   if (!a || !a->x || !a->eps || !a->logsnr || !a->z) return fail_arg("q_sample: null pointer");
   if (a->D % 4) return fail_arg("q_sample: D must be a multiple of 4");
   const size_t total = static_cast<size_t>(a->B) * (a->D / 4);
-  q_sample_kernel<<<ew_grid1(total), 256, 0, static_cast<cudaStream_t>(stream)>>>(a->x, a->eps, a->logsnr, a->z, a->B,
+  q_sample_kernel<<<ew_grid1(total, kEwUnroll), 256, 0, static_cast<cudaStream_t>(stream)>>>(a->x, a->eps, a->logsnr, a->z, a->B,
                                                                                   a->D / 4);
   return after_launch("q_sample_kernel");
 }
@@ -269,8 +357,10 @@ extern "C" int b200_loss(const b200_loss_args* a, void* ws, size_t ws_bytes, voi
   if (!a || !a->out || !a->z || !a->x || !a->eps || !a->logsnr || !a->loss_b) return fail_arg("loss: null pointer");
   if (a->mean_type < 0 || a->mean_type > 2) return fail_arg("loss: mean_type must be 0 (eps), 1 (x) or 2 (v)");
   cudaStream_t st = static_cast<cudaStream_t>(stream);
+  if (a->D % 4) return fail_arg("loss: D must be a multiple of 4");
+  if (a->loss_type != 0 && a->loss_type != 1) return fail_arg("loss: loss_type must be 0 (snr_trunc) or 1 (snr)");
   loss_kernel<<<a->B, 256, 0, st>>>(a->out, a->z, a->x, a->eps, a->logsnr, a->loss_b, a->mse2, a->dout, a->D,
-                                    a->mean_type, a->grad_scale);
+                                    a->mean_type, a->grad_scale, a->loss_type);
   if (int r = after_launch("loss_kernel")) return r;
   if (a->loss_mean) {
     mean_kernel<<<1, 256, 0, st>>>(a->loss_b, a->loss_mean, a->B);
@@ -296,7 +386,7 @@ extern "C" int b200_sampler_step(const b200_sampler_step_args* a, void* ws, size
   k.x_hist = a->x_hist; k.e_hist = a->e_hist;
   k.n = a->n; k.D = a->D; k.step = a->step; k.mean_type = a->mean_type; k.sampler = a->sampler;
   const size_t total = static_cast<size_t>(a->n) * (a->D / 4);
-  sampler_step_kernel<<<ew_grid1(total), 256, 0, static_cast<cudaStream_t>(stream)>>>(k);
+  sampler_step_kernel<<<ew_grid1(total, 2), 256, 0, static_cast<cudaStream_t>(stream)>>>(k);
   return after_launch("sampler_step_kernel");
 }
 

@@ -65,7 +65,7 @@ class LossArgs(C.Structure):
     _fields_ = [
         ("out", _f32p), ("z", _f32p), ("x", _f32p), ("eps", _f32p), ("logsnr", _f32p),
         ("loss_b", _f32p), ("mse2", _f32p), ("dout", _f32p), ("loss_mean", _f32p),
-        ("B", C.c_int), ("D", C.c_int), ("mean_type", C.c_int), ("grad_scale", C.c_float),
+        ("B", C.c_int), ("D", C.c_int), ("mean_type", C.c_int), ("grad_scale", C.c_float), ("loss_type", C.c_int),
     ]
 
 

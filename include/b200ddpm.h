@@ -179,8 +179,10 @@ typedef struct {
   float* mse2;
   float* dout;
   float* loss_mean;
-  int B, D, mean_type;
+  int B, D, mean_type; /* D a multiple of 4 */
   float grad_scale;
+  int loss_type; /* 0 = 'snr_trunc': max(x_mse, eps_mse) (gaussian_diffusion.py:166-168); 1 = 'snr': eps_mse (:169-170,
+                  * the weighting of distillation step1, :40-41).  x / eps are then the teacher's targets. */
 } b200_loss_args;
 int b200_loss(const b200_loss_args* a, void* ws, size_t ws_bytes, void* stream);
 

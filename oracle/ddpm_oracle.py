@@ -76,7 +76,7 @@ def run_model(out, z, logsnr, mean_type):
 def sincos_embedding(t, dim, max_period):
     """simple_unet.py:205-224 timestep_embedding (cos first, then sin)."""
     half = dim // 2
-    freqs = torch.exp(-math.log(max_period) * torch.arange(half, dtype=torch.float32) / half).to(t.dtype)
+    freqs = torch.exp(-math.log(max_period) * torch.arange(half, dtype=torch.float32) / half).to(device=t.device, dtype=t.dtype)
     args = t[:, None] * freqs[None]
     return torch.cat([torch.cos(args), torch.sin(args)], dim=-1)
 
@@ -165,6 +165,59 @@ def training_loss(sd, x, y, eps, u, mean_type="eps"):
     e_mse = ((ec - eps) ** 2).flatten(1).mean(1)
     per = torch.maximum(x_mse, e_mse)
     return per.mean(), per, {"logsnr": logsnr, "z": z, "out": out, "x_mse": x_mse, "eps_mse": e_mse}
+
+
+# ----------------------------------------------------------------------------- progressive distillation
+def ddim_step(net, z_t, logsnr_t, logsnr_s, mean_type, cond_w=None):
+    """gaussian_diffusion.py:189-213.  net(z, logsnr_vec, uncond) -> raw output; logsnr_t / logsnr_s are [B] vectors.
+    Returns (z_s, x_pred, eps_pred)."""
+    xc, ec = run_model(net(z_t, logsnr_t, False), z_t, logsnr_t, mean_type)
+    if cond_w is not None:
+        _, eu = run_model(net(z_t, logsnr_t, True), z_t, logsnr_t, mean_type)
+        xc, ec = cf_guidance(ec, eu, z_t, logsnr_t, cond_w)
+    return posterior_ddim(xc, ec, logsnr_s), xc, ec
+
+
+def distill_targets(sd_teacher, z_t, y, logsnr, u, cond_w, mode, num_steps, mean_type, i=None):
+    """gaussian_diffusion.py:105-154: the teacher's denoising targets (x_target, eps_target), no gradient.
+    step1: one classifier-free-guided DDIM step of the (unconditioned-on-w) teacher; step2: two half DDIM steps of the
+    w-conditioned teacher and the x implied by where they land."""
+    with torch.no_grad():
+        u_s = u - 1.0 / num_steps
+        logsnr_s = logsnr_cosine(u_s)
+        if mode == "step1":
+            net = lambda z, l, uncond: unet_forward(sd_teacher, z, l, guide=(-torch.ones_like(y) if uncond else y))
+            _, x_t, e_t = ddim_step(net, z_t, logsnr, logsnr_s, mean_type, cond_w=cond_w)
+            return x_t, e_t
+        assert mode == "step2"
+        net = lambda z, l, uncond: unet_forward(sd_teacher, z, l, guide=y, cond_w=cond_w)
+        logsnr_mid = logsnr_cosine(u - 0.5 / num_steps)
+        z_mid, _, _ = ddim_step(net, z_t, logsnr, logsnr_mid, mean_type)
+        z_teacher, x_pred_teacher, _ = ddim_step(net, z_mid, logsnr_mid, logsnr_s, mean_type)
+        bc = lambda v: bcast(v, z_t)
+        alpha_s = bc(torch.sqrt(torch.sigmoid(logsnr_s)))
+        alpha_t = bc(torch.sqrt(torch.sigmoid(logsnr)))
+        stdv_frac = bc(torch.exp(0.5 * (F.softplus(logsnr) - F.softplus(logsnr_s))))
+        x_target = (z_teacher - stdv_frac * z_t) / (alpha_s - stdv_frac * alpha_t)
+        x_target = torch.where(bc(i == 0), x_pred_teacher, x_target)
+        return x_target, eps_from_x(z_t, x_target, logsnr)
+
+
+def training_loss_distill(sd, sd_teacher, x, y, eps, u, cond_w, mode, num_steps, mean_type="eps", i=None):
+    """gaussian_diffusion.py:81-172 with a teacher: the student is conditioned on cond_w (simple_unet.py:60-64), the
+    targets come from the teacher, the loss is eps_mse ('snr', step1) or max(x_mse, eps_mse) ('snr_trunc', step2).
+    step2 draws a discrete u = (i+1)/num_steps (:87-91): pass `i` (int64 [B]) and u is derived from it."""
+    if mode == "step2":
+        u = (i + 1).to(x.dtype) / num_steps
+    logsnr = logsnr_cosine(u)
+    z = q_sample(x, logsnr, eps)
+    x_t, e_t = distill_targets(sd_teacher, z, y, logsnr, u, cond_w, mode, num_steps, mean_type, i=i)
+    out = unet_forward(sd, z, logsnr, guide=y, cond_w=cond_w)
+    xc, ec = run_model(out, z, logsnr, mean_type)
+    x_mse = ((xc - x_t) ** 2).flatten(1).mean(1)
+    e_mse = ((ec - e_t) ** 2).flatten(1).mean(1)
+    per = e_mse if mode == "step1" else torch.maximum(x_mse, e_mse)
+    return per.mean(), per, {"logsnr": logsnr, "z": z, "out": out, "x_target": x_t, "eps_target": e_t}
 
 
 def loss_from_out(out, z, x, eps, logsnr, mean_type="eps"):

@@ -134,6 +134,63 @@ def main():
                                          "down.seq.4.in_layers.2.weight", "turn.emb_layers.1.weight",
                                          "up.seq.3.0.skip_connection.weight", "up.seq.6.in_layers.2.bias", "out.2.weight")}
 
+    # ---- 7. progressive distillation (gaussian_diffusion.py:105-154, diffusion_model.py:34-43): step1 and step2 losses,
+    # all four cond_w_embed gradients and a few more, through the reference's own DiffusionModel.loss with a teacher
+    import tempfile
+    from gms import common
+    from gms.diffusion.diffusion_model import DiffusionModel
+    tdir = tempfile.mkdtemp()
+    teacher_sd = {"net." + k: v for k, v in O.random_state_dict(2).items()}
+    torch.save(teacher_sd, os.path.join(tdir, "teacher.pt"))
+    for mode, mt, T in (("step1", "eps", 8), ("step2", "eps", 4), ("step2", "v", 4)):
+        G = common.AttrDict(lr=3e-4, bs=64, device="cpu", pad32=0, weights_from=Path("."), logdir=Path("/tmp"))
+        G.update(DiffusionModel.DG)
+        G.update(mean_type=mt, sampler="ddim", timesteps=T, teacher_path=Path(os.path.join(tdir, "teacher.pt")), teacher_mode=mode)
+        m = DiffusionModel(G)
+        assert m.teacher_net is not None
+        m.net.load_state_dict(O.random_state_dict(1))  # student != teacher, so the targets are not trivially met
+        m.eval()
+        g = torch.Generator().manual_seed(50)
+        x = torch.rand(4, 1, 28, 28, generator=g) * 2 - 1
+        y = torch.tensor([3, -1, 0, 8])
+        torch.manual_seed(321)
+        m.zero_grad()
+        loss, _ = m.loss(x, y)
+        loss.backward()
+        torch.manual_seed(321)
+        eps = torch.randn(x.shape)
+        if mode == "step2":
+            ii = torch.randint(T, (4,))
+            uu = (ii + 1).to(x.dtype) / T
+        else:
+            ii = None
+            uu = torch.rand(4)
+        cw = 4.0 * torch.rand_like(uu)
+        tag = f"distill_{mode}_{mt}"
+        fx[tag] = dict(x=x, y=y, eps=eps, u=uu, i=ii, cond_w=cw, T=T, mode=mode, mean_type=mt, loss=loss.detach())
+        grads = {k: p.grad for k, p in m.net.named_parameters() if p.grad is not None}
+        fx[tag]["gradnorms"] = {k: v.norm() for k, v in grads.items()}
+        fx[tag]["grads"] = {k: grads[k].clone() for k in ("cond_w_embed.0.weight", "cond_w_embed.0.bias", "cond_w_embed.2.weight",
+                                                         "cond_w_embed.2.bias", "out.2.weight", "time_embed.0.bias",
+                                                         "turn.in_layers.0.weight")}
+        assert all(p.grad is None for p in m.teacher_net.parameters())
+        # student sampling with a teacher present (gaussian_diffusion.py:252-255): net conditioned on w, no guidance
+        if mode == "step1":
+            init = torch.randn(2, 1, 28, 28, generator=g)
+            ys = torch.tensor([4, 8])
+            torch.manual_seed(78)
+            with torch.no_grad():
+                zs, xs, es = m.diffusion.sample(net=partial(m.net, guide=ys), init_x=init, cond_w=0.5)
+            torch.manual_seed(78)
+            fx[tag]["sample"] = dict(init=init, y=ys, net_cond_w=4.0 * torch.rand(2), zs=zs, xs=xs, es=es)
+            # sampler='teacher_test' (:271-278): guided DDIM steps of the teacher itself
+            m.diffusion.sampler = "teacher_test"
+            torch.manual_seed(79)
+            with torch.no_grad():
+                zs, xs, es = m.diffusion.sample(net=partial(m.net, guide=ys), init_x=init, cond_w=0.5)
+            torch.manual_seed(79)
+            fx[tag]["teacher_test"] = dict(init=init, y=ys, net_cond_w=4.0 * torch.rand(2), zs=zs, xs=xs, es=es)
+
     torch.save(fx, os.path.join(out_dir, "reference_fixtures.pt"))
     print("wrote", os.path.join(out_dir, "reference_fixtures.pt"),
           os.path.getsize(os.path.join(out_dir, "reference_fixtures.pt")) // 1024, "KiB")

@@ -1,6 +1,7 @@
 """The CPU oracle (oracle/ddpm_oracle.py) against fixtures produced by the reference itself (oracle/make_golden.py).
 Both sides are CPU fp32 torch, so agreement is expected to ~1e-6; tolerances are written per check."""
 import torch
+import pytest
 
 from oracle import ddpm_oracle as O
 
@@ -76,3 +77,37 @@ def test_adam_step(golden):
             d = sd[k].detach() - sd0[k]
             # the first Adam step moves every weight by ~lr*sign(g): compare the deltas
             assert (d - golden[key]).abs().max().item() < 3e-5, k
+
+
+@pytest.mark.parametrize("tag", ["distill_step1_eps", "distill_step2_eps", "distill_step2_v"])
+def test_distillation_loss_and_grads_vs_reference_fixture(golden, tag):
+    """Progressive distillation (gaussian_diffusion.py:105-154) through the reference's own DiffusionModel.loss with a
+    teacher: loss, the four cond_w_embed gradients (simple_unet.py:60-64) and every gradient norm."""
+    f = golden[tag]
+    sd = {k: v.clone().requires_grad_(True) for k, v in O.random_state_dict(1).items()}
+    loss, _, _ = O.training_loss_distill(sd, O.random_state_dict(2), f["x"], f["y"], f["eps"], f["u"], f["cond_w"], f["mode"],
+                                         f["T"], f["mean_type"], i=f["i"])
+    loss.backward()
+    assert abs(loss.item() - f["loss"].item()) <= 1e-6 * abs(f["loss"].item())
+    for k, g in f["grads"].items():
+        assert ((sd[k].grad - g).abs().max() / g.abs().max()).item() < 1e-5, k
+    for k, n in f["gradnorms"].items():
+        assert abs(sd[k].grad.norm().item() - n.item()) <= 1e-4 * n.item() + 1e-12, k
+    assert all(sd[k].grad is not None for k in sd if k.startswith("cond_w_embed."))
+
+
+def test_distilled_student_sampling_vs_reference_fixture(golden):
+    """With a teacher present the student is conditioned on w = 4*rand(n) and sampled WITHOUT guidance
+    (gaussian_diffusion.py:252-255); sampler='teacher_test' runs guided DDIM steps of the teacher (:271-278)."""
+    f = golden["distill_step1_eps"]
+    sd, sdt = O.random_state_dict(1), O.random_state_dict(2)
+    s = f["sample"]
+    with torch.no_grad():
+        net = lambda z, l, uncond: O.unet_forward(sd, z, l, guide=s["y"], cond_w=s["net_cond_w"])
+        zs, xs, es = O.sample_loop(net, s["init"], f["T"], sampler="ddim", mean_type="eps", cond_w=None)
+    assert (zs - s["zs"]).abs().max() < 1e-4 and (xs - s["xs"]).abs().max() < 1e-4
+    t = f["teacher_test"]
+    with torch.no_grad():
+        net = lambda z, l, uncond: O.unet_forward(sdt, z, l, guide=(-torch.ones_like(t["y"]) if uncond else t["y"]))
+        zs, xs, es = O.sample_loop(net, t["init"], f["T"], sampler="ddim", mean_type="eps", cond_w=t["net_cond_w"])
+    assert (zs - t["zs"]).abs().max() < 1e-4 and (xs - t["xs"]).abs().max() < 1e-4
