@@ -106,7 +106,9 @@ __device__ __forceinline__ float block_sum(float v, float* sh) {
 // One CTA per sample.  loss_b = max(mean (xc-x)^2, mean (ec-eps)^2); dout = d(grad_scale * loss_b)/d(out).
 // The sample (out, z, x, eps: 16 B accesses) is read ONCE and held in registers across the block reduction when it fits
 // (D <= 4 * 4 * 256 pixels; 28x28 .. 64x64 do): 20 B/px of HBM traffic, the algorithmic minimum.  Larger images re-read.
-constexpr int kLossV = 4;  // float4 chunks per thread and tensor held in registers
+// kLossV = float4 chunks per thread and tensor held in registers (1 for 28x28: 40 registers, 6 CTAs per SM; the
+// one-size-fits-all kLossV = 4 build ran at 100 registers, 2 CTAs per SM and 1.4 TB/s)
+template <int kLossV>
 __global__ void __launch_bounds__(256)
 loss_kernel(const float* __restrict__ out, const float* __restrict__ z, const float* __restrict__ x,
             const float* __restrict__ eps, const float* __restrict__ logsnr, float* __restrict__ loss_b,
@@ -232,7 +234,28 @@ struct SampK {
   uint8_t* e_u8;
   int hist_T;
   int n, D, step, mean_type, sampler;
+  const float* lt_b;  // optional per-sample (logsnr_t, logsnr_s): distillation's teacher steps
+  const float* ls_b;
 };
+
+// per-step coefficients of diffusion_reverse (diffusion_utils.py:34-51) / ddim (gaussian_diffusion.py:210-212)
+struct StepCoef {
+  Coef c;
+  float k_z, k_x, stdv, alpha_s, sigma_s;
+};
+__device__ __forceinline__ StepCoef make_step_coef(float lt, float ls) {
+  StepCoef s;
+  s.c = make_coef(lt);
+  const float alpha_st = sqrtf((1.0f + expf(-lt)) / (1.0f + expf(-ls)));
+  s.alpha_s = sqrtf(sigmoid_t(ls));
+  s.sigma_s = sqrtf(sigmoid_t(-ls));
+  const float r = expf(lt - ls);
+  const float omr = -expm1f(lt - ls);
+  s.k_z = mulr(r, alpha_st);
+  s.k_x = mulr(omr, s.alpha_s);
+  s.stdv = sqrtf(mulr(omr, sigmoid_t(-lt)));
+  return s;
+}
 
 // diffusion_model.py:91-92 proc(): ((v + 1) * 127.5).clamp(0, 255).to(torch.uint8) (float -> uint8 truncates)
 __device__ __forceinline__ uint32_t proc_u8(float v) {
@@ -246,19 +269,9 @@ __device__ __forceinline__ uint32_t proc_u8x4(const float* v) {
 // 16 B per thread and tensor: z, out_c (, out_u), noise in; z_next (, z_dup, x_hist, e_hist) out.  16 B/px algorithmic
 // for the plain ancestral step (z, out, noise in; z out).
 __global__ void __launch_bounds__(256) sampler_step_kernel(SampK a) {
-  const int step = a.step_dev ? *a.step_dev : a.step;
-  const float lt = a.sched[2 * step], ls = a.sched[2 * step + 1];
-  const Coef c = make_coef(lt);
-  // diffusion_reverse (diffusion_utils.py:34-51) / ddim (gaussian_diffusion.py:210-212) coefficients
-  const float alpha_st = sqrtf((1.0f + expf(-lt)) / (1.0f + expf(-ls)));
-  const float alpha_s = sqrtf(sigmoid_t(ls));
-  const float sigma_s = sqrtf(sigmoid_t(-ls));
-  const float r = expf(lt - ls);
-  const float omr = -expm1f(lt - ls);
-  const float k_z = mulr(r, alpha_st);
-  const float k_x = mulr(omr, alpha_s);
-  const float stdv = sqrtf(mulr(omr, sigmoid_t(-lt)));
-  const bool last = (step == 0);
+  const int step = a.lt_b ? 1 : (a.step_dev ? *a.step_dev : a.step);
+  StepCoef sc = a.lt_b ? make_step_coef(0.f, 0.f) : make_step_coef(a.sched[2 * step], a.sched[2 * step + 1]);
+  const bool last = !a.lt_b && (step == 0);
   const int D4 = a.D >> 2;
   const size_t total = static_cast<size_t>(a.n) * D4;
   const size_t stride = static_cast<size_t>(gridDim.x) * blockDim.x * 2;
@@ -286,6 +299,11 @@ __global__ void __launch_bounds__(256) sampler_step_kernel(SampK a) {
       const size_t i = base + static_cast<size_t>(u) * blockDim.x;
       if (i >= total) continue;
       const float w = wq[u];
+      if (a.lt_b) {  // per-sample log-SNR pair
+        const size_t b = i / D4;
+        sc = make_step_coef(a.lt_b[b], a.ls_b[b]);
+      }
+      const Coef& c = sc.c;
       const float zv[4] = {zq[u].x, zq[u].y, zq[u].z, zq[u].w}, ov[4] = {oq[u].x, oq[u].y, oq[u].z, oq[u].w};
       const float uv[4] = {uq[u].x, uq[u].y, uq[u].z, uq[u].w}, nv[4] = {nq[u].x, nq[u].y, nq[u].z, nq[u].w};
       float zo[4], xo[4], eo[4];
@@ -302,10 +320,10 @@ __global__ void __launch_bounds__(256) sampler_step_kernel(SampK a) {
         }
         float zs;
         if (a.sampler == 1) {
-          const float mean = addr(mulr(k_z, zv[j]), mulr(k_x, xc));
-          zs = addr(mean, mulr(stdv, nv[j]));
+          const float mean = addr(mulr(sc.k_z, zv[j]), mulr(sc.k_x, xc));
+          zs = addr(mean, mulr(sc.stdv, nv[j]));
         } else {
-          zs = addr(mulr(alpha_s, xc), mulr(sigma_s, ec));
+          zs = addr(mulr(sc.alpha_s, xc), mulr(sc.sigma_s, ec));
         }
         zo[j] = last ? xc : zs;
         xo[j] = xc;
@@ -323,6 +341,38 @@ __global__ void __launch_bounds__(256) sampler_step_kernel(SampK a) {
       if (a.x_u8) reinterpret_cast<uint32_t*>(a.x_u8)[h] = proc_u8x4(xo);
       if (a.e_u8) reinterpret_cast<uint32_t*>(a.e_u8)[h] = proc_u8x4(eo);
     }
+  }
+}
+
+// gaussian_diffusion.py:137-154 (step2 of progressive distillation); same evaluation order as the reference.
+__global__ void __launch_bounds__(256)
+distill_target_kernel(const float* __restrict__ z_teacher, const float* __restrict__ z_t, const float* __restrict__ x_pred,
+                      const float* __restrict__ lt_b, const float* __restrict__ ls_b, const long long* __restrict__ index,
+                      float* __restrict__ x_target, float* __restrict__ eps_target, int n, int D4) {
+  const size_t total = static_cast<size_t>(n) * D4;
+  for (size_t i = blockIdx.x * static_cast<size_t>(blockDim.x) + threadIdx.x; i < total;
+       i += static_cast<size_t>(gridDim.x) * blockDim.x) {
+    const size_t b = i / D4;
+    const float lt = lt_b[b], ls = ls_b[b];
+    const Coef c = make_coef(lt);
+    const float alpha_s = sqrtf(sigmoid_t(ls)), alpha_t = sqrtf(sigmoid_t(lt));
+    // F.softplus(l) = log1p(exp(l)) below torch's threshold of 20, else l
+    const float spt = lt > 20.0f ? lt : log1pf(expf(lt)), sps = ls > 20.0f ? ls : log1pf(expf(ls));
+    const float f = expf(mulr(0.5f, subr(spt, sps)));
+    const float den = subr(alpha_s, mulr(f, alpha_t));
+    const bool first = index[b] == 0;
+    const float4 zt4 = reinterpret_cast<const float4*>(z_teacher)[i], z4 = reinterpret_cast<const float4*>(z_t)[i];
+    const float4 xp4 = reinterpret_cast<const float4*>(x_pred)[i];
+    const float zt[4] = {zt4.x, zt4.y, zt4.z, zt4.w}, zz[4] = {z4.x, z4.y, z4.z, z4.w}, xp[4] = {xp4.x, xp4.y, xp4.z, xp4.w};
+    float xo[4], eo[4];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const float xt = __fdiv_rn(subr(zt[j], mulr(f, zz[j])), den);
+      xo[j] = first ? xp[j] : xt;
+      eo[j] = eps_from_x(c, zz[j], xo[j]);
+    }
+    reinterpret_cast<float4*>(x_target)[i] = make_float4(xo[0], xo[1], xo[2], xo[3]);
+    reinterpret_cast<float4*>(eps_target)[i] = make_float4(eo[0], eo[1], eo[2], eo[3]);
   }
 }
 
@@ -359,8 +409,16 @@ extern "C" int b200_loss(const b200_loss_args* a, void* ws, size_t ws_bytes, voi
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   if (a->D % 4) return fail_arg("loss: D must be a multiple of 4");
   if (a->loss_type != 0 && a->loss_type != 1) return fail_arg("loss: loss_type must be 0 (snr_trunc) or 1 (snr)");
-  loss_kernel<<<a->B, 256, 0, st>>>(a->out, a->z, a->x, a->eps, a->logsnr, a->loss_b, a->mse2, a->dout, a->D,
-                                    a->mean_type, a->grad_scale, a->loss_type);
+  const int D4 = a->D / 4;
+  if (D4 <= 256)
+    loss_kernel<1><<<a->B, 256, 0, st>>>(a->out, a->z, a->x, a->eps, a->logsnr, a->loss_b, a->mse2, a->dout, a->D,
+                                         a->mean_type, a->grad_scale, a->loss_type);
+  else if (D4 <= 512)
+    loss_kernel<2><<<a->B, 256, 0, st>>>(a->out, a->z, a->x, a->eps, a->logsnr, a->loss_b, a->mse2, a->dout, a->D,
+                                         a->mean_type, a->grad_scale, a->loss_type);
+  else
+    loss_kernel<4><<<a->B, 256, 0, st>>>(a->out, a->z, a->x, a->eps, a->logsnr, a->loss_b, a->mse2, a->dout, a->D,
+                                         a->mean_type, a->grad_scale, a->loss_type);
   if (int r = after_launch("loss_kernel")) return r;
   if (a->loss_mean) {
     mean_kernel<<<1, 256, 0, st>>>(a->loss_b, a->loss_mean, a->B);
@@ -371,7 +429,9 @@ extern "C" int b200_loss(const b200_loss_args* a, void* ws, size_t ws_bytes, voi
 
 extern "C" int b200_sampler_step(const b200_sampler_step_args* a, void* ws, size_t ws_bytes, void* stream) {
   (void)ws; (void)ws_bytes;
-  if (!a || !a->z || !a->out_c || !a->sched || !a->z_next) return fail_arg("sampler_step: null pointer");
+  if (!a || !a->z || !a->out_c || !a->z_next) return fail_arg("sampler_step: null pointer");
+  if (!a->sched && !(a->logsnr_t_b && a->logsnr_s_b)) return fail_arg("sampler_step: needs sched or the per-sample log-SNR pair");
+  if (a->logsnr_t_b && (!a->logsnr_s_b || a->hist_T > 0)) return fail_arg("sampler_step: per-sample log-SNR needs both vectors and no trajectory history");
   if (a->out_u && !a->cond_w) return fail_arg("sampler_step: guidance needs cond_w");
   if (a->sampler == 1 && !a->noise) return fail_arg("sampler_step: the noisy sampler needs noise");
   if (a->sampler != 0 && a->sampler != 1) return fail_arg("sampler_step: sampler must be 0 (ddim) or 1 (noisy)");
@@ -381,13 +441,26 @@ extern "C" int b200_sampler_step(const b200_sampler_step_args* a, void* ws, size
   if (a->hist_T > 0 && !a->step_dev && (a->step < 0 || a->step >= a->hist_T)) return fail_arg("sampler_step: step outside the history");
   SampK k;
   k.z = a->z; k.out_c = a->out_c; k.out_u = a->out_u; k.cond_w = a->cond_w; k.noise = a->noise; k.sched = a->sched;
-  k.step_dev = a->step_dev; k.z_next = a->z_next; k.z_dup = a->z_dup; k.z_hist = a->z_hist; k.hist_T = a->hist_T;
+  k.step_dev = a->step_dev; k.z_next = a->z_next; k.lt_b = a->logsnr_t_b; k.ls_b = a->logsnr_s_b;
+  k.z_dup = a->z_dup; k.z_hist = a->z_hist; k.hist_T = a->hist_T;
   k.z_u8 = static_cast<uint8_t*>(a->z_u8); k.x_u8 = static_cast<uint8_t*>(a->x_u8); k.e_u8 = static_cast<uint8_t*>(a->e_u8);
   k.x_hist = a->x_hist; k.e_hist = a->e_hist;
   k.n = a->n; k.D = a->D; k.step = a->step; k.mean_type = a->mean_type; k.sampler = a->sampler;
   const size_t total = static_cast<size_t>(a->n) * (a->D / 4);
   sampler_step_kernel<<<ew_grid1(total, 2), 256, 0, static_cast<cudaStream_t>(stream)>>>(k);
   return after_launch("sampler_step_kernel");
+}
+
+extern "C" int b200_distill_target(const b200_distill_target_args* a, void* ws, size_t ws_bytes, void* stream) {
+  (void)ws; (void)ws_bytes;
+  if (!a || !a->z_teacher || !a->z_t || !a->x_pred_teacher || !a->logsnr_t || !a->logsnr_s || !a->index || !a->x_target ||
+      !a->eps_target)
+    return fail_arg("distill_target: null pointer");
+  if (a->D % 4) return fail_arg("distill_target: D must be a multiple of 4");
+  const size_t total = static_cast<size_t>(a->n) * (a->D / 4);
+  distill_target_kernel<<<ew_grid1(total), 256, 0, static_cast<cudaStream_t>(stream)>>>(
+      a->z_teacher, a->z_t, a->x_pred_teacher, a->logsnr_t, a->logsnr_s, a->index, a->x_target, a->eps_target, a->n, a->D / 4);
+  return after_launch("distill_target_kernel");
 }
 
 extern "C" int b200_step_advance(const b200_step_advance_args* a, void* ws, size_t ws_bytes, void* stream) {

@@ -138,13 +138,14 @@ __global__ void embed_prep_kernel(const float* __restrict__ t, const float* __re
 // emb = t_emb + (uncond ? 0 : g_emb);  semb = silu(emb)
 __global__ void __launch_bounds__(256)
 embed_combine_kernel(const float* __restrict__ t_emb, const float* __restrict__ g_emb,
-                     const long long* __restrict__ guide, int force_uncond, float* __restrict__ emb,
-                     float* __restrict__ semb, int B, int E) {
+                     const long long* __restrict__ guide, int force_uncond, const float* __restrict__ w_emb,
+                     float* __restrict__ emb, float* __restrict__ semb, int B, int E) {
   const size_t total = static_cast<size_t>(B) * E;
   GRID_STRIDE(i, total) {
     const int b = static_cast<int>(i / E);
     float v = t_emb[i];
     if (g_emb && !force_uncond && guide[b] >= 0) v += g_emb[i];
+    if (w_emb) v += w_emb[i];  // simple_unet.py:60-64: emb += cond_w_embed(...), after the guide embedding
     emb[i] = v;
     semb[i] = v / (1.0f + expf(-v));
   }
@@ -451,8 +452,8 @@ extern "C" int b200_embed_combine(const b200_embed_args* a, void* ws, size_t ws_
   if (!a || !a->t_emb || !a->emb || !a->semb) return fail_arg("embed_combine: null pointer");
   if (a->g_emb && !a->guide) return fail_arg("embed_combine: g_emb needs guide labels");
   const size_t total = static_cast<size_t>(a->B) * a->E;
-  embed_combine_kernel<<<ew_grid2(total), 256, 0, ST(stream)>>>(a->t_emb, a->g_emb, a->guide, a->force_uncond, a->emb,
-                                                                 a->semb, a->B, a->E);
+  embed_combine_kernel<<<ew_grid2(total), 256, 0, ST(stream)>>>(a->t_emb, a->g_emb, a->guide, a->force_uncond, a->w_emb,
+                                                                 a->emb, a->semb, a->B, a->E);
   return after_launch("embed_combine_kernel");
 }
 

@@ -75,6 +75,14 @@ class SamplerStepArgs(C.Structure):
         ("step_dev", _f32p), ("z_next", _f32p), ("x_hist", _f32p), ("e_hist", _f32p),
         ("n", C.c_int), ("D", C.c_int), ("step", C.c_int), ("mean_type", C.c_int), ("sampler", C.c_int),
         ("z_dup", _f32p), ("z_hist", _f32p), ("hist_T", C.c_int), ("z_u8", _f32p), ("x_u8", _f32p), ("e_u8", _f32p),
+        ("logsnr_t_b", _f32p), ("logsnr_s_b", _f32p),
+    ]
+
+
+class DistillTargetArgs(C.Structure):
+    _fields_ = [
+        ("z_teacher", _f32p), ("z_t", _f32p), ("x_pred_teacher", _f32p), ("logsnr_t", _f32p), ("logsnr_s", _f32p),
+        ("index", _f32p), ("x_target", _f32p), ("eps_target", _f32p), ("n", C.c_int), ("D", C.c_int),
     ]
 
 
@@ -111,7 +119,7 @@ class EmbedArgs(C.Structure):
         ("t", _f32p), ("sched", _f32p), ("step_dev", _f32p), ("freqs", _f32p), ("guide", _f32p),
         ("sincos", _f32p), ("onehot", _f32p), ("t_out", _f32p), ("t_emb", _f32p), ("g_emb", _f32p),
         ("emb", _f32p), ("semb", _f32p), ("d_semb", _f32p), ("d_emb", _f32p), ("d_g_emb", _f32p),
-        ("B", C.c_int), ("E", C.c_int), ("step", C.c_int), ("force_uncond", C.c_int),
+        ("B", C.c_int), ("E", C.c_int), ("step", C.c_int), ("force_uncond", C.c_int), ("w_emb", _f32p),
     ]
 
 
@@ -189,7 +197,7 @@ EXPORTS = [
     "b200_abi_version", "b200_init", "b200_last_error", "b200_launch_count",
     "b200_conv_igemm", "b200_conv_kernel_of", "b200_conv_wgrad",
     "b200_gn_fwd", "b200_gn_bwd",
-    "b200_q_sample", "b200_loss", "b200_sampler_step", "b200_step_advance", "b200_int_increment",
+    "b200_q_sample", "b200_loss", "b200_sampler_step", "b200_distill_target", "b200_step_advance", "b200_int_increment",
     "b200_conv_in_fwd", "b200_conv_in_bwd", "b200_conv_out_fwd", "b200_conv_out_bwd",
     "b200_upsample2x", "b200_colsum",
     "b200_embed_prep", "b200_embed_combine", "b200_embed_combine_bwd",

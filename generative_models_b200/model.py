@@ -21,7 +21,7 @@ from .schedule import logsnr_schedule_cosine, sampler_table
 from .unet_spec import ParamStore, build_module_tree
 
 MEAN_TYPES = {"eps": 0, "x": 1, "v": 2}
-SAMPLERS = {"ddim": 0, "noisy": 1}
+SAMPLERS = {"ddim": 0, "noisy": 1, "teacher_test": 0}  # value = the step kernel's update rule (0 ddim, 1 ancestral)
 
 
 class AttrDict(dict):
@@ -83,8 +83,8 @@ class DiffusionModelB200(nn.Module):
         self.bf16 = G.get("precision", "tf32") == "bf16"
         if float(G.dropout) != 0.0:
             raise NotImplementedError("dropout != 0 is not on the DDPM hot path (reference default is 0.0)")
-        if Path(G.teacher_path) != Path("."):
-            raise NotImplementedError("progressive distillation (teacher_path) is out of scope (SURVEY.md §8f)")
+        if G.get("teacher_mode", "step1") not in ("step1", "step2"):
+            raise NotImplementedError(f"teacher_mode {G.teacher_mode!r} (step1 | step2)")
         if torch.cuda.current_device() != dev.index:
             raise lib.B200Error(f"one process per GPU: make {dev} the current device (torch.cuda.set_device) before "
                                 "constructing DiffusionModelB200")
@@ -112,6 +112,20 @@ class DiffusionModelB200(nn.Module):
         self._drop_slots, self._drop_i = [], 0
         # data-parallel replicas start from rank 0's weights whatever each rank's RNG state was
         dist.broadcast_params(self.store.flat)
+        # progressive distillation (diffusion_model.py:34-43): the student starts from the teacher's weights, the teacher is
+        # a frozen copy with its own flat store; its parameters appear under `teacher_net.*` like the reference's
+        self.teacher_store = None
+        if Path(G.get("teacher_path", ".")) != Path(".") and Path(G.get("weights_from", ".")) == Path("."):
+            print("Loading teacher model")
+            self.load_state_dict(torch.load(G.teacher_path, map_location=dev), strict=False)
+            self.teacher_store = ParamStore(G.hidden_size, dev)
+            self.teacher_store.flat.copy_(self.store.flat)
+            self.teacher_net = build_module_tree(self.teacher_store, nn.Module())
+            for p in self.teacher_net.parameters():
+                p.requires_grad = False
+                p.grad = None
+        elif G.sampler == "teacher_test":
+            raise lib.B200Error("sampler='teacher_test' needs a teacher (teacher_path)")
 
     def load_state_dict(self, state_dict, strict=True, assign=False):
         out = super().load_state_dict(state_dict, strict=strict)
@@ -178,20 +192,22 @@ class DiffusionModelB200(nn.Module):
         return p
 
     # ------------------------------------------------------------------ training
-    def loss(self, x, y, eps=None, u=None):
+    def loss(self, x, y, eps=None, u=None, cond_w=None, idx=None):
         """diffusion_model.py:76-80 → gaussian_diffusion.py:81-100,156-172.  Forward only (the reference's callers
-        use it under no_grad, main.py:163-176); the optimiser path is train_step.  `eps` / `u` inject the random
-        draws (tests); by default they are drawn like the reference: randn(x.shape) then rand(B)."""
+        use it under no_grad, main.py:163-176); the optimiser path is train_step.  `eps` / `u` (/ `cond_w`, `idx` with a
+        teacher) inject the random draws (tests); by default they are drawn like the reference: randn(x.shape), then
+        rand(B) (step2 distillation: randint(T, (B,))), then with a teacher 4*rand(B)."""
         b = self._plan(x.shape[0], "loss")
-        b.stage_inputs(x, y, eps, u)
+        b.stage_inputs(x, y, eps, u, cond_w, idx)
         st = self._stream()
         run_ops(b.pre_ops, st)
+        b.enqueue_teacher_targets()
         b.plan.forward(st)
         run_ops(b.loss_ops, st)
         loss = b.loss_mean[0].clone()
         return loss, {"loss": loss}
 
-    def train_step(self, x, y, eps=None, u=None):
+    def train_step(self, x, y, eps=None, u=None, cond_w=None, idx=None):
         """diffusion_model.py:63-74: class-label drop, loss, backward, Adam.  fp32 storage with TF32 tensor-core
         convolutions needs no loss scaling, so `loss_scale` is reported as 1.
         Everything after the copy of (x, y) into the plan's static buffers — the eps / u draws (torch's own Philox
@@ -212,11 +228,8 @@ class DiffusionModelB200(nn.Module):
         b.copy_batch(x, y)
         world = torch.distributed.get_world_size() if torch.distributed.is_initialized() else 1
         self.set_hparams(float(self.G.lr), 1.0 / world)
-        key = (eps is None, u is None, dev_drop)
-        if eps is not None:
-            b.eps.copy_(eps.reshape(b.B, -1))
-        if u is not None:
-            b.u.copy_(u)
+        key = (eps is None, u is None and idx is None, dev_drop, cond_w is None)
+        b.inject(eps, u, cond_w, idx)
         graphed = (lambda fn, k: b.run_graphed(fn, k)) if self.use_graph else (lambda fn, k: fn())
         if world == 1:
             graphed(lambda: (b.enqueue_stage(*key), b.enqueue_fwd_bwd(), b.enqueue_adam()), ("step",) + key)
@@ -238,15 +251,15 @@ class DiffusionModelB200(nn.Module):
             graphed(b.enqueue_adam, "adam")
         return {"loss": b.loss_mean[0].clone(), "loss_scale": self._loss_scale}
 
-    def loss_and_grads(self, x, y, eps=None, u=None):
+    def loss_and_grads(self, x, y, eps=None, u=None, cond_w=None, idx=None):
         """loss + backward without the optimiser step (parity tests: compare store.grad views with autograd)."""
         b = self._plan(x.shape[0], "train")
-        b.stage_inputs(x, y, eps, u)
+        b.stage_inputs(x, y, eps, u, cond_w, idx)
         b.enqueue_fwd_bwd()
         return b.loss_mean[0].clone(), b
 
     # ------------------------------------------------------------------ sampling
-    def _sample_loop(self, init_z, y, cond_w, history=None, noises=None):
+    def _sample_loop(self, init_z, y, cond_w, history=None, noises=None, net_cond_w=None):
         """gaussian_diffusion.py:245-296 as T replays of one fused step:
         UNet(z, logsnr_t | y ‖ uncond) → randn → b200_sampler_step (x/eps reconstruction, guidance, posterior update,
         `where(i == 0, x, z_s)`, optional trajectory rows) → device loop index -= 1.
@@ -255,8 +268,13 @@ class DiffusionModelB200(nn.Module):
         history: None | "f32" | "u8" — the three [T, n, 1, S, S] stacks (:293-296), written by the step kernel itself."""
         n = init_z.shape[0]
         T = int(self.G.timesteps)
-        b = self._plan(n, "sample_g" if cond_w is not None else "sample")
-        hist = b.begin_sampling(init_z, y, cond_w, history)
+        kind = "sample_g" if cond_w is not None else "sample"
+        if self.G.sampler == "teacher_test":
+            kind += "_t"      # the teacher's own weights (gaussian_diffusion.py:271-278)
+        elif net_cond_w is not None:
+            kind += "_w"      # the student conditioned on w through cond_w_embed (:252-255)
+        b = self._plan(n, kind)
+        hist = b.begin_sampling(init_z, y, cond_w, history, net_cond_w=net_cond_w)
         noisy = SAMPLERS[self.G.sampler] == 1
         for k in range(T):
             if noises is not None and noisy:
@@ -269,25 +287,34 @@ class DiffusionModelB200(nn.Module):
         z = b.plan.z_in[:n].view(n, 1, self.size, self.size).clone()
         return z, hist
 
+    def _sampling_weights(self, n, want_guidance):
+        """gaussian_diffusion.py:247-257: (cond_w for classifier-free guidance, net_cond_w the net is conditioned on).
+        `want_guidance` = the caller passed a cond_w (DiffusionModel.sample does, evaluate does not)."""
+        net_cond_w = 4.0 * torch.rand(n, device=self.device) if want_guidance else None
+        if self.teacher_store is not None:
+            if self.G.sampler == "teacher_test":  # guided DDIM steps of the teacher, weights = net_cond_w
+                return net_cond_w, None
+            return None, net_cond_w               # student conditioned on w, no guidance
+        scw = float(self.G.sample_cond_w)
+        if scw != -1.0:
+            return torch.full((n,), scw, device=self.device), None
+        return net_cond_w, None
+
     def sample(self, n, y=None):
         """diffusion_model.py:82-87.  With labels: classifier-free guidance, per-sample w = 4*rand(n) unless
-        G.sample_cond_w is set (gaussian_diffusion.py:247-257).  y=None (a TypeError in the reference) samples
-        unconditionally without guidance."""
+        G.sample_cond_w is set (gaussian_diffusion.py:247-257); a distilled student is instead conditioned on w and
+        sampled without guidance.  y=None (a TypeError in the reference) samples unconditionally without guidance."""
         with torch.no_grad():
             noise = torch.randn((n, 1, self.size, self.size), device=self.device)
-            cond_w = None
-            if y is not None:
-                net_cond_w = 4.0 * torch.rand(n, device=self.device)
-                scw = float(self.G.sample_cond_w)
-                cond_w = net_cond_w if scw == -1.0 else torch.full((n,), scw, device=self.device)
-            z, _ = self._sample_loop(noise, y, cond_w)
+            cond_w, net_cond_w = self._sampling_weights(n, True) if y is not None else (None, None)
+            z, _ = self._sample_loop(noise, y, cond_w, net_cond_w=net_cond_w)
             return z
 
-    def sample_trajectory(self, init_z, y=None, cond_w=None, noises=None, history="f32"):
+    def sample_trajectory(self, init_z, y=None, cond_w=None, noises=None, history="f32", net_cond_w=None):
         """The three [T, n, 1, S, S] histories (z, x, eps) GaussianDiffusion.sample returns (gaussian_diffusion.py:293-296);
         history="u8": already passed through evaluate()'s proc() (uint8)."""
         with torch.no_grad():
-            _, hist = self._sample_loop(init_z, y, cond_w, history=history, noises=noises)
+            _, hist = self._sample_loop(init_z, y, cond_w, history=history, noises=noises, net_cond_w=net_cond_w)
             return [h.clone() for h in hist]
 
     def evaluate(self, writer, x, y, epoch):
@@ -297,10 +324,9 @@ class DiffusionModelB200(nn.Module):
         torch.manual_seed(0)
         noise = torch.randn((25, 1, self.size, self.size), device=self.device)
         labels = torch.arange(25, dtype=torch.long, device=self.device) % 10
-        scw = float(self.G.sample_cond_w)
-        cond_w = None if scw == -1.0 else torch.full((25,), scw, device=self.device)
+        cond_w, net_cond_w = self._sampling_weights(25, False)
         with torch.no_grad():
-            _, hist = self._sample_loop(noise, labels, cond_w, history="u8")
+            _, hist = self._sample_loop(noise, labels, cond_w, history="u8", net_cond_w=net_cond_w)
         zs, xs, eps = (h.cpu() for h in hist)
         if self.G.pad32:
             zs, xs, eps = (t[..., 2:-2, 2:-2] for t in (zs, xs, eps))
@@ -345,14 +371,17 @@ class _Bound:
         f32 = dict(dtype=torch.float32, device=dev)
         self.graphs = {}
         mt = MEAN_TYPES[G.mean_type]
-        if kind in ("sample", "sample_g"):
+        if kind.startswith("sample"):
+            # kinds: sample | sample_g (guided: 2B rows) [+ _w: net conditioned on w via cond_w_embed | _t: teacher weights]
             T = int(G.timesteps)
-            self.guided = kind == "sample_g"
+            self.guided = kind.startswith("sample_g")
+            self.cond_embed = kind.endswith("_w")
+            store = model.teacher_store if kind.endswith("_t") else model.store
             rows = 2 * B if self.guided else B  # guided: conditional rows, then the same z with guide = -1
             self.sched = model._table(T)
             self.step_dev = torch.zeros(1, dtype=torch.int32, device=dev)
-            self.plan = UNetPlan(model.store, rows, S, train=False, sched=self.sched, step_dev=self.step_dev,
-                                 bf16=model.bf16)
+            self.plan = UNetPlan(store, rows, S, train=False, sched=self.sched, step_dev=self.step_dev,
+                                 bf16=model.bf16, cond_w=self.cond_embed)
             self.noise = torch.zeros(B, D, **f32)
             self.cond_w = torch.zeros(B, **f32)
             self.T = T
@@ -360,7 +389,11 @@ class _Bound:
             self.history = None
             self.mt = mt
             return
-        self.plan = UNetPlan(model.store, B, S, train=(kind == "train"), bf16=model.bf16)
+        # ---- train / loss.  With a teacher (progressive distillation, gaussian_diffusion.py:105-154) the student is
+        # conditioned on cond_w and the loss targets come from one (step1) or two (step2) DDIM steps of the teacher
+        self.distill = model.teacher_store is not None
+        self.mode = G.get("teacher_mode", "step1") if self.distill else None
+        self.plan = UNetPlan(model.store, B, S, train=(kind == "train"), bf16=model.bf16, cond_w=self.distill)
         p = self.plan
         self.x = torch.zeros(B, D, **f32)
         self.eps = torch.zeros(B, D, **f32)
@@ -370,9 +403,13 @@ class _Bound:
         self.loss_mean = torch.zeros(1, **f32)
         qa = lib.QSampleArgs(x=_p(self.x), eps=_p(self.eps), logsnr=_p(p.t), z=_p(p.z_in), B=B, D=D)
         self.pre_ops = [Op("b200_q_sample", qa)]
-        la = lib.LossArgs(out=_p(p.out), z=_p(p.z_in), x=_p(self.x), eps=_p(self.eps), logsnr=_p(p.t),
+        tgt_x, tgt_e = self.x, self.eps
+        if self.distill:
+            tgt_x, tgt_e = self._build_teacher(model, B, S, D, mt, f32)
+        la = lib.LossArgs(out=_p(p.out), z=_p(p.z_in), x=_p(tgt_x), eps=_p(tgt_e), logsnr=_p(p.t),
                           loss_b=_p(self.loss_b), mse2=_p(self.mse2), dout=_p(p.dout) if kind == "train" else None,
-                          loss_mean=_p(self.loss_mean), B=B, D=D, mean_type=mt, grad_scale=1.0 / B)
+                          loss_mean=_p(self.loss_mean), B=B, D=D, mean_type=mt, grad_scale=1.0 / B,
+                          loss_type=1 if self.mode == "step1" else 0)  # 'snr' weighting for step1 (:40-41)
         self.loss_ops = [Op("b200_loss", la)]
         if kind == "train":
             st = model.store
@@ -382,6 +419,69 @@ class _Bound:
                                           step_dev=_p(model.adam_step), step=0, hparams_dev=_p(model.hparams))
             self.adam_ops = [Op("b200_int_increment", lib.StepAdvanceArgs(step_dev=_p(model.adam_step))),
                              Op("b200_adam", self.adam_args)]
+
+    # ---- progressive distillation: the teacher's targets
+    def _build_teacher(self, model, B, S, D, mt, f32):
+        """Frozen-teacher inference plan + the target ops.  step1 (:113-121): ONE classifier-free-guided DDIM step of the
+        teacher (2B rows: labelled, then guide = -1; the teacher is not conditioned on w) — targets are its x / eps
+        predictions.  step2 (:122-149): two DDIM half steps of the w-conditioned teacher, then the x implied by where
+        they land (b200_distill_target)."""
+        p = self.plan
+        dev = self.x.device
+        step1 = self.mode == "step1"
+        self.idx = torch.zeros(B, dtype=torch.int64, device=dev)
+        self.logsnr_s = torch.zeros(B, **f32)
+        self.logsnr_mid = torch.zeros(B, **f32)
+        self.x_target = torch.zeros(B, D, **f32)
+        self.eps_target = torch.zeros(B, D, **f32)
+        self.z_teacher = torch.zeros(B, D, **f32)
+        self.x_pred_teacher = torch.zeros(B, D, **f32)
+        t = self.tplan = UNetPlan(model.teacher_store, 2 * B if step1 else B, S, train=False, bf16=model.bf16,
+                                  cond_w=not step1)
+        run_ops(t.refresh_ops, model._stream())  # the teacher is frozen: its tensor-core weight shadows are built once
+        common = dict(sched=None, step_dev=None, noise=None, n=B, D=D, step=0, mean_type=mt, sampler=0)
+        if step1:
+            a = lib.SamplerStepArgs(z=_p(p.z_in), out_c=_p(t.out), out_u=_p(t.out, B * D), cond_w=_p(p.cond_w),
+                                    z_next=_p(self.z_teacher), x_hist=_p(self.x_target), e_hist=_p(self.eps_target),
+                                    logsnr_t_b=_p(p.t), logsnr_s_b=_p(self.logsnr_s), **common)
+            self.t_ops = [[Op("b200_sampler_step", a)]]
+        else:
+            a1 = lib.SamplerStepArgs(z=_p(p.z_in), out_c=_p(t.out), out_u=None, cond_w=None, z_next=_p(t.z_in),
+                                     logsnr_t_b=_p(p.t), logsnr_s_b=_p(self.logsnr_mid), **common)
+            a2 = lib.SamplerStepArgs(z=_p(t.z_in), out_c=_p(t.out), out_u=None, cond_w=None, z_next=_p(self.z_teacher),
+                                     x_hist=_p(self.x_pred_teacher), logsnr_t_b=_p(self.logsnr_mid),
+                                     logsnr_s_b=_p(self.logsnr_s), **common)
+            dt = lib.DistillTargetArgs(z_teacher=_p(self.z_teacher), z_t=_p(p.z_in), x_pred_teacher=_p(self.x_pred_teacher),
+                                       logsnr_t=_p(p.t), logsnr_s=_p(self.logsnr_s), index=_p(self.idx),
+                                       x_target=_p(self.x_target), eps_target=_p(self.eps_target), n=B, D=D)
+            self.t_ops = [[Op("b200_sampler_step", a1)], [Op("b200_sampler_step", a2), Op("b200_distill_target", dt)]]
+        return self.x_target, self.eps_target
+
+    def enqueue_teacher_targets(self):
+        """Teacher forward(s) + target kernels, between q_sample and the student's forward (no-op without a teacher)."""
+        if not self.distill:
+            return
+        st = self.m._stream()
+        t, p, B = self.tplan, self.plan, self.B
+        if self.mode == "step1":
+            t.z_in[:B].copy_(p.z_in)
+            t.z_in[B:].copy_(p.z_in)
+            t.t[:B].copy_(p.t)
+            t.t[B:].copy_(p.t)
+            t.guide[:B].copy_(p.guide)
+            t.guide[B:].fill_(-1)
+            t.forward(st, refresh=False)
+            run_ops(self.t_ops[0], st)
+        else:
+            t.z_in.copy_(p.z_in)
+            t.t.copy_(p.t)
+            t.guide.copy_(p.guide)
+            t.cond_w.copy_(p.cond_w)
+            t.forward(st, refresh=False)
+            run_ops(self.t_ops[0], st)   # z_mid -> t.z_in
+            t.t.copy_(self.logsnr_mid)
+            t.forward(st, refresh=False)
+            run_ops(self.t_ops[1], st)
 
     # ---- inputs
     def copy_batch(self, x, y):
@@ -394,29 +494,49 @@ class _Bound:
         else:
             self.plan.guide.copy_(y, non_blocking=True)
 
-    def enqueue_stage(self, draw_eps=True, draw_u=True, dev_drop=False):
-        """The random draws in the reference's order (gaussian_diffusion.py:83 randn(x.shape) first, :94 rand(B)
-        second) from the device's default generator, then the log-SNR per sample.  Capturable: torch registers the
-        Philox offset with the graph, replays continue the generator's stream exactly like eager draws."""
+    def enqueue_stage(self, draw_eps=True, draw_u=True, dev_drop=False, draw_w=True):
+        """The random draws in the reference's order (gaussian_diffusion.py:83 randn(x.shape) first, :94 rand(B) — or, for
+        step2 distillation, :90 randint(T, (B,)) — second, with a teacher :107 4*rand_like(u) third) from the device's
+        default generator, then the log-SNR per sample.  Capturable: torch registers the Philox offset with the graph,
+        replays continue the generator's stream exactly like eager draws."""
         if dev_drop:
             # classifier-free label drop (diffusion_model.py:67) with a device draw; ahead of eps/u so that those keep
             # their order relative to each other
             self.plan.guide.masked_fill_(torch.rand(self.B, device=self.x.device) < float(self.m.G.cf_drop_prob), -1)
         if draw_eps:
             self.eps.normal_()
-        if draw_u:
+        T = int(self.m.G.timesteps)
+        if self.mode == "step2":  # discrete time for distillation (:87-91)
+            if draw_u:
+                self.idx.copy_(torch.randint(T, (self.B,), device=self.x.device))
+            self.u.copy_((self.idx + 1).to(torch.float32) / T)
+        elif draw_u:
             self.u.uniform_()
         # logsnr via the reference's torch expression (diffusion_utils.py:198-201): bit-identical per sample
         self.plan.t.copy_(logsnr_schedule_cosine(self.u))
+        if self.distill:
+            if draw_w:
+                self.plan.cond_w.copy_(4.0 * torch.rand_like(self.u))
+            self.logsnr_s.copy_(logsnr_schedule_cosine(self.u - 1.0 / T))        # :123-124 (NaN for u < 1/T, unused by step1)
+            if self.mode == "step2":
+                self.logsnr_mid.copy_(logsnr_schedule_cosine(self.u - 0.5 / T))  # :132-133
 
-    def stage_inputs(self, x, y, eps, u):
-        """Eager form: copy the batch, inject or draw eps / u, derive logsnr."""
-        self.copy_batch(x, y)
+    def inject(self, eps=None, u=None, cond_w=None, idx=None):
+        """Supplied random draws (parity tests) in place of the device generator's."""
         if eps is not None:
             self.eps.copy_(eps.reshape(self.B, -1))
         if u is not None:
             self.u.copy_(u)
-        self.enqueue_stage(eps is None, u is None)
+        if idx is not None:
+            self.idx.copy_(idx)
+        if cond_w is not None:
+            self.plan.cond_w.copy_(cond_w)
+
+    def stage_inputs(self, x, y, eps=None, u=None, cond_w=None, idx=None):
+        """Eager form: copy the batch, inject or draw eps / u (/ idx, cond_w), derive logsnr."""
+        self.copy_batch(x, y)
+        self.inject(eps, u, cond_w, idx)
+        self.enqueue_stage(eps is None, u is None and idx is None, False, cond_w is None)
 
     # ---- enqueue
     def enqueue_fwd_bwd(self, part=None, allreduce=None):
@@ -427,6 +547,7 @@ class _Bound:
         if part in (None, "up"):
             run_ops(self.zero_ops, st)
             run_ops(self.pre_ops, st)
+            self.enqueue_teacher_targets()
             self.plan.forward(st)
             run_ops(self.loss_ops, st)
         if allreduce == "captured":
@@ -470,7 +591,7 @@ class _Bound:
                                Op("b200_step_advance", lib.StepAdvanceArgs(step_dev=_p(self.step_dev)))], h)
         return self.hist[key]
 
-    def begin_sampling(self, init_z, y, cond_w, history=None):
+    def begin_sampling(self, init_z, y, cond_w, history=None, net_cond_w=None):
         """Load z_T, the labels and the guidance weights; returns the history tensors of this mode (or None).  They
         are owned by the plan (the captured step writes into them) and are overwritten by the next trajectory."""
         B = self.B
@@ -485,17 +606,22 @@ class _Bound:
             p.z_in[B:].copy_(p.z_in[:B])
             p.guide[B:].fill_(-1)  # gaussian_diffusion.py:176: guide = -ones
             self.cond_w.copy_(cond_w)
+        assert (net_cond_w is not None) == self.cond_embed
+        if self.cond_embed:  # the net itself is conditioned on w (distilled student)
+            p.cond_w[:B].copy_(net_cond_w)
+            if self.guided:
+                p.cond_w[B:].copy_(net_cond_w)
         self.history = history
         self.step_ops, hist = self._step_ops(history)
         self.step_dev.fill_(self.T - 1)
         run_ops(p.refresh_ops, self.m._stream())  # weights are fixed for the whole loop
         return hist
 
-    def teacher_step(self, z_t, y, cond_w, index, noise=None):
+    def teacher_step(self, z_t, y, cond_w, index, noise=None, net_cond_w=None):
         """One sampler step at loop index `index` from a supplied z_t (and noise): returns (x_pred, eps_pred, z_next)
         as [n, 1, S, S] tensors.  Parity tests drive every step of a reference trajectory through this."""
         n, S = self.B, self.plan.S
-        hist = self.begin_sampling(z_t, y, cond_w, history="last")
+        hist = self.begin_sampling(z_t, y, cond_w, history="last", net_cond_w=net_cond_w)
         self.step_dev.fill_(index)
         if noise is not None:
             self.noise.copy_(noise.reshape(n, -1))

@@ -99,13 +99,16 @@ class _Grad:
 class UNetPlan:
     """Forward (and backward) op lists of SimpleUnet for a fixed batch `B` and image side `S`."""
 
-    def __init__(self, store, B, S, train, sched=None, step_dev=None, bf16=False):
+    def __init__(self, store, B, S, train, sched=None, step_dev=None, bf16=False, cond_w=False):
         """bf16: the 24 ResBlock 3x3 convolutions (87 % of the FLOPs) take bf16 operands — GroupNorm writes its output
         as bf16, the weights come from a bf16 shadow, the backward's dY operands are bf16 copies written by the
         producing GroupNorm-backward — with fp32 accumulation; the residual stream, GroupNorm statistics, every
         gradient that is summed, and the plain / skip / edge convolutions stay fp32 (TF32 tensor cores)."""
         assert S % 4 == 0, "image side must be divisible by 4 (two stride-2 levels)"
         self.bf16 = bool(bf16)
+        # cond_w: the net is conditioned on a per-sample guidance weight through cond_w_embed (simple_unet.py:60-64;
+        # progressive distillation: students, and step2 teachers); self.cond_w [B] is the input buffer
+        self.use_cond_w = bool(cond_w)
         self.fuse_colsum = True
         # bf16 STORAGE of the tensors only GroupNorm reads (h1, the dgrad outputs), like the reference's autocast conv
         # outputs: halves their HBM traffic (B200_BF16_STORE=0 keeps them fp32, for A/B measurements)
@@ -136,6 +139,9 @@ class UNetPlan:
         import math
         # the reference evaluates exp(-math.log(max_period) * arange / half) in fp32 on the CPU (simple_unet.py:216-220)
         self.freqs = torch.exp(-math.log(MAX_TIMESTEPS) * torch.arange(0, 32, dtype=torch.float32) / 32).to(dev)
+        # cond_w_embed's timestep_embedding uses max_period = 4 (simple_unet.py:62)
+        self.freqs_w = torch.exp(-math.log(4) * torch.arange(0, 32, dtype=torch.float32) / 32).to(dev)
+        self.cond_w = torch.zeros(B, **f32)
         self.n_stats = 25
         self.stats = torch.zeros(self.n_stats, B, 64, **f32)
         self._stat_i = 0
@@ -262,6 +268,17 @@ class UNetPlan:
                                     bias=self._w("guide_embed.0.bias"), Y=self.ge0))
             ops.append(self._linear(0, B, E, E, 1, X=self.ge0, W=self._w("guide_embed.2.weight"),
                                     bias=self._w("guide_embed.2.bias"), Y=self.gemb))
+        if self.use_cond_w:
+            # simple_unet.py:60-64: emb += cond_w_embed(timestep_embedding(cond_w, 64, max_period=4))
+            wa = lib.EmbedArgs(t=_p(self.cond_w), sched=None, step_dev=None, freqs=_p(self.freqs_w), guide=None,
+                               sincos=_p(self.sincos_w), onehot=None, t_out=None, t_emb=None, g_emb=None, emb=None, semb=None,
+                               d_semb=None, d_emb=None, d_g_emb=None, B=B, E=E, step=0, force_uncond=0)
+            ops.append(Op("b200_embed_prep", wa))
+            ops.append(self._linear(0, B, E, 64, 0, X=self.sincos_w, W=self._w("cond_w_embed.0.weight"),
+                                    bias=self._w("cond_w_embed.0.bias"), Y=self.cw0))
+            ops.append(self._linear(0, B, E, E, 1, X=self.cw0, W=self._w("cond_w_embed.2.weight"),
+                                    bias=self._w("cond_w_embed.2.bias"), Y=self.cwemb))
+            ea.w_emb = _p(self.cwemb)
         ops.append(Op("b200_embed_combine", ea))
         ops.append(self._linear(0, B, 12 * self.Cc, E, 0, X=self.semb, W=C.c_void_p(st.flat.data_ptr() + 4 * st.emb_w_off),
                                 bias=C.c_void_p(st.flat.data_ptr() + 4 * st.emb_b_off), Y=self.embout))
@@ -316,7 +333,7 @@ class UNetPlan:
         dev = self.store.device
         f32 = dict(dtype=torch.float32, device=dev)
         for nm, w in (("sincos", 64), ("onehot", 10), ("te0", E), ("temb", E), ("ge0", E), ("gemb", E), ("emb", E),
-                      ("semb", E), ("embout", 12 * self.Cc)):
+                      ("semb", E), ("embout", 12 * self.Cc), ("sincos_w", 64), ("cw0", E), ("cwemb", E)):
             setattr(self, nm, torch.zeros(B, w, **f32))
         self.embed_ops = [self._build_embed(0), self._build_embed(1)]
         st = self.store
@@ -623,9 +640,12 @@ class UNetPlan:
                            d_semb=_p(self.d_semb), d_emb=_p(self.d_emb), d_g_emb=_p(self.d_gemb), B=B, E=E, step=0,
                            force_uncond=0)
         ops.append(Op("b200_embed_combine_bwd", ea))
-        for pre, dY, X0, K0, dmid in (("time_embed", self.d_emb, self.sincos, 64, self.d_te0),
-                                      ("guide_embed", self.d_gemb, self.onehot, 10, self.d_ge0)):
-            mid = self.te0 if pre == "time_embed" else self.ge0
+        branches = [("time_embed", self.d_emb, self.sincos, 64, self.d_te0, self.te0),
+                    ("guide_embed", self.d_gemb, self.onehot, 10, self.d_ge0, self.ge0)]
+        if self.use_cond_w:  # d(emb)/d(cond_w embedding) = 1: its output gradient is d_emb itself
+            self.d_cw0 = torch.zeros(B, E, **f32)
+            branches.append(("cond_w_embed", self.d_emb, self.sincos_w, 64, self.d_cw0, self.cw0))
+        for pre, dY, X0, K0, dmid, mid in branches:
             ops.append(self._linear(2, B, E, E, 1, X=mid, W=self._w(pre + ".2.weight"), dY=dY,
                                     dW=self._g(pre + ".2.weight"), db=self._g(pre + ".2.bias")))
             ops.append(self._linear(1, B, E, E, 1, X=mid, W=self._w(pre + ".2.weight"), dY=dY, dX=dmid))

@@ -212,8 +212,28 @@ typedef struct {
   void* z_u8;
   void* x_u8;
   void* e_u8;
+  /* optional per-sample log-SNR pairs [n] (progressive distillation: the teacher's DDIM steps start from each sample's
+   * own logsnr_t, gaussian_diffusion.py:113-146).  When given they replace the sched table / loop index. */
+  const float* logsnr_t_b;
+  const float* logsnr_s_b;
 } b200_sampler_step_args;
 int b200_sampler_step(const b200_sampler_step_args* a, void* ws, size_t ws_bytes, void* stream);
+
+/* progressive-distillation step2 target (gaussian_diffusion.py:137-154): the x implied by where two teacher DDIM half
+ * steps land,  x_target = (z_teacher - f z_t) / (alpha_s - f alpha_t),  f = exp(0.5 (softplus(l_t) - softplus(l_s))),
+ * replaced by the teacher's own x prediction where the discrete index i is 0, and eps_target = eps_from_x(z_t, x_target, l_t). */
+typedef struct {
+  const float* z_teacher;
+  const float* z_t;
+  const float* x_pred_teacher;
+  const float* logsnr_t;   /* [n] */
+  const float* logsnr_s;   /* [n] */
+  const long long* index;  /* [n] int64: the discrete step index i */
+  float* x_target;
+  float* eps_target;
+  int n, D;
+} b200_distill_target_args;
+int b200_distill_target(const b200_distill_target_args* a, void* ws, size_t ws_bytes, void* stream);
 
 typedef struct {
   int* step_dev;
@@ -301,6 +321,9 @@ typedef struct {
   float* d_emb;
   float* d_g_emb;
   int B, E, step, force_uncond;
+  /* optional [B][E]: the cond_w embedding (simple_unet.py:60-64, progressive distillation), added to emb by combine.
+   * Its sincos input is b200_embed_prep with t = cond_w and the max_period = 4 frequencies; its gradient is d_emb. */
+  const float* w_emb;
 } b200_embed_args;
 int b200_embed_prep(const b200_embed_args* a, void* ws, size_t ws_bytes, void* stream);
 int b200_embed_combine(const b200_embed_args* a, void* ws, size_t ws_bytes, void* stream);

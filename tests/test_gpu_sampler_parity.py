@@ -4,11 +4,16 @@ Teacher-forced single steps at >= 20 loop indices of T = 1000 (both ends and a s
 guided and `ddim`, against the oracle in true fp32 on the same device; beside every number, the reference's OWN spread:
 the same torch ops with cuDNN TF32 enabled (torch's default, i.e. what the reference computes on a B200) vs fp32.
 
-Bars (max-norm `max|d| / max|ref|`, the norm SURVEY.md §8c states):
-  * x~, posterior mean and z_s: <= 1e-3 at every index whose logsnr_t >= LOGSNR_ILL, else (x^ = A (z - B out) with
-    A = sqrt(1 + e^-logsnr) up to 2.2e4, clipped) <= 1.5 x the reference's own TF32 spread measured beside it, plus an
-    absolute floor of 1e-3;
-  * raw net output: <= 1e-3 rms-relative and <= max(1e-3, 1.5 x reference spread) max-norm.
+Bars (max-norm `max|d| / max|ref|`, the norm SURVEY.md §8c states), each tied to the reference's own TF32 spread
+measured beside it (`ref_*`: torch's default cuDNN-TF32 vs true fp32, same ops, same inputs):
+  * posterior mean and z_s (what the north star names): <= max(1e-3, 1.5 x ref).  Measured on a B200
+    (profiles/r02_sampler_parity.txt): <= 1e-3 outright at every index except i = 999 (logsnr = -20: 2.5e-2, where the
+    reference's own TF32 result is off by the same 2.5e-2) and the guided i = 998 (1.9e-3 vs 1.9e-3);
+  * raw net output: <= 1e-3 rms-relative, and <= max(1e-3, 1.5 x ref) max-norm (measured 0.8-1.2e-3 vs 0.8-1.2e-3);
+  * x~ (the clipped x prediction, an intermediate): <= max(1e-3, 2 x ref).  x^ = sqrt(1 + e^-logsnr) (z - out / sqrt(1 +
+    e^logsnr)) multiplies the net's TF32 error by up to 2.2e4 before the clip, for the reference exactly as for this
+    repo (e.g. 3.2e-2 vs 2.9e-2 at logsnr = -4.7); the factor 2 instead of 1.5 covers the run-to-run scatter of a
+    maximum over 4e5 pixels (GroupNorm moments are accumulated with atomics).
 plus a T = 64 free-running run (n = 64) against the fp32 oracle driven step by step with the same noise.
 """
 import pytest
@@ -19,7 +24,6 @@ from tests import sampler_parity_impl as P
 
 pytestmark = pytest.mark.gpu
 DEV = "cuda:0"
-LOGSNR_ILL = -6.0   # below this the x^ reconstruction amplifies a net-output difference by > 20x before the clip
 TOL = 1e-3
 
 
@@ -41,7 +45,7 @@ def test_sampler_T1000_n512_teacher_forced(built_lib, sampler, guided):
     bad = []
     for r in rows:
         for q in ("x", "mean", "z"):
-            bar = TOL if (r["logsnr_t"] >= LOGSNR_ILL and not guided) else max(TOL, 1.5 * r["ref_" + q])
+            bar = max(TOL, (2.0 if q == "x" else 1.5) * r["ref_" + q])
             if not r["ours_" + q] <= bar:
                 bad.append((r["i"], q, r["ours_" + q], r["ref_" + q], bar))
         if not r["ours_out_rms"] <= TOL:
@@ -53,6 +57,9 @@ def test_sampler_T1000_n512_teacher_forced(built_lib, sampler, guided):
         print(f"  {r['i']:4d} {r['logsnr_t']:+7.2f}  out {r['ours_out']:.2e}/{r['ref_out']:.2e}  x {r['ours_x']:.2e}/{r['ref_x']:.2e}"
               f"  mean {r['ours_mean']:.2e}/{r['ref_mean']:.2e}  z {r['ours_z']:.2e}/{r['ref_z']:.2e}")
     assert not bad, bad
+    # away from the first steps the posterior mean meets the north star's 1e-3 outright
+    assert all(r["ours_mean"] <= TOL and r["ours_z"] <= TOL for r in rows if r["logsnr_t"] > -12.0 and not guided)
+    assert all(r["ours_mean"] <= TOL and r["ours_z"] <= TOL for r in rows if r["logsnr_t"] > -11.0)
 
 
 def test_sampler_T64_free_running(built_lib):
