@@ -36,11 +36,12 @@
 namespace b200 {
 
 constexpr int kSBMax = 10;                // weight-tile ring: as deep as the strips leave room for (6 at W = 64, 8 at 28/14, 9 at 7)
-constexpr int kSS = 2;                    // strip double buffer
+constexpr int kSSMax = 6;                 // strip buffers: 2 for the 3x3 layers; flat (1x1) layers, which are HBM-bound and do one
+                                          // tap per 32 KB strip, keep up to 6 in flight (a.nss)
 constexpr int kBTile = 16384;             // 128 x 128 B
 constexpr int kStripBytes = 58 * 1024;    // >= (256 + 2*Wp + 2 rounded up to whole rows) * 128 B for W <= 64 (7 rows of 65)
 constexpr int kTileM = 256;               // positions per CTA tile (the N of one UMMA)
-constexpr int kStripTail = 256 + 2 * 512 * 4;  // barriers + the two position tables
+constexpr int kStripTail = 512 + 2 * 512 * 4;  // barriers + the two position tables
 constexpr int kStripSmem = 232448;             // the whole 227 KB opt-in maximum; strips first, the ring takes the rest
 
 struct StripK {
@@ -72,6 +73,7 @@ struct StripK {
   int sb;          // weight-tile ring depth (slots)
   int strip_alloc; // bytes between the two strip buffers (1 KB multiple)
   int split;       // filter tap before whose weight load the next chunk's strip is requested
+  int nss;         // strip buffers in flight (2; more for flat layers)
   int cl;          // launched as 2-CTA clusters: each weight tile is fetched once per pair (half by each CTA, multicast)
   int dbg;         // developer knobs (B200_STRIP_DBG): 1 = skip TMA loads (timing of the MMA issue path only)
 };
@@ -133,17 +135,18 @@ conv_strip_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   uint8_t* strip0 = smem;
+  const uint32_t kSS = static_cast<uint32_t>(a.nss);
   uint8_t* bring = smem + kSS * a.strip_alloc;
   const int slot_bytes = a.wpair ? 2 * kBTile : kBTile;
   uint64_t* bars = reinterpret_cast<uint64_t*>(bring + a.sb * slot_bytes);
-  uint64_t* s_full = bars;                // [kSS]
-  uint64_t* s_empty = s_full + kSS;       // [kSS]
-  uint64_t* b_full = s_empty + kSS;       // [kSBMax]
+  uint64_t* s_full = bars;                // [kSSMax]
+  uint64_t* s_empty = s_full + kSSMax;    // [kSSMax]
+  uint64_t* b_full = s_empty + kSSMax;    // [kSBMax]
   uint64_t* b_empty = b_full + kSBMax;    // [kSBMax]
   uint64_t* acc_full = b_empty + kSBMax;  // [2]
   uint64_t* acc_empty = acc_full + 2;  // [2]
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(acc_empty + 2);
-  int* tab = reinterpret_cast<int*>(bars + 32);  // 256 B past the barriers, 16 B-aligned: [2 acc stages][m[256], n[256]]
+  int* tab = reinterpret_cast<int*>(bars + 64);  // 512 B past the barriers, 16 B-aligned: [2 acc stages][m[256], n[256]]
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
@@ -165,7 +168,7 @@ conv_strip_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
       tma_prefetch_desc(&tmS2);
       tma_prefetch_desc(&tmW2);
     }
-    for (int s = 0; s < kSS; ++s) {
+    for (int s = 0; s < a.nss; ++s) {
       mbar_init(&s_full[s], 1);
       mbar_init(&s_empty[s], 1);
     }
@@ -257,6 +260,7 @@ conv_strip_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
         }
       };
       if (total_chunks > 0) load_strip(0);
+      int next_strip = 1;  // flat layers: the next strip to request (they run a.nss - 1 chunks ahead of the weights)
       for (int q = 0; q < total_chunks; ++q) {
         const int ch = q % CH;
         const bool is_skip = ch >= a.chunks;
@@ -264,7 +268,13 @@ conv_strip_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
         const int split = ntaps > 4 ? a.split : 0;
         const int tstep = a.wpair ? 2 : 1;
         for (int tap = 0; tap < ntaps; tap += tstep, bs = (bs + 1 == static_cast<uint32_t>(a.sb)) ? (bph ^= 1, 0u) : bs + 1) {
-          if (tap == split && q + 1 < total_chunks) load_strip(q + 1);
+          if (a.flat) {
+            // never blocks for long: strip next_strip reuses the buffer of chunk next_strip - nss < q, whose weights
+            // have already been issued
+            while (next_strip < total_chunks && next_strip < q + a.nss) load_strip(next_strip++);
+          } else if (tap == split && q + 1 < total_chunks) {
+            load_strip(q + 1);
+          }
           mbar_wait(&b_empty[bs], bph);
           if (a.dbg & 1) {
             mbar_arrive(&b_full[bs]);
@@ -768,7 +778,18 @@ int conv_strip_launch(const b200_conv_args* a, void* stream) {
       sb_cap = e ? atoi(e) : kSBMax;
     }
     k.wpair = wpair;
-    int sb = (kStripSmem - 1024 - kStripTail - kSS * k.strip_alloc) / (wpair ? 2 * kBTile : kBTile);
+    // flat (1x1) layers move 32 KB of activations per 16 KB weight tile and 4 MMAs: they are bound by how many bytes the
+    // CTA keeps in flight, so they get more strip buffers (measured with 2: 135 us for the 28x28 256->128 skip conv,
+    // 4.6 TB/s, against cuDNN's 99 us) and a shorter weight ring
+    static int nss_flat = -1;  // developer knob B200_STRIP_NSS_FLAT
+    if (nss_flat < 0) {
+      const char* e = getenv("B200_STRIP_NSS_FLAT");
+      nss_flat = e ? atoi(e) : 5;
+      if (nss_flat < 2) nss_flat = 2;
+      if (nss_flat > kSSMax) nss_flat = kSSMax;
+    }
+    k.nss = flat ? nss_flat : 2;
+    int sb = (kStripSmem - 1024 - kStripTail - k.nss * k.strip_alloc) / (wpair ? 2 * kBTile : kBTile);
     sb = sb > kSBMax ? kSBMax : sb;
     k.sb = sb > sb_cap ? sb_cap : sb;
     if (k.sb < 2) return fail_arg("conv_strip: no room for the weight ring");

@@ -85,6 +85,57 @@ __device__ __forceinline__ float lane_group_sum(float v, bool pair) {
   return v;
 }
 
+// Block reduction of per-channel partial sums without shared-memory atomics (atomicAdd on a shared float compiles to a
+// compare-and-swap spin loop — ATOMS.CAST.SPIN — and sixteen warps hammering the same 2*CS words made the reduction a
+// visible share of the backward's instruction count; ncu: 1536 instructions per warp for 6 loop iterations).
+// Every warp writes its lane-reduced values to its own row of `wred`, a barrier, then 2*CS threads add the rows up in
+// a fixed order (so the per-CTA sums are also reproducible run to run).
+//   in : dg[4], db[4] — this thread's sums of du*xhat and du for its 4 channels (already reduced over the warp's lanes
+//        that share the channel quad: lanes 0..L-1 hold the result)
+//   out: chan[0..CS) = sum du*xhat per channel, chan[CS..2CS) = sum du per channel; gsum = the same times gamma
+// and dgamma / dbeta receive one global atomic per channel.  Ends with a barrier.
+template <int CS, int NW>
+__device__ __forceinline__ void gn_bwd_block_sums(const float (&dg)[4], const float (&db)[4], int tid, int lane, int l,
+                                                  float (*wred)[2 * CS], float* chan, float* gsum,
+                                                  const float* __restrict__ gamma, int c0, float* __restrict__ dgamma,
+                                                  float* __restrict__ dbeta) {
+  constexpr int L = CS / 4;
+  if (lane < L) {
+    float4* w = reinterpret_cast<float4*>(&wred[tid >> 5][0]);
+    w[l] = make_float4(dg[0], dg[1], dg[2], dg[3]);
+    w[L + l] = make_float4(db[0], db[1], db[2], db[3]);
+  }
+  __syncthreads();
+  if (tid < 2 * CS) {
+    float v = 0.f;
+#pragma unroll
+    for (int w = 0; w < NW; ++w) v += wred[w][tid];
+    chan[tid] = v;
+    const int ch = tid < CS ? tid : tid - CS;
+    gsum[tid] = v * __ldg(gamma + c0 + ch);
+    atomicAdd(tid < CS ? &dgamma[c0 + ch] : &dbeta[c0 + ch], v);
+  }
+  __syncthreads();
+}
+// fused column sums of dx: same scheme, CS values per warp
+template <int CS, int NW>
+__device__ __forceinline__ void gn_bwd_colsum(float (&ca)[4], int tid, int lane, int l, float (*wred)[2 * CS], int n, int c0,
+                                              const GnColsum& cs) {
+  constexpr int L = CS / 4;
+#pragma unroll
+  for (int j = 0; j < 4; ++j) ca[j] = lane_group_sum<L>(ca[j], false);
+  if (lane < L) reinterpret_cast<float4*>(&wred[tid >> 5][0])[l] = make_float4(ca[0], ca[1], ca[2], ca[3]);
+  __syncthreads();
+  if (tid < CS) {
+    float v = 0.f;
+#pragma unroll
+    for (int w = 0; w < NW; ++w) v += wred[w][tid];
+    if (cs.per_sample) atomicAdd(&cs.per_sample[static_cast<size_t>(n) * cs.ps_ld + c0 + tid], v);
+    if (cs.total1) atomicAdd(&cs.total1[c0 + tid], v);
+    if (cs.total2) atomicAdd(&cs.total2[c0 + tid], v);
+  }
+}
+
 // ---------------------------------------------------------------------------------------------------- fused forward
 // grid = N * (C / CS); block 256; dynamic smem = HW * CS * 4 bytes.
 template <int CS, int kGnThreads>
@@ -92,7 +143,7 @@ __global__ void __launch_bounds__(kGnThreads)
 gn_fwd_fused_kernel(GnSrc s, float* __restrict__ stats, const float* __restrict__ gamma, const float* __restrict__ beta,
                     float* __restrict__ y, float eps, int silu, int tf32) {
   extern __shared__ float4 gn_smem[];
-  __shared__ float red[16];
+  __shared__ float fred[2][kGnThreads / 32][8];  // [sum | centred squares][warp][group of the slice]
   constexpr int L = CS / 4;  // float4 lanes per pixel of the slice
   const int slices = s.C / CS;
   const int n = blockIdx.x / slices;
@@ -113,7 +164,6 @@ gn_fwd_fused_kernel(GnSrc s, float* __restrict__ stats, const float* __restrict_
     src = s.x2 + (c - s.C1);
     ld = s.ld2;
   }
-  if (tid < 16) red[tid] = 0.f;
   src += static_cast<size_t>(n) * s.HW * ld;
   for (int idx = tid; idx < total; idx += kGnThreads) cp_async16(&gn_smem[idx], src + static_cast<size_t>(idx / L) * ld);
   const float4 ga = __ldg(reinterpret_cast<const float4*>(gamma + c));  // in flight with the slice
@@ -129,9 +179,12 @@ gn_fwd_fused_kernel(GnSrc s, float* __restrict__ stats, const float* __restrict_
     sum += (v.x + v.y) + (v.z + v.w);
   }
   sum = lane_group_sum<L>(sum, pair);
-  if (leader) atomicAdd(&red[gl], sum);
+  if (leader) fred[0][tid >> 5][gl] = sum;  // one slot per (warp, group): no shared-memory atomics (CAS spin loops)
   __syncthreads();
-  const float mean = red[gl] * inv_cnt;
+  float tot = 0.f;
+#pragma unroll
+  for (int w = 0; w < kGnThreads / 32; ++w) tot += fred[0][w][gl];
+  const float mean = tot * inv_cnt;
   float sq = 0.f;
   for (int idx = tid; idx < total; idx += kGnThreads) {
     const float4 v = gn_smem[idx];
@@ -139,9 +192,12 @@ gn_fwd_fused_kernel(GnSrc s, float* __restrict__ stats, const float* __restrict_
     sq += (a * a + b * b) + (cc * cc + d * d);
   }
   sq = lane_group_sum<L>(sq, pair);
-  if (leader) atomicAdd(&red[8 + gl], sq);
+  if (leader) fred[1][tid >> 5][gl] = sq;
   __syncthreads();
-  const float rstd = rsqrtf(red[8 + gl] * inv_cnt + eps);
+  tot = 0.f;
+#pragma unroll
+  for (int w = 0; w < kGnThreads / 32; ++w) tot += fred[1][w][gl];
+  const float rstd = rsqrtf(tot * inv_cnt + eps);
   if (tid < L && (!pair || !(tid & 1)))
     *reinterpret_cast<float2*>(stats + (static_cast<size_t>(n) * 32 + c / cpg) * 2) = make_float2(mean, rstd);
   const float4 sc = make_float4(rstd * ga.x, rstd * ga.y, rstd * ga.z, rstd * ga.w);
@@ -186,9 +242,9 @@ gn_bwd_fused_kernel(GnSrc s, const float* __restrict__ stats, const float* __res
                     float* __restrict__ dgamma, float* __restrict__ dbeta, int silu, int round_dx,
                     uint16_t* __restrict__ dxb, int dxb_c, GnColsum cs) {
   extern __shared__ float4 gn_smem[];
-  __shared__ float red[16];
+  __shared__ __align__(16) float wred[kGnThreads / 32][2 * CS];
   __shared__ float chan[2 * CS];
-  __shared__ float csum[CS];
+  __shared__ float gsum[2 * CS];
   constexpr int L = CS / 4;
   const int slices = s.C / CS;
   const int n = blockIdx.x / slices;
@@ -214,9 +270,6 @@ gn_bwd_fused_kernel(GnSrc s, const float* __restrict__ stats, const float* __res
   src += static_cast<size_t>(n) * s.HW * ld;
   const size_t row0 = static_cast<size_t>(n) * s.HW;
   const float* dsrc = dy + row0 * s.C + c;
-  if (tid < 16) red[tid] = 0.f;
-  if (tid < 2 * CS) chan[tid] = 0.f;
-  if (tid < CS) csum[tid] = 0.f;
   for (int idx = tid; idx < total; idx += kGnThreads) {
     const size_t pix = idx / L;
     cp_async16(&xs[idx], src + pix * ld);
@@ -258,37 +311,21 @@ gn_bwd_fused_kernel(GnSrc s, const float* __restrict__ stats, const float* __res
     xs[idx] = make_float4(xh[0], xh[1], xh[2], xh[3]);  // own slot: re-read by this thread only
     ds[idx] = make_float4(du[0], du[1], du[2], du[3]);
   }
-  // sum(du * gamma) and sum(du * gamma * xhat) over this thread's elements follow from its per-channel sums
-  // (gamma is constant along the pixels): three instructions per element less in the loop above
-#pragma unroll
-  for (int j = 0; j < 4; ++j) {
-    s1 = fmaf(ga[j], db[j], s1);
-    s2 = fmaf(ga[j], dg[j], s2);
-  }
-  const bool pair = (cpg == 8);
-  s1 = lane_group_sum<L>(s1, pair);
-  s2 = lane_group_sum<L>(s2, pair);
 #pragma unroll
   for (int j = 0; j < 4; ++j) {
     dg[j] = lane_group_sum<L>(dg[j], false);
     db[j] = lane_group_sum<L>(db[j], false);
   }
-  if (lane < L) {
-    if (!pair || !(lane & 1)) {
-      atomicAdd(&red[gl], s1);
-      atomicAdd(&red[8 + gl], s2);
-    }
-#pragma unroll
-    for (int j = 0; j < 4; ++j) {
-      atomicAdd(&chan[l * 4 + j], dg[j]);
-      atomicAdd(&chan[CS + l * 4 + j], db[j]);
-    }
+  gn_bwd_block_sums<CS, kGnThreads / 32>(dg, db, tid, lane, l, wred, chan, gsum, gamma, c0, dgamma, dbeta);
+  // sum(du * gamma) and sum(du * gamma * xhat) over the group follow from the per-channel sums (gamma is constant along
+  // the pixels): cpg shared-memory words each
+  s1 = s2 = 0.f;
+  for (int k = 0; k < cpg; ++k) {
+    s2 += gsum[gl * cpg + k];
+    s1 += gsum[CS + gl * cpg + k];
   }
-  __syncthreads();
-  if (tid < CS) atomicAdd(&dgamma[c0 + tid], chan[tid]);
-  else if (tid < 2 * CS) atomicAdd(&dbeta[c0 + tid - CS], chan[tid]);
   const float inv_cnt = 1.0f / static_cast<float>(s.HW * cpg);
-  const float m1 = red[gl] * inv_cnt, m2 = red[8 + gl] * inv_cnt;
+  const float m1 = s1 * inv_cnt, m2 = s2 * inv_cnt;
   const bool has_add = c < add_c;
   const float* a1 = (has_add && add1) ? add1 + row0 * add1_ld + c : nullptr;
   const float* a2 = (has_add && add2) ? add2 + row0 * add2_ld + c : nullptr;
@@ -323,19 +360,7 @@ gn_bwd_fused_kernel(GnSrc s, const float* __restrict__ stats, const float* __res
   // timestep-embedding broadcast add): this CTA owns all pixels of (n, channel slice)
   if (cs.c > 0 && c0 < cs.c) {  // uniform per CTA
     float ca[4] = {cacc.x, cacc.y, cacc.z, cacc.w};
-#pragma unroll
-    for (int j = 0; j < 4; ++j) ca[j] = lane_group_sum<L>(ca[j], false);
-    if (lane < L) {
-#pragma unroll
-      for (int j = 0; j < 4; ++j) atomicAdd(&csum[l * 4 + j], ca[j]);
-    }
-    __syncthreads();
-    if (tid < CS) {
-      const float v = csum[tid];
-      if (cs.per_sample) atomicAdd(&cs.per_sample[static_cast<size_t>(n) * cs.ps_ld + c0 + tid], v);
-      if (cs.total1) atomicAdd(&cs.total1[c0 + tid], v);
-      if (cs.total2) atomicAdd(&cs.total2[c0 + tid], v);
-    }
+    gn_bwd_colsum<CS, kGnThreads / 32>(ca, tid, lane, l, wred, n, c0, cs);
   }
 }
 
@@ -371,7 +396,7 @@ __global__ void __launch_bounds__(T)
 gn_fwd_bfx_kernel(GnSrc s, float* __restrict__ stats, const float* __restrict__ gamma, const float* __restrict__ beta,
                   float* __restrict__ y, float eps, int silu, int tf32) {
   extern __shared__ float4 gn_smem[];
-  __shared__ float red[16];
+  __shared__ float fred[2][T / 32][8];  // [sum | centred squares][warp][group of the slice]
   const uint8_t* raw = reinterpret_cast<const uint8_t*>(gn_smem);
   constexpr int L = CS / 4;
   const int slices = s.C / CS;
@@ -386,7 +411,6 @@ gn_fwd_bfx_kernel(GnSrc s, float* __restrict__ stats, const float* __restrict__ 
   const int ld = first ? s.ld1 : s.ld2;
   const uint16_t* base = reinterpret_cast<const uint16_t*>(first ? s.x : s.x2) + (first ? c0 : c0 - s.C1) +
                          static_cast<size_t>(n) * s.HW * ld;
-  if (tid < 16) red[tid] = 0.f;
   gn_stage<CS, 2, T>(reinterpret_cast<uint8_t*>(gn_smem), base, ld, s.HW, tid);
   const float4 ga = __ldg(reinterpret_cast<const float4*>(gamma + c));  // in flight with the slice
   const float4 be = __ldg(reinterpret_cast<const float4*>(beta + c));
@@ -401,9 +425,12 @@ gn_fwd_bfx_kernel(GnSrc s, float* __restrict__ stats, const float* __restrict__ 
     sum += (v.x + v.y) + (v.z + v.w);
   }
   sum = lane_group_sum<L>(sum, pair);
-  if (leader) atomicAdd(&red[gl], sum);
+  if (leader) fred[0][tid >> 5][gl] = sum;  // one slot per (warp, group): no shared-memory atomics (CAS spin loops)
   __syncthreads();
-  const float mean = red[gl] * inv_cnt;
+  float tot = 0.f;
+#pragma unroll
+  for (int w = 0; w < T / 32; ++w) tot += fred[0][w][gl];
+  const float mean = tot * inv_cnt;
   float sq = 0.f;
   for (int idx = tid; idx < total; idx += T) {
     const float4 v = gn_elem<2>(raw, idx);
@@ -411,9 +438,12 @@ gn_fwd_bfx_kernel(GnSrc s, float* __restrict__ stats, const float* __restrict__ 
     sq += (a * a + b * b) + (cc * cc + d * d);
   }
   sq = lane_group_sum<L>(sq, pair);
-  if (leader) atomicAdd(&red[8 + gl], sq);
+  if (leader) fred[1][tid >> 5][gl] = sq;
   __syncthreads();
-  const float rstd = rsqrtf(red[8 + gl] * inv_cnt + eps);
+  tot = 0.f;
+#pragma unroll
+  for (int w = 0; w < T / 32; ++w) tot += fred[1][w][gl];
+  const float rstd = rsqrtf(tot * inv_cnt + eps);
   if (tid < L && (!pair || !(tid & 1)))
     *reinterpret_cast<float2*>(stats + (static_cast<size_t>(n) * 32 + c / cpg) * 2) = make_float2(mean, rstd);
   const float4 sc = make_float4(rstd * ga.x, rstd * ga.y, rstd * ga.z, rstd * ga.w);
@@ -447,9 +477,9 @@ gn_bwd_raw_kernel(GnSrc s, const float* __restrict__ stats, const float* __restr
                   float* __restrict__ dgamma, float* __restrict__ dbeta, int silu, int round_dx,
                   uint16_t* __restrict__ dxb, int dxb_c, GnColsum cs) {
   extern __shared__ float4 gn_smem[];
-  __shared__ float red[16];
+  __shared__ __align__(16) float wred[T / 32][2 * CS];
   __shared__ float chan[2 * CS];
-  __shared__ float csum[CS];
+  __shared__ float gsum[2 * CS];
   constexpr int L = CS / 4;
   const int slices = s.C / CS;
   const int n = blockIdx.x / slices;
@@ -467,9 +497,6 @@ gn_bwd_raw_kernel(GnSrc s, const float* __restrict__ stats, const float* __restr
   const uint8_t* xbase = reinterpret_cast<const uint8_t*>(first ? s.x : s.x2) +
                          (static_cast<size_t>(first ? c0 : c0 - s.C1) + row0 * ld) * XB;
   const uint8_t* dbase = static_cast<const uint8_t*>(dy) + (row0 * s.C + c0) * DB;
-  if (tid < 16) red[tid] = 0.f;
-  if (tid < 2 * CS) chan[tid] = 0.f;
-  if (tid < CS) csum[tid] = 0.f;
   gn_stage<CS, XB, T>(xraw, xbase, ld, s.HW, tid);
   gn_stage<CS, DB, T>(draw, dbase, s.C, s.HW, tid);
   if (c0 < add_c) {  // add-tensor rows of phase 2 into L2 now
@@ -504,34 +531,17 @@ gn_bwd_raw_kernel(GnSrc s, const float* __restrict__ stats, const float* __restr
     }
   }
 #pragma unroll
-  for (int j = 0; j < 4; ++j) {  // gamma is constant along the pixels: the group sums follow from the channel sums
-    s1 = fmaf(ga[j], db[j], s1);
-    s2 = fmaf(ga[j], dg[j], s2);
-  }
-  const bool pair = (cpg == 8);
-  s1 = lane_group_sum<L>(s1, pair);
-  s2 = lane_group_sum<L>(s2, pair);
-#pragma unroll
   for (int j = 0; j < 4; ++j) {
     dg[j] = lane_group_sum<L>(dg[j], false);
     db[j] = lane_group_sum<L>(db[j], false);
   }
-  if (lane < L) {
-    if (!pair || !(lane & 1)) {
-      atomicAdd(&red[gl], s1);
-      atomicAdd(&red[8 + gl], s2);
-    }
-#pragma unroll
-    for (int j = 0; j < 4; ++j) {
-      atomicAdd(&chan[l * 4 + j], dg[j]);
-      atomicAdd(&chan[CS + l * 4 + j], db[j]);
-    }
+  gn_bwd_block_sums<CS, T / 32>(dg, db, tid, lane, l, wred, chan, gsum, gamma, c0, dgamma, dbeta);
+  for (int k = 0; k < cpg; ++k) {  // gamma is constant along the pixels: the group sums follow from the channel sums
+    s2 += gsum[gl * cpg + k];
+    s1 += gsum[CS + gl * cpg + k];
   }
-  __syncthreads();
-  if (tid < CS) atomicAdd(&dgamma[c0 + tid], chan[tid]);
-  else if (tid < 2 * CS) atomicAdd(&dbeta[c0 + tid - CS], chan[tid]);
   const float inv_cnt = 1.0f / static_cast<float>(s.HW * cpg);
-  const float m1 = red[gl] * inv_cnt, m2 = red[8 + gl] * inv_cnt;
+  const float m1 = s1 * inv_cnt, m2 = s2 * inv_cnt;
   const bool has_add = c < add_c;
   const float* a1 = (has_add && add1) ? add1 + row0 * add1_ld + c : nullptr;
   const float* a2 = (has_add && add2) ? add2 + row0 * add2_ld + c : nullptr;
@@ -567,21 +577,8 @@ gn_bwd_raw_kernel(GnSrc s, const float* __restrict__ stats, const float* __restr
     if (dst) *reinterpret_cast<float4*>(dst + pix * s.C) = o;
     cacc[0] += o.x; cacc[1] += o.y; cacc[2] += o.z; cacc[3] += o.w;
   }
-  if (cs.c > 0 && c0 < cs.c) {  // uniform per CTA
-#pragma unroll
-    for (int j = 0; j < 4; ++j) cacc[j] = lane_group_sum<L>(cacc[j], false);
-    if (lane < L) {
-#pragma unroll
-      for (int j = 0; j < 4; ++j) atomicAdd(&csum[l * 4 + j], cacc[j]);
-    }
-    __syncthreads();
-    if (tid < CS) {
-      const float v = csum[tid];
-      if (cs.per_sample) atomicAdd(&cs.per_sample[static_cast<size_t>(n) * cs.ps_ld + c0 + tid], v);
-      if (cs.total1) atomicAdd(&cs.total1[c0 + tid], v);
-      if (cs.total2) atomicAdd(&cs.total2[c0 + tid], v);
-    }
-  }
+  if (cs.c > 0 && c0 < cs.c)  // uniform per CTA
+    gn_bwd_colsum<CS, T / 32>(cacc, tid, lane, l, wred, n, c0, cs);
 }
 
 // ---------------------------------------------------------------------------------------------------- streaming path
