@@ -263,6 +263,81 @@ def run_gpu_torch_baseline(batch, variants="ref_amp_fp16,tf32,bf16", steps=5, sa
         return {"error": repr(e)[:300]}
 
 
+def run_config3(args, rank, world, local_rank):
+    """BASELINE.json configs[3]: 65 536 images x 1000 ancestral steps, sharded by batch over the ranks, no communication
+    (dist.sample_sharded; every rank walks its shard in chunks of --sample-chunk images so the activations of one chunk
+    are what is resident).  value = whole-job sampled images/s, device time, max over ranks."""
+    import torch.distributed as dist
+    torch.cuda.set_device(local_rank)
+    dev = f"cuda:{local_rank}"
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device(dev))
+    import __graft_entry__ as ge
+    if local_rank == 0:
+        ge.build()
+    if world > 1:
+        dist.barrier()
+    from generative_models_b200 import dist as bdist
+    from generative_models_b200 import lib
+    from generative_models_b200.model import DiffusionModelB200, default_G
+    torch.manual_seed(0)
+    T, total = args.sample_steps, args.config3_images
+    m = DiffusionModelB200(default_G(device=dev, mean_type="eps", sampler="noisy", timesteps=T, graph=1, precision=args.precision))
+    gen = torch.Generator().manual_seed(1)
+    for k, p in m.net.named_parameters():
+        if ".out_layers.3." in k:
+            p.data.copy_((torch.randn(p.shape, generator=gen) * 0.02).to(dev))
+    lo, hi = bdist.shard_range(total, rank, world)
+    chunk = min(args.sample_chunk, hi - lo)
+    clocks = ClockSampler(local_rank if rank == 0 else -1)
+    clocks.start()
+    b = m._plan(chunk, "sample")  # warm-up: eager, capture, replay
+    b.begin_sampling(torch.randn(chunk, 1, 28, 28, device=dev), torch.zeros(chunk, dtype=torch.long, device=dev), None)
+    for _ in range(3):
+        b.run_graphed(b.enqueue_sampler_step, ("sampler_step", None))
+    torch.cuda.synchronize()
+    if world > 1:
+        dist.barrier()
+    l0 = lib.launch_count()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    t0 = time.time()
+    e0.record()
+    done, finite = lo, True
+    while done < hi:
+        n_ = min(chunk, hi - done)
+        n_pad = chunk  # a ragged last chunk is padded to the captured plan's size; its first n_ images are kept
+        labels = (torch.arange(done, done + n_pad, device=dev) % 10)
+        init = torch.randn(n_pad, 1, 28, 28, device=dev)
+        z = m._sample_loop(init, labels, None)[0][:n_]
+        finite = finite and bool(torch.isfinite(z).all().item())
+        done += n_
+    e1.record()
+    torch.cuda.synchronize()
+    if world > 1:
+        dist.barrier()
+    t1 = time.time()
+    clocks.stop()
+    ms = e0.elapsed_time(e1)
+    if world > 1:
+        t = torch.tensor([ms], device=dev, dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms = t.item()
+    if rank == 0:
+        line = {"metric": "ddpm_sampled_images_per_sec", "value": total / (ms / 1e3), "unit": UNIT, "n_gpus": world,
+                "steps": T, "warmup": 3, "ms_per_step": ms / (T * ((hi - lo + chunk - 1) // chunk)), "higher_is_better": True,
+                "scaling": "strong", "vs_baseline": None, "dtype": args.precision, "data": "synthetic",
+                "config": {"workload": f"configs[3]: {total} images x {T} ancestral steps (unguided), sharded by batch over "
+                                       f"{world} GPU(s), chunks of {chunk} images, no communication",
+                           "images_per_gpu": hi - lo, "parallelism": f"dp{world} (independent shards)", "cuda_graph": True},
+                "seconds": ms / 1e3, "wall_seconds": t1 - t0, "finite": finite,
+                "tensor_tflops_per_gpu": (hi - lo) * T * FWD_FLOP_PER_IMG / (ms / 1e3) / 1e12,
+                "gpu_launches": None, "clocks": clocks.summary(t0, t1)}
+        print(json.dumps(line), file=RESULT_OUT, flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+    return 0
+
+
 def run_ours(args, rank, world, local_rank):
     import torch.distributed as dist
     torch.cuda.set_device(local_rank)
@@ -554,7 +629,7 @@ def run_ours(args, rank, world, local_rank):
 
     # ---- comparison arms measured beside it: the unmodified reference on the host cores (bounded sample) and, on this
     # same GPU, in torch eager (cuDNN / cuBLAS)
-    cpu = run_cpu_reference(args.cpu_steps, 1, args.cpu_batch, 16, min(args.cpu_sample_steps, 6), T) if world == 1 else None
+    cpu = run_cpu_reference(args.cpu_steps, 1, args.cpu_batch, 16, min(args.cpu_sample_steps, 6), T) if (world == 1 and args.config == 1) else None
     if cpu and "error" not in cpu:
         cpu_baseline = {"value": cpu["train"]["img_s"], "unit": UNIT, "cores": cpu["threads"], "kind": "reference",
                         "sample": cpu_sample_string(cpu, args.cpu_batch),
@@ -562,14 +637,15 @@ def run_ours(args, rank, world, local_rank):
                         "sampling_img_s_guided": ((cpu.get("sampling") or {}).get("guided") or {}).get("img_s_1000_steps")}
     else:
         cpu_baseline = {"value": None, "unit": UNIT, "cores": os.cpu_count(), "kind": "reference",
-                        "sample": "not run" if world > 1 else "failed: " + (cpu or {}).get("error", "")[-200:]}
+                        "sample": "not run (only at N=1 of the default config)" if cpu is None else "failed: " + cpu.get("error", "")[-200:]}
     gpu_base = run_gpu_torch_baseline(B) if (world == 1 and args.gpu_baseline) else None
 
     line = {
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": K, "warmup": W, "settle_steps": settle_steps,
-        "ms_per_step": ms / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": args.precision,
-        "data": "synthetic",
-        "config": {"workload": workload_string(args),
+        "ms_per_step": ms / K, "higher_is_better": True, "scaling": "strong" if args.config == 2 else "weak",
+        "vs_baseline": None, "dtype": args.precision, "data": "synthetic",
+        "config": {"workload": workload_string(args) if args.config != 2 else
+                   f"configs[2]: DDPM data-parallel training, bf16 ResBlock convs, GLOBAL batch {B * world} = {B}/GPU x {world}",
                    "global_batch": B * world, "mean_type": "eps", "sampler": "noisy", "timesteps": T,
                    "parallelism": f"dp{world}", "cuda_graph": True,
                    "l2": "per-step working set (~22 MB/img of activations) >> 126 MB L2; no flush needed",
@@ -632,15 +708,27 @@ def main():
     ap.add_argument("--precision", default="tf32", choices=["tf32", "bf16"],
                     help="tensor-core operand type of the ResBlock convs (tf32 = configs[1], the headline)")
     ap.add_argument("--bf16-leg", type=int, default=1, help="also time the bf16 configuration (configs[2]) beside the headline")
+    ap.add_argument("--config", type=int, default=1, choices=[1, 2, 3],
+                    help="BASELINE.json configs[k]: 1 = batch 512/GPU fp32/TF32 (the default bench line); 2 = bf16 data-parallel "
+                         "training at GLOBAL batch 4096 (4096/N per GPU, strong scaling); 3 = 65536 images x 1000 steps sharded")
+    ap.add_argument("--config3-images", type=int, default=65536)
+    ap.add_argument("--sample-chunk", type=int, default=8192, help="configs[3]: images per resident sampling plan")
     args = ap.parse_args()
     rank, world, local_rank = env_int("RANK", 0), env_int("WORLD_SIZE", 1), env_int("LOCAL_RANK", 0)
     if args.impl == "reference":
         return run_reference(args, rank)
+    nworld = world if world > 1 else max(1, args.gpus)
+    if args.config == 2:
+        args.precision, args.batch = "bf16", 4096 // nworld
+        args.bf16_leg = args.small_n = args.gpu_baseline = args.sample_api = 0
+        args.sample_n = 0
     if world == 1 and args.gpus > 1:
         # convenience: re-launch under torchrun, one rank per GPU
         cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={args.gpus}",
                "--master-addr", "127.0.0.1", "--master-port", "29511", os.path.abspath(__file__)] + sys.argv[1:]
         return subprocess.call(cmd, stdout=RESULT_OUT)
+    if args.config == 3:
+        return run_config3(args, rank, world, local_rank)
     return run_ours(args, rank, world, local_rank)
 
 

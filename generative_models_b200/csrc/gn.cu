@@ -914,6 +914,14 @@ extern "C" int b200_gn_fwd(const b200_gn_args* a, void* ws, size_t ws_bytes, voi
   return after_launch("gn_apply_kernel");
 }
 
+// Bytes of workspace b200_gn_bwd wants for these arguments (SURVEY.md §8b's `b200_<op>_workspace`): the streaming path
+// (slices that do not fit in shared memory) reduces into N*64 floats; the shared-memory-resident kernels need none, but
+// which path a shape takes depends on developer knobs, so the upper bound is reported for every shape.
+extern "C" size_t b200_gn_bwd_workspace(const b200_gn_bwd_args* b) {
+  if (!b || b->fwd.N <= 0) return 0;
+  return static_cast<size_t>(b->fwd.N) * 64 * sizeof(float);
+}
+
 extern "C" int b200_gn_bwd(const b200_gn_bwd_args* b, void* ws, size_t ws_bytes, void* stream) {
   if (!b) return fail_arg("gn_bwd: null args");
   GnSrc s;

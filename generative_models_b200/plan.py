@@ -571,7 +571,9 @@ class UNetPlan:
                     out_dtype=1)))
         self.pool_dcat = _Pool(dev, recycle=False)  # concat gradients live until the Down path consumes their 2nd half
         self.bfpool = _Pool(dev, recycle=False)     # bf16 copies of block-output gradients (live across blocks)
-        self.gn_ws = torch.zeros(B * 64, **f32)
+        # one workspace shared by every b200_gn_bwd launch of the plan, sized by the library's own query
+        probe = lib.GnBwdArgs(fwd=lib.GnArgs(N=B, HW=S * S, C1=128, C2=128))
+        self.gn_ws = torch.zeros(max(1, lib.load().b200_gn_bwd_workspace(C.byref(probe)) // 4), **f32)
         self.d_embout = torch.zeros(B, 12 * self.Cc, **f32)
         for nm in ("d_semb", "d_emb", "d_gemb", "d_te0", "d_ge0"):
             setattr(self, nm, torch.zeros(B, E, **f32))

@@ -23,7 +23,7 @@ def sampler_table(num_steps, device):
     """[T, 2] fp32 table, row i = (logsnr_t, logsnr_s) of loop index i, built like gaussian_diffusion.py:288-290
     (int64 index on the target device, `+ 1.0`, `/ num_steps`, then the schedule).  The reference does this on 0-dim
     tensors one step at a time; the same elementwise kernels applied to an arange give the same bits per element
-    (tests/test_schedule.py checks it against the one-at-a-time form)."""
+    (tests/test_cpu_host.py::test_sampler_table_matches_scalar_form_and_fixture checks it against the one-at-a-time form)."""
     i = torch.arange(num_steps, device=device)
     lt = logsnr_schedule_cosine((i + 1.0) / num_steps)
     ls = logsnr_schedule_cosine(i / num_steps)

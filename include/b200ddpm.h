@@ -152,6 +152,9 @@ typedef struct {
   int dy_dtype; /* 0 = fp32, 1 = dy holds bf16.  dx may be NULL when only dx_bf16 (and the column sums) are wanted. */
 } b200_gn_bwd_args;
 int b200_gn_bwd(const b200_gn_bwd_args* a, void* ws, size_t ws_bytes, void* stream);
+/* bytes of workspace b200_gn_bwd needs for these arguments (the only entry point that takes one; every other call
+ * accepts ws = NULL).  The caller allocates it (PyTorch) and may share one buffer between all launches of a stream. */
+size_t b200_gn_bwd_workspace(const b200_gn_bwd_args* a);
 
 /* ------------------------------------------------------------------ diffusion math around the net (D = pixels/img)
  * mean_type: 0 = 'eps', 1 = 'x', 2 = 'v' (gaussian_diffusion.py:55-63).  sampler: 0 = 'ddim', 1 = 'noisy'. */
