@@ -259,8 +259,36 @@ conv_strip_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
           }
         }
       };
+      if (a.flat && !a.skip_chunks && !a.cl && !(a.dbg & 1)) {
+        // 1x1 layers: one 32 KB strip and one 16 KB weight tile per chunk, four MMAs — the CTA is bound by the bytes it
+        // keeps in flight, so strips and weight tiles are two independent streams, each issued as far ahead as its own
+        // buffers allow (polling: a blocking wait on one stream would hold back the other)
+        int si = 0, wi = 0;
+        while (si < total_chunks || wi < total_chunks) {
+          bool did = false;
+          if (si < total_chunks && mbar_try_wait(&s_empty[si % kSS], ((si / kSS) & 1) ^ 1)) {
+            load_strip(si++);
+            did = true;
+          }
+          if (wi < total_chunks && mbar_try_wait(&b_empty[wi % a.sb], ((wi / a.sb) & 1) ^ 1)) {
+            const uint32_t slot = wi % a.sb;
+            const int ch = wi % CH;
+            mbar_expect_tx(&b_full[slot], slot_bytes);
+            uint8_t* sB = bring + slot * slot_bytes;
+            if (a.mode == 0) {
+              tma_load_2d(sB, &tmB, &b_full[slot], ch * CK, 0);
+            } else {
+#pragma unroll
+              for (int jj = 0; jj < 128 / CK; ++jj)
+                tma_load_2d(sB + jj * (CK * 128), &tmB, &b_full[slot], a.n_off + jj * CK, ch * CK);
+            }
+            ++wi;
+            did = true;
+          }
+          if (!did) __nanosleep(20);
+        }
+      } else {
       if (total_chunks > 0) load_strip(0);
-      int next_strip = 1;  // flat layers: the next strip to request (they run a.nss - 1 chunks ahead of the weights)
       for (int q = 0; q < total_chunks; ++q) {
         const int ch = q % CH;
         const bool is_skip = ch >= a.chunks;
@@ -268,13 +296,7 @@ conv_strip_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
         const int split = ntaps > 4 ? a.split : 0;
         const int tstep = a.wpair ? 2 : 1;
         for (int tap = 0; tap < ntaps; tap += tstep, bs = (bs + 1 == static_cast<uint32_t>(a.sb)) ? (bph ^= 1, 0u) : bs + 1) {
-          if (a.flat) {
-            // never blocks for long: strip next_strip reuses the buffer of chunk next_strip - nss < q, whose weights
-            // have already been issued
-            while (next_strip < total_chunks && next_strip < q + a.nss) load_strip(next_strip++);
-          } else if (tap == split && q + 1 < total_chunks) {
-            load_strip(q + 1);
-          }
+          if (tap == split && q + 1 < total_chunks) load_strip(q + 1);
           mbar_wait(&b_empty[bs], bph);
           if (a.dbg & 1) {
             mbar_arrive(&b_full[bs]);
@@ -307,6 +329,7 @@ conv_strip_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
               tma_load_2d(sB + jj * (CK * 128), &tmB, &b_full[bs], wtap * a.w_rowlen_tap + a.n_off + jj * CK, ch * CK);
           }
         }
+      }
       }
     }
   } else if (warp == 1) {

@@ -820,7 +820,7 @@ static int gn_init() {
   cudaGetDevice(&dev);
   cudaError_t e = cudaDeviceGetAttribute(&optin, cudaDevAttrMaxSharedMemoryPerBlockOptin, dev);
   if (e != cudaSuccess) return check_cuda(e, "cudaDeviceGetAttribute(smem optin)");
-  const int max_dyn = optin - 1024;
+  const int max_dyn = optin - 8192;  // room for the kernels' static shared memory (per-warp reduction slots: up to 4.6 KB)
   e = gn_optin(gn_fwd_fused_kernel<32, 256>, max_dyn);
   if (e == cudaSuccess) e = gn_optin(gn_fwd_fused_kernel<16, 256>, max_dyn);
   if (e == cudaSuccess) e = gn_optin(gn_fwd_fused_kernel<32, 512>, max_dyn);

@@ -215,8 +215,9 @@ def test_sample_graph_equals_eager_and_is_deterministic(built_lib):
         y = torch.tensor([1, 2, 3, 4], device=DEV)
         outs.append(m.sample(4, y))
         assert outs[-1].shape == (4, 1, 28, 28) and outs[-1].abs().max().item() <= 1.0
-    # float atomics (GN moments) make runs differ in the last bits, which the clipped x^ amplifies: close, not equal
-    assert frac_far(outs[0], outs[1], 3e-2) < 0.03 and frac_far(outs[1], outs[2], 3e-2) < 0.03
+    # the forward path has no floating-point atomics (GroupNorm moments are summed in a fixed order since round 2), so
+    # sampling is bit-reproducible: eager == graph replay == a second model's graph replay
+    assert torch.equal(outs[0], outs[1]) and torch.equal(outs[1], outs[2])
     # unconditional, unguided path for y=None (the reference raises TypeError there)
     m, _ = make_model(built_lib, mean_type="v", sampler="ddim", timesteps=3)
     assert m.sample(2).shape == (2, 1, 28, 28)
