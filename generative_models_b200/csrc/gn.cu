@@ -270,10 +270,22 @@ gn_bwd_fused_kernel(GnSrc s, const float* __restrict__ stats, const float* __res
   src += static_cast<size_t>(n) * s.HW * ld;
   const size_t row0 = static_cast<size_t>(n) * s.HW;
   const float* dsrc = dy + row0 * s.C + c;
-  for (int idx = tid; idx < total; idx += kGnThreads) {
-    const size_t pix = idx / L;
-    cp_async16(&xs[idx], src + pix * ld);
-    cp_async16(&ds[idx], dsrc + pix * s.C);
+  // Running pointers instead of per-iteration index arithmetic: the ncu source view of round 1's kernel charged 23
+  // instructions to every cp.async and 79 to every float4 of phase 2 (idx / L, 64-bit multiplies, one address per
+  // optional tensor); a thread's successive elements are a constant kGnThreads / L pixels apart.
+  constexpr int PSTEP = kGnThreads / L;  // pixels between a thread's consecutive elements
+  const int pix0 = tid / L;
+  {
+    const float* sp = src + static_cast<size_t>(pix0) * ld;
+    const float* dp = dsrc + static_cast<size_t>(pix0) * s.C;
+    const unsigned sstep = PSTEP * ld, dstep = PSTEP * s.C;
+    uint32_t xa = static_cast<uint32_t>(__cvta_generic_to_shared(&xs[tid]));
+    const uint32_t dsoff = static_cast<uint32_t>(total) * 16u;
+#pragma unroll 2
+    for (int idx = tid; idx < total; idx += kGnThreads, sp += sstep, dp += dstep, xa += kGnThreads * 16) {
+      asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(xa), "l"(sp) : "memory");
+      asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(xa + dsoff), "l"(dp) : "memory");
+    }
   }
   // the rows of the add tensors that phase 2 will read are pulled into L2 now (its loads were the top stall)
   if (c0 < add_c) {
@@ -329,13 +341,17 @@ gn_bwd_fused_kernel(GnSrc s, const float* __restrict__ stats, const float* __res
   const bool has_add = c < add_c;
   const float* a1 = (has_add && add1) ? add1 + row0 * add1_ld + c : nullptr;
   const float* a2 = (has_add && add2) ? add2 + row0 * add2_ld + c : nullptr;
-  float* dst = dx + row0 * s.C + c;
-  uint16_t* dstb = (dxb && c < dxb_c) ? dxb + row0 * dxb_c + c : nullptr;  // bf16 copy of the first dxb_c channels
+  float* dst = dx ? dx + (row0 + pix0) * s.C + c : nullptr;  // dx may be NULL when only the bf16 copy is wanted
+  uint16_t* dstb = (dxb && c < dxb_c) ? dxb + (row0 + pix0) * dxb_c + c : nullptr;  // bf16 copy of the first dxb_c channels
+  if (a1) a1 += static_cast<size_t>(pix0) * add1_ld;
+  if (a2) a2 += static_cast<size_t>(pix0) * add2_ld;
+  const unsigned ostep = PSTEP * s.C, bstep = PSTEP * dxb_c;  // elements; < 2^32 (PSTEP <= 128 pixels)
+  const unsigned a1step = PSTEP * add1_ld, a2step = PSTEP * add2_ld;
   float4 cacc = make_float4(0.f, 0.f, 0.f, 0.f);  // per-channel sum of dx over this sample's pixels (fused colsum)
   const float k1 = -m1 * rstd, k2 = -m2 * rstd;
   const float gr[4] = {ga[0] * rstd, ga[1] * rstd, ga[2] * rstd, ga[3] * rstd};
+#pragma unroll 2
   for (int idx = tid; idx < total; idx += kGnThreads) {
-    const size_t pix = idx / L;
     const float4 xh = xs[idx];
     const float4 du = ds[idx];
     float4 o;
@@ -344,16 +360,24 @@ gn_bwd_fused_kernel(GnSrc s, const float* __restrict__ stats, const float* __res
     o.z = fmaf(xh.z, k2, fmaf(du.z, gr[2], k1));
     o.w = fmaf(xh.w, k2, fmaf(du.w, gr[3], k1));
     if (a1) {
-      const float4 a = __ldg(reinterpret_cast<const float4*>(a1 + pix * add1_ld));
+      const float4 a = __ldg(reinterpret_cast<const float4*>(a1));
       o.x += a.x; o.y += a.y; o.z += a.z; o.w += a.w;
+      a1 += a1step;
     }
     if (a2) {
-      const float4 a = __ldg(reinterpret_cast<const float4*>(a2 + pix * add2_ld));
+      const float4 a = __ldg(reinterpret_cast<const float4*>(a2));
       o.x += a.x; o.y += a.y; o.z += a.z; o.w += a.w;
+      a2 += a2step;
     }
-    if (dstb) *reinterpret_cast<uint2*>(dstb + pix * dxb_c) = pack_bf16x4(o);
+    if (dstb) {
+      *reinterpret_cast<uint2*>(dstb) = pack_bf16x4(o);
+      dstb += bstep;
+    }
     if (round_dx) o = round_tf32(o);
-    if (dx) *reinterpret_cast<float4*>(dst + pix * s.C) = o;  // dx may be NULL when only the bf16 copy is wanted
+    if (dst) {
+      *reinterpret_cast<float4*>(dst) = o;
+      dst += ostep;
+    }
     cacc.x += o.x; cacc.y += o.y; cacc.z += o.z; cacc.w += o.w;
   }
   // fused column sums of dx (bias gradient of the convolution that produced x, and the per-sample gradient of the
@@ -545,13 +569,18 @@ gn_bwd_raw_kernel(GnSrc s, const float* __restrict__ stats, const float* __restr
   const bool has_add = c < add_c;
   const float* a1 = (has_add && add1) ? add1 + row0 * add1_ld + c : nullptr;
   const float* a2 = (has_add && add2) ? add2 + row0 * add2_ld + c : nullptr;
-  float* dst = dx ? dx + row0 * s.C + c : nullptr;
-  uint16_t* dstb = (dxb && c < dxb_c) ? dxb + row0 * dxb_c + c : nullptr;
+  constexpr int PSTEP = T / L;  // pixels between a thread's consecutive elements (running pointers, see the fp32 kernel)
+  const int pix0 = tid / L;
+  float* dst = dx ? dx + (row0 + pix0) * s.C + c : nullptr;
+  uint16_t* dstb = (dxb && c < dxb_c) ? dxb + (row0 + pix0) * dxb_c + c : nullptr;
+  if (a1) a1 += static_cast<size_t>(pix0) * add1_ld;
+  if (a2) a2 += static_cast<size_t>(pix0) * add2_ld;
+  const unsigned ostep = PSTEP * s.C, bstep = PSTEP * dxb_c, a1step = PSTEP * add1_ld, a2step = PSTEP * add2_ld;
   const float k1 = -m1 * rstd, k2 = -m2 * rstd;
   const float gr[4] = {ga[0] * rstd, ga[1] * rstd, ga[2] * rstd, ga[3] * rstd};
   float cacc[4] = {0.f, 0.f, 0.f, 0.f};
+#pragma unroll 2
   for (int idx = tid; idx < total; idx += T) {
-    const size_t pix = idx / L;
     const float4 v = gn_elem<XB>(xraw, idx);
     const float4 d = gn_elem<DB>(draw, idx);
     const float xv[4] = {v.x, v.y, v.z, v.w};
@@ -565,16 +594,24 @@ gn_bwd_raw_kernel(GnSrc s, const float* __restrict__ stats, const float* __restr
     }
     float4 o = make_float4(ov[0], ov[1], ov[2], ov[3]);
     if (a1) {
-      const float4 a = __ldg(reinterpret_cast<const float4*>(a1 + pix * add1_ld));
+      const float4 a = __ldg(reinterpret_cast<const float4*>(a1));
       o.x += a.x; o.y += a.y; o.z += a.z; o.w += a.w;
+      a1 += a1step;
     }
     if (a2) {
-      const float4 a = __ldg(reinterpret_cast<const float4*>(a2 + pix * add2_ld));
+      const float4 a = __ldg(reinterpret_cast<const float4*>(a2));
       o.x += a.x; o.y += a.y; o.z += a.z; o.w += a.w;
+      a2 += a2step;
     }
-    if (dstb) *reinterpret_cast<uint2*>(dstb + pix * dxb_c) = pack_bf16x4(o);
+    if (dstb) {
+      *reinterpret_cast<uint2*>(dstb) = pack_bf16x4(o);
+      dstb += bstep;
+    }
     if (round_dx) o = round_tf32(o);
-    if (dst) *reinterpret_cast<float4*>(dst + pix * s.C) = o;
+    if (dst) {
+      *reinterpret_cast<float4*>(dst) = o;
+      dst += ostep;
+    }
     cacc[0] += o.x; cacc[1] += o.y; cacc[2] += o.z; cacc[3] += o.w;
   }
   if (cs.c > 0 && c0 < cs.c)  // uniform per CTA
