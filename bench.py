@@ -86,9 +86,9 @@ class ClockSampler:
                 "power_w_max": max(float(r[3]) for r in rows), "samples": len(rows)}
 
 
-def synthetic_batch(B, seed, size=28):
+def synthetic_batch(B, seed, size=28, channels=1):
     g = torch.Generator().manual_seed(seed)
-    x = torch.rand(B, 1, size, size, generator=g) * 2 - 1
+    x = torch.rand(B, channels, size, size, generator=g) * 2 - 1
     y = torch.randint(0, 10, (B,), generator=g)
     return x, y
 
@@ -182,10 +182,10 @@ def profile_ops(model, bound, kind):
     groups = []
     p = bound.plan
     if kind == "train":
-        groups = [bound.zero_ops, bound.pre_ops, p.refresh_ops, p.embed_ops[0], p.body_ops, p.head_ops[:1],
+        groups = [bound.zero_ops, bound.pre_ops, p.refresh_ops, p.embed_ops[0], p.body_ops, p.head_ops[0],
                   bound.loss_ops, p.refreshT_ops, p.bwd_ops, bound.adam_ops]
     else:
-        groups = [p.embed_ops[0], p.body_ops, p.head_ops[:1], bound._step_ops(None)[0]]
+        groups = [p.embed_ops[0], p.body_ops, p.head_ops[0], bound._step_ops(None)[0]]
     ops = [o for g in groups for o in g]
     st = torch.cuda.current_stream()
     sp = model._stream()
@@ -359,7 +359,7 @@ def run_ours(args, rank, world, local_rank):
     def make_model(precision):
         torch.manual_seed(0)
         G = default_G(device=dev, mean_type="eps", sampler="noisy", timesteps=args.sample_steps, bs=B, graph=1,
-                      precision=precision)
+                      precision=precision, img_channels=args.img_channels, image_size=args.image_size)
         m = DiffusionModelB200(G)
         # reference init at seed 0, then a small fill of the zero-initialised convs so every layer does real work
         gen = torch.Generator().manual_seed(1)
@@ -387,7 +387,9 @@ def run_ours(args, rank, world, local_rank):
 
     # ---- device-resident leg: batches already in HBM
     nb = 4
-    host = [synthetic_batch(B, 100 * rank + i) for i in range(nb)]
+    S_img, C_img = (args.image_size or 28), args.img_channels
+    flop_scale = (S_img / 28.0) ** 2  # conv FLOPs scale with the pixel count (the two edge convs also with C_img: < 0.1 %)
+    host = [synthetic_batch(B, 100 * rank + i, S_img, C_img) for i in range(nb)]
     host = [(x.pin_memory(), y.pin_memory()) for x, y in host]
     devb = [(x.to(dev), y.to(dev)) for x, y in host]
     W, K = max(args.warmup, 3), args.steps
@@ -471,7 +473,7 @@ def run_ours(args, rank, world, local_rank):
 
     def warm_sampler(mdl, n_, guided):
         labels = (torch.arange(n_, device=dev) % 10)
-        init = torch.randn(n_, 1, 28, 28, device=dev)
+        init = torch.randn(n_, C_img, S_img, S_img, device=dev)
         bs = mdl._plan(n_, "sample_g" if guided else "sample")  # warm-up: 3 steps of the real plan (eager, capture, replay)
         bs.begin_sampling(init, labels, torch.ones(n_, device=dev) if guided else None)
         for _ in range(min(3, T)):
@@ -490,7 +492,7 @@ def run_ours(args, rank, world, local_rank):
         barrier()
         ms_s = max_over_ranks(e0.elapsed_time(e1))
         return {"value": n * world / (ms_s / 1e3), "unit": "img/s", "n_per_gpu": n, "timesteps": T, "guided": False,
-                "seconds": ms_s / 1e3, "tensor_tflops": n * T * FWD_FLOP_PER_IMG / (ms_s / 1e3) / 1e12,
+                "seconds": ms_s / 1e3, "tensor_tflops": n * T * FWD_FLOP_PER_IMG * flop_scale / (ms_s / 1e3) / 1e12,
                 "finite": bool(torch.isfinite(z).all().item())}
 
     def time_sample_api(mdl, n_):
@@ -509,7 +511,7 @@ def run_ours(args, rank, world, local_rank):
         ms_s = max_over_ranks(e0.elapsed_time(e1))
         return {"img_s": n_ * world / (ms_s / 1e3), "seconds": ms_s / 1e3, "wall_seconds": wall, "n": n_ * world, "T": T,
                 "guided": True, "net_evals_per_step": 2, "ms_per_step": ms_s / T, "d2h_bytes": out.numel() * 4,
-                "tensor_tflops": 2 * n_ * T * FWD_FLOP_PER_IMG / (ms_s / 1e3) / 1e12,
+                "tensor_tflops": 2 * n_ * T * FWD_FLOP_PER_IMG * flop_scale / (ms_s / 1e3) / 1e12,
                 "finite": bool(torch.isfinite(out).all().item())}
 
     samp = time_sampling(model)
@@ -562,7 +564,7 @@ def run_ours(args, rank, world, local_rank):
         bf16 = {"config": "configs[2]: ResBlock 3x3 convs with bf16 operands / fp32 accumulate, everything else fp32/TF32; "
                           f"batch {B}/GPU",
                 "train_img_s": B * world * K / (ms_b / 1e3), "ms_per_step": ms_b / K,
-                "tensor_tflops": B * K / (ms_b / 1e3) * TRAIN_FLOP_PER_IMG / 1e12,
+                "tensor_tflops": B * K / (ms_b / 1e3) * TRAIN_FLOP_PER_IMG * flop_scale / 1e12,
                 "sampling_img_s": sb["value"] if sb else None, "sampling_seconds": sb["seconds"] if sb else None,
                 "activation_bytes": bound2.plan.activation_bytes()}
         if prof2:
@@ -644,7 +646,9 @@ def run_ours(args, rank, world, local_rank):
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": K, "warmup": W, "settle_steps": settle_steps,
         "ms_per_step": ms / K, "higher_is_better": True, "scaling": "strong" if args.config == 2 else "weak",
         "vs_baseline": None, "dtype": args.precision, "data": "synthetic",
-        "config": {"workload": workload_string(args) if args.config != 2 else
+        "config": {"workload": (f"configs[4] (extension: no reference counterpart): DDPM UNet C=128 on 3x64x64, batch {B}/GPU "
+                                f"{args.precision}, train step + {T}-step sampling of {n} img/GPU") if args.config == 4 else
+                   workload_string(args) if args.config != 2 else
                    f"configs[2]: DDPM data-parallel training, bf16 ResBlock convs, GLOBAL batch {B * world} = {B}/GPU x {world}",
                    "global_batch": B * world, "mean_type": "eps", "sampler": "noisy", "timesteps": T,
                    "parallelism": f"dp{world}", "cuda_graph": True,
@@ -660,7 +664,7 @@ def run_ours(args, rank, world, local_rank):
         "gpu_launches_per_step": launches_per_step,
         "ms_per_step_min_over_ranks": ms_min / K,
         "allreduce_ms": allreduce_ms,
-        "tensor_tflops": value * TRAIN_FLOP_PER_IMG / 1e12 / world,
+        "tensor_tflops": value * TRAIN_FLOP_PER_IMG * flop_scale / 1e12 / world,
         "roofline": roofline,
         "cpu_baseline": cpu_baseline,
         "gpu_torch_baseline": gpu_base,
@@ -708,7 +712,9 @@ def main():
     ap.add_argument("--precision", default="tf32", choices=["tf32", "bf16"],
                     help="tensor-core operand type of the ResBlock convs (tf32 = configs[1], the headline)")
     ap.add_argument("--bf16-leg", type=int, default=1, help="also time the bf16 configuration (configs[2]) beside the headline")
-    ap.add_argument("--config", type=int, default=1, choices=[1, 2, 3],
+    ap.add_argument("--img-channels", type=int, default=1)
+    ap.add_argument("--image-size", type=int, default=0, help="0 = 28 (the reference's MNIST shape)")
+    ap.add_argument("--config", type=int, default=1, choices=[1, 2, 3, 4],
                     help="BASELINE.json configs[k]: 1 = batch 512/GPU fp32/TF32 (the default bench line); 2 = bf16 data-parallel "
                          "training at GLOBAL batch 4096 (4096/N per GPU, strong scaling); 3 = 65536 images x 1000 steps sharded")
     ap.add_argument("--config3-images", type=int, default=65536)
@@ -718,6 +724,12 @@ def main():
     if args.impl == "reference":
         return run_reference(args, rank)
     nworld = world if world > 1 else max(1, args.gpus)
+    if args.config == 4:
+        # BASELINE.json configs[4]: 3 x 64 x 64, base 128 channels — an extension (the reference UNet is 1-channel, 28 x 28)
+        args.img_channels, args.image_size = 3, 64
+        args.batch = args.batch if args.batch != 512 else 64
+        args.sample_n = min(args.sample_n, args.batch)
+        args.small_n = args.gpu_baseline = 0
     if args.config == 2:
         args.precision, args.batch = "bf16", 4096 // nworld
         args.bf16_leg = args.small_n = args.gpu_baseline = args.sample_api = 0

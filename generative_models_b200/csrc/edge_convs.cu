@@ -16,19 +16,21 @@ namespace b200 {
 // integer division: the kernel is bound by the HBM write (the per-element version spent its time on index math).
 __global__ void __launch_bounds__(256)
 conv_in_fwd_kernel(const float* __restrict__ x, const float* __restrict__ w, const float* __restrict__ bias,
-                   float* __restrict__ out, int N, int H, int W, int round_out) {
+                   float* __restrict__ out, int N, int H, int W, int round_out, int x_ld, int w_co_ld, int w_tap_ld,
+                   int accumulate) {
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int c = lane * 4;
   float wv[4][9];
 #pragma unroll
   for (int j = 0; j < 4; ++j)
 #pragma unroll
-    for (int t = 0; t < 9; ++t) wv[j][t] = w[(c + j) * 9 + t];  // w is [c][tap]
-  const float4 b4 = *reinterpret_cast<const float4*>(bias + c);
+    for (int t = 0; t < 9; ++t) wv[j][t] = w[(c + j) * w_co_ld + t * w_tap_ld];  // w is [c][tap][image channel]
+  // image channels beyond the first (3-channel extension) are further launches that add onto out
+  const float4 b4 = accumulate ? make_float4(0.f, 0.f, 0.f, 0.f) : *reinterpret_cast<const float4*>(bias + c);
   const int rows = N * H;
   for (int row = blockIdx.x * 8 + warp; row < rows; row += gridDim.x * 8) {
     const int n = row / H, y = row - n * H;
-    const float* img = x + static_cast<size_t>(n) * H * W;
+    const float* img = x + static_cast<size_t>(n) * x_ld;
     const float* r0 = (y > 0) ? img + (y - 1) * W : nullptr;
     const float* r1 = img + y * W;
     const float* r2 = (y + 1 < H) ? img + (y + 1) * W : nullptr;
@@ -51,6 +53,10 @@ conv_in_fwd_kernel(const float* __restrict__ x, const float* __restrict__ w, con
 #pragma unroll
           for (int j = 0; j < 4; ++j) acc[j] += a[kh][kw] * wv[j][kh * 3 + kw];
       float4 o = make_float4(acc[0], acc[1], acc[2], acc[3]);
+      if (accumulate) {
+        const float4 p = *reinterpret_cast<const float4*>(orow + static_cast<size_t>(xx) * 128);
+        o.x += p.x; o.y += p.y; o.z += p.z; o.w += p.w;
+      }
       if (round_out) o = round_tf32(o);
       *reinterpret_cast<float4*>(orow + static_cast<size_t>(xx) * 128) = o;
 #pragma unroll
@@ -70,13 +76,13 @@ conv_in_fwd_kernel(const float* __restrict__ x, const float* __restrict__ w, con
 // latency per pixel (112 us; 31 us is the HBM time).
 __global__ void __launch_bounds__(256)
 conv_in_bwd_kernel(const float* __restrict__ x, const float* __restrict__ dy, float* __restrict__ dw,
-                   float* __restrict__ db, int H, int W, int pix_per_chunk) {
+                   float* __restrict__ db, int H, int W, int pix_per_chunk, int x_ld, int w_co_ld, int w_tap_ld) {
   __shared__ float sh[8][32][41];
   extern __shared__ float simg[];  // (H + 2) x (W + 2), zero border
   const int n = blockIdx.y;
   const int q = threadIdx.x & 31, r = threadIdx.x >> 5;
   const int HW = H * W, Wp = W + 2;
-  const float* img = x + static_cast<size_t>(n) * HW;
+  const float* img = x + static_cast<size_t>(n) * x_ld;
   for (int i = threadIdx.x; i < (H + 2) * Wp; i += 256) {
     const int yy = i / Wp - 1, xx = i - (yy + 1) * Wp - 1;
     simg[i] = (yy >= 0 && yy < H && xx >= 0 && xx < W) ? img[yy * W + xx] : 0.f;
@@ -125,8 +131,8 @@ conv_in_bwd_kernel(const float* __restrict__ x, const float* __restrict__ dy, fl
     float s = 0.f;
 #pragma unroll
     for (int rr = 0; rr < 8; ++rr) s += sh[rr][c >> 2][t * 4 + (c & 3)];
-    if (t < 9) atomicAdd(&dw[c * 9 + t], s);
-    else atomicAdd(&db[c], s);
+    if (t < 9) atomicAdd(&dw[c * w_co_ld + t * w_tap_ld], s);
+    else if (db) atomicAdd(&db[c], s);  // db only from the first image channel's launch
   }
 }
 
@@ -135,7 +141,7 @@ conv_in_bwd_kernel(const float* __restrict__ x, const float* __restrict__ dy, fl
 // once, its 9 per-tap dot products are parked in smem, then each output pixel gathers its 9 partials.
 __global__ void __launch_bounds__(256)
 conv_out_fwd_kernel(const float* __restrict__ h, const float* __restrict__ w, const float* __restrict__ bias,
-                    float* __restrict__ out, int H, int W) {
+                    float* __restrict__ out, int H, int W, int out_ld) {
   extern __shared__ float part[];  // [HW][9]
   const int n = blockIdx.x;
   const int HW = H * W;
@@ -195,7 +201,7 @@ conv_out_fwd_kernel(const float* __restrict__ h, const float* __restrict__ w, co
         const int yy = y + kh - 1, xw = xx + kw - 1;
         if (yy >= 0 && yy < H && xw >= 0 && xw < W) s += part[(yy * W + xw) * 9 + kh * 3 + kw];
       }
-    out[static_cast<size_t>(n) * HW + p] = s;
+    out[static_cast<size_t>(n) * out_ld + p] = s;
   }
 }
 
@@ -204,7 +210,8 @@ conv_out_fwd_kernel(const float* __restrict__ h, const float* __restrict__ w, co
 // db += sum dout.  One CTA per image; dout of the image lives in smem.
 __global__ void __launch_bounds__(256)
 conv_out_bwd_kernel(const float* __restrict__ h, const float* __restrict__ w, const float* __restrict__ dout,
-                    float* __restrict__ dh, float* __restrict__ dw, float* __restrict__ db, int H, int W, int round_dh) {
+                    float* __restrict__ dh, float* __restrict__ dw, float* __restrict__ db, int H, int W, int round_dh,
+                    int out_ld, int accumulate) {
   extern __shared__ float sm[];  // [(H+2)(W+2)] zero-padded dout, then [8][9][128] dw partials
   const int n = blockIdx.x;
   const int HW = H * W, Wp = W + 2;
@@ -216,7 +223,7 @@ conv_out_bwd_kernel(const float* __restrict__ h, const float* __restrict__ w, co
   for (int i = threadIdx.x; i < padded; i += blockDim.x) {
     const int yy = i / Wp - 1, xx = i - (yy + 1) * Wp - 1;
     float v = 0.f;
-    if (yy >= 0 && yy < H && xx >= 0 && xx < W) v = dout[static_cast<size_t>(n) * HW + yy * W + xx];
+    if (yy >= 0 && yy < H && xx >= 0 && xx < W) v = dout[static_cast<size_t>(n) * out_ld + yy * W + xx];
     sd[i] = v;
     bsum += v;
   }
@@ -251,6 +258,10 @@ conv_out_bwd_kernel(const float* __restrict__ h, const float* __restrict__ w, co
           g.x += d * wv[t].x; g.y += d * wv[t].y; g.z += d * wv[t].z; g.w += d * wv[t].w;
           aw[t].x += d * v.x; aw[t].y += d * v.y; aw[t].z += d * v.z; aw[t].w += d * v.w;
         }
+      if (accumulate) {  // image channels beyond the first add onto dh (3-channel extension)
+        const float4 p4 = *reinterpret_cast<const float4*>(dh + base + static_cast<size_t>(pp) * 128);
+        g.x += p4.x; g.y += p4.y; g.z += p4.z; g.w += p4.w;
+      }
       if (round_dh) g = round_tf32(g);
       *reinterpret_cast<float4*>(dh + base + static_cast<size_t>(pp) * 128) = g;
     }
@@ -278,14 +289,15 @@ extern "C" int b200_conv_in_fwd(const b200_conv_in_args* a, void* ws, size_t ws_
   if (!a || !a->x || !a->w || !a->bias || !a->out) return fail_arg("conv_in_fwd: null pointer");
   size_t blocks = (static_cast<size_t>(a->N) * a->H + 7) / 8;  // one warp per image row
   if (blocks > 148 * 8) blocks = 148 * 8;
-  conv_in_fwd_kernel<<<static_cast<int>(blocks), 256, 0, static_cast<cudaStream_t>(stream)>>>(a->x, a->w, a->bias, a->out,
-                                                                                              a->N, a->H, a->W, a->round_out);
+  conv_in_fwd_kernel<<<static_cast<int>(blocks), 256, 0, static_cast<cudaStream_t>(stream)>>>(
+      a->x, a->w, a->bias, a->out, a->N, a->H, a->W, a->round_out, a->x_ld ? a->x_ld : a->H * a->W, a->w_co_ld ? a->w_co_ld : 9,
+      a->w_tap_ld ? a->w_tap_ld : 1, a->accumulate);
   return after_launch("conv_in_fwd_kernel");
 }
 
 extern "C" int b200_conv_in_bwd(const b200_conv_in_args* a, void* ws, size_t ws_bytes, void* stream) {
   (void)ws; (void)ws_bytes;
-  if (!a || !a->x || !a->dy || !a->dw || !a->db) return fail_arg("conv_in_bwd: null pointer");
+  if (!a || !a->x || !a->dy || !a->dw) return fail_arg("conv_in_bwd: null pointer");
   const int HW = a->H * a->W;
   int chunks = (592 + a->N - 1) / a->N;
   if (chunks > (HW + 63) / 64) chunks = (HW + 63) / 64;
@@ -299,8 +311,8 @@ extern "C" int b200_conv_in_bwd(const b200_conv_in_args* a, void* ws, size_t ws_
     if (e != cudaSuccess) return check_cuda(e, "cudaFuncSetAttribute(conv_in_bwd)");
     in_bwd_attr = true;
   }
-  conv_in_bwd_kernel<<<dim3(chunks, a->N), 256, img_smem, static_cast<cudaStream_t>(stream)>>>(a->x, a->dy, a->dw, a->db,
-                                                                                               a->H, a->W, ppc);
+  conv_in_bwd_kernel<<<dim3(chunks, a->N), 256, img_smem, static_cast<cudaStream_t>(stream)>>>(
+      a->x, a->dy, a->dw, a->db, a->H, a->W, ppc, a->x_ld ? a->x_ld : HW, a->w_co_ld ? a->w_co_ld : 9, a->w_tap_ld ? a->w_tap_ld : 1);
   return after_launch("conv_in_bwd_kernel");
 }
 
@@ -316,7 +328,8 @@ extern "C" int b200_conv_out_fwd(const b200_conv_out_args* a, void* ws, size_t w
     if (e != cudaSuccess) return check_cuda(e, "cudaFuncSetAttribute(conv_out_fwd)");
     fwd_attr_set = true;
   }
-  conv_out_fwd_kernel<<<a->N, 256, smem, static_cast<cudaStream_t>(stream)>>>(a->h, a->w, a->bias, a->out, a->H, a->W);
+  conv_out_fwd_kernel<<<a->N, 256, smem, static_cast<cudaStream_t>(stream)>>>(a->h, a->w, a->bias, a->out, a->H, a->W,
+                                                                              a->out_ld ? a->out_ld : HW);
   return after_launch("conv_out_fwd_kernel");
 }
 
@@ -333,6 +346,7 @@ extern "C" int b200_conv_out_bwd(const b200_conv_out_args* a, void* ws, size_t w
     attr_set = true;
   }
   conv_out_bwd_kernel<<<a->N, 256, smem, static_cast<cudaStream_t>(stream)>>>(a->h, a->w, a->dout, a->dh, a->dw, a->db,
-                                                                              a->H, a->W, a->round_dh);
+                                                                              a->H, a->W, a->round_dh, a->out_ld ? a->out_ld : HW,
+                                                                              a->accumulate_dh);
   return after_launch("conv_out_bwd_kernel");
 }

@@ -94,6 +94,7 @@ class ConvInArgs(C.Structure):
     _fields_ = [
         ("x", _f32p), ("w", _f32p), ("bias", _f32p), ("out", _f32p), ("dy", _f32p), ("dw", _f32p), ("db", _f32p),
         ("N", C.c_int), ("H", C.c_int), ("W", C.c_int), ("round_out", C.c_int),
+        ("x_ld", C.c_int), ("w_co_ld", C.c_int), ("w_tap_ld", C.c_int), ("accumulate", C.c_int),
     ]
 
 
@@ -101,6 +102,7 @@ class ConvOutArgs(C.Structure):
     _fields_ = [
         ("h", _f32p), ("w", _f32p), ("bias", _f32p), ("out", _f32p), ("dout", _f32p), ("dh", _f32p),
         ("dw", _f32p), ("db", _f32p), ("N", C.c_int), ("H", C.c_int), ("W", C.c_int), ("round_dh", C.c_int),
+        ("out_ld", C.c_int), ("accumulate_dh", C.c_int),
     ]
 
 

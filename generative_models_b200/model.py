@@ -64,6 +64,10 @@ class DiffusionModelB200(nn.Module):
     # the caller's y is left untouched).  0 (default) mirrors diffusion_model.py:67 bit for bit: CPU generator draw,
     # in-place edit of the caller's y.
     DG.device_label_drop = 0
+    # image channels: 1 = the reference's MNIST UNet (simple_unet.py:92-94, :41); 3 = the 3x64x64 extension of
+    # BASELINE.json configs[4] (together with G.image_size), for which the reference has no counterpart
+    DG.img_channels = 1
+    DG.image_size = 0  # 0: 28 (or 32 with pad32), as the reference; else the image side (a multiple of 4, <= 64)
 
     def __init__(self, G):
         super().__init__()
@@ -91,8 +95,9 @@ class DiffusionModelB200(nn.Module):
         rc = lib.load().b200_init(dev.index)
         if rc != 0:
             raise lib.B200Error(f"b200_init failed: {lib.load().b200_last_error().decode()}")
-        self.size = 32 if G.pad32 else 28
-        self.store = ParamStore(G.hidden_size, dev)
+        self.size = int(G.get("image_size", 0)) or (32 if G.pad32 else 28)
+        self.img_channels = int(G.get("img_channels", 1))
+        self.store = ParamStore(G.hidden_size, dev, self.img_channels)
         self.store.init_like_reference()
         self.net = build_module_tree(self.store, nn.Module())
         self.optimizer = None  # the fused flat Adam below replaces torch.optim.Adam (diffusion_model.py:56)
@@ -118,7 +123,7 @@ class DiffusionModelB200(nn.Module):
         if Path(G.get("teacher_path", ".")) != Path(".") and Path(G.get("weights_from", ".")) == Path("."):
             print("Loading teacher model")
             self.load_state_dict(torch.load(G.teacher_path, map_location=dev), strict=False)
-            self.teacher_store = ParamStore(G.hidden_size, dev)
+            self.teacher_store = ParamStore(G.hidden_size, dev, self.img_channels)
             self.teacher_store.flat.copy_(self.store.flat)
             self.teacher_net = build_module_tree(self.teacher_store, nn.Module())
             for p in self.teacher_net.parameters():
@@ -284,7 +289,7 @@ class DiffusionModelB200(nn.Module):
                 b.run_graphed(b.enqueue_sampler_step, ("sampler_step", history))
             else:
                 b.enqueue_sampler_step()
-        z = b.plan.z_in[:n].view(n, 1, self.size, self.size).clone()
+        z = b.plan.z_in[:n].view(n, self.img_channels, self.size, self.size).clone()
         return z, hist
 
     def _sampling_weights(self, n, want_guidance):
@@ -305,7 +310,7 @@ class DiffusionModelB200(nn.Module):
         G.sample_cond_w is set (gaussian_diffusion.py:247-257); a distilled student is instead conditioned on w and
         sampled without guidance.  y=None (a TypeError in the reference) samples unconditionally without guidance."""
         with torch.no_grad():
-            noise = torch.randn((n, 1, self.size, self.size), device=self.device)
+            noise = torch.randn((n, self.img_channels, self.size, self.size), device=self.device)
             cond_w, net_cond_w = self._sampling_weights(n, True) if y is not None else (None, None)
             z, _ = self._sample_loop(noise, y, cond_w, net_cond_w=net_cond_w)
             return z
@@ -322,7 +327,7 @@ class DiffusionModelB200(nn.Module):
         set, gaussian_diffusion.py:257); grid + three grid-videos.  proc() — ((t+1)*127.5).clamp(0,255).uint8 — is
         fused into the sampler step: the trajectories leave the device as uint8, 1 B/px."""
         torch.manual_seed(0)
-        noise = torch.randn((25, 1, self.size, self.size), device=self.device)
+        noise = torch.randn((25, self.img_channels, self.size, self.size), device=self.device)
         labels = torch.arange(25, dtype=torch.long, device=self.device) % 10
         cond_w, net_cond_w = self._sampling_weights(25, False)
         with torch.no_grad():
@@ -354,7 +359,9 @@ def _write_grid(writer, tag, x, epoch):
 def _write_gridvid(writer, tag, x, epoch):
     """gms/common.py:183-193."""
     T = x.shape[0]
-    vid = _grid(x)[None].repeat(1, 1, 3, 1, 1)
+    vid = _grid(x)[None]
+    if vid.shape[2] == 1:  # grey -> RGB, as common.write_gridvid does for the reference's 1-channel images
+        vid = vid.repeat(1, 1, 3, 1, 1)
     writer.add_video(tag, vid, epoch, fps=min(T // 3, 60))
 
 
@@ -366,7 +373,7 @@ class _Bound:
         self.B, self.kind = B, kind
         dev = model.device
         S = model.size
-        D = S * S
+        D = model.img_channels * S * S
         G = model.G
         f32 = dict(dtype=torch.float32, device=dev)
         self.graphs = {}
@@ -568,15 +575,15 @@ class _Bound:
         """b200_sampler_step + the loop-index decrement for one history mode (argument structs are built once)."""
         key = ("ops", history)
         if key not in self.hist:
-            p, B, D, T = self.plan, self.B, self.plan.S * self.plan.S, self.T
+            p, B, D, T = self.plan, self.B, self.plan.Ci * self.plan.S * self.plan.S, self.T
             dev = self.noise.device
             h = None
             if history == "f32":
-                h = [torch.empty(T, B, 1, p.S, p.S, dtype=torch.float32, device=dev) for _ in range(3)]
+                h = [torch.empty(T, B, p.Ci, p.S, p.S, dtype=torch.float32, device=dev) for _ in range(3)]
             elif history == "u8":
-                h = [torch.empty(T, B, 1, p.S, p.S, dtype=torch.uint8, device=dev) for _ in range(3)]
+                h = [torch.empty(T, B, p.Ci, p.S, p.S, dtype=torch.uint8, device=dev) for _ in range(3)]
             elif history == "last":  # single-row x / eps of the most recent step only (teacher-forced parity tests)
-                h = [None] + [torch.empty(B, 1, p.S, p.S, dtype=torch.float32, device=dev) for _ in range(2)]
+                h = [None] + [torch.empty(B, p.Ci, p.S, p.S, dtype=torch.float32, device=dev) for _ in range(2)]
             elif history is not None:
                 raise ValueError(history)
             f, u = (h if history in ("f32", "last") else [None] * 3), (h if history == "u8" else [None] * 3)
@@ -628,7 +635,7 @@ class _Bound:
         else:
             self.noise.zero_()
         self.enqueue_sampler_step(draw_noise=False)
-        return hist[1].clone(), hist[2].clone(), self.plan.z_in[:n].view(n, 1, S, S).clone()
+        return hist[1].clone(), hist[2].clone(), self.plan.z_in[:n].view(n, self.plan.Ci, S, S).clone()
 
     def enqueue_sampler_step(self, draw_noise=True):
         st = self.m._stream()

@@ -121,6 +121,7 @@ class UNetPlan:
         if self.bf16:
             store.ensure_bf16()
         self.store = store
+        self.Ci = Ci = getattr(store, "img_channels", 1)  # image channels (1 = the reference; 3 = configs[4] extension)
         self.B, self.S, self.train = B, S, train
         self.Cc = Cc = store.C
         assert Cc == 128, "the tcgen05 conv kernels are specialised for hidden_size=128 (N tile = 128 channels)"
@@ -130,11 +131,11 @@ class UNetPlan:
         self.gpool = _Pool(dev, recycle=True)
         f32 = dict(dtype=torch.float32, device=dev)
         # ---- static inputs / outputs
-        self.z_in = torch.zeros(B, S * S, **f32)
+        self.z_in = torch.zeros(B, Ci * S * S, **f32)  # planar [B][Ci][S*S] (NCHW; == NHWC when Ci == 1)
         self.t = torch.zeros(B, **f32)
         self.guide = torch.full((B,), -1, dtype=torch.int64, device=dev)
-        self.out = torch.zeros(B, S * S, **f32)
-        self.out2 = torch.zeros(B, S * S, **f32)
+        self.out = torch.zeros(B, Ci * S * S, **f32)
+        self.out2 = torch.zeros(B, Ci * S * S, **f32)
         self.sched, self.step_dev = sched, step_dev
         import math
         # the reference evaluates exp(-math.log(max_period) * arange / half) in fp32 on the CPU (simple_unet.py:216-220)
@@ -149,7 +150,7 @@ class UNetPlan:
         self.skips = {}
         self._build_forward()
         if train:
-            self.dout = torch.zeros(B, S * S, **f32)
+            self.dout = torch.zeros(B, self.Ci * S * S, **f32)
             self._build_backward()
 
     # ------------------------------------------------------------------ small constructors
@@ -346,9 +347,13 @@ class UNetPlan:
         H0, H1, H2 = S, S // 2, S // 4
         # ---- Down (simple_unet.py:87-109)
         d0 = pool.get(B, H0 * H0, 128)
-        cin = lib.ConvInArgs(x=_p(self.z_in), w=self._w("down.seq.0.conv.weight"), bias=self._w("down.seq.0.conv.bias"),
-                             out=_p(d0), dy=None, dw=None, db=None, N=B, H=H0, W=H0, round_out=1)
-        ops.append(Op("b200_conv_in_fwd", cin))
+        Ci = self.Ci
+        for ci in range(Ci):  # one launch per image channel; launches after the first accumulate onto d0
+            cin = lib.ConvInArgs(x=_p(self.z_in, ci * H0 * H0), w=C.c_void_p(st.ptr("down.seq.0.conv.weight") + 4 * ci),
+                                 bias=self._w("down.seq.0.conv.bias"), out=_p(d0), dy=None, dw=None, db=None, N=B, H=H0,
+                                 W=H0, round_out=1 if ci == Ci - 1 else 0, x_ld=Ci * H0 * H0, w_co_ld=9 * Ci, w_tap_ld=Ci,
+                                 accumulate=1 if ci else 0)
+            ops.append(Op("b200_conv_in_fwd", cin))
         bf = self.bf16
         if bf:
             self._cast_copy(ops, d0, B * H0 * H0)
@@ -404,10 +409,14 @@ class UNetPlan:
         ops.append(Op("b200_gn_fwd", gh))
         self.body_ops = ops
         self.head_ops = []
-        for o in (self.out, self.out2):
-            ca = lib.ConvOutArgs(h=_p(ah), w=self._w("out.2.weight"), bias=self._w("out.2.bias"), out=_p(o), dout=None,
-                                 dh=None, dw=None, db=None, N=B, H=H0, W=H0)
-            self.head_ops.append(Op("b200_conv_out_fwd", ca))
+        for o in (self.out, self.out2):  # head_ops[k] = the launches (one per image channel) that write output buffer k
+            grp = []
+            for ci in range(Ci):
+                ca = lib.ConvOutArgs(h=_p(ah), w=C.c_void_p(st.ptr("out.2.weight") + 4 * ci * 1152),
+                                     bias=C.c_void_p(st.ptr("out.2.bias") + 4 * ci), out=_p(o, ci * H0 * H0), dout=None,
+                                     dh=None, dw=None, db=None, N=B, H=H0, W=H0, out_ld=Ci * H0 * H0)
+                grp.append(Op("b200_conv_out_fwd", ca))
+            self.head_ops.append(grp)
         self.saved = dict(d0=d0, d1=d1, d2=d2, d3=d3, d4=d4, d5=d5, d6=d6, t=t, r0=r0, up0=up0, u0=u0, u1=u1, u2=u2,
                           r3=r3, up3=up3, u3=u3, u4=u4, u5=u5, u6=u6, ah=ah, gh=gh)
 
@@ -418,7 +427,7 @@ class UNetPlan:
             run_ops(self.refresh_ops, stream_ptr)
         run_ops(self.embed_ops[1 if uncond else 0], stream_ptr)
         run_ops(self.body_ops, stream_ptr)
-        run_ops(self.head_ops[1 if to_out2 else 0:][:1], stream_ptr)
+        run_ops(self.head_ops[1 if to_out2 else 0], stream_ptr)
 
     # ------------------------------------------------------------------ backward
     def _gn_bwd(self, ops, g_fwd, dy, dx, gname, add1=None, add2=None, add_c=0, dx_bf=None, dy_bf=False):
@@ -581,10 +590,14 @@ class UNetPlan:
         ops.append(Op("b200_zero", lib.ZeroArgs(ptr=_p(self.d_embout), bytes=self.d_embout.numel() * 4)))
         # ---- out head
         dah = gp.get(B, H0 * H0, 128)
-        ca = lib.ConvOutArgs(h=_p(sv["ah"]), w=self._w("out.2.weight"), bias=self._w("out.2.bias"), out=None,
-                             dout=_p(self.dout), dh=_p(dah), dw=self._g("out.2.weight"), db=self._g("out.2.bias"), N=B,
-                             H=H0, W=H0, round_dh=1)
-        ops.append(Op("b200_conv_out_bwd", ca))
+        Ci = self.Ci
+        for ci in range(Ci):
+            ca = lib.ConvOutArgs(h=_p(sv["ah"]), w=C.c_void_p(st.ptr("out.2.weight") + 4 * ci * 1152),
+                                 bias=self._w("out.2.bias"), out=None, dout=_p(self.dout, ci * H0 * H0), dh=_p(dah),
+                                 dw=C.c_void_p(st.gptr("out.2.weight") + 4 * ci * 1152),
+                                 db=C.c_void_p(st.gptr("out.2.bias") + 4 * ci), N=B, H=H0, W=H0,
+                                 round_dh=1 if ci == Ci - 1 else 0, out_ld=Ci * H0 * H0, accumulate_dh=1 if ci else 0)
+            ops.append(Op("b200_conv_out_bwd", ca))
         du6 = gp.get(B, H0 * H0, 128)
         self._gn_bwd(ops, sv["gh"], dah, du6, "out.0",
                      dx_bf=self._get_bf(self.bfpool, B, H0 * H0, 128) if self.bf16 else None)
@@ -627,9 +640,12 @@ class UNetPlan:
         gp.release(dd2)
         dd0 = self._rb_bwd(ops, "down.seq.1", _Grad(dd1), extra=tail(dc6))
         gp.release(dd1)
-        cin = lib.ConvInArgs(x=_p(self.z_in), w=self._w("down.seq.0.conv.weight"), bias=None, out=None, dy=_p(dd0),
-                             dw=self._g("down.seq.0.conv.weight"), db=self._g("down.seq.0.conv.bias"), N=B, H=H0, W=H0)
-        ops.append(Op("b200_conv_in_bwd", cin))
+        for ci in range(Ci):
+            cin = lib.ConvInArgs(x=_p(self.z_in, ci * H0 * H0), w=self._w("down.seq.0.conv.weight"), bias=None, out=None,
+                                 dy=_p(dd0), dw=C.c_void_p(st.gptr("down.seq.0.conv.weight") + 4 * ci),
+                                 db=self._g("down.seq.0.conv.bias") if ci == 0 else None, N=B, H=H0, W=H0,
+                                 x_ld=Ci * H0 * H0, w_co_ld=9 * Ci, w_tap_ld=Ci)
+            ops.append(Op("b200_conv_in_bwd", cin))
         gp.release(dd0)
         # ---- embeddings (simple_unet.py:45-58 and the emb_layers), reversed
         embw = C.c_void_p(st.flat.data_ptr() + 4 * st.emb_w_off)

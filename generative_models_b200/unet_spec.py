@@ -19,9 +19,10 @@ RESBLOCKS = ["down.seq.1", "down.seq.2", "down.seq.4", "down.seq.5", "turn", "up
              "up.seq.3.0", "up.seq.4", "up.seq.5", "up.seq.6"]
 
 
-def param_specs(C=128):
+def param_specs(C=128, img_channels=1):
     """[(name, shape, kind)] in the reference's registration order; kind in {lin_w, lin_b, conv_w, conv_b, gn_w, gn_b}.
-    `zero` convs (simple_unet.py:172 zero_module) are flagged in ZERO_INIT."""
+    `zero` convs (simple_unet.py:172 zero_module) are flagged in ZERO_INIT.  img_channels = 1 is the reference
+    (simple_unet.py:92-94 Conv2d(1, C, 3), :41 Conv2d(C, 1, 3)); 3 is the 3x64x64 extension of BASELINE.json configs[4]."""
     E = 2 * C
     out = []
 
@@ -49,7 +50,7 @@ def param_specs(C=128):
     for nm, i in (("time_embed", 64), ("cond_w_embed", 64), ("guide_embed", 10)):
         lin(nm + ".0", i, E)
         lin(nm + ".2", E, E)
-    conv("down.seq.0.conv", 1, C, 3)
+    conv("down.seq.0.conv", img_channels, C, 3)
     rb("down.seq.1", C, C)
     rb("down.seq.2", C, C)
     conv("down.seq.3.conv", C, C, 3)
@@ -64,7 +65,7 @@ def param_specs(C=128):
         else:
             rb(f"up.seq.{i}", 2 * C, C)
     gn("out.0", C)
-    conv("out.2", C, 1, 3)
+    conv("out.2", C, img_channels, 3)
     return out
 
 
@@ -79,10 +80,11 @@ def _align(n, a=64):
 class ParamStore:
     """Flat fp32 parameter / gradient / Adam-state buffers on one device, plus named views."""
 
-    def __init__(self, C, device):
+    def __init__(self, C, device, img_channels=1):
         self.C = C
+        self.img_channels = img_channels
         self.device = torch.device(device)
-        self.specs = param_specs(C)
+        self.specs = param_specs(C, img_channels)
         self.offsets = {}
         off = 0
         # the fused emb_layers block first: weights [12*C][2C] contiguous, then biases [12*C]

@@ -259,6 +259,11 @@ typedef struct {
   float* db;
   int N, H, W;
   int round_out; /* fwd: store out rounded to TF32 */
+  /* multi-channel images (3x64x64 extension, BASELINE.json configs[4]; the reference is 1-channel): one launch per image
+   * channel ci over planar input x[n][ci][H][W] — x points at plane ci of sample 0, x_ld = floats between samples
+   * (0 = H*W), the weight is [128][3][3][Cimg] so w / dw point at element ci with w_co_ld = 9*Cimg and w_tap_ld = Cimg
+   * (0 = 9 / 1); launches after the first set accumulate (fwd: out += , no bias) and pass db = NULL (bwd). */
+  int x_ld, w_co_ld, w_tap_ld, accumulate;
 } b200_conv_in_args;
 int b200_conv_in_fwd(const b200_conv_in_args* a, void* ws, size_t ws_bytes, void* stream);
 int b200_conv_in_bwd(const b200_conv_in_args* a, void* ws, size_t ws_bytes, void* stream);
@@ -274,6 +279,10 @@ typedef struct {
   float* db;
   int N, H, W;
   int round_dh; /* store dh rounded to TF32 */
+  /* multi-channel images: one launch per image channel c with w / dw = weight row c ([3][3][128]), bias / db = element c,
+   * out / dout = plane c of sample 0, out_ld = floats between samples (0 = H*W); backward launches after the first set
+   * accumulate_dh (dh += ). */
+  int out_ld, accumulate_dh;
 } b200_conv_out_args;
 int b200_conv_out_fwd(const b200_conv_out_args* a, void* ws, size_t ws_bytes, void* stream);
 int b200_conv_out_bwd(const b200_conv_out_args* a, void* ws, size_t ws_bytes, void* stream);

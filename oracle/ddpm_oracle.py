@@ -284,7 +284,7 @@ def sample_loop(net, init_z, num_steps, sampler="noisy", mean_type="eps", cond_w
 
 
 # ----------------------------------------------------------------------------- helpers for tests / fixtures
-def param_shapes(C=128):
+def param_shapes(C=128, img_channels=1):
     """Appendix C of SURVEY.md: the 160 tensors of SimpleUnet(C) (keys without the 'net.' prefix), in
     registration order (simple_unet.py:16-42,87-186)."""
     E = 2 * C
@@ -314,7 +314,7 @@ def param_shapes(C=128):
     for nm, i in (("time_embed", 64), ("cond_w_embed", 64), ("guide_embed", 10)):
         lin(nm + ".0", i, E)
         lin(nm + ".2", E, E)
-    conv("down.seq.0.conv", 1, C, 3)
+    conv("down.seq.0.conv", img_channels, C, 3)
     rb("down.seq.1", C, C)
     rb("down.seq.2", C, C)
     conv("down.seq.3.conv", C, C, 3)
@@ -329,16 +329,16 @@ def param_shapes(C=128):
         else:
             rb(f"up.seq.{i}", 2 * C, C)
     gn("out.0", C)
-    conv("out.2", C, 1, 3)
+    conv("out.2", C, img_channels, 3)  # img_channels = 3: the configs[4] extension (no reference counterpart)
     return out
 
 
-def random_state_dict(seed, C=128, dtype=torch.float32):
+def random_state_dict(seed, C=128, dtype=torch.float32, img_channels=1):
     """Deterministic non-degenerate weights (the reference zero-inits every out_layers.3, simple_unet.py:172,
     which would hide conv2/GN2 bugs): fan-in scaled normals from a CPU generator, GN weights near 1."""
     g = torch.Generator().manual_seed(seed)
     sd = {}
-    for name, shape in param_shapes(C):
+    for name, shape in param_shapes(C, img_channels):
         if ".weight" in name and len(shape) == 1:  # GroupNorm gamma
             t = 1.0 + 0.1 * torch.randn(shape, generator=g)
         elif name.endswith(".bias"):

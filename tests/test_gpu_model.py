@@ -456,3 +456,55 @@ def test_ragged_batch_sizes_vs_oracle(built_lib, B, precision):
     m2, _ = make_model(built_lib, mean_type="eps", precision=precision, timesteps=4, sampler="noisy")
     z = m2.sample(B, y=torch.randint(0, 10, (B,), device=DEV))
     assert z.shape == (B, 1, 28, 28) and torch.isfinite(z).all()
+
+
+@pytest.mark.parametrize("S,prec", [(32, "tf32"), (64, "tf32"), (64, "bf16")])
+def test_three_channel_images_vs_oracle(built_lib, S, prec):
+    """BASELINE.json configs[4] (3 x 64 x 64, base 128 channels) — an EXTENSION: the reference's SimpleUnet is hard-wired to
+    one image channel (simple_unet.py:92-94 Conv2d(1, C, 3), :41 Conv2d(C, 1, 3)), so the checker is the oracle's own
+    functional UNet with (128, 3, 3, 3) / (3, 128, 3, 3) edge weights ("parity unpinned" for this configuration).
+    Forward, every parameter gradient of a linear loss, one train step and a 3-step sample through the public API."""
+    from generative_models_b200.model import DiffusionModelB200, default_G
+    from generative_models_b200.plan import UNetPlan
+    G = default_G(device=DEV, mean_type="eps", sampler="noisy", timesteps=3, precision=prec, img_channels=3, image_size=S)
+    m = DiffusionModelB200(G)
+    sd0 = O.random_state_dict(1, img_channels=3)
+    m.net.load_state_dict(sd0)
+    assert m.state_dict()["net.down.seq.0.conv.weight"].shape == (128, 3, 3, 3)
+    assert m.state_dict()["net.out.2.weight"].shape == (3, 128, 3, 3)
+    g = torch.Generator().manual_seed(S)
+    B = 2
+    z = torch.randn(B, 3, S, S, generator=g)
+    logsnr = torch.tensor([1.5, -3.0])
+    y = torch.tensor([7, -1])
+    r = torch.randn(B, 3, S, S, generator=g)
+    sd = {k: v.clone().requires_grad_(True) for k, v in sd0.items()}
+    out_ref = O.unet_forward(sd, z, logsnr, guide=y)
+    (out_ref * r).sum().backward()
+    p = UNetPlan(m.store, B, S, train=True, bf16=(prec == "bf16"))
+    p.z_in.copy_(z.reshape(B, -1))
+    p.t.copy_(logsnr)
+    p.guide.copy_(y)
+    st = m._stream()
+    m.store.grad.zero_()
+    p.forward(st)
+    ours = p.out.cpu().view(B, 3, S, S)
+    net_tol = NET_TOL if prec == "tf32" else 8e-3
+    assert rms_rel(ours, out_ref.detach()) < net_tol, rms_rel(ours, out_ref.detach())
+    p.dout.copy_(r.reshape(B, -1))
+    p.backward(st)
+    grad_tol = GRAD_TOL if prec == "tf32" else 4e-2
+    worst = ("", 0.0)
+    for k, prm in m.net.named_parameters():
+        if sd[k].grad is None:
+            continue
+        worst = max(worst, (k, rel(prm.grad.cpu(), sd[k].grad)), key=lambda t: t[1])
+    assert worst[1] < grad_tol, worst
+    # public API on 3-channel images
+    x = (torch.rand(B, 3, S, S, generator=g) * 2 - 1).to(DEV)
+    eps, u = torch.randn(B, 3, S, S, generator=g), torch.tensor([0.3, 0.7])
+    loss = m.train_step(x, y.to(DEV).clone(), eps=eps.to(DEV), u=u.to(DEV))["loss"].item()
+    ref_loss, _, _ = O.training_loss(sd0, x.cpu(), y, eps, u, "eps")
+    assert abs(loss - ref_loss.item()) < (3e-3 if prec == "tf32" else 3e-2) * abs(ref_loss.item()), (loss, ref_loss.item())
+    out = m.sample(2, y.to(DEV))
+    assert out.shape == (2, 3, S, S) and torch.isfinite(out).all() and out.abs().max() <= 1.0

@@ -48,7 +48,7 @@ def main():
         m.train_step(x, y.clone())
     b = m._plan(a.batch, "train")
     p = b.plan
-    ops = [o for g in (b.zero_ops, b.pre_ops, p.refresh_ops, p.embed_ops[0], p.body_ops, p.head_ops[:1], b.loss_ops,
+    ops = [o for g in (b.zero_ops, b.pre_ops, p.refresh_ops, p.embed_ops[0], p.body_ops, p.head_ops[0], b.loss_ops,
                        p.bwd_ops, b.adam_ops) for o in g]
     st = torch.cuda.current_stream()
     sp = m._stream()
