@@ -47,11 +47,6 @@ def allreduce_flat_grad(flat_grad, async_op=False):
     return work if async_op else None
 
 
-def nccl_in_graph():
-    """Opt-in (B200_NCCL_GRAPH=1): capture the gradient allreduce inside the step's CUDA graph."""
-    return os.environ.get("B200_NCCL_GRAPH", "0") == "1"
-
-
 def broadcast_params(flat_params, src=0):
     """Make every replica start from rank `src`'s weights (one broadcast of the flat parameter buffer)."""
     if dist.is_initialized() and dist.get_world_size() > 1:

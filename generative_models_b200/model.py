@@ -238,10 +238,6 @@ class DiffusionModelB200(nn.Module):
         graphed = (lambda fn, k: b.run_graphed(fn, k)) if self.use_graph else (lambda fn, k: fn())
         if world == 1:
             graphed(lambda: (b.enqueue_stage(*key), b.enqueue_fwd_bwd(), b.enqueue_adam()), ("step",) + key)
-        elif dist.nccl_in_graph():
-            # opt-in (B200_NCCL_GRAPH=1): the two allreduce buckets captured inside the one step graph
-            graphed(lambda: (b.enqueue_stage(*key), b.enqueue_fwd_bwd(allreduce="captured"), b.enqueue_adam()),
-                    ("step_dp",) + key)
         else:
             # the one collective of the path: sum of the flat fp32 gradient over NVLink, as two
             # buckets.  The Up-path half (complete once the backward has walked the out head and the Up blocks) is
@@ -546,10 +542,9 @@ class _Bound:
         self.enqueue_stage(eps is None, u is None and idx is None, False, cond_w is None)
 
     # ---- enqueue
-    def enqueue_fwd_bwd(self, part=None, allreduce=None):
+    def enqueue_fwd_bwd(self, part=None):
         """part: None = whole step; "up" = everything up to the point where the out/Up gradients are final;
-        "down" = the rest of the backward.  allreduce="captured": issue the two bucket allreduces from inside
-        (only when the whole step is being captured with NCCL in the graph)."""
+        "down" = the rest of the backward."""
         st = self.m._stream()
         if part in (None, "up"):
             run_ops(self.zero_ops, st)
@@ -557,16 +552,7 @@ class _Bound:
             self.enqueue_teacher_targets()
             self.plan.forward(st)
             run_ops(self.loss_ops, st)
-        if allreduce == "captured":
-            store = self.m.store
-            self.plan.backward(st, "up")
-            w1 = dist.allreduce_flat_grad(store.grad[store.bucket_split:], async_op=True)
-            self.plan.backward(st, "down")
-            dist.allreduce_flat_grad(store.grad[:store.bucket_split])
-            if w1 is not None:
-                w1.wait()
-        else:
-            self.plan.backward(st, part)
+        self.plan.backward(st, part)
 
     def enqueue_adam(self):
         run_ops(self.adam_ops, self.m._stream())

@@ -6,8 +6,12 @@
 Every rank runs `train_step` on its shard of one global batch (same weights, injected eps / u, no label drop) through the
 product's data-parallel path — Up-bucket allreduce overlapped with the Down-path backward, then the rest, then the fused
 Adam with grad_scale = 1/world — for 3 steps (eager warm-up, capture, replay).  Rank 0 then repeats the same 3 steps on
-the WHOLE batch alone (world-size-1 path, one graph) and compares: the summed gradient times 1/world against the
-global-batch gradient, and the weights after 3 Adam steps.  Prints one JSON line; exit code 1 on mismatch.
+the WHOLE batch alone (world-size-1 path, one graph) and compares the summed gradient times 1/world against the
+global-batch gradient.  The learning rate is 0 in both runs: the first Adam steps move every weight by lr * sign(g), so
+with lr > 0 a 1e-6 difference in a near-zero gradient flips a weight by 2 lr and the later steps are no longer
+comparable (the first version of this tool measured exactly that: 4e-3 weight differences after 3 steps at lr 1e-3);
+the Adam moments still go through the reduced gradient and are compared too.  Prints one JSON line; exit code 1 on
+mismatch.
 """
 import json
 import os
@@ -40,14 +44,14 @@ def main():
     sd = O.random_state_dict(1)
 
     def run(lo, hi, use_dist):
-        m = DiffusionModelB200(default_G(device=str(dev), mean_type="eps", cf_drop_prob=0.0, lr=1e-3))
+        m = DiffusionModelB200(default_G(device=str(dev), mean_type="eps", cf_drop_prob=0.0, lr=0.0))
         m.net.load_state_dict(sd)
         losses = []
         for _ in range(3):
             out = m.train_step(x[lo:hi].to(dev), y[lo:hi].to(dev), eps=eps[lo:hi].to(dev), u=u[lo:hi].to(dev))
             losses.append(out["loss"].item())
         torch.cuda.synchronize()
-        return m.store.flat.clone(), m.store.grad.clone(), losses
+        return m.store.exp_avg.clone(), m.store.grad.clone(), losses
 
     lo, hi = D.shard_range(Bg, rank, world)
     w_dp, g_dp, l_dp = run(lo, hi, True)
@@ -65,14 +69,14 @@ def main():
         rel = lambda a, b: ((a - b).abs().max() / b.abs().max().clamp_min(1e-30)).item()
         # store.grad after the step = the SUM over ranks of local-mean gradients; x 1/world = the global-batch mean gradient
         e_g = rel(g_dp / world, g_1)
-        e_w = rel(w_dp, w_1)
-        res = {"world": world, "global_batch": Bg, "grad_rel_err": e_g, "weights_rel_err_after_3_steps": e_w,
+        e_w = rel(w_dp, w_1)  # Adam's first moment after 3 steps: (1 - 0.9^3) * mean gradient
+        res = {"world": world, "global_batch": Bg, "grad_rel_err": e_g, "exp_avg_rel_err_after_3_steps": e_w,
                "loss_local_shard": l_dp, "loss_global_batch": l_1}
         print(json.dumps(res), flush=True)
     if world > 1:
         dist.barrier()
         dist.destroy_process_group()
-    if res is not None and not (res["grad_rel_err"] < 5e-3 and res["weights_rel_err_after_3_steps"] < 1e-3):
+    if res is not None and not (res["grad_rel_err"] < 1e-3 and res["exp_avg_rel_err_after_3_steps"] < 1e-3):
         sys.exit(1)
 
 
