@@ -157,6 +157,20 @@ class ZeroArgs(C.Structure):
     _fields_ = [("ptr", _f32p), ("bytes", C.c_size_t)]
 
 
+class BgemmArgs(C.Structure):
+    _fields_ = [
+        ("A", _f32p), ("B", _f32p), ("C", _f32p), ("M", C.c_int), ("N", C.c_int), ("K", C.c_int), ("batch", C.c_int),
+        ("lda", C.c_int), ("ldb", C.c_int), ("ldc", C.c_int),
+        ("strideA", C.c_longlong), ("strideB", C.c_longlong), ("strideC", C.c_longlong),
+        ("a_mn", C.c_int), ("b_mn", C.c_int), ("alpha", C.c_float), ("round_out", C.c_int),
+    ]
+
+
+class SoftmaxArgs(C.Structure):
+    _fields_ = [("s", _f32p), ("p", _f32p), ("dp", _f32p), ("ds", _f32p), ("rows", C.c_longlong), ("T", C.c_int),
+                ("ld", C.c_int)]
+
+
 class B200Error(RuntimeError):
     pass
 
@@ -203,6 +217,7 @@ EXPORTS = [
     "b200_conv_igemm", "b200_conv_kernel_of", "b200_conv_wgrad",
     "b200_gn_fwd", "b200_gn_bwd", "b200_gn_bwd_workspace",
     "b200_q_sample", "b200_loss", "b200_sampler_step", "b200_distill_target", "b200_step_advance", "b200_int_increment",
+    "b200_bgemm", "b200_softmax_fwd", "b200_softmax_bwd",
     "b200_conv_in_fwd", "b200_conv_in_bwd", "b200_conv_out_fwd", "b200_conv_out_bwd",
     "b200_upsample2x", "b200_colsum",
     "b200_embed_prep", "b200_embed_combine", "b200_embed_combine_bwd",

@@ -246,6 +246,43 @@ int b200_step_advance(const b200_step_advance_args* a, void* ws, size_t ws_bytes
 /* also used to bump the device-side Adam step counter */
 int b200_int_increment(const b200_step_advance_args* a, void* ws, size_t ws_bytes, void* stream);
 
+/* ------------------------------------------------------------------ self-attention at the lowest UNet level (EXTENSION)
+ * The reference's SimpleUnet has no attention (simple_unet.py:16-72); the north star / BASELINE.json configs[4] ask for
+ * one on the tensor cores (7x7 = 49 tokens at 28x28, 16x16 = 256 tokens at 64x64; one head of 128 channels).  Shape of
+ * the block (guided-diffusion's AttentionBlock, the family SimpleUnet derives from): x + proj(softmax(q k^T / sqrt(C)) v),
+ * q / k / v / proj = 1x1 convolutions (b200_conv_igemm) of GroupNorm(x) (b200_gn_fwd, silu = 0).
+ *
+ * b200_bgemm: C[b] = alpha * op(A[b]) op(B[b])^T, batched, tcgen05 kind::tf32 with fp32 accumulation.
+ *   A is [M][K] rows with pitch lda (a_mn = 0) or [K][M] rows (a_mn = 1); B is [N][K] rows with pitch ldb (b_mn = 0) or
+ *   [K][N] rows (b_mn = 1); C is [M][N] rows with pitch ldc.  strideX = floats between batch elements.  N <= 256; lda, ldb
+ *   and the strides are multiples of 4 floats; A and B hold TF32-rounded values.  M, N, K need not be multiples of
+ *   anything (49 tokens): out-of-range operand elements read as zero, out-of-range results are not stored. */
+typedef struct {
+  const float* A;
+  const float* B;
+  float* C;
+  int M, N, K, batch;
+  int lda, ldb, ldc;
+  long long strideA, strideB, strideC;
+  int a_mn, b_mn;
+  float alpha;
+  int round_out; /* store C rounded to TF32 (it feeds another tensor-core operand) */
+} b200_bgemm_args;
+int b200_bgemm(const b200_bgemm_args* a, void* ws, size_t ws_bytes, void* stream);
+
+/* row softmax over T <= 256 scores per row (pitch ld, T <= ld <= 256) and its backward; outputs are rounded to TF32 and
+ * the pad columns [T, ld) are written as zeros.  fwd: p = softmax(s).  bwd: ds = p * (dp - sum_j dp_j p_j). */
+typedef struct {
+  const float* s;
+  float* p;        /* fwd: output; bwd: input */
+  const float* dp;
+  float* ds;
+  long long rows;
+  int T, ld;
+} b200_softmax_args;
+int b200_softmax_fwd(const b200_softmax_args* a, void* ws, size_t ws_bytes, void* stream);
+int b200_softmax_bwd(const b200_softmax_args* a, void* ws, size_t ws_bytes, void* stream);
+
 /* ------------------------------------------------------------------ edge convolutions (not tensor-core shaped)
  * conv_in: Conv2d(1, 128, 3, padding=1) (simple_unet.py:92-94); x [N,H,W], w [128][3][3], out/dy [N,H,W,128].
  * conv_out: Conv2d(128, 1, 3, padding=1) (simple_unet.py:41); h/dh [N,H,W,128], w [3][3][128], out/dout [N,H,W]. */

@@ -34,7 +34,8 @@ def test_ctypes_structs_match_header_field_order(built_lib):
               "b200_colsum_args": built_lib.ColsumArgs, "b200_embed_args": built_lib.EmbedArgs,
               "b200_linear_args": built_lib.LinearArgs, "b200_zero_args": built_lib.ZeroArgs,
               "b200_round_args": built_lib.RoundArgs, "b200_cast_args": built_lib.CastArgs, "b200_wtranspose_args": built_lib.WTransposeArgs,
-              "b200_adam_args": built_lib.AdamArgs, "b200_distill_target_args": built_lib.DistillTargetArgs}
+              "b200_adam_args": built_lib.AdamArgs, "b200_distill_target_args": built_lib.DistillTargetArgs, "b200_bgemm_args": built_lib.BgemmArgs,
+              "b200_softmax_args": built_lib.SoftmaxArgs}
     for m in re.finditer(r"typedef struct \{(.*?)\}\s*(b200_\w+);", hdr, re.S):
         body, name = m.group(1), m.group(2)
         body = re.sub(r"/\*.*?\*/", "", body, flags=re.S)

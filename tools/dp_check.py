@@ -63,6 +63,11 @@ def main():
         torch.distributed.is_initialized = dist.is_initialized
         try:
             w_1, g_1, l_1 = run(0, Bg, False)
+            # the same shards, one after the other on this GPU alone (same per-launch batch as the data-parallel ranks,
+            # hence the same kernel selection and tile geometry): their gradient sum is what the allreduce must produce
+            parts = [run(*D.shard_range(Bg, r, world), False) for r in range(world)]
+            g_sum = sum(p_[1] for p_ in parts)
+            m_sum = sum(p_[0] for p_ in parts)
         finally:
             dist.is_initialized = real_is_init
             torch.distributed.is_initialized = real_is_init
@@ -70,13 +75,20 @@ def main():
         # store.grad after the step = the SUM over ranks of local-mean gradients; x 1/world = the global-batch mean gradient
         e_g = rel(g_dp / world, g_1)
         e_w = rel(w_dp, w_1)  # Adam's first moment after 3 steps: (1 - 0.9^3) * mean gradient
-        res = {"world": world, "global_batch": Bg, "grad_rel_err": e_g, "exp_avg_rel_err_after_3_steps": e_w,
+        res = {"world": world, "global_batch": Bg,
+               # the collective path itself: allreduced gradient vs the sum of the same shards computed on one GPU
+               "allreduce_vs_shard_sum_rel_err": rel(g_dp, g_sum),
+               "exp_avg_vs_shard_sum_rel_err": rel(w_dp * world, m_sum),
+               # against ONE launch over the whole batch (other kernel selection for the small Linears and other tile
+               # boundaries: fp32 reordering noise of ~1e-7 that TF32-rounded stores and the clip mask amplify)
+               "grad_rel_err": e_g, "exp_avg_rel_err_after_3_steps": e_w,
                "loss_local_shard": l_dp, "loss_global_batch": l_1}
         print(json.dumps(res), flush=True)
     if world > 1:
         dist.barrier()
         dist.destroy_process_group()
-    if res is not None and not (res["grad_rel_err"] < 1e-3 and res["exp_avg_rel_err_after_3_steps"] < 1e-3):
+    if res is not None and not (res["allreduce_vs_shard_sum_rel_err"] < 1e-4 and res["exp_avg_vs_shard_sum_rel_err"] < 1e-4
+                                and res["grad_rel_err"] < 2e-2):
         sys.exit(1)
 
 
