@@ -68,6 +68,9 @@ class DiffusionModelB200(nn.Module):
     # BASELINE.json configs[4] (together with G.image_size), for which the reference has no counterpart
     DG.img_channels = 1
     DG.image_size = 0  # 0: 28 (or 32 with pad32), as the reference; else the image side (a multiple of 4, <= 64)
+    # 1: single-head self-attention after the turn block, at the lowest-resolution level (7x7 tokens at 28x28, 16x16 at
+    # 64x64) on the tensor cores — an extension named by the north star / configs[4]; adds 10 `net.attn.*` tensors
+    DG.attention = 0
 
     def __init__(self, G):
         super().__init__()
@@ -97,7 +100,8 @@ class DiffusionModelB200(nn.Module):
             raise lib.B200Error(f"b200_init failed: {lib.load().b200_last_error().decode()}")
         self.size = int(G.get("image_size", 0)) or (32 if G.pad32 else 28)
         self.img_channels = int(G.get("img_channels", 1))
-        self.store = ParamStore(G.hidden_size, dev, self.img_channels)
+        self.attention = bool(int(G.get("attention", 0)))
+        self.store = ParamStore(G.hidden_size, dev, self.img_channels, self.attention)
         self.store.init_like_reference()
         self.net = build_module_tree(self.store, nn.Module())
         self.optimizer = None  # the fused flat Adam below replaces torch.optim.Adam (diffusion_model.py:56)
@@ -123,7 +127,7 @@ class DiffusionModelB200(nn.Module):
         if Path(G.get("teacher_path", ".")) != Path(".") and Path(G.get("weights_from", ".")) == Path("."):
             print("Loading teacher model")
             self.load_state_dict(torch.load(G.teacher_path, map_location=dev), strict=False)
-            self.teacher_store = ParamStore(G.hidden_size, dev, self.img_channels)
+            self.teacher_store = ParamStore(G.hidden_size, dev, self.img_channels, self.attention)
             self.teacher_store.flat.copy_(self.store.flat)
             self.teacher_net = build_module_tree(self.teacher_store, nn.Module())
             for p in self.teacher_net.parameters():

@@ -143,7 +143,8 @@ class UNetPlan:
         # cond_w_embed's timestep_embedding uses max_period = 4 (simple_unet.py:62)
         self.freqs_w = torch.exp(-math.log(4) * torch.arange(0, 32, dtype=torch.float32) / 32).to(dev)
         self.cond_w = torch.zeros(B, **f32)
-        self.n_stats = 25
+        self.attention = bool(getattr(store, "attention", False))
+        self.n_stats = 25 + (1 if self.attention else 0)
         self.stats = torch.zeros(self.n_stats, B, 64, **f32)
         self._stat_i = 0
         self.records = {}
@@ -247,6 +248,77 @@ class UNetPlan:
         a = lib.LinearArgs(X=_p(X), W=W, bias=bias, Y=_p(Y), dY=_p(dY), dX=_p(dX), dW=dW, db=db, M=M, N=N, K=K,
                            act=act, mode=mode)
         return Op("b200_linear", a)
+
+    # ------------------------------------------------------------------ self-attention (extension; csrc/attn_small.cu)
+    def _bgemm(self, A, Bm, Cm, M, N, K, lda, ldb, ldc, sA, sB, sC, a_mn=0, b_mn=0, alpha=1.0, round_out=0):
+        a = lib.BgemmArgs(A=_p(A), B=_p(Bm), C=_p(Cm), M=M, N=N, K=K, batch=self.B, lda=lda, ldb=ldb, ldc=ldc, strideA=sA,
+                          strideB=sB, strideC=sC, a_mn=a_mn, b_mn=b_mn, alpha=alpha, round_out=round_out)
+        return Op("b200_bgemm", a)
+
+    def _attn_fwd(self, ops, x, H):
+        """x + proj(softmax(q k^T / sqrt(C)) v) over the H*H tokens of each sample, q / k / v / proj = 1x1 convolutions of
+        GroupNorm(x) (oracle.attention_block).  Everything stays fp32 / TF32, also in bf16 mode (0.3 % of the FLOPs)."""
+        import math
+        B, T = self.B, H * H
+        Tp = (T + 31) // 32 * 32
+        pool = self.pool
+        hn = pool.get(B, T, 128)
+        g = self._gn(x, None, "attn.norm", hn, T, 0, self._next_stats(), silu=0, tf32=1)
+        ops.append(Op("b200_gn_fwd", g))
+        q, k, v = (pool.get(B, T, 128) for _ in range(3))
+        for nm, t in (("q", q), ("k", k), ("v", v)):
+            ops.append(self._conv(hn, None, "attn." + nm, t, H, H, 1, 1, 0, 128, 0))
+        S, P = pool.get(B, T, Tp), pool.get(B, T, Tp)
+        scale = 1.0 / math.sqrt(128.0)
+        ops.append(self._bgemm(q, k, S, T, T, 128, 128, 128, Tp, T * 128, T * 128, T * Tp, alpha=scale))        # S = q k^T / sqrt(C)
+        ops.append(Op("b200_softmax_fwd", lib.SoftmaxArgs(s=_p(S), p=_p(P), dp=None, ds=None, rows=B * T, T=T, ld=Tp)))
+        a = pool.get(B, T, 128)
+        ops.append(self._bgemm(P, v, a, T, 128, T, Tp, 128, 128, T * Tp, T * 128, T * 128, b_mn=1, round_out=1))  # a = P v
+        out = pool.get(B, T, 128)
+        out_bf = self._get_bf(pool, B, T, 128) if self.bf16 else None
+        ops.append(self._conv(a, None, "attn.proj_out", out, H, H, 1, 1, 0, 128, 0, residual=_p(x), out_bf=out_bf))
+        for t in (S, hn, q, k, v, P, a):
+            pool.release(t)  # inference plans recycle; training plans keep everything
+        self.records["attn"] = dict(x=x, H=H, Tp=Tp, hn=hn, q=q, k=k, v=v, P=P, a=a, g=g, scale=scale)
+        return out
+
+    def _attn_bwd(self, ops, dOut):
+        """Reverse of _attn_fwd.  dOut: _Grad w.r.t. the block output; returns the dense gradient of its input."""
+        r = self.records["attn"]
+        B, H, Tp, scale = self.B, r["H"], r["Tp"], r["scale"]
+        T = H * H
+        gp = self.gpool
+        q, k, v, P = r["q"], r["k"], r["v"], r["P"]
+        # proj_out (1x1 conv): bias, weight and data gradients
+        self._colsum(ops, dOut, T, total1=self._g("attn.proj_out.bias"))
+        ops.append(self._wgrad(r["a"], None, dOut, "attn.proj_out", H, H, 1, 1, 0, 128, 0))
+        dA = gp.get(B, T, 128)
+        ops.append(self._dgrad(dOut, "attn.proj_out", dA, H, 1, 0, 128, 0, 128))
+        # attention core: dV = P^T dA, dP = dA v^T, dS = softmax'(P, dP), dQ = dS k / sqrt(C), dK = dS^T q / sqrt(C)
+        dV, dQ, dK = (gp.get(B, T, 128) for _ in range(3))
+        dP, dS = gp.get(B, T, Tp), gp.get(B, T, Tp)
+        ops.append(self._bgemm(P, dA, dV, T, 128, T, Tp, 128, 128, T * Tp, T * 128, T * 128, a_mn=1, b_mn=1, round_out=1))
+        ops.append(self._bgemm(dA, v, dP, T, T, 128, 128, 128, Tp, T * 128, T * 128, T * Tp))
+        ops.append(Op("b200_softmax_bwd", lib.SoftmaxArgs(s=None, p=_p(P), dp=_p(dP), ds=_p(dS), rows=B * T, T=T, ld=Tp)))
+        ops.append(self._bgemm(dS, k, dQ, T, 128, T, Tp, 128, 128, T * Tp, T * 128, T * 128, b_mn=1, alpha=scale, round_out=1))
+        ops.append(self._bgemm(dS, q, dK, T, 128, T, Tp, 128, 128, T * Tp, T * 128, T * 128, a_mn=1, b_mn=1, alpha=scale,
+                               round_out=1))
+        gp.release(dA), gp.release(dP), gp.release(dS)
+        # q / k / v convs: their input gradients add up in dhn
+        dhn = None
+        for nm, gq in (("q", dQ), ("k", dK), ("v", dV)):
+            gg = _Grad(gq)
+            self._colsum(ops, gg, T, total1=self._g(f"attn.{nm}.bias"))
+            ops.append(self._wgrad(r["hn"], None, gg, "attn." + nm, H, H, 1, 1, 0, 128, 0))
+            nxt = gp.get(B, T, 128)
+            ops.append(self._dgrad(gg, "attn." + nm, nxt, H, 1, 0, 128, 0, 128,
+                                   residual=_p(dhn) if dhn is not None else None, res_ld=128))
+            gp.release(dhn), gp.release(gq)
+            dhn = nxt
+        dx = gp.get(B, T, 128)
+        self._gn_bwd(ops, r["g"], dhn, dx, "attn.norm", add1=dOut, add_c=128)  # + the residual path's gradient
+        gp.release(dhn)
+        return dx
 
     # ------------------------------------------------------------------ forward
     def _build_embed(self, force_uncond):
@@ -369,6 +441,10 @@ class UNetPlan:
                               out_bf=self._get_bf(pool, B, H2 * H2, 128) if bf else None))
         # ---- turn (simple_unet.py:36,68)
         t = self._rb_fwd(ops, "turn", d6, None, H2)
+        if self.attention:
+            t_in = t
+            t = self._attn_fwd(ops, t_in, H2)
+            self._rel(t_in)
         # ---- Up (simple_unet.py:125-152): block i consumes cat([h, cache.pop()])
         r0 = self._rb_fwd(ops, "up.seq.0.0", t, d6, H2)
         self._rel(t), self._rel(d6)
@@ -627,7 +703,12 @@ class UNetPlan:
         # allreduce of that bucket while the ops below (turn, Down, embeddings) still run
         self.bwd_split = len(ops)
         # ---- turn, then Down reversed; each Down tensor also receives the tail of its concat consumer
-        dd6 = self._rb_bwd(ops, "turn", half(dc0), extra=tail(dc0))
+        if self.attention:
+            dt = self._attn_bwd(ops, half(dc0))
+            dd6 = self._rb_bwd(ops, "turn", _Grad(dt), extra=tail(dc0))
+            gp.release(dt)
+        else:
+            dd6 = self._rb_bwd(ops, "turn", half(dc0), extra=tail(dc0))
         dd5 = self._conv_bwd(ops, "down.seq.6.conv", sv["d5"], _Grad(dd6), H1, H2, 2, residual=tail(dc1))
         gp.release(dd6)
         dd4 = self._rb_bwd(ops, "down.seq.5", _Grad(dd5), extra=tail(dc2))

@@ -19,7 +19,7 @@ RESBLOCKS = ["down.seq.1", "down.seq.2", "down.seq.4", "down.seq.5", "turn", "up
              "up.seq.3.0", "up.seq.4", "up.seq.5", "up.seq.6"]
 
 
-def param_specs(C=128, img_channels=1):
+def param_specs(C=128, img_channels=1, attention=False):
     """[(name, shape, kind)] in the reference's registration order; kind in {lin_w, lin_b, conv_w, conv_b, gn_w, gn_b}.
     `zero` convs (simple_unet.py:172 zero_module) are flagged in ZERO_INIT.  img_channels = 1 is the reference
     (simple_unet.py:92-94 Conv2d(1, C, 3), :41 Conv2d(C, 1, 3)); 3 is the 3x64x64 extension of BASELINE.json configs[4]."""
@@ -58,6 +58,10 @@ def param_specs(C=128, img_channels=1):
     rb("down.seq.5", C, C)
     conv("down.seq.6.conv", C, C, 3)
     rb("turn", C, C)
+    if attention:  # extension (no reference counterpart): self-attention after the turn block, at the lowest resolution
+        gn("attn.norm", C)
+        for n in ("q", "k", "v", "proj_out"):
+            conv("attn." + n, C, C, 1)
     for i in range(7):
         if i in (0, 3):
             rb(f"up.seq.{i}.0", 2 * C, C)
@@ -70,7 +74,7 @@ def param_specs(C=128, img_channels=1):
 
 
 def is_zero_init(name):
-    return ".out_layers.3." in name
+    return ".out_layers.3." in name or name.startswith("attn.proj_out.")
 
 
 def _align(n, a=64):
@@ -80,11 +84,12 @@ def _align(n, a=64):
 class ParamStore:
     """Flat fp32 parameter / gradient / Adam-state buffers on one device, plus named views."""
 
-    def __init__(self, C, device, img_channels=1):
+    def __init__(self, C, device, img_channels=1, attention=False):
         self.C = C
         self.img_channels = img_channels
+        self.attention = bool(attention)
         self.device = torch.device(device)
-        self.specs = param_specs(C, img_channels)
+        self.specs = param_specs(C, img_channels, attention)
         self.offsets = {}
         off = 0
         # the fused emb_layers block first: weights [12*C][2C] contiguous, then biases [12*C]

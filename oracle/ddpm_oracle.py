@@ -103,6 +103,19 @@ def resblock(sd, pre, x, emb):
     return x + h
 
 
+def attention_block(sd, pre, x):
+    """EXTENSION (no reference counterpart: simple_unet.py:16-72 has no attention; the north star / BASELINE.json
+    configs[4] ask for one): guided-diffusion's single-head AttentionBlock — x + proj(softmax(q k^T / sqrt(C)) v) with
+    q, k, v, proj 1x1 convolutions of GroupNorm(32, C)(x), proj zero-initialised.  "Parity unpinned": this function is the
+    only checker."""
+    B, C, H, W = x.shape
+    h = F.group_norm(x, 32, sd[pre + ".norm.weight"], sd[pre + ".norm.bias"], eps=1e-5)
+    q, k, v = (_conv(sd, f"{pre}.{n}", h, padding=0).reshape(B, C, H * W) for n in ("q", "k", "v"))
+    w = torch.softmax(torch.einsum("bct,bcs->bts", q, k) / math.sqrt(C), dim=-1)
+    a = torch.einsum("bts,bcs->bct", w, v).reshape(B, C, H, W)
+    return x + _conv(sd, pre + ".proj_out", a, padding=0)
+
+
 def embed(sd, logsnr, guide=None, cond_w=None):
     """simple_unet.py:45-64: time MLP (+ masked class-guide MLP) (+ cond_w MLP)."""
     e = _lin(sd, "time_embed.2", F.silu(_lin(sd, "time_embed.0", sincos_embedding(logsnr.float(), 64, 256))))
@@ -137,6 +150,8 @@ def unet_forward(sd, x, logsnr, guide=None, cond_w=None, taps=None):
         taps["emb"] = emb
         taps["down"] = h
     h = resblock(sd, "turn", h, emb)
+    if "attn.q.weight" in sd:  # extension: self-attention at the lowest-resolution level, after the turn block
+        h = attention_block(sd, "attn", h)
     if taps is not None:
         taps["turn"] = h
     for i in range(7):
@@ -284,7 +299,7 @@ def sample_loop(net, init_z, num_steps, sampler="noisy", mean_type="eps", cond_w
 
 
 # ----------------------------------------------------------------------------- helpers for tests / fixtures
-def param_shapes(C=128, img_channels=1):
+def param_shapes(C=128, img_channels=1, attention=False):
     """Appendix C of SURVEY.md: the 160 tensors of SimpleUnet(C) (keys without the 'net.' prefix), in
     registration order (simple_unet.py:16-42,87-186)."""
     E = 2 * C
@@ -322,6 +337,10 @@ def param_shapes(C=128, img_channels=1):
     rb("down.seq.5", C, C)
     conv("down.seq.6.conv", C, C, 3)
     rb("turn", C, C)
+    if attention:
+        gn("attn.norm", C)
+        for n in ("q", "k", "v", "proj_out"):
+            conv("attn." + n, C, C, 1)
     for i in range(7):
         if i in (0, 3):
             rb(f"up.seq.{i}.0", 2 * C, C)
@@ -333,12 +352,12 @@ def param_shapes(C=128, img_channels=1):
     return out
 
 
-def random_state_dict(seed, C=128, dtype=torch.float32, img_channels=1):
+def random_state_dict(seed, C=128, dtype=torch.float32, img_channels=1, attention=False):
     """Deterministic non-degenerate weights (the reference zero-inits every out_layers.3, simple_unet.py:172,
     which would hide conv2/GN2 bugs): fan-in scaled normals from a CPU generator, GN weights near 1."""
     g = torch.Generator().manual_seed(seed)
     sd = {}
-    for name, shape in param_shapes(C, img_channels):
+    for name, shape in param_shapes(C, img_channels, attention):
         if ".weight" in name and len(shape) == 1:  # GroupNorm gamma
             t = 1.0 + 0.1 * torch.randn(shape, generator=g)
         elif name.endswith(".bias"):
