@@ -359,7 +359,7 @@ def run_ours(args, rank, world, local_rank):
     def make_model(precision):
         torch.manual_seed(0)
         G = default_G(device=dev, mean_type="eps", sampler="noisy", timesteps=args.sample_steps, bs=B, graph=1,
-                      precision=precision, img_channels=args.img_channels, image_size=args.image_size)
+                      precision=precision, img_channels=args.img_channels, image_size=args.image_size, attention=args.attention)
         m = DiffusionModelB200(G)
         # reference init at seed 0, then a small fill of the zero-initialised convs so every layer does real work
         gen = torch.Generator().manual_seed(1)
@@ -646,7 +646,7 @@ def run_ours(args, rank, world, local_rank):
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": K, "warmup": W, "settle_steps": settle_steps,
         "ms_per_step": ms / K, "higher_is_better": True, "scaling": "strong" if args.config == 2 else "weak",
         "vs_baseline": None, "dtype": args.precision, "data": "synthetic",
-        "config": {"workload": (f"configs[4] (extension: no reference counterpart): DDPM UNet C=128 on 3x64x64, batch {B}/GPU "
+        "config": {"workload": (f"configs[4] (extension: no reference counterpart): DDPM UNet C=128 with self-attention at 16x16 on 3x64x64, batch {B}/GPU "
                                 f"{args.precision}, train step + {T}-step sampling of {n} img/GPU") if args.config == 4 else
                    workload_string(args) if args.config != 2 else
                    f"configs[2]: DDPM data-parallel training, bf16 ResBlock convs, GLOBAL batch {B * world} = {B}/GPU x {world}",
@@ -655,7 +655,7 @@ def run_ours(args, rank, world, local_rank):
                    "l2": "per-step working set (~22 MB/img of activations) >> 126 MB L2; no flush needed",
                    "settle": "1.5 s of untimed steps after the W warm-up steps, before each timed region"},
         "clocks": clocks.summary(t_wall0, t_wall2),
-        "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": B * (784 * 4 + 8), "d2h_bytes_per_step": 4,
+        "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": B * (C_img * S_img * S_img * 4 + 8), "d2h_bytes_per_step": 4,
                 "ms_per_step": ms_e2e / K, "last_loss": last,
                 # the other half of BASELINE.json's metric, through the public model.sample(n, y) with the result read back
                 "sampling": samp_api,
@@ -712,6 +712,7 @@ def main():
     ap.add_argument("--precision", default="tf32", choices=["tf32", "bf16"],
                     help="tensor-core operand type of the ResBlock convs (tf32 = configs[1], the headline)")
     ap.add_argument("--bf16-leg", type=int, default=1, help="also time the bf16 configuration (configs[2]) beside the headline")
+    ap.add_argument("--attention", type=int, default=0, help="1: the self-attention extension at the lowest-resolution level")
     ap.add_argument("--img-channels", type=int, default=1)
     ap.add_argument("--image-size", type=int, default=0, help="0 = 28 (the reference's MNIST shape)")
     ap.add_argument("--config", type=int, default=1, choices=[1, 2, 3, 4],
@@ -726,7 +727,7 @@ def main():
     nworld = world if world > 1 else max(1, args.gpus)
     if args.config == 4:
         # BASELINE.json configs[4]: 3 x 64 x 64, base 128 channels — an extension (the reference UNet is 1-channel, 28 x 28)
-        args.img_channels, args.image_size = 3, 64
+        args.img_channels, args.image_size, args.attention = 3, 64, 1
         args.batch = args.batch if args.batch != 512 else 64
         args.sample_n = min(args.sample_n, args.batch)
         args.small_n = args.gpu_baseline = 0

@@ -636,9 +636,13 @@ __global__ void __launch_bounds__(256) gn_stats_kernel(GnSrc s, float* __restric
   __syncthreads();
   const int p0 = blockIdx.x * pix_per_chunk;
   const int p1 = min(p0 + pix_per_chunk, s.HW);
+  // Shifted moments: sums of (x - K) and (x - K)^2 with K = the group's first element of this sample, so that
+  // var = E[(x-K)^2] - E[x-K]^2 does not cancel catastrophically when |mean| >> std (E[x^2] - mean^2 did)
+  const float K = ld_src(s, static_cast<size_t>(n) * s.HW, g * cpg).x;
   float sum = 0.f, sq = 0.f;
   for (int p = p0 + prow; p < p1; p += prows) {
-    const float4 v = ld_src(s, static_cast<size_t>(n) * s.HW + p, c);
+    float4 v = ld_src(s, static_cast<size_t>(n) * s.HW + p, c);
+    v.x -= K; v.y -= K; v.z -= K; v.w -= K;
     sum += (v.x + v.y) + (v.z + v.w);
     sq += (v.x * v.x + v.y * v.y) + (v.z * v.z + v.w * v.w);
   }
@@ -648,13 +652,15 @@ __global__ void __launch_bounds__(256) gn_stats_kernel(GnSrc s, float* __restric
   if (threadIdx.x < 64) atomicAdd(&acc[n * 64 + threadIdx.x], sh[threadIdx.x]);
 }
 
-__global__ void gn_finalize_kernel(float* __restrict__ stats, int n_groups, float inv_cnt, float eps) {
+__global__ void gn_finalize_kernel(GnSrc s, float* __restrict__ stats, int n_groups, float inv_cnt, float eps) {
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= n_groups) return;
+  const int n = i >> 5, g = i & 31;
+  const float K = ld_src(s, static_cast<size_t>(n) * s.HW, g * (s.C >> 5)).x;  // the shift gn_stats_kernel used
   const float2 a = *reinterpret_cast<const float2*>(stats + 2 * i);
-  const float mean = a.x * inv_cnt;
-  const float var = fmaxf(a.y * inv_cnt - mean * mean, 0.f);
-  *reinterpret_cast<float2*>(stats + 2 * i) = make_float2(mean, rsqrtf(var + eps));
+  const float d = a.x * inv_cnt;  // E[x - K]
+  const float var = fmaxf(a.y * inv_cnt - d * d, 0.f);
+  *reinterpret_cast<float2*>(stats + 2 * i) = make_float2(K + d, rsqrtf(var + eps));
 }
 
 __global__ void __launch_bounds__(256)
@@ -944,7 +950,7 @@ extern "C" int b200_gn_fwd(const b200_gn_args* a, void* ws, size_t ws_bytes, voi
   gn_stats_kernel<<<dim3(chunks, s.N), 256, 0, st>>>(s, a->stats, ppc);
   if (int r = after_launch("gn_stats_kernel")) return r;
   const int ng = s.N * 32;
-  gn_finalize_kernel<<<(ng + 255) / 256, 256, 0, st>>>(a->stats, ng, 1.0f / static_cast<float>(s.HW * (s.C >> 5)), a->eps);
+  gn_finalize_kernel<<<(ng + 255) / 256, 256, 0, st>>>(s, a->stats, ng, 1.0f / static_cast<float>(s.HW * (s.C >> 5)), a->eps);
   if (int r = after_launch("gn_finalize_kernel")) return r;
   const size_t total = static_cast<size_t>(s.N) * s.HW * (s.C / 4);
   gn_apply_kernel<<<ew_grid(total), 256, 0, st>>>(s, a->stats, a->gamma, a->beta, static_cast<float*>(a->y), a->silu, ymode);

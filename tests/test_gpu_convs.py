@@ -224,6 +224,26 @@ def test_gn_silu_fwd_bwd(lib, N, HW, C2):
     assert rel(dbet.cpu(), beta.grad) < 1e-4
 
 
+@pytest.mark.parametrize("HW", [784, 4096])
+def test_gn_large_mean_statistics(lib, HW):
+    """|mean| >> std (mean 300, std 0.5): the shared-memory kernels use a two-pass variance, the streaming path (HW = 4096)
+    shifted moments — E[x^2] - mean^2 would lose every digit of the variance here."""
+    g = torch.Generator().manual_seed(HW)
+    N, Cc = 2, 128
+    x = (300.0 + 0.5 * rn(g, N, Cc, HW))
+    gamma, beta = torch.ones(Cc), torch.zeros(Cc)
+    y = F.group_norm(x.double(), 32, gamma.double(), beta.double(), eps=1e-5)
+    x1 = x.permute(0, 2, 1).contiguous().to(DEV)
+    stats = torch.zeros(N, 64, device=DEV)
+    yd = torch.empty(N, HW, Cc, device=DEV)
+    a = lib.GnArgs(x=ptr(x1), x2=None, stats=ptr(stats), gamma=ptr(gamma.to(DEV)), beta=ptr(beta.to(DEV)), y=ptr(yd), N=N,
+                   HW=HW, C1=128, C2=0, x_ld=0, x2_ld=0, eps=1e-5, silu=0, round_tf32=0)
+    lib.call("b200_gn_fwd", a, stream())
+    xd = x.double().view(N, 32, -1)
+    assert rel(stats.cpu().view(N, 32, 2)[..., 1].double(), (xd.var(-1, unbiased=False) + 1e-5).rsqrt()) < 2e-4
+    assert rel(yd.cpu().permute(0, 2, 1).double(), y) < 2e-3  # (x - mean) itself carries fp32 cancellation at 300 +- 0.5
+
+
 # ------------------------------------------------------------------------------------------------ edge convs
 @pytest.mark.parametrize("N,H", [(3, 28), (2, 32), (1, 7)])
 def test_conv_in_fwd_bwd(lib, N, H):
