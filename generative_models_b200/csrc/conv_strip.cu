@@ -43,7 +43,6 @@ constexpr int kStripBytes = 58 * 1024;    // >= (256 + 2*Wp + 2 rounded up to wh
 constexpr int kTileM = 256;               // positions per CTA tile (the N of one UMMA)
 constexpr int kStripTail = 512 + 2 * 512 * 4;  // barriers + the two position tables
 constexpr int kStripSmem = 232448;             // the whole 227 KB opt-in maximum; strips first, the ring takes the rest
-constexpr int kStageBytes = 2 * 16384;         // epilogue staging: per column half, 32 positions x 128 channels x 4 B
 
 struct StripK {
   float* out;
@@ -75,7 +74,6 @@ struct StripK {
   int strip_alloc; // bytes between the two strip buffers (1 KB multiple)
   int split;       // filter tap before whose weight load the next chunk's strip is requested
   int nss;         // strip buffers in flight (2; more for flat layers)
-  int stage;       // epilogue stores go through a shared-memory staging buffer and one bulk copy per 32-position chunk
   int cl;          // launched as 2-CTA clusters: each weight tile is fetched once per pair (half by each CTA, multicast)
   int dbg;         // developer knobs (B200_STRIP_DBG): 1 = skip TMA loads (timing of the MMA issue path only)
 };
@@ -149,7 +147,6 @@ conv_strip_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
   uint64_t* acc_empty = acc_full + 2;  // [2]
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(acc_empty + 2);
   int* tab = reinterpret_cast<int*>(bars + 64);  // 512 B past the barriers, 16 B-aligned: [2 acc stages][m[256], n[256]]
-  uint8_t* stg_base = reinterpret_cast<uint8_t*>(tab) + 2 * 512 * 4;  // kStageBytes, present when a.stage
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
@@ -487,67 +484,6 @@ conv_strip_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
           }
         }
         tmem_ld_wait();
-        if (a.stage) {
-          // ---- staged stores.  The valid positions of a chunk are consecutive output rows (raster order == memory
-          // order once the halo positions are dropped), and an output row is 128 contiguous channels: the four quarter
-          // warps of this column half write their 128 B segments of every valid row into a [row][128 ch] staging buffer
-          // (one conflict-free st.shared per position instead of a predicated st.global with 64-bit address math), then
-          // ONE bulk copy moves the block.  fp32 rows first, then — same buffer — the bf16 copy when there is one.
-          const uint32_t sbuf = smem_u32(stg_base) + colhalf * (kStageBytes / 2);
-          const int bar_a = 2 + colhalf, bar_b = 4 + colhalf;
-          const bool leader = (quarter == 0) && (lane == 0);
-          int mf = -1, ml = -1;  // first / last valid output row of the chunk
-#pragma unroll
-          for (int j = 0; j < 32; j += 4) {
-            const int4 q = lds_int4(tm_s + (cb + j) * 4);
-            const int mq[4] = {q.x, q.y, q.z, q.w};
-#pragma unroll
-            for (int i = 0; i < 4; ++i) {
-              if (mq[i] >= 0) {
-                mf = mf < 0 ? mq[i] : mf;
-                ml = mq[i];
-              }
-            }
-          }
-          const uint32_t nv = mf < 0 ? 0u : static_cast<uint32_t>(ml - mf + 1);
-#pragma unroll
-          for (int j = 0; j < 32; ++j) add[j] += __uint_as_float(r[j]);  // the values; r[] is dead from here on
-          for (int pass = 0; pass < 2; ++pass) {
-            const bool bfp = pass == 1 || a.out_is_bf;  // this pass writes bf16 rows (256 B) instead of fp32 rows (512 B)
-            if (pass == 1 && (a.out_is_bf || !a.out_bf)) break;
-            // the previous bulk copy out of this buffer has finished reading it
-            if (leader) bulk_wait_read<0>();
-            asm volatile("bar.sync %0, 128;" ::"r"(bar_a) : "memory");
-            const uint32_t srow = sbuf + (bfp ? co * 2 : co * 4) - static_cast<uint32_t>(mf) * (bfp ? 256u : 512u);
-#pragma unroll
-            for (int j = 0; j < 32; j += 4) {
-              const int4 q = lds_int4(tm_s + (cb + j) * 4);  // re-read: 32 row indices in registers would spill
-              const int mq[4] = {q.x, q.y, q.z, q.w};
-#pragma unroll
-              for (int i = 0; i < 4; ++i) {
-                if (mq[i] < 0) continue;
-                if (bfp) {
-                  asm volatile("st.shared.u16 [%0], %1;" ::"r"(srow + mq[i] * 256), "h"(bf16_bits(add[j + i])) : "memory");
-                } else {
-                  const float o = a.round_out ? round_tf32(add[j + i]) : add[j + i];
-                  asm volatile("st.shared.f32 [%0], %1;" ::"r"(srow + mq[i] * 512), "f"(o) : "memory");
-                }
-              }
-            }
-            fence_proxy_async();  // generic-proxy writes -> visible to the bulk-copy (async proxy) read
-            asm volatile("bar.sync %0, 128;" ::"r"(bar_b) : "memory");
-            if (leader && nv) {
-              if (bfp) {
-                uint16_t* ob = a.out_is_bf ? reinterpret_cast<uint16_t*>(a.out) : a.out_bf;
-                bulk_store_s2g(ob + static_cast<size_t>(mf) * 128, sbuf, nv * 256u);
-              } else {
-                bulk_store_s2g(a.out + static_cast<size_t>(mf) * 128, sbuf, nv * 512u);
-              }
-              bulk_commit();
-            }
-          }
-          continue;
-        }
         if (!a.out_is_bf) {
 #pragma unroll
           for (int j = 0; j < 32; j += 4) {
@@ -585,7 +521,6 @@ conv_strip_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
       tc_fence_before();
       mbar_arrive(&acc_empty[as]);
     }
-    if (a.stage) bulk_wait_all<0>();  // (threads that issued nothing return at once) smem must outlive the copies
   }
   tc_fence_before();
   __syncthreads();
@@ -877,19 +812,7 @@ int conv_strip_launch(const b200_conv_args* a, void* stream) {
       if (nss_flat > kSSMax) nss_flat = kSSMax;
     }
     k.nss = flat ? nss_flat : 2;
-    // Epilogue staging (32 KB) when every output row is a dense run of 128 channels (out_ld == 128; the bf16 copy always
-    // is) and the weight ring keeps at least 3 slots (measured: 4 -> 3 two-tap slots costs nothing, 2 costs 7 %).
-    static int stage_on = -1;  // developer knob B200_STRIP_STAGE=0: per-lane global stores
-    if (stage_on < 0) {
-      const char* e = getenv("B200_STRIP_STAGE");
-      stage_on = e ? atoi(e) : 1;
-    }
-    k.stage = 0;
-    if (stage_on && a->out_ld == 128 && !cl) {
-      const int sb_staged = (kStripSmem - 1024 - kStripTail - kStageBytes - k.nss * k.strip_alloc) / (wpair ? 2 * kBTile : kBTile);
-      if (sb_staged >= 3) k.stage = 1;
-    }
-    int sb = (kStripSmem - 1024 - kStripTail - (k.stage ? kStageBytes : 0) - k.nss * k.strip_alloc) / (wpair ? 2 * kBTile : kBTile);
+    int sb = (kStripSmem - 1024 - kStripTail - k.nss * k.strip_alloc) / (wpair ? 2 * kBTile : kBTile);
     sb = sb > kSBMax ? kSBMax : sb;
     k.sb = sb > sb_cap ? sb_cap : sb;
     if (k.sb < 2) return fail_arg("conv_strip: no room for the weight ring");

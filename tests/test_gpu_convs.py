@@ -236,7 +236,8 @@ def test_gn_large_mean_statistics(lib, HW):
     x1 = x.permute(0, 2, 1).contiguous().to(DEV)
     stats = torch.zeros(N, 64, device=DEV)
     yd = torch.empty(N, HW, Cc, device=DEV)
-    a = lib.GnArgs(x=ptr(x1), x2=None, stats=ptr(stats), gamma=ptr(gamma.to(DEV)), beta=ptr(beta.to(DEV)), y=ptr(yd), N=N,
+    gd, bd = gamma.to(DEV), beta.to(DEV)  # (kept alive: the struct only holds raw pointers)
+    a = lib.GnArgs(x=ptr(x1), x2=None, stats=ptr(stats), gamma=ptr(gd), beta=ptr(bd), y=ptr(yd), N=N,
                    HW=HW, C1=128, C2=0, x_ld=0, x2_ld=0, eps=1e-5, silu=0, round_tf32=0)
     lib.call("b200_gn_fwd", a, stream())
     xd = x.double().view(N, 32, -1)
