@@ -5,6 +5,7 @@
 mkdir -p gpurun_out
 O=gpurun_out
 timeout 1500 python -m pytest tests -m gpu -q > $O/r02z_pytest_gpu.log 2>&1; echo "pytest rc=$?"; tail -4 $O/r02z_pytest_gpu.log
+timeout 300 python -c "import __graft_entry__ as g; g.smoke()" > $O/r02z_smoke.log 2>&1; echo "smoke rc=$?"; tail -2 $O/r02z_smoke.log
 timeout 900 python bench.py --gpus 1 --steps 20 --warmup 5 > $O/r02z_bench_n1.json 2> $O/r02z_bench_n1.err; echo "bench rc=$?"; tail -2 $O/r02z_bench_n1.err
 timeout 600 python bench.py --impl reference --gpus 1 --steps 20 --warmup 5 > $O/r02z_bench_reference.json 2> $O/r02z_bench_reference.err; echo "reference arm rc=$?"
 timeout 900 python tools/run_gms_main.py --synthetic-mnist --git-cwd -- --model diffusion_model --bs 512 --epochs 1 --mean_type eps --sampler noisy --timesteps 1000 --eval_heavy 0 --logdir /tmp/gms_logs > $O/r02z_gms_main_b512_T1000.log 2>&1; echo "gms.main rc=$?"; tail -4 $O/r02z_gms_main_b512_T1000.log
