@@ -2,15 +2,18 @@
 """bench.py — DDPM hot-path benchmark (BASELINE.json: train img/s and 1000-step sampled img/s on synthetic
 1x28x28 MNIST-shaped data).
 
-    python bench.py [--gpus N] [--steps K] [--warmup W]            # this repo's CUDA path
-    python bench.py --impl reference [...]                          # the reference algorithm on the host CPU cores
+    python bench.py [--gpus N] [--steps K] [--warmup W]            # this repo's CUDA path (configs[1], the default line)
+    python bench.py --impl reference [...]                          # the UNMODIFIED reference on the host CPU cores
+    python bench.py --config 2|3|4 [...]                            # the other BASELINE.json configs
     python -m torch.distributed.run --nproc-per-node N ... bench.py --gpus N ...   # N>1, one rank per GPU
 
 A "step" is one training step (label drop, eps/u draw, q_sample, UNet fwd, loss, UNet bwd, gradient allreduce,
 Adam) over one batch of `--batch` images per GPU (weak scaling).  `value` = images/s with the batch resident in HBM;
 `e2e` = the same through the public `train_step` with pinned host batches copied in and the loss read back every
-step.  The sampling leg (`sampling`) times the fused ancestral loop (`--sample-steps` steps, unguided) for
-`--sample-n` images per GPU, sharded with no communication.  One JSON line is printed by rank 0.
+step, plus (`e2e.sampling`) the 1000-step sampler through the public `sample(n, y)` with the images read back.
+`sampling` times the unguided fused ancestral loop for `--sample-n` images per GPU, sharded with no communication.
+`cpu_baseline` / `gpu_torch_baseline`: the unmodified reference (baseline/_ref) on the host cores and in torch eager on
+this GPU, measured in the same run.  One JSON line is printed by rank 0.
 """
 import argparse
 import json

@@ -70,7 +70,6 @@ def test_distillation_loss_and_grads_vs_reference_fixture(built_lib, golden, tmp
         assert rms_rel(grads[k].cpu(), g) < LOSS_GRAD_TOL, k
     assert all(grads[k].abs().max().item() > 0 for k in grads if k.startswith("cond_w_embed."))
     # the teacher is frozen
-    assert torch.equal(m.teacher_store.flat.cpu(), torch.cat([torch.zeros(0)]) if False else m.teacher_store.flat.cpu())
     before = m.teacher_store.flat.clone()
     m.train_step(dev(f["x"]), dev(f["y"]).clone())
     m.train_step(dev(f["x"]), dev(f["y"]).clone())
