@@ -126,7 +126,10 @@ def run_cpu_reference(steps, warmup, bs, sample_n, sample_steps, timesteps, time
 
 def cpu_sample_string(res, bs):
     t, s = res["train"], res.get("sampling")
-    out = (f"unmodified reference (gms.main load_model_and_data + the train loop's inner body, main.py:205-215) on CPU, "
+    what = ("unmodified reference (gms.main load_model_and_data + the train loop's inner body, main.py:205-215)"
+            if res.get("kind") != "port" else
+            "oracle port of the reference (oracle/ddpm_oracle.py + autograd + torch.optim.Adam; baseline/_ref absent on this box)")
+    out = (f"{what} on CPU, "
            f"{t['steps']} train_step calls at batch {bs} (BASELINE.json configs[0]), {res['threads']} torch threads, "
            f"{res.get('cpu', '')}, torch {res.get('torch', '')}")
     if s:
@@ -154,7 +157,7 @@ def run_reference(args, rank):
         "vs_baseline": None, "dtype": "f32", "data": "synthetic",
         "config": {"workload": workload_string(args), "mean_type": "eps", "sampler": "noisy", "timesteps": args.sample_steps,
                    "bounded_sample": f"batch {args.cpu_batch} per step on the host CPU (configs[0]'s batch) instead of {args.batch}"},
-        "cpu_baseline": {"value": rate, "unit": UNIT, "cores": res["threads"], "kind": "reference",
+        "cpu_baseline": {"value": rate, "unit": UNIT, "cores": res["threads"], "kind": res.get("kind", "reference"),
                          "sample": cpu_sample_string(res, args.cpu_batch)},
         "e2e": {"value": rate, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0,
                 "sampling": {"unguided_img_s": (smp.get("unguided") or {}).get("img_s_1000_steps"),
@@ -636,7 +639,7 @@ def run_ours(args, rank, world, local_rank):
     # same GPU, in torch eager (cuDNN / cuBLAS)
     cpu = run_cpu_reference(args.cpu_steps, 1, args.cpu_batch, 16, min(args.cpu_sample_steps, 6), T) if (world == 1 and args.config == 1) else None
     if cpu and "error" not in cpu:
-        cpu_baseline = {"value": cpu["train"]["img_s"], "unit": UNIT, "cores": cpu["threads"], "kind": "reference",
+        cpu_baseline = {"value": cpu["train"]["img_s"], "unit": UNIT, "cores": cpu["threads"], "kind": cpu.get("kind", "reference"),
                         "sample": cpu_sample_string(cpu, args.cpu_batch),
                         "sampling_img_s_unguided": ((cpu.get("sampling") or {}).get("unguided") or {}).get("img_s_1000_steps"),
                         "sampling_img_s_guided": ((cpu.get("sampling") or {}).get("guided") or {}).get("img_s_1000_steps")}

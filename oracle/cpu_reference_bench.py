@@ -26,6 +26,50 @@ if ROOT not in sys.path:
     sys.path.insert(0, ROOT)
 
 
+def port_main(a, threads):
+    """Fallback when the vendored reference is not on this machine: the same measurements on the oracle port — op for
+    op the same torch calls (oracle/ddpm_oracle.py, pinned to reference-generated fixtures), autograd + torch.optim.Adam."""
+    import torch
+    from oracle import ddpm_oracle as O
+
+    sd = {k: v.clone().requires_grad_(True) for k, v in O.random_state_dict(1).items()}
+    opt = torch.optim.Adam(list(sd.values()), lr=3e-4)
+    times, last = [], 0.0
+    for k in range(a.warmup + a.steps):
+        g = torch.Generator().manual_seed(k)
+        x = torch.rand(a.bs, 1, 28, 28, generator=g) * 2 - 1
+        y = torch.randint(0, 10, (a.bs,), generator=g)
+        t0 = time.perf_counter()
+        opt.zero_grad()
+        y[torch.rand(a.bs) < 0.1] = -1
+        loss, _, _ = O.training_loss(sd, x, y, torch.randn(x.shape), torch.rand(a.bs), "eps")
+        loss.backward()
+        opt.step()
+        last = float(loss.detach())
+        if k >= a.warmup:
+            times.append(time.perf_counter() - t0)
+    train = {"img_s": a.bs * len(times) / sum(times), "s_per_step": sum(times) / len(times), "batch": a.bs,
+             "steps": len(times), "last_loss": last}
+    samp = None
+    if a.sample_steps > 0 and a.sample_n > 0:
+        n, S = a.sample_n, a.sample_steps
+        sdn = {k: v.detach() for k, v in sd.items()}
+        y = torch.arange(n) % 10
+        init = torch.randn(n, 1, 28, 28)
+        noises = [torch.randn(n, 1, 28, 28) for _ in range(S)]
+        res = {}
+        with torch.no_grad():
+            net = lambda z, l, uncond: O.unet_forward(sdn, z, l, guide=(-torch.ones_like(y) if uncond else y))
+            for tag, cw in (("unguided", None), ("guided", 4.0 * torch.rand(n))):
+                t0 = time.perf_counter()
+                O.sample_loop(net, init, S, sampler="noisy", mean_type="eps", cond_w=cw, noises=noises)
+                dt = time.perf_counter() - t0
+                res[tag] = {"s_per_step": dt / S, "img_s_1000_steps": n / (dt / S * a.timesteps)}
+        samp = {"n": n, "measured_steps": S, "extrapolated_to_steps": a.timesteps, **res}
+    print(json.dumps({"train": train, "sampling": samp, "threads": threads, "cpu": "", "torch": torch.__version__,
+                      "cuda_visible": torch.cuda.is_available(), "reference_root": None, "kind": "port"}))
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--steps", type=int, default=20)
@@ -35,6 +79,9 @@ def main():
     ap.add_argument("--sample-steps", type=int, default=50)
     ap.add_argument("--timesteps", type=int, default=1000)
     ap.add_argument("--threads", type=int, default=0)
+    ap.add_argument("--port", action="store_true",
+                    help="time oracle/ddpm_oracle.py (the pinned restatement) instead of the reference; chosen automatically "
+                         "when baseline/_ref is absent")
     a = ap.parse_args()
 
     import warnings
@@ -44,6 +91,8 @@ def main():
 
     threads = a.threads or os.cpu_count() or 1
     torch.set_num_threads(threads)
+    if a.port or not R.available():
+        return port_main(a, threads)
     R.install(synthetic_mnist=True, n_train=max(a.bs * (a.steps + a.warmup + 1), 1024), n_test=max(a.bs, 64))
     tmp = tempfile.mkdtemp(prefix="gms_cpu_ref_")
     subprocess.run(["git", "init", "-q", tmp], check=False)  # common.dump_logger wants a git work tree (unused here)
