@@ -156,3 +156,25 @@ def test_launcher_registers_model_in_reference_registry():
     train, test = common.load_mnist(8, binarize=False)
     x, y = next(iter(train))
     assert x.shape == (8, 1, 28, 28) and x.min() >= -1 and x.max() <= 1 and y.dtype == torch.int64
+
+
+@pytest.mark.parametrize("mode", ["reference", "port"])
+def test_cpu_reference_arm_emits_the_bench_schema(mode):
+    """oracle/cpu_reference_bench.py — what `bench.py --impl reference` and the `cpu_baseline` leg run: the unmodified
+    reference through gms.main's own construction path (when tools/vendor_reference.sh has installed it into baseline/_ref),
+    else the oracle port.  Tiny sizes: this checks the plumbing, not a rate."""
+    import json
+    import subprocess
+    import sys
+    from oracle import reference_runtime as R
+    if mode == "reference" and not R.available():
+        pytest.skip("reference not vendored on this machine")
+    cmd = [sys.executable, os.path.join(ROOT, "oracle", "cpu_reference_bench.py"), "--steps", "1", "--warmup", "0", "--bs", "4",
+           "--sample-n", "2", "--sample-steps", "1", "--threads", "4"] + (["--port"] if mode == "port" else [])
+    r = subprocess.run(cmd, env=dict(os.environ, CUDA_VISIBLE_DEVICES=""), stdout=subprocess.PIPE, stderr=subprocess.PIPE,
+                       text=True, timeout=600)
+    assert r.returncode == 0, r.stderr[-2000:]
+    res = json.loads([ln for ln in r.stdout.splitlines() if ln.startswith("{")][-1])
+    assert res["train"]["img_s"] > 0 and res["train"]["batch"] == 4 and res["threads"] == 4
+    assert res["sampling"]["unguided"]["img_s_1000_steps"] > res["sampling"]["guided"]["img_s_1000_steps"] > 0
+    assert res.get("kind", "reference") == mode and res["cuda_visible"] is False
