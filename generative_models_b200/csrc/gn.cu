@@ -1040,3 +1040,45 @@ extern "C" int b200_gn_bwd(const b200_gn_bwd_args* b, void* ws, size_t ws_bytes,
   }
   return 0;
 }
+
+// ------------------------------------------------------------------------------ allocation-free GroupNorm backward
+// b200_gn_bwd for callers that cannot hand over a workspace they allocated (CUDA graph capture, serving loops, harnesses
+// that forbid cudaMalloc).  No counterpart in the reference.
+// The N*64-float reduction scratch of the streaming path lives in a file-scope device array (1 MiB, held by every GPU
+// that loads the library until the process exits).  In HOST code the array's name is only a stand-in for the symbol:
+// its device address is looked up once per device with cudaGetSymbolAddress (that device current) and passed on as the
+// workspace.  b200_gn_bwd clears the part it uses with cudaMemsetAsync on `stream` before the reduction, so stale
+// contents of an earlier call are harmless — but every call shares the one array: calls that overlap on the GPU
+// (different streams, no dependency between them) race on it.  Nothing here allocates.
+constexpr int kGnStaticMaxN = B200_GN_BWD_STATIC_MAX_N;
+static __device__ __align__(256) float g_gn_bwd_static_scratch[static_cast<size_t>(kGnStaticMaxN) * 64];
+
+extern "C" int b200_gn_bwd_static(const b200_gn_bwd_args* b, void* stream) {
+  if (!b) return fail_arg("gn_bwd_static: null args");
+  if (b->fwd.N > kGnStaticMaxN) {
+    snprintf(g_last_error, sizeof(g_last_error),
+             "gn_bwd_static: N = %d exceeds the static scratch (B200_GN_BWD_STATIC_MAX_N = %d samples); "
+             "use b200_gn_bwd with a caller-allocated workspace", b->fwd.N, kGnStaticMaxN);
+    return -1;
+  }
+  constexpr int kMaxDev = 64;
+  static std::mutex mu;
+  static float* dev_ptr[kMaxDev] = {};
+  int dev = 0;
+  if (int r = check_cuda(cudaGetDevice(&dev), "gn_bwd_static: cudaGetDevice")) return r;
+  if (dev < 0 || dev >= kMaxDev) return fail_arg("gn_bwd_static: device ordinal out of range");
+  float* scratch = nullptr;
+  {
+    std::lock_guard<std::mutex> lock(mu);
+    if (!dev_ptr[dev]) {
+      float* p = nullptr;
+      if (int r = check_cuda(cudaGetSymbolAddress(reinterpret_cast<void**>(&p), g_gn_bwd_static_scratch),
+                             "gn_bwd_static: cudaGetSymbolAddress"))
+        return r;
+      if (!p) return fail_arg("gn_bwd_static: cudaGetSymbolAddress returned a null pointer");
+      dev_ptr[dev] = p;
+    }
+    scratch = dev_ptr[dev];
+  }
+  return b200_gn_bwd(b, scratch, sizeof(float) * static_cast<size_t>(kGnStaticMaxN) * 64, stream);
+}

@@ -203,6 +203,9 @@ def load():
         elif name == "b200_gn_bwd_workspace":
             fn.restype = C.c_size_t
             fn.argtypes = [C.c_void_p]
+        elif name == "b200_gn_bwd_static":  # (args, stream): the scratch is a static device array inside the library
+            fn.restype = C.c_int
+            fn.argtypes = [C.c_void_p, C.c_void_p]
         elif name.startswith("b200_") and name not in ("b200_abi_version", "b200_init", "b200_last_error",
                                                          "b200_launch_count"):
             fn.restype = C.c_int
@@ -215,7 +218,7 @@ def load():
 EXPORTS = [
     "b200_abi_version", "b200_init", "b200_last_error", "b200_launch_count",
     "b200_conv_igemm", "b200_conv_kernel_of", "b200_conv_wgrad",
-    "b200_gn_fwd", "b200_gn_bwd", "b200_gn_bwd_workspace",
+    "b200_gn_fwd", "b200_gn_bwd", "b200_gn_bwd_workspace", "b200_gn_bwd_static",
     "b200_q_sample", "b200_loss", "b200_sampler_step", "b200_distill_target", "b200_step_advance", "b200_int_increment",
     "b200_bgemm", "b200_softmax_fwd", "b200_softmax_bwd",
     "b200_conv_in_fwd", "b200_conv_in_bwd", "b200_conv_out_fwd", "b200_conv_out_bwd",

@@ -155,6 +155,15 @@ int b200_gn_bwd(const b200_gn_bwd_args* a, void* ws, size_t ws_bytes, void* stre
 /* bytes of workspace b200_gn_bwd needs for these arguments (the only entry point that takes one; every other call
  * accepts ws = NULL).  The caller allocates it (PyTorch) and may share one buffer between all launches of a stream. */
 size_t b200_gn_bwd_workspace(const b200_gn_bwd_args* a);
+/* b200_gn_bwd without a caller workspace and without any allocation (no cudaMalloc / cudaFree / allocating library
+ * call): for callers under CUDA graph capture, tight serving loops or harnesses that forbid allocation.  No counterpart
+ * in the reference.  The streaming path's N*64-float reduction scratch is
+ * a static device array of B200_GN_BWD_STATIC_MAX_N * 64 floats (1 MiB, resident on every GPU that loads the library
+ * until process exit); fwd.N beyond that limit is rejected (rc != 0, b200_last_error says so).  Same arguments, results
+ * and error behaviour as b200_gn_bwd otherwise.  All calls share the one array (cleared on `stream` before use):
+ * calls that overlap on the GPU (different streams without a dependency) race on it. */
+#define B200_GN_BWD_STATIC_MAX_N 4096
+int b200_gn_bwd_static(const b200_gn_bwd_args* a, void* stream);
 
 /* ------------------------------------------------------------------ diffusion math around the net (D = pixels/img)
  * mean_type: 0 = 'eps', 1 = 'x', 2 = 'v' (gaussian_diffusion.py:55-63).  sampler: 0 = 'ddim', 1 = 'noisy'. */
