@@ -202,9 +202,13 @@ gn_fwd_fused_kernel(GnSrc s, float* __restrict__ stats, const float* __restrict_
     *reinterpret_cast<float2*>(stats + (static_cast<size_t>(n) * 32 + c / cpg) * 2) = make_float2(mean, rstd);
   const float4 sc = make_float4(rstd * ga.x, rstd * ga.y, rstd * ga.z, rstd * ga.w);
   // tf32: 0 = plain fp32, 1 = fp32 rounded to TF32, 2 = bf16 (y then holds 2-byte elements)
-  float* dst = y + static_cast<size_t>(n) * s.HW * s.C + c;
-  uint16_t* dstb = reinterpret_cast<uint16_t*>(y) + static_cast<size_t>(n) * s.HW * s.C + c;
-  for (int idx = tid; idx < total; idx += kGnThreads) {
+  // running output pointers: a thread's successive elements are kGnThreads / L pixels apart (see the backward kernel)
+  const size_t o0 = (static_cast<size_t>(n) * s.HW + tid / L) * s.C + c;
+  float* dst = y + o0;
+  uint16_t* dstb = reinterpret_cast<uint16_t*>(y) + o0;
+  const unsigned ostep = static_cast<unsigned>(kGnThreads / L) * static_cast<unsigned>(s.C);
+#pragma unroll 2
+  for (int idx = tid; idx < total; idx += kGnThreads, dst += ostep, dstb += ostep) {
     const float4 v = gn_smem[idx];
     float4 o;
     o.x = (v.x - mean) * sc.x + be.x;
@@ -219,12 +223,75 @@ gn_fwd_fused_kernel(GnSrc s, float* __restrict__ stats, const float* __restrict_
       }
     }
     if (tf32 == 2) {
-      *reinterpret_cast<uint2*>(dstb + static_cast<size_t>(idx / L) * s.C) = pack_bf16x4(o);
+      *reinterpret_cast<uint2*>(dstb) = pack_bf16x4(o);
     } else {
       if (tf32) o = round_tf32(o);
-      *reinterpret_cast<float4*>(dst + static_cast<size_t>(idx / L) * s.C) = o;
+      *reinterpret_cast<float4*>(dst) = o;
     }
   }
+}
+
+// Phase 2 of the shared-memory-resident backward kernels: dx = elem(idx) (+ add1 + add2) -> bf16 copy / fp32 store, and
+// the per-channel sums for the fused column sums.  Which optional tensors exist is a compile-time property of the loop
+// (NA add tensors, DX fp32 output, DXB bf16 copy): with run-time pointers every iteration carried four 64-bit null
+// tests, predicated pointer moves and the TF32 rounding of a value nobody stores — the ncu source view of the bf16-step
+// kernel charged 70 instructions to a float4 of this loop and 58 to one of phase 1, which computes the SiLU derivative.
+template <int T, int NA, bool DX, bool DXB, typename Elem>
+__device__ __forceinline__ void gn_bwd_phase2_loop(int tid, int total, Elem elem, const float* a1, unsigned a1step,
+                                                   const float* a2, unsigned a2step, float* dst, unsigned ostep,
+                                                   uint16_t* dstb, unsigned bstep, int round_dx, float cacc[4]) {
+#pragma unroll 2
+  for (int idx = tid; idx < total; idx += T) {
+    float4 o = elem(idx);
+    if (NA >= 1) {
+      const float4 a = __ldg(reinterpret_cast<const float4*>(a1));
+      o.x += a.x; o.y += a.y; o.z += a.z; o.w += a.w;
+      a1 += a1step;
+    }
+    if (NA >= 2) {
+      const float4 a = __ldg(reinterpret_cast<const float4*>(a2));
+      o.x += a.x; o.y += a.y; o.z += a.z; o.w += a.w;
+      a2 += a2step;
+    }
+    if (DXB) {
+      *reinterpret_cast<uint2*>(dstb) = pack_bf16x4(o);
+      dstb += bstep;
+    }
+    if (DX) {
+      if (round_dx) o = round_tf32(o);
+      *reinterpret_cast<float4*>(dst) = o;
+      dst += ostep;
+    }
+    cacc[0] += o.x; cacc[1] += o.y; cacc[2] += o.z; cacc[3] += o.w;
+  }
+}
+// a1 / a2 / dst / dstb: this thread's running pointers (NULL = absent; a2 without a1 is passed as a1)
+template <int T, typename Elem>
+__device__ __forceinline__ void gn_bwd_phase2(int tid, int total, Elem elem, const float* a1, unsigned a1step,
+                                              const float* a2, unsigned a2step, float* dst, unsigned ostep, uint16_t* dstb,
+                                              unsigned bstep, int round_dx, float cacc[4]) {
+  if (!a1 && a2) {
+    a1 = a2;
+    a1step = a2step;
+    a2 = nullptr;
+  }
+  const int na = a1 ? (a2 ? 2 : 1) : 0;
+#define GN_P2(NA, DX, DXB) \
+  gn_bwd_phase2_loop<T, NA, DX, DXB>(tid, total, elem, a1, a1step, a2, a2step, dst, ostep, dstb, bstep, round_dx, cacc)
+  if (dst && dstb) {
+    if (na == 0) GN_P2(0, true, true);
+    else if (na == 1) GN_P2(1, true, true);
+    else GN_P2(2, true, true);
+  } else if (dst) {
+    if (na == 0) GN_P2(0, true, false);
+    else if (na == 1) GN_P2(1, true, false);
+    else GN_P2(2, true, false);
+  } else if (dstb) {
+    if (na == 0) GN_P2(0, false, true);
+    else if (na == 1) GN_P2(1, false, true);
+    else GN_P2(2, false, true);
+  }
+#undef GN_P2
 }
 
 // ---------------------------------------------------------------------------------------------------- fused backward
@@ -347,11 +414,10 @@ gn_bwd_fused_kernel(GnSrc s, const float* __restrict__ stats, const float* __res
   if (a2) a2 += static_cast<size_t>(pix0) * add2_ld;
   const unsigned ostep = PSTEP * s.C, bstep = PSTEP * dxb_c;  // elements; < 2^32 (PSTEP <= 128 pixels)
   const unsigned a1step = PSTEP * add1_ld, a2step = PSTEP * add2_ld;
-  float4 cacc = make_float4(0.f, 0.f, 0.f, 0.f);  // per-channel sum of dx over this sample's pixels (fused colsum)
+  float ca[4] = {0.f, 0.f, 0.f, 0.f};  // per-channel sum of dx over this sample's pixels (fused colsum)
   const float k1 = -m1 * rstd, k2 = -m2 * rstd;
   const float gr[4] = {ga[0] * rstd, ga[1] * rstd, ga[2] * rstd, ga[3] * rstd};
-#pragma unroll 2
-  for (int idx = tid; idx < total; idx += kGnThreads) {
+  auto elem = [&](int idx) {
     const float4 xh = xs[idx];
     const float4 du = ds[idx];
     float4 o;
@@ -359,33 +425,13 @@ gn_bwd_fused_kernel(GnSrc s, const float* __restrict__ stats, const float* __res
     o.y = fmaf(xh.y, k2, fmaf(du.y, gr[1], k1));
     o.z = fmaf(xh.z, k2, fmaf(du.z, gr[2], k1));
     o.w = fmaf(xh.w, k2, fmaf(du.w, gr[3], k1));
-    if (a1) {
-      const float4 a = __ldg(reinterpret_cast<const float4*>(a1));
-      o.x += a.x; o.y += a.y; o.z += a.z; o.w += a.w;
-      a1 += a1step;
-    }
-    if (a2) {
-      const float4 a = __ldg(reinterpret_cast<const float4*>(a2));
-      o.x += a.x; o.y += a.y; o.z += a.z; o.w += a.w;
-      a2 += a2step;
-    }
-    if (dstb) {
-      *reinterpret_cast<uint2*>(dstb) = pack_bf16x4(o);
-      dstb += bstep;
-    }
-    if (round_dx) o = round_tf32(o);
-    if (dst) {
-      *reinterpret_cast<float4*>(dst) = o;
-      dst += ostep;
-    }
-    cacc.x += o.x; cacc.y += o.y; cacc.z += o.z; cacc.w += o.w;
-  }
+    return o;
+  };
+  gn_bwd_phase2<kGnThreads>(tid, total, elem, a1, a1step, a2, a2step, dst, ostep, dstb, bstep, round_dx, ca);
   // fused column sums of dx (bias gradient of the convolution that produced x, and the per-sample gradient of the
   // timestep-embedding broadcast add): this CTA owns all pixels of (n, channel slice)
-  if (cs.c > 0 && c0 < cs.c) {  // uniform per CTA
-    float ca[4] = {cacc.x, cacc.y, cacc.z, cacc.w};
+  if (cs.c > 0 && c0 < cs.c)  // uniform per CTA
     gn_bwd_colsum<CS, kGnThreads / 32>(ca, tid, lane, l, wred, n, c0, cs);
-  }
 }
 
 // ---------------------------------------------------------------------------------------------------- bf16 sources
@@ -402,12 +448,15 @@ __device__ __forceinline__ float4 widen_bf16x4(uint2 r) {
 template <int CS, int EB, int T>
 __device__ __forceinline__ void gn_stage(uint8_t* dst, const void* base, int ld, int HW, int tid) {
   constexpr int CPR = CS * EB / 16;  // 16 B chunks per pixel row of the slice
-  const uint8_t* b = static_cast<const uint8_t*>(base);
+  static_assert(T % CPR == 0, "a thread keeps its chunk column");
+  // chunk i = tid + k*T: pixel tid / CPR + k * (T / CPR), chunk column tid % CPR — running pointers, no per-chunk division
+  const uint8_t* src = static_cast<const uint8_t*>(base) + (static_cast<size_t>(tid / CPR) * ld * EB + (tid % CPR) * 16);
+  const unsigned sstep = static_cast<unsigned>(T / CPR) * static_cast<unsigned>(ld) * EB;
+  uint32_t da = static_cast<uint32_t>(__cvta_generic_to_shared(dst)) + static_cast<uint32_t>(tid) * 16u;
   const int total = HW * CPR;
-  for (int i = tid; i < total; i += T) {
-    const int pix = i / CPR, ch = i - pix * CPR;
-    cp_async16(dst + static_cast<size_t>(i) * 16, b + (static_cast<size_t>(pix) * ld * EB + ch * 16));
-  }
+#pragma unroll 2
+  for (int i = tid; i < total; i += T, src += sstep, da += T * 16)
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(da), "l"(src) : "memory");
 }
 template <int EB>
 __device__ __forceinline__ float4 gn_elem(const uint8_t* raw, int idx) {
@@ -471,9 +520,13 @@ gn_fwd_bfx_kernel(GnSrc s, float* __restrict__ stats, const float* __restrict__ 
   if (tid < L && (!pair || !(tid & 1)))
     *reinterpret_cast<float2*>(stats + (static_cast<size_t>(n) * 32 + c / cpg) * 2) = make_float2(mean, rstd);
   const float4 sc = make_float4(rstd * ga.x, rstd * ga.y, rstd * ga.z, rstd * ga.w);
-  float* dst = y + static_cast<size_t>(n) * s.HW * s.C + c;
-  uint16_t* dstb = reinterpret_cast<uint16_t*>(y) + static_cast<size_t>(n) * s.HW * s.C + c;
-  for (int idx = tid; idx < total; idx += T) {
+  // running output pointers: a thread's successive elements are T / L pixels apart (see the backward kernels)
+  const size_t o0 = (static_cast<size_t>(n) * s.HW + tid / L) * s.C + c;
+  float* dst = y + o0;
+  uint16_t* dstb = reinterpret_cast<uint16_t*>(y) + o0;
+  const unsigned ostep = static_cast<unsigned>(T / L) * static_cast<unsigned>(s.C);
+#pragma unroll 2
+  for (int idx = tid; idx < total; idx += T, dst += ostep, dstb += ostep) {
     const float4 v = gn_elem<2>(raw, idx);
     float4 o;
     o.x = (v.x - mean) * sc.x + be.x;
@@ -484,17 +537,20 @@ gn_fwd_bfx_kernel(GnSrc s, float* __restrict__ stats, const float* __restrict__ 
       o.x = silu_fast(o.x); o.y = silu_fast(o.y); o.z = silu_fast(o.z); o.w = silu_fast(o.w);
     }
     if (tf32 == 2) {
-      *reinterpret_cast<uint2*>(dstb + static_cast<size_t>(idx / L) * s.C) = pack_bf16x4(o);
+      *reinterpret_cast<uint2*>(dstb) = pack_bf16x4(o);
     } else {
       if (tf32) o = round_tf32(o);
-      *reinterpret_cast<float4*>(dst + static_cast<size_t>(idx / L) * s.C) = o;
+      *reinterpret_cast<float4*>(dst) = o;
     }
   }
 }
 
 // XB / DB: bytes per element of x / dy (2 or 4; at least one is 2)
+// (Parking du over dy in shared memory, in dy's format, so that phase 2 skips the SiLU derivative: another 3-8 % — 88 ->
+// 81 us at 28x28, 128 bf16 channels — but du is then rounded to bf16 once more and the fused column sums move by 1e-3;
+// not taken.)
 template <int CS, int T, int XB, int DB>
-__global__ void __launch_bounds__(T, 1024 / T)
+__global__ void __launch_bounds__(T, (XB + DB == 4) ? 1024 / T : 768 / T)  // CTAs/SM the slice footprint allows: 4 or 3
 gn_bwd_raw_kernel(GnSrc s, const float* __restrict__ stats, const float* __restrict__ gamma,
                   const float* __restrict__ beta, const void* __restrict__ dy, float* __restrict__ dx,
                   const float* __restrict__ add1, int add1_ld, const float* __restrict__ add2, int add2_ld, int add_c,
@@ -547,6 +603,7 @@ gn_bwd_raw_kernel(GnSrc s, const float* __restrict__ stats, const float* __restr
     const float xv[4] = {v.x, v.y, v.z, v.w};
     const float dv[4] = {d.x, d.y, d.z, d.w};
 #pragma unroll
+#pragma unroll
     for (int j = 0; j < 4; ++j) {
       const float xh = fmaf(xv[j], rstd, nmr);
       const float du = silu ? dv[j] * dsilu_fast(fmaf(xh, ga[j], be[j])) : dv[j];
@@ -579,8 +636,7 @@ gn_bwd_raw_kernel(GnSrc s, const float* __restrict__ stats, const float* __restr
   const float k1 = -m1 * rstd, k2 = -m2 * rstd;
   const float gr[4] = {ga[0] * rstd, ga[1] * rstd, ga[2] * rstd, ga[3] * rstd};
   float cacc[4] = {0.f, 0.f, 0.f, 0.f};
-#pragma unroll 2
-  for (int idx = tid; idx < total; idx += T) {
+  auto elem = [&](int idx) {
     const float4 v = gn_elem<XB>(xraw, idx);
     const float4 d = gn_elem<DB>(draw, idx);
     const float xv[4] = {v.x, v.y, v.z, v.w};
@@ -592,28 +648,9 @@ gn_bwd_raw_kernel(GnSrc s, const float* __restrict__ stats, const float* __restr
       const float du = silu ? dv[j] * dsilu_fast(fmaf(xh, ga[j], be[j])) : dv[j];
       ov[j] = fmaf(xh, k2, fmaf(du, gr[j], k1));  // rstd * (du * gamma - m1 - xhat * m2)
     }
-    float4 o = make_float4(ov[0], ov[1], ov[2], ov[3]);
-    if (a1) {
-      const float4 a = __ldg(reinterpret_cast<const float4*>(a1));
-      o.x += a.x; o.y += a.y; o.z += a.z; o.w += a.w;
-      a1 += a1step;
-    }
-    if (a2) {
-      const float4 a = __ldg(reinterpret_cast<const float4*>(a2));
-      o.x += a.x; o.y += a.y; o.z += a.z; o.w += a.w;
-      a2 += a2step;
-    }
-    if (dstb) {
-      *reinterpret_cast<uint2*>(dstb) = pack_bf16x4(o);
-      dstb += bstep;
-    }
-    if (round_dx) o = round_tf32(o);
-    if (dst) {
-      *reinterpret_cast<float4*>(dst) = o;
-      dst += ostep;
-    }
-    cacc[0] += o.x; cacc[1] += o.y; cacc[2] += o.z; cacc[3] += o.w;
-  }
+    return make_float4(ov[0], ov[1], ov[2], ov[3]);
+  };
+  gn_bwd_phase2<T>(tid, total, elem, a1, a1step, a2, a2step, dst, ostep, dstb, bstep, round_dx, cacc);
   if (cs.c > 0 && c0 < cs.c)  // uniform per CTA
     gn_bwd_colsum<CS, T / 32>(cacc, tid, lane, l, wred, n, c0, cs);
 }
