@@ -31,6 +31,8 @@
 
 #include <stdlib.h>
 
+#include <type_traits>
+
 #include <mutex>
 
 namespace b200 {
@@ -119,9 +121,19 @@ __device__ __forceinline__ int lds_int(uint32_t saddr) {
 }
 
 // *p = v when m >= 0, as one predicated store
-__device__ __forceinline__ void st_if_nonneg(float* p, float v, int m) {
+__device__ __forceinline__ void st_if_nonneg(uint64_t p, float v, int m) {
   asm volatile("{\n\t.reg .pred q;\n\tsetp.ge.s32 q, %2, 0;\n\t@q st.global.f32 [%0], %1;\n\t}" ::"l"(p), "f"(v), "r"(m)
                : "memory");
+}
+// base + m * ld_bytes as ONE instruction (IMAD.WIDE.U32): the epilogue forms three such addresses per position (residual
+// row, fp32 row, bf16 row); written as size_t(max(m, 0)) * ld + co the compiler spent 7 instructions on each load
+// address and 14 on each store (ncu source view, bf16 step: 1 106 instructions per 32-position chunk per warp, the two
+// epilogue warps of a scheduler issue-bound).  A negative m (halo position) gives a wild address that is only ever
+// used by a predicated-off store.
+__device__ __forceinline__ uint64_t row_addr(uint64_t base, int m, uint32_t ld_bytes) {
+  uint64_t p;
+  asm("mad.wide.u32 %0, %1, %2, %3;" : "=l"(p) : "r"(m), "r"(ld_bytes), "l"(base));
+  return p;
 }
 
 template <bool BF16>
@@ -441,18 +453,22 @@ conv_strip_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
       // exposed four times per tile.  The position table is re-read from shared memory instead of living in 32
       // registers, which is what makes room for the second buffer under the 168-register cap.
       const float* res_co = a.residual ? a.residual + co : nullptr;
+      const uint64_t res_base = reinterpret_cast<uint64_t>(res_co);
+      const uint32_t res_ldb = static_cast<uint32_t>(a.res_ld) * 4u;
       float nxt[32];
       auto fetch_residual = [&](int cb) {
 #pragma unroll
         for (int j = 0; j < 32; j += 4) {
           const int4 q = lds_int4(tm_s + (cb + j) * 4);
           // unconditional (halo positions read row 0): predicates would serialise the loads
-          nxt[j] = __ldg(res_co + static_cast<size_t>(q.x < 0 ? 0 : q.x) * a.res_ld);
-          nxt[j + 1] = __ldg(res_co + static_cast<size_t>(q.y < 0 ? 0 : q.y) * a.res_ld);
-          nxt[j + 2] = __ldg(res_co + static_cast<size_t>(q.z < 0 ? 0 : q.z) * a.res_ld);
-          nxt[j + 3] = __ldg(res_co + static_cast<size_t>(q.w < 0 ? 0 : q.w) * a.res_ld);
+          nxt[j] = __ldg(reinterpret_cast<const float*>(row_addr(res_base, max(q.x, 0), res_ldb)));
+          nxt[j + 1] = __ldg(reinterpret_cast<const float*>(row_addr(res_base, max(q.y, 0), res_ldb)));
+          nxt[j + 2] = __ldg(reinterpret_cast<const float*>(row_addr(res_base, max(q.z, 0), res_ldb)));
+          nxt[j + 3] = __ldg(reinterpret_cast<const float*>(row_addr(res_base, max(q.w, 0), res_ldb)));
         }
       };
+      const uint64_t out_base = reinterpret_cast<uint64_t>(a.out + co);
+      const uint32_t out_ldb = static_cast<uint32_t>(a.out_ld) * 4u;
       if (res_co) fetch_residual(colhalf * 128);
       mbar_wait(&acc_full[as], (tc >> 1) & 1);
       tc_fence_after();
@@ -485,36 +501,42 @@ conv_strip_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
         }
         tmem_ld_wait();
         if (!a.out_is_bf) {
+          auto store_f32 = [&](auto rnd) {  // rnd: compile-time "round to TF32" (uniform for the launch)
 #pragma unroll
-          for (int j = 0; j < 32; j += 4) {
-            const int4 q = lds_int4(tm_s + (cb + j) * 4);
-            const int mq[4] = {q.x, q.y, q.z, q.w};
+            for (int j = 0; j < 32; j += 4) {
+              const int4 q = lds_int4(tm_s + (cb + j) * 4);
+              const int mq[4] = {q.x, q.y, q.z, q.w};
 #pragma unroll
-            for (int i = 0; i < 4; ++i) {
-              // predicated store (a branch per position costs more than the store)
-              const float v = __uint_as_float(r[j + i]) + add[j + i];
-              st_if_nonneg(a.out + static_cast<size_t>(mq[i] < 0 ? 0 : mq[i]) * a.out_ld + co,
-                           a.round_out ? round_tf32(v) : v, mq[i]);
+              for (int i = 0; i < 4; ++i) {
+                // predicated store (a branch per position costs more than the store)
+                const float v = __uint_as_float(r[j + i]) + add[j + i];
+                st_if_nonneg(row_addr(out_base, mq[i], out_ldb), decltype(rnd)::value ? round_tf32(v) : v, mq[i]);
+              }
             }
-          }
+          };
+          if (a.round_out) store_f32(std::true_type{});
+          else store_f32(std::false_type{});
         }
         uint16_t* ob = a.out_is_bf ? reinterpret_cast<uint16_t*>(a.out) : a.out_bf;
         if (ob) {
           // bf16 stores: neighbouring lanes (channels c, c+1) trade one value per position pair so that every lane
           // stores a 4 B word {c, c+1} — even lanes for position j, odd lanes for j+1 — instead of 2 B per lane:
           // half the store instructions, whole 32 B sectors per pixel
-          const int obld = a.out_is_bf ? a.out_ld : 128;
+          const uint32_t obldb = static_cast<uint32_t>(a.out_is_bf ? a.out_ld : 128) * 2u;
+          const uint64_t ob_base = reinterpret_cast<uint64_t>(ob + (co & ~1));
           const int odd = lane & 1;
+          // pack this channel's two positions first, trade the packed word, pick the halves with one byte permute
+          // (even lane: {own j, neighbour j}; odd lane: {neighbour j+1, own j+1}) — 3 instructions per pair, was 5
+          const uint32_t sel = odd ? 0x3276u : 0x5410u;
 #pragma unroll
           for (int j = 0; j < 32; j += 2) {
             const float v0 = __uint_as_float(r[j]) + add[j], v1 = __uint_as_float(r[j + 1]) + add[j + 1];
-            const float got = __shfl_xor_sync(0xffffffffu, odd ? v0 : v1, 1);
-            const float lo = odd ? got : v0, hi = odd ? v1 : got;
-            uint32_t wrd;
-            asm("cvt.rn.bf16x2.f32 %0, %1, %2;" : "=r"(wrd) : "f"(hi), "f"(lo));
+            uint32_t own;
+            asm("cvt.rn.bf16x2.f32 %0, %1, %2;" : "=r"(own) : "f"(v1), "f"(v0));  // low half = position j
+            const uint32_t nbr = __shfl_xor_sync(0xffffffffu, own, 1);
+            const uint32_t wrd = __byte_perm(own, nbr, sel);
             const int m = lds_int(tm_s + (cb + j + odd) * 4);
-            st_if_nonneg(reinterpret_cast<float*>(ob + static_cast<size_t>(m < 0 ? 0 : m) * obld + (co & ~1)),
-                         __uint_as_float(wrd), m);
+            st_if_nonneg(row_addr(ob_base, m, obldb), __uint_as_float(wrd), m);
           }
         }
       }

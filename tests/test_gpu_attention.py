@@ -83,8 +83,10 @@ def test_softmax_fwd_bwd(built_lib):
 def test_unet_with_attention_vs_oracle(built_lib, S, Ci, prec):
     from generative_models_b200.model import DiffusionModelB200, default_G
     from generative_models_b200.plan import UNetPlan
+    # cf_drop_prob = 0: train_step's label drop draws from the global CPU RNG (diffusion_model.py:67); the oracle loss
+    # below is computed for the labels as given (with the default 0.1 and three samples the test failed one run in four)
     G = default_G(device=DEV, mean_type="eps", sampler="noisy", timesteps=3, precision=prec, img_channels=Ci, image_size=S,
-                  attention=1)
+                  attention=1, cf_drop_prob=0.0)
     m = DiffusionModelB200(G)
     assert len(m.state_dict()) == 170 and m.state_dict()["net.attn.proj_out.weight"].abs().max().item() == 0.0  # zero-init
     sd0 = O.random_state_dict(1, img_channels=Ci, attention=True)

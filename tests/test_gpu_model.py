@@ -466,7 +466,10 @@ def test_three_channel_images_vs_oracle(built_lib, S, prec):
     Forward, every parameter gradient of a linear loss, one train step and a 3-step sample through the public API."""
     from generative_models_b200.model import DiffusionModelB200, default_G
     from generative_models_b200.plan import UNetPlan
-    G = default_G(device=DEV, mean_type="eps", sampler="noisy", timesteps=3, precision=prec, img_channels=3, image_size=S)
+    # cf_drop_prob = 0: train_step's label drop draws from the global CPU RNG (diffusion_model.py:67); the oracle loss
+    # below is computed for the labels as given
+    G = default_G(device=DEV, mean_type="eps", sampler="noisy", timesteps=3, precision=prec, img_channels=3, image_size=S,
+                  cf_drop_prob=0.0)
     m = DiffusionModelB200(G)
     sd0 = O.random_state_dict(1, img_channels=3)
     m.net.load_state_dict(sd0)
