@@ -35,6 +35,35 @@ struct GnSrc {
   int bf;            // x / x2 hold bf16 (ld in elements); fused kernels only
 };
 
+// nn.Dropout(p) between the SiLU and the convolution of a ResBlock's out_layers (simple_unet.py:168-172), fused into the
+// GroupNorm kernels: y = silu(...) * keep / (1 - p) in the forward, dy * keep / (1 - p) in front of the SiLU derivative
+// in the backward.  keep is a pure function of (seed, step, position of the float4 in the dense [N*HW][C] output), so
+// forward and backward agree without a stored mask, and a captured graph draws a fresh mask every replay through the
+// device step counter.  16 random bits per element: p is quantised to 1/65536 and `scale` is 1 / (1 - p quantised).
+struct GnDrop {
+  uint32_t thr;     // element kept when its 16 bits >= thr; 0 = dropout off
+  float scale;
+  uint32_t seed;    // per layer
+  const int* step;  // optional device counter mixed into the seed
+};
+__device__ __forceinline__ uint32_t fmix32(uint32_t h) {  // murmur3 finaliser
+  h ^= h >> 16; h *= 0x85EBCA6Bu; h ^= h >> 13; h *= 0xC2B2AE35u; h ^= h >> 16;
+  return h;
+}
+__device__ __forceinline__ uint32_t drop_seed(const GnDrop& d) {
+  return fmix32(d.seed ^ fmix32(0x9E3779B9u * static_cast<uint32_t>(d.step ? __ldg(d.step) : 0) + 0x7F4A7C15u));
+}
+// v * keep * scale for the float4 number e4 of the output tensor
+__device__ __forceinline__ float4 drop_apply(float4 v, const GnDrop& d, uint32_t seed, uint32_t e4) {
+  const uint32_t a = fmix32(e4 * 0x9E3779B1u + seed);
+  const uint32_t b = fmix32(a + 0x632BE5ABu);
+  v.x = (a & 0xffffu) >= d.thr ? v.x * d.scale : 0.f;
+  v.y = (a >> 16) >= d.thr ? v.y * d.scale : 0.f;
+  v.z = (b & 0xffffu) >= d.thr ? v.z * d.scale : 0.f;
+  v.w = (b >> 16) >= d.thr ? v.w * d.scale : 0.f;
+  return v;
+}
+
 __device__ __forceinline__ float4 ld_src(const GnSrc& s, size_t pix, int c) {
   return (c < s.C1) ? *reinterpret_cast<const float4*>(s.x + pix * s.ld1 + c)
                     : *reinterpret_cast<const float4*>(s.x2 + pix * s.ld2 + (c - s.C1));
@@ -138,10 +167,10 @@ __device__ __forceinline__ void gn_bwd_colsum(float (&ca)[4], int tid, int lane,
 
 // ---------------------------------------------------------------------------------------------------- fused forward
 // grid = N * (C / CS); block 256; dynamic smem = HW * CS * 4 bytes.
-template <int CS, int kGnThreads>
+template <int CS, int kGnThreads, bool DROP>
 __global__ void __launch_bounds__(kGnThreads)
 gn_fwd_fused_kernel(GnSrc s, float* __restrict__ stats, const float* __restrict__ gamma, const float* __restrict__ beta,
-                    float* __restrict__ y, float eps, int silu, int tf32) {
+                    float* __restrict__ y, float eps, int silu, int tf32, GnDrop dp) {
   extern __shared__ float4 gn_smem[];
   __shared__ float fred[2][kGnThreads / 32][8];  // [sum | centred squares][warp][group of the slice]
   constexpr int L = CS / 4;  // float4 lanes per pixel of the slice
@@ -207,8 +236,10 @@ gn_fwd_fused_kernel(GnSrc s, float* __restrict__ stats, const float* __restrict_
   float* dst = y + o0;
   uint16_t* dstb = reinterpret_cast<uint16_t*>(y) + o0;
   const unsigned ostep = static_cast<unsigned>(kGnThreads / L) * static_cast<unsigned>(s.C);
+  const uint32_t dseed = DROP ? drop_seed(dp) : 0u;
+  uint32_t e4 = static_cast<uint32_t>(o0 >> 2);
 #pragma unroll 2
-  for (int idx = tid; idx < total; idx += kGnThreads, dst += ostep, dstb += ostep) {
+  for (int idx = tid; idx < total; idx += kGnThreads, dst += ostep, dstb += ostep, e4 += ostep >> 2) {
     const float4 v = gn_smem[idx];
     float4 o;
     o.x = (v.x - mean) * sc.x + be.x;
@@ -222,6 +253,7 @@ gn_fwd_fused_kernel(GnSrc s, float* __restrict__ stats, const float* __restrict_
         o.x = silu_f(o.x); o.y = silu_f(o.y); o.z = silu_f(o.z); o.w = silu_f(o.w);
       }
     }
+    if (DROP) o = drop_apply(o, dp, dseed, e4);
     if (tf32 == 2) {
       *reinterpret_cast<uint2*>(dstb) = pack_bf16x4(o);
     } else {
@@ -301,13 +333,13 @@ __device__ __forceinline__ void gn_bwd_phase2(int tid, int total, Elem elem, con
 // place by xhat and du).  A variant that kept only dy in smem and re-read x through L2 (twice the CTAs per SM) measured
 // slower (201 vs 159 us at N512 HW784 C128): the register-staged global loads of phase 1 do not stay in flight the way
 // the cp.async bulk does.
-template <int CS, int kGnThreads>
+template <int CS, int kGnThreads, bool DROP>
 __global__ void __launch_bounds__(kGnThreads, 1024 / kGnThreads)  // <= 64 registers: two 512-thread CTAs per SM
 gn_bwd_fused_kernel(GnSrc s, const float* __restrict__ stats, const float* __restrict__ gamma,
                     const float* __restrict__ beta, const float* __restrict__ dy, float* __restrict__ dx,
                     const float* __restrict__ add1, int add1_ld, const float* __restrict__ add2, int add2_ld, int add_c,
                     float* __restrict__ dgamma, float* __restrict__ dbeta, int silu, int round_dx,
-                    uint16_t* __restrict__ dxb, int dxb_c, GnColsum cs) {
+                    uint16_t* __restrict__ dxb, int dxb_c, GnColsum cs, GnDrop dp) {
   extern __shared__ float4 gn_smem[];
   __shared__ __align__(16) float wred[kGnThreads / 32][2 * CS];
   __shared__ float chan[2 * CS];
@@ -374,9 +406,12 @@ gn_bwd_fused_kernel(GnSrc s, const float* __restrict__ stats, const float* __res
   float dg[4] = {0.f, 0.f, 0.f, 0.f}, db[4] = {0.f, 0.f, 0.f, 0.f};
   float s1 = 0.f, s2 = 0.f;
   const float nmr = -mean * rstd;
-  for (int idx = tid; idx < total; idx += kGnThreads) {
+  const uint32_t dseed = DROP ? drop_seed(dp) : 0u;
+  uint32_t e4 = static_cast<uint32_t>(((row0 + pix0) * s.C + c) >> 2);  // float4 number of dy[idx] in the dense tensor
+  for (int idx = tid; idx < total; idx += kGnThreads, e4 += (PSTEP * s.C) >> 2) {
     const float4 v = xs[idx];
-    const float4 d = ds[idx];
+    float4 d = ds[idx];
+    if (DROP) d = drop_apply(d, dp, dseed, e4);  // gradient through the dropout that follows the SiLU
     const float xv[4] = {v.x, v.y, v.z, v.w};
     const float dv[4] = {d.x, d.y, d.z, d.w};
     float xh[4], du[4];
@@ -464,10 +499,10 @@ __device__ __forceinline__ float4 gn_elem(const uint8_t* raw, int idx) {
   return widen_bf16x4(reinterpret_cast<const uint2*>(raw)[idx]);
 }
 
-template <int CS, int T>
+template <int CS, int T, bool DROP>
 __global__ void __launch_bounds__(T)
 gn_fwd_bfx_kernel(GnSrc s, float* __restrict__ stats, const float* __restrict__ gamma, const float* __restrict__ beta,
-                  float* __restrict__ y, float eps, int silu, int tf32) {
+                  float* __restrict__ y, float eps, int silu, int tf32, GnDrop dp) {
   extern __shared__ float4 gn_smem[];
   __shared__ float fred[2][T / 32][8];  // [sum | centred squares][warp][group of the slice]
   const uint8_t* raw = reinterpret_cast<const uint8_t*>(gn_smem);
@@ -525,8 +560,10 @@ gn_fwd_bfx_kernel(GnSrc s, float* __restrict__ stats, const float* __restrict__ 
   float* dst = y + o0;
   uint16_t* dstb = reinterpret_cast<uint16_t*>(y) + o0;
   const unsigned ostep = static_cast<unsigned>(T / L) * static_cast<unsigned>(s.C);
+  const uint32_t dseed = DROP ? drop_seed(dp) : 0u;
+  uint32_t e4 = static_cast<uint32_t>(o0 >> 2);
 #pragma unroll 2
-  for (int idx = tid; idx < total; idx += T, dst += ostep, dstb += ostep) {
+  for (int idx = tid; idx < total; idx += T, dst += ostep, dstb += ostep, e4 += ostep >> 2) {
     const float4 v = gn_elem<2>(raw, idx);
     float4 o;
     o.x = (v.x - mean) * sc.x + be.x;
@@ -536,6 +573,7 @@ gn_fwd_bfx_kernel(GnSrc s, float* __restrict__ stats, const float* __restrict__ 
     if (silu) {
       o.x = silu_fast(o.x); o.y = silu_fast(o.y); o.z = silu_fast(o.z); o.w = silu_fast(o.w);
     }
+    if (DROP) o = drop_apply(o, dp, dseed, e4);
     if (tf32 == 2) {
       *reinterpret_cast<uint2*>(dstb) = pack_bf16x4(o);
     } else {
@@ -549,13 +587,13 @@ gn_fwd_bfx_kernel(GnSrc s, float* __restrict__ stats, const float* __restrict__ 
 // (Parking du over dy in shared memory, in dy's format, so that phase 2 skips the SiLU derivative: another 3-8 % — 88 ->
 // 81 us at 28x28, 128 bf16 channels — but du is then rounded to bf16 once more and the fused column sums move by 1e-3;
 // not taken.)
-template <int CS, int T, int XB, int DB>
+template <int CS, int T, int XB, int DB, bool DROP>
 __global__ void __launch_bounds__(T, (XB + DB == 4) ? 1024 / T : 768 / T)  // CTAs/SM the slice footprint allows: 4 or 3
 gn_bwd_raw_kernel(GnSrc s, const float* __restrict__ stats, const float* __restrict__ gamma,
                   const float* __restrict__ beta, const void* __restrict__ dy, float* __restrict__ dx,
                   const float* __restrict__ add1, int add1_ld, const float* __restrict__ add2, int add2_ld, int add_c,
                   float* __restrict__ dgamma, float* __restrict__ dbeta, int silu, int round_dx,
-                  uint16_t* __restrict__ dxb, int dxb_c, GnColsum cs) {
+                  uint16_t* __restrict__ dxb, int dxb_c, GnColsum cs, GnDrop dp) {
   extern __shared__ float4 gn_smem[];
   __shared__ __align__(16) float wred[T / 32][2 * CS];
   __shared__ float chan[2 * CS];
@@ -597,9 +635,14 @@ gn_bwd_raw_kernel(GnSrc s, const float* __restrict__ stats, const float* __restr
   const float nmr = -mean * rstd;
   float dg[4] = {0.f, 0.f, 0.f, 0.f}, db[4] = {0.f, 0.f, 0.f, 0.f};
   float s1 = 0.f, s2 = 0.f;
-  for (int idx = tid; idx < total; idx += T) {
+  const uint32_t dseed = DROP ? drop_seed(dp) : 0u;
+  const uint32_t e40 = static_cast<uint32_t>(((row0 + tid / L) * s.C + c) >> 2);  // float4 number of dy[idx = tid]
+  const uint32_t e4step = static_cast<uint32_t>((T / L) * s.C) >> 2;
+  uint32_t e4 = e40;
+  for (int idx = tid; idx < total; idx += T, e4 += e4step) {
     const float4 v = gn_elem<XB>(xraw, idx);
-    const float4 d = gn_elem<DB>(draw, idx);
+    float4 d = gn_elem<DB>(draw, idx);
+    if (DROP) d = drop_apply(d, dp, dseed, e4);  // gradient through the dropout that follows the SiLU
     const float xv[4] = {v.x, v.y, v.z, v.w};
     const float dv[4] = {d.x, d.y, d.z, d.w};
 #pragma unroll
@@ -638,7 +681,8 @@ gn_bwd_raw_kernel(GnSrc s, const float* __restrict__ stats, const float* __restr
   float cacc[4] = {0.f, 0.f, 0.f, 0.f};
   auto elem = [&](int idx) {
     const float4 v = gn_elem<XB>(xraw, idx);
-    const float4 d = gn_elem<DB>(draw, idx);
+    float4 d = gn_elem<DB>(draw, idx);
+    if (DROP) d = drop_apply(d, dp, dseed, e40 + static_cast<uint32_t>(idx / T) * e4step);
     const float xv[4] = {v.x, v.y, v.z, v.w};
     const float dv[4] = {d.x, d.y, d.z, d.w};
     float ov[4];
@@ -702,7 +746,8 @@ __global__ void gn_finalize_kernel(GnSrc s, float* __restrict__ stats, int n_gro
 
 __global__ void __launch_bounds__(256)
 gn_apply_kernel(GnSrc s, const float* __restrict__ stats, const float* __restrict__ gamma,
-                const float* __restrict__ beta, float* __restrict__ y, int silu, int tf32) {
+                const float* __restrict__ beta, float* __restrict__ y, int silu, int tf32, GnDrop dp) {
+  const uint32_t dseed = dp.thr ? drop_seed(dp) : 0u;
   const int lanes = s.C >> 2;
   const size_t total = static_cast<size_t>(s.N) * s.HW * lanes;
   const int cpg = s.C >> 5;
@@ -724,6 +769,7 @@ gn_apply_kernel(GnSrc s, const float* __restrict__ stats, const float* __restric
     if (silu) {
       o.x = silu_f(o.x); o.y = silu_f(o.y); o.z = silu_f(o.z); o.w = silu_f(o.w);
     }
+    if (dp.thr) o = drop_apply(o, dp, dseed, static_cast<uint32_t>(i));
     if (tf32 == 2) {
       *reinterpret_cast<uint2*>(reinterpret_cast<uint16_t*>(y) + pix * s.C + c) = pack_bf16x4(o);
     } else {
@@ -736,7 +782,8 @@ gn_apply_kernel(GnSrc s, const float* __restrict__ stats, const float* __restric
 __global__ void __launch_bounds__(256)
 gn_bwd_reduce_kernel(GnSrc s, const float* __restrict__ stats, const float* __restrict__ gamma,
                      const float* __restrict__ beta, const float* __restrict__ dy, float* __restrict__ red,
-                     float* __restrict__ dgamma, float* __restrict__ dbeta, int silu, int pix_per_chunk) {
+                     float* __restrict__ dgamma, float* __restrict__ dbeta, int silu, int pix_per_chunk, GnDrop dp) {
+  const uint32_t dseed = dp.thr ? drop_seed(dp) : 0u;
   __shared__ float sh[64];
   __shared__ float shg[256 * 8];
   const int n = blockIdx.y;
@@ -762,7 +809,8 @@ gn_bwd_reduce_kernel(GnSrc s, const float* __restrict__ stats, const float* __re
   for (int p = p0 + prow; p < p1; p += prows) {
     const size_t pix = static_cast<size_t>(n) * s.HW + p;
     const float4 v = ld_src(s, pix, c);
-    const float4 d = *reinterpret_cast<const float4*>(dy + pix * s.C + c);
+    float4 d = *reinterpret_cast<const float4*>(dy + pix * s.C + c);
+    if (dp.thr) d = drop_apply(d, dp, dseed, static_cast<uint32_t>(pix * lanes + lane4));
     const float xv[4] = {v.x, v.y, v.z, v.w};
     const float dv[4] = {d.x, d.y, d.z, d.w};
 #pragma unroll
@@ -803,7 +851,8 @@ gn_bwd_apply_kernel(GnSrc s, const float* __restrict__ stats, const float* __res
                     const float* __restrict__ beta, const float* __restrict__ dy, const float* __restrict__ red,
                     float* __restrict__ dx, const float* __restrict__ add1, int add1_ld,
                     const float* __restrict__ add2, int add2_ld, int add_c, int silu, int round_dx,
-                    uint16_t* __restrict__ dxb, int dxb_c) {
+                    uint16_t* __restrict__ dxb, int dxb_c, GnDrop dp) {
+  const uint32_t dseed = dp.thr ? drop_seed(dp) : 0u;
   const int lanes = s.C >> 2;
   const size_t total = static_cast<size_t>(s.N) * s.HW * lanes;
   const int cpg = s.C >> 5;
@@ -819,7 +868,8 @@ gn_bwd_apply_kernel(GnSrc s, const float* __restrict__ stats, const float* __res
     const float mean = st.x, rstd = st.y;
     const float m1 = rd.x * inv_cnt, m2 = rd.y * inv_cnt;
     const float4 v = ld_src(s, pix, c);
-    const float4 d = *reinterpret_cast<const float4*>(dy + pix * s.C + c);
+    float4 d = *reinterpret_cast<const float4*>(dy + pix * s.C + c);
+    if (dp.thr) d = drop_apply(d, dp, dseed, static_cast<uint32_t>(i));
     const float4 ga = *reinterpret_cast<const float4*>(gamma + c);
     const float4 be = *reinterpret_cast<const float4*>(beta + c);
     const float xv[4] = {v.x, v.y, v.z, v.w};
@@ -894,6 +944,11 @@ template <typename K>
 static cudaError_t gn_optin(K kernel, int bytes) {
   return cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
 }
+#define GN_OPTIN2(KERNEL, ...)                                                   \
+  do {                                                                           \
+    if (e == cudaSuccess) e = gn_optin(KERNEL<__VA_ARGS__, false>, max_dyn);      \
+    if (e == cudaSuccess) e = gn_optin(KERNEL<__VA_ARGS__, true>, max_dyn);       \
+  } while (0)
 static int gn_init() {
   if (g_gn_max_dyn) return 0;
   int dev = 0, optin = 0;
@@ -901,24 +956,24 @@ static int gn_init() {
   cudaError_t e = cudaDeviceGetAttribute(&optin, cudaDevAttrMaxSharedMemoryPerBlockOptin, dev);
   if (e != cudaSuccess) return check_cuda(e, "cudaDeviceGetAttribute(smem optin)");
   const int max_dyn = optin - 8192;  // room for the kernels' static shared memory (per-warp reduction slots: up to 4.6 KB)
-  e = gn_optin(gn_fwd_fused_kernel<32, 256>, max_dyn);
-  if (e == cudaSuccess) e = gn_optin(gn_fwd_fused_kernel<16, 256>, max_dyn);
-  if (e == cudaSuccess) e = gn_optin(gn_fwd_fused_kernel<32, 512>, max_dyn);
-  if (e == cudaSuccess) e = gn_optin(gn_fwd_fused_kernel<16, 512>, max_dyn);
-  if (e == cudaSuccess) e = gn_optin(gn_bwd_fused_kernel<32, 256>, max_dyn);
-  if (e == cudaSuccess) e = gn_optin(gn_bwd_fused_kernel<16, 256>, max_dyn);
-  if (e == cudaSuccess) e = gn_optin(gn_bwd_fused_kernel<32, 512>, max_dyn);
-  if (e == cudaSuccess) e = gn_optin(gn_bwd_fused_kernel<16, 512>, max_dyn);
-  if (e == cudaSuccess) e = gn_optin(gn_fwd_bfx_kernel<16, 256>, max_dyn);
-  if (e == cudaSuccess) e = gn_optin(gn_fwd_bfx_kernel<32, 256>, max_dyn);
-  if (e == cudaSuccess) e = gn_optin(gn_bwd_raw_kernel<16, 256, 2, 2>, max_dyn);
-  if (e == cudaSuccess) e = gn_optin(gn_bwd_raw_kernel<32, 256, 2, 2>, max_dyn);
-  if (e == cudaSuccess) e = gn_optin(gn_bwd_raw_kernel<16, 256, 4, 2>, max_dyn);
-  if (e == cudaSuccess) e = gn_optin(gn_bwd_raw_kernel<32, 256, 4, 2>, max_dyn);
-  if (e == cudaSuccess) e = gn_optin(gn_bwd_raw_kernel<16, 256, 2, 4>, max_dyn);
-  if (e == cudaSuccess) e = gn_optin(gn_bwd_raw_kernel<32, 256, 2, 4>, max_dyn);
-  if (e == cudaSuccess) e = gn_optin(gn_fwd_fused_kernel<8, 256>, max_dyn);
-  if (e == cudaSuccess) e = gn_optin(gn_bwd_fused_kernel<8, 256>, max_dyn);
+  GN_OPTIN2(gn_fwd_fused_kernel, 32, 256);
+  GN_OPTIN2(gn_fwd_fused_kernel, 16, 256);
+  GN_OPTIN2(gn_fwd_fused_kernel, 32, 512);
+  GN_OPTIN2(gn_fwd_fused_kernel, 16, 512);
+  GN_OPTIN2(gn_bwd_fused_kernel, 32, 256);
+  GN_OPTIN2(gn_bwd_fused_kernel, 16, 256);
+  GN_OPTIN2(gn_bwd_fused_kernel, 32, 512);
+  GN_OPTIN2(gn_bwd_fused_kernel, 16, 512);
+  GN_OPTIN2(gn_fwd_bfx_kernel, 16, 256);
+  GN_OPTIN2(gn_fwd_bfx_kernel, 32, 256);
+  GN_OPTIN2(gn_bwd_raw_kernel, 16, 256, 2, 2);
+  GN_OPTIN2(gn_bwd_raw_kernel, 32, 256, 2, 2);
+  GN_OPTIN2(gn_bwd_raw_kernel, 16, 256, 4, 2);
+  GN_OPTIN2(gn_bwd_raw_kernel, 32, 256, 4, 2);
+  GN_OPTIN2(gn_bwd_raw_kernel, 16, 256, 2, 4);
+  GN_OPTIN2(gn_bwd_raw_kernel, 32, 256, 2, 4);
+  GN_OPTIN2(gn_fwd_fused_kernel, 8, 256);
+  GN_OPTIN2(gn_bwd_fused_kernel, 8, 256);
   if (e != cudaSuccess) return check_cuda(e, "cudaFuncSetAttribute(gn fused)");
   const char* env = getenv("B200_GN_STREAM");
   g_gn_stream = env ? atoi(env) : 0;
@@ -945,6 +1000,18 @@ static int gn_threads(size_t smem) {
   return smem > 64 * 1024 ? 512 : 256;
 }
 
+// dropout fields of the arguments -> kernel form (thr = 0: off)
+static int gn_drop(const b200_gn_args* a, GnDrop* d) {
+  d->thr = 0; d->scale = 1.f; d->seed = a->dropout_seed; d->step = a->dropout_step;
+  if (a->dropout_p == 0.f) return 0;
+  if (!(a->dropout_p > 0.f && a->dropout_p < 1.f)) return fail_arg("gn: dropout_p must be in [0, 1)");
+  uint32_t thr = static_cast<uint32_t>(a->dropout_p * 65536.0f + 0.5f);
+  if (thr > 65535u) thr = 65535u;
+  d->thr = thr;  // (a p below 2^-17 rounds to "off")
+  d->scale = 65536.0f / static_cast<float>(65536u - thr);
+  return 0;
+}
+
 extern "C" int b200_gn_fwd(const b200_gn_args* a, void* ws, size_t ws_bytes, void* stream) {
   (void)ws; (void)ws_bytes;
   GnSrc s;
@@ -953,6 +1020,8 @@ extern "C" int b200_gn_fwd(const b200_gn_args* a, void* ws, size_t ws_bytes, voi
   if (a->y_dtype != 0 && a->y_dtype != 1) return fail_arg("gn_fwd: y_dtype must be 0 (fp32) or 1 (bf16)");
   const int ymode = a->y_dtype == 1 ? 2 : (a->round_tf32 ? 1 : 0);
   if (int r = gn_init()) return r;
+  GnDrop dp;
+  if (int r = gn_drop(a, &dp)) return r;
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   if (s.bf) {  // bf16 x: raw-staged kernel, 2 B per element of shared memory
     const size_t b16 = static_cast<size_t>(s.HW) * 16 * 2;
@@ -961,8 +1030,11 @@ extern "C" int b200_gn_fwd(const b200_gn_args* a, void* ws, size_t ws_bytes, voi
     const int cs = (2 * b16 <= 50 * 1024) ? 32 : 16;
     const int grid = s.N * (s.C / cs);
     const size_t smem = static_cast<size_t>(s.HW) * cs * 2;
-    if (cs == 32) gn_fwd_bfx_kernel<32, 256><<<grid, 256, smem, st>>>(s, a->stats, a->gamma, a->beta, static_cast<float*>(a->y), a->eps, a->silu, ymode);
-    else gn_fwd_bfx_kernel<16, 256><<<grid, 256, smem, st>>>(s, a->stats, a->gamma, a->beta, static_cast<float*>(a->y), a->eps, a->silu, ymode);
+#define GN_FWD_BFX(CS, DROP) \
+  gn_fwd_bfx_kernel<CS, 256, DROP><<<grid, 256, smem, st>>>(s, a->stats, a->gamma, a->beta, static_cast<float*>(a->y), a->eps, a->silu, ymode, dp)
+    if (cs == 32) { if (dp.thr) GN_FWD_BFX(32, true); else GN_FWD_BFX(32, false); }
+    else { if (dp.thr) GN_FWD_BFX(16, true); else GN_FWD_BFX(16, false); }
+#undef GN_FWD_BFX
     return after_launch("gn_fwd_bfx_kernel");
   }
   const int cs = gn_slice(s, 1);
@@ -970,14 +1042,16 @@ extern "C" int b200_gn_fwd(const b200_gn_args* a, void* ws, size_t ws_bytes, voi
     const int grid = s.N * (s.C / cs);
     const size_t smem = static_cast<size_t>(s.HW) * cs * 4;
     const int th = gn_threads(smem);
-#define GN_FWD(CS, TH) \
-  gn_fwd_fused_kernel<CS, TH><<<grid, TH, smem, st>>>(s, a->stats, a->gamma, a->beta, static_cast<float*>(a->y), a->eps, a->silu, ymode)
+#define GN_FWD_D(CS, TH, DROP) \
+  gn_fwd_fused_kernel<CS, TH, DROP><<<grid, TH, smem, st>>>(s, a->stats, a->gamma, a->beta, static_cast<float*>(a->y), a->eps, a->silu, ymode, dp)
+#define GN_FWD(CS, TH) do { if (dp.thr) GN_FWD_D(CS, TH, true); else GN_FWD_D(CS, TH, false); } while (0)
     if (cs == 8) GN_FWD(8, 256);
     else if (cs == 32 && th == 256) GN_FWD(32, 256);
     else if (cs == 32) GN_FWD(32, 512);
     else if (th == 256) GN_FWD(16, 256);
     else GN_FWD(16, 512);
 #undef GN_FWD
+#undef GN_FWD_D
     return after_launch("gn_fwd_fused_kernel");
   }
   if (s.bf) return fail_arg("gn_fwd: a bf16 input needs the shared-memory-resident kernel (HW too large)");
@@ -990,7 +1064,7 @@ extern "C" int b200_gn_fwd(const b200_gn_args* a, void* ws, size_t ws_bytes, voi
   gn_finalize_kernel<<<(ng + 255) / 256, 256, 0, st>>>(s, a->stats, ng, 1.0f / static_cast<float>(s.HW * (s.C >> 5)), a->eps);
   if (int r = after_launch("gn_finalize_kernel")) return r;
   const size_t total = static_cast<size_t>(s.N) * s.HW * (s.C / 4);
-  gn_apply_kernel<<<ew_grid(total), 256, 0, st>>>(s, a->stats, a->gamma, a->beta, static_cast<float*>(a->y), a->silu, ymode);
+  gn_apply_kernel<<<ew_grid(total), 256, 0, st>>>(s, a->stats, a->gamma, a->beta, static_cast<float*>(a->y), a->silu, ymode, dp);
   return after_launch("gn_apply_kernel");
 }
 
@@ -1010,6 +1084,8 @@ extern "C" int b200_gn_bwd(const b200_gn_bwd_args* b, void* ws, size_t ws_bytes,
   if (!b->dx && !b->dx_bf16) return fail_arg("gn_bwd: neither dx nor dx_bf16 given");
   if (b->dy_dtype != 0 && b->dy_dtype != 1) return fail_arg("gn_bwd: dy_dtype must be 0 (fp32) or 1 (bf16)");
   if (int r = gn_init()) return r;
+  GnDrop dp;
+  if (int r = gn_drop(&b->fwd, &dp)) return r;
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   const int add_c = b->add_c ? b->add_c : s.C;
   uint16_t* dxb = static_cast<uint16_t*>(b->dx_bf16);
@@ -1028,14 +1104,17 @@ extern "C" int b200_gn_bwd(const b200_gn_bwd_args* b, void* ws, size_t ws_bytes,
     const int cs = (2 * b16 <= 50 * 1024) ? 32 : 16;
     const int grid = s.N * (s.C / cs);
     const size_t smem = static_cast<size_t>(s.HW) * cs * (xb + dbb);
-#define GN_BWD_RAW(CS, XB, DB)                                                                                          \
-  gn_bwd_raw_kernel<CS, 256, XB, DB><<<grid, 256, smem, st>>>(s, b->fwd.stats, b->fwd.gamma, b->fwd.beta, b->dy, b->dx,  \
-                                                              b->add1, b->add1_ld, b->add2, b->add2_ld, add_c, b->dgamma, \
-                                                              b->dbeta, b->fwd.silu, b->round_dx, dxb, dxb_c, csm)
+#define GN_BWD_RAW_D(CS, XB, DB, DROP)                                                                                  \
+  gn_bwd_raw_kernel<CS, 256, XB, DB, DROP><<<grid, 256, smem, st>>>(s, b->fwd.stats, b->fwd.gamma, b->fwd.beta, b->dy,   \
+                                                                    b->dx, b->add1, b->add1_ld, b->add2, b->add2_ld,     \
+                                                                    add_c, b->dgamma, b->dbeta, b->fwd.silu,             \
+                                                                    b->round_dx, dxb, dxb_c, csm, dp)
+#define GN_BWD_RAW(CS, XB, DB) do { if (dp.thr) GN_BWD_RAW_D(CS, XB, DB, true); else GN_BWD_RAW_D(CS, XB, DB, false); } while (0)
     if (xb == 2 && dbb == 2) { if (cs == 32) GN_BWD_RAW(32, 2, 2); else GN_BWD_RAW(16, 2, 2); }
     else if (xb == 4) { if (cs == 32) GN_BWD_RAW(32, 4, 2); else GN_BWD_RAW(16, 4, 2); }
     else { if (cs == 32) GN_BWD_RAW(32, 2, 4); else GN_BWD_RAW(16, 2, 4); }
 #undef GN_BWD_RAW
+#undef GN_BWD_RAW_D
     return after_launch("gn_bwd_raw_kernel");
   }
   const int cs = gn_slice(s, 2);
@@ -1043,16 +1122,18 @@ extern "C" int b200_gn_bwd(const b200_gn_bwd_args* b, void* ws, size_t ws_bytes,
     const int grid = s.N * (s.C / cs);
     const size_t smem = static_cast<size_t>(s.HW) * cs * 4 * 2;
     const int th = gn_threads(smem);
-#define GN_BWD(CS, TH)                                                                                                  \
-  gn_bwd_fused_kernel<CS, TH><<<grid, TH, smem, st>>>(s, b->fwd.stats, b->fwd.gamma, b->fwd.beta, b->dy, b->dx, b->add1, \
-                                                      b->add1_ld, b->add2, b->add2_ld, add_c, b->dgamma, b->dbeta,       \
-                                                      b->fwd.silu, b->round_dx, dxb, dxb_c, csm)
+#define GN_BWD_D(CS, TH, DROP)                                                                                          \
+  gn_bwd_fused_kernel<CS, TH, DROP><<<grid, TH, smem, st>>>(s, b->fwd.stats, b->fwd.gamma, b->fwd.beta, b->dy, b->dx,    \
+                                                            b->add1, b->add1_ld, b->add2, b->add2_ld, add_c, b->dgamma,  \
+                                                            b->dbeta, b->fwd.silu, b->round_dx, dxb, dxb_c, csm, dp)
+#define GN_BWD(CS, TH) do { if (dp.thr) GN_BWD_D(CS, TH, true); else GN_BWD_D(CS, TH, false); } while (0)
     if (cs == 8) GN_BWD(8, 256);
     else if (cs == 32 && th == 256) GN_BWD(32, 256);
     else if (cs == 32) GN_BWD(32, 512);
     else if (th == 256) GN_BWD(16, 256);
     else GN_BWD(16, 512);
 #undef GN_BWD
+#undef GN_BWD_D
     return after_launch("gn_bwd_fused_kernel");
   }
   if (s.bf || b->dy_dtype || !b->dx)
@@ -1064,12 +1145,12 @@ extern "C" int b200_gn_bwd(const b200_gn_bwd_args* b, void* ws, size_t ws_bytes,
   const int chunks = gn_chunks(s.N, s.HW);
   const int ppc = (s.HW + chunks - 1) / chunks;
   gn_bwd_reduce_kernel<<<dim3(chunks, s.N), 256, 0, st>>>(s, b->fwd.stats, b->fwd.gamma, b->fwd.beta, b->dy, red,
-                                                          b->dgamma, b->dbeta, b->fwd.silu, ppc);
+                                                          b->dgamma, b->dbeta, b->fwd.silu, ppc, dp);
   if (int r = after_launch("gn_bwd_reduce_kernel")) return r;
   const size_t total = static_cast<size_t>(s.N) * s.HW * (s.C / 4);
   gn_bwd_apply_kernel<<<ew_grid(total), 256, 0, st>>>(s, b->fwd.stats, b->fwd.gamma, b->fwd.beta, b->dy, red, b->dx,
                                                       b->add1, b->add1_ld, b->add2, b->add2_ld, add_c, b->fwd.silu,
-                                                      b->round_dx, dxb, dxb_c);
+                                                      b->round_dx, dxb, dxb_c, dp);
   if (int r = after_launch("gn_bwd_apply_kernel")) return r;
   if (csm.c) {  // streaming path: the column sums take their own pass over dx
     b200_colsum_args ca = {b->dx, csm.per_sample, csm.total1, csm.total2, s.N, s.HW, s.C, csm.ps_ld};

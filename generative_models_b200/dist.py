@@ -28,6 +28,10 @@ def init_from_env(backend=None):
     return rank, world, device
 
 
+def rank():
+    return dist.get_rank() if dist.is_initialized() else 0
+
+
 def shard_range(n, rank, world):
     """[lo, hi) of `n` items for `rank`: contiguous, disjoint, covering, sizes differ by at most one."""
     base, rem = divmod(n, world)

@@ -44,6 +44,7 @@ class GnArgs(C.Structure):
         ("N", C.c_int), ("HW", C.c_int), ("C1", C.c_int), ("C2", C.c_int),
         ("x_ld", C.c_int), ("x2_ld", C.c_int),
         ("eps", C.c_float), ("silu", C.c_int), ("round_tf32", C.c_int), ("y_dtype", C.c_int), ("x_dtype", C.c_int),
+        ("dropout_p", C.c_float), ("dropout_seed", C.c_uint), ("dropout_step", _f32p),
     ]
 
 
@@ -193,7 +194,7 @@ def load():
     lib.b200_last_error.restype = C.c_char_p
     lib.b200_launch_count.restype = C.c_ulonglong
     lib.b200_init.argtypes = [C.c_int]
-    if lib.b200_abi_version() != 5:
+    if lib.b200_abi_version() != 6:
         raise B200Error("libb200ddpm.so ABI version mismatch")
     for name in EXPORTS:
         fn = getattr(lib, name)  # AttributeError if the symbol is missing

@@ -88,8 +88,12 @@ class DiffusionModelB200(nn.Module):
         if G.get("precision", "tf32") not in ("tf32", "bf16"):
             raise NotImplementedError(f"precision {G.precision!r} (tf32 | bf16)")
         self.bf16 = G.get("precision", "tf32") == "bf16"
-        if float(G.dropout) != 0.0:
-            raise NotImplementedError("dropout != 0 is not on the DDPM hot path (reference default is 0.0)")
+        if not 0.0 <= float(G.dropout) < 1.0:
+            raise ValueError(f"dropout {G.dropout!r} must be in [0, 1)")
+        # nn.Dropout(p) of ResBlock.out_layers (simple_unet.py:171), fused into the GroupNorm kernels; the masks are a
+        # hash of (this seed, layer, optimiser step, position) — another stream than torch's Philox, same distribution.
+        # Ranks of a data-parallel job draw different masks.
+        self.drop_seed = (torch.initial_seed() + 0x9E3779B9 * (1 + dist.rank())) & 0x7FFFFFFF
         if G.get("teacher_mode", "step1") not in ("step1", "step2"):
             raise NotImplementedError(f"teacher_mode {G.teacher_mode!r} (step1 | step2)")
         if torch.cuda.current_device() != dev.index:
@@ -186,7 +190,9 @@ class DiffusionModelB200(nn.Module):
     def _plan(self, B, kind):
         """kind: 'train' | 'loss' | 'sample' | 'sample_g' (guided: 2B rows).  At most two plans per kind are kept
         (activations are large)."""
-        key = (kind, B, self.size, int(self.G.timesteps))
+        # dropout follows nn.Module's train() / eval() switch, like the reference's nn.Dropout
+        drop = float(self.G.dropout) if (self.training and kind in ("train", "loss")) else 0.0
+        key = (kind, B, self.size, int(self.G.timesteps), drop)
         p = self._plans.get(key)
         if p is not None:
             return p
@@ -196,7 +202,7 @@ class DiffusionModelB200(nn.Module):
             del self._plans[old]
             self._train_graphs.pop(old, None)
             torch.cuda.empty_cache()
-        p = _Bound(self, B, kind)
+        p = _Bound(self, B, kind, dropout=drop)
         self._plans[key] = p
         return p
 
@@ -368,7 +374,7 @@ def _write_gridvid(writer, tag, x, epoch):
 class _Bound:
     """A UNetPlan bound to the diffusion-level buffers and ops of one use: 'train', 'loss' or 'sample'."""
 
-    def __init__(self, model, B, kind):
+    def __init__(self, model, B, kind, dropout=0.0):
         self.m = model
         self.B, self.kind = B, kind
         dev = model.device
@@ -400,7 +406,8 @@ class _Bound:
         # conditioned on cond_w and the loss targets come from one (step1) or two (step2) DDIM steps of the teacher
         self.distill = model.teacher_store is not None
         self.mode = G.get("teacher_mode", "step1") if self.distill else None
-        self.plan = UNetPlan(model.store, B, S, train=(kind == "train"), bf16=model.bf16, cond_w=self.distill)
+        self.plan = UNetPlan(model.store, B, S, train=(kind == "train"), bf16=model.bf16, cond_w=self.distill,
+                             dropout=dropout, drop_step=model.adam_step, drop_seed=model.drop_seed)
         p = self.plan
         self.x = torch.zeros(B, D, **f32)
         self.eps = torch.zeros(B, D, **f32)

@@ -12,6 +12,9 @@ takes two base pointers.  The reverse pass accumulates parameter gradients strai
 `unet_spec.ParamStore` (the NCCL allreduce bucket).
 """
 import ctypes as C
+import os
+
+import zlib
 
 import torch
 
@@ -67,6 +70,8 @@ class _Pool:
         if self.recycle and self.free_list.get(n):
             return self.free_list[n].pop().view(*shape)
         t = torch.empty(n, dtype=torch.float32, device=self.device)
+        if os.environ.get("B200_POISON"):  # developer check: a read-before-write shows up as NaN
+            t.fill_(float("nan"))
         self.all.append(t)
         return t.view(*shape)
 
@@ -99,13 +104,17 @@ class _Grad:
 class UNetPlan:
     """Forward (and backward) op lists of SimpleUnet for a fixed batch `B` and image side `S`."""
 
-    def __init__(self, store, B, S, train, sched=None, step_dev=None, bf16=False, cond_w=False):
+    def __init__(self, store, B, S, train, sched=None, step_dev=None, bf16=False, cond_w=False, dropout=0.0,
+                 drop_step=None, drop_seed=0):
         """bf16: the 24 ResBlock 3x3 convolutions (87 % of the FLOPs) take bf16 operands — GroupNorm writes its output
         as bf16, the weights come from a bf16 shadow, the backward's dY operands are bf16 copies written by the
         producing GroupNorm-backward — with fp32 accumulation; the residual stream, GroupNorm statistics, every
         gradient that is summed, and the plain / skip / edge convolutions stay fp32 (TF32 tensor cores)."""
         assert S % 4 == 0, "image side must be divisible by 4 (two stride-2 levels)"
         self.bf16 = bool(bf16)
+        # nn.Dropout(p) of ResBlock.out_layers (simple_unet.py:171), fused into that block's second GroupNorm (b200ddpm.h:
+        # dropout_p / dropout_seed / dropout_step); drop_step is a device counter that advances once per optimiser step
+        self.dropout, self.drop_step, self.drop_seed = float(dropout), drop_step, int(drop_seed)
         # cond_w: the net is conditioned on a per-sample guidance weight through cond_w_embed (simple_unet.py:60-64;
         # progressive distillation: students, and step2 teachers); self.cond_w [B] is the input buffer
         self.use_cond_w = bool(cond_w)
@@ -232,10 +241,15 @@ class UNetPlan:
                           x2_ld=0, dy_ld=128 if bf else dy.ld, op_dtype=1 if bf else 0)
         return Op("b200_conv_wgrad", a)
 
-    def _gn(self, x, x2, gname, y, HW, C2, stats, silu=1, tf32=1, bf=False, x_bf=False):
-        return lib.GnArgs(x=_p(x), x2=_p(x2), stats=_p(stats), gamma=self._w(gname + ".weight"),
-                          beta=self._w(gname + ".bias"), y=_p(y), N=self.B, HW=HW, C1=128, C2=C2, x_ld=0, x2_ld=0,
-                          eps=GN_EPS, silu=silu, round_tf32=tf32, y_dtype=1 if bf else 0, x_dtype=1 if x_bf else 0)
+    def _gn(self, x, x2, gname, y, HW, C2, stats, silu=1, tf32=1, bf=False, x_bf=False, drop=False):
+        a = lib.GnArgs(x=_p(x), x2=_p(x2), stats=_p(stats), gamma=self._w(gname + ".weight"),
+                       beta=self._w(gname + ".bias"), y=_p(y), N=self.B, HW=HW, C1=128, C2=C2, x_ld=0, x2_ld=0,
+                       eps=GN_EPS, silu=silu, round_tf32=tf32, y_dtype=1 if bf else 0, x_dtype=1 if x_bf else 0)
+        if drop and self.dropout > 0.0:
+            a.dropout_p = self.dropout
+            a.dropout_seed = (zlib.crc32(gname.encode()) ^ self.drop_seed) & 0xFFFFFFFF
+            a.dropout_step = _p(self.drop_step)
+        return a
 
     def _ensure_bf(self, ops, g, HW):
         """bf16 mode: make sure the 128-channel gradient slice `g` has its dense bf16 copy (producers that are not a
@@ -377,7 +391,7 @@ class UNetPlan:
                               emb=_p(self.embout, k * 128), round_out=0, bf=bf, out_dtype=1 if bfs else 0))
         pool.release(a1)
         a2 = self._get_bf(pool, B, HW, 128) if bf else pool.get(B, HW, 128)
-        g2 = self._gn(h1, None, name + ".out_layers.0", a2, HW, 0, st2, bf=bf, x_bf=bfs)
+        g2 = self._gn(h1, None, name + ".out_layers.0", a2, HW, 0, st2, bf=bf, x_bf=bfs, drop=True)
         ops.append(Op("b200_gn_fwd", g2))
         pool.release(h1)
         skip = None

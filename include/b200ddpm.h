@@ -21,7 +21,7 @@
 extern "C" {
 #endif
 
-#define B200_ABI_VERSION 5
+#define B200_ABI_VERSION 6
 
 int b200_abi_version(void);
 /* validates `device` (compute capability 10.x, equal to the caller's current device); never changes the current
@@ -121,6 +121,13 @@ typedef struct {
   int round_tf32;
   int y_dtype;     /* 0 = fp32 (optionally TF32-rounded), 1 = bf16 (the operand of a bf16 convolution) */
   int x_dtype;     /* 0 = fp32, 1 = x / x2 hold bf16 (x_ld in elements; shared-memory-resident kernels only) */
+  /* nn.Dropout(p) between the SiLU and the convolution of ResBlock.out_layers (simple_unet.py:168-172), fused:
+   * y = silu(...) * keep / (1 - p); b200_gn_bwd applies the same keep / (1 - p) to dy.  keep is a hash of
+   * (dropout_seed, *dropout_step, position in y), so no mask is stored and a captured graph whose step counter advances
+   * draws a fresh mask every replay.  p is quantised to 1/65536; 0 = off (the three fields are then ignored). */
+  float dropout_p;
+  unsigned dropout_seed;   /* per layer */
+  const int* dropout_step; /* optional device counter mixed into the seed; NULL = 0 */
 } b200_gn_args;
 int b200_gn_fwd(const b200_gn_args* a, void* ws, size_t ws_bytes, void* stream);
 

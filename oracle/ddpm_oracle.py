@@ -93,11 +93,16 @@ def _gn_silu(sd, name, x):
     return F.silu(F.group_norm(x, 32, sd[name + ".weight"], sd[name + ".bias"], eps=1e-5))
 
 
-def resblock(sd, pre, x, emb):
-    """simple_unet.py:155-186 (dropout p=0)."""
+def resblock(sd, pre, x, emb, drop=None):
+    """simple_unet.py:155-186.  `drop` (optional dict: block name -> [B, C, H, W] multiplier, i.e. keep / (1 - p)) stands
+    for nn.Dropout(p) between the SiLU and the convolution of out_layers (:168-172) with an explicit mask, so that a test
+    can hand the oracle the mask the device drew; None = p = 0 / eval mode."""
     h = _conv(sd, pre + ".in_layers.2", _gn_silu(sd, pre + ".in_layers.0", x))
     h = h + _lin(sd, pre + ".emb_layers.1", F.silu(emb))[:, :, None, None]
-    h = _conv(sd, pre + ".out_layers.3", _gn_silu(sd, pre + ".out_layers.0", h))
+    a = _gn_silu(sd, pre + ".out_layers.0", h)
+    if drop is not None and pre in drop:
+        a = a * drop[pre]
+    h = _conv(sd, pre + ".out_layers.3", a)
     if (pre + ".skip_connection.weight") in sd:
         x = _conv(sd, pre + ".skip_connection", x, padding=0)
     return x + h
@@ -129,7 +134,7 @@ def embed(sd, logsnr, guide=None, cond_w=None):
     return e
 
 
-def unet_forward(sd, x, logsnr, guide=None, cond_w=None, taps=None):
+def unet_forward(sd, x, logsnr, guide=None, cond_w=None, taps=None, drop=None):
     """simple_unet.py:44-72 + Down :87-109, Up :125-152, out head :38-42.  `sd` keys have no 'net.' prefix.
     `taps` (optional dict) receives named intermediates for layer-level parity tests."""
     emb = embed(sd, logsnr, guide, cond_w)
@@ -137,19 +142,19 @@ def unet_forward(sd, x, logsnr, guide=None, cond_w=None, taps=None):
     h = _conv(sd, "down.seq.0.conv", x)
     skips.append(h)
     for i in (1, 2):
-        h = resblock(sd, f"down.seq.{i}", h, emb)
+        h = resblock(sd, f"down.seq.{i}", h, emb, drop)
         skips.append(h)
     h = _conv(sd, "down.seq.3.conv", h, stride=2)
     skips.append(h)
     for i in (4, 5):
-        h = resblock(sd, f"down.seq.{i}", h, emb)
+        h = resblock(sd, f"down.seq.{i}", h, emb, drop)
         skips.append(h)
     h = _conv(sd, "down.seq.6.conv", h, stride=2)
     skips.append(h)
     if taps is not None:
         taps["emb"] = emb
         taps["down"] = h
-    h = resblock(sd, "turn", h, emb)
+    h = resblock(sd, "turn", h, emb, drop)
     if "attn.q.weight" in sd:  # extension: self-attention at the lowest-resolution level, after the turn block
         h = attention_block(sd, "attn", h)
     if taps is not None:
@@ -157,24 +162,24 @@ def unet_forward(sd, x, logsnr, guide=None, cond_w=None, taps=None):
     for i in range(7):
         h = torch.cat([h, skips.pop()], 1)
         if i in (0, 3):
-            h = resblock(sd, f"up.seq.{i}.0", h, emb)
+            h = resblock(sd, f"up.seq.{i}.0", h, emb, drop)
             h = F.interpolate(h, scale_factor=2, mode="nearest")
             h = _conv(sd, f"up.seq.{i}.1.conv", h)
         else:
-            h = resblock(sd, f"up.seq.{i}", h, emb)
+            h = resblock(sd, f"up.seq.{i}", h, emb, drop)
     if taps is not None:
         taps["up"] = h
     return _conv(sd, "out.2", _gn_silu(sd, "out.0", h))
 
 
 # ----------------------------------------------------------------------------- training loss
-def training_loss(sd, x, y, eps, u, mean_type="eps"):
+def training_loss(sd, x, y, eps, u, mean_type="eps", drop=None):
     """gaussian_diffusion.py:81-100,156-172 (non-distillation) + diffusion_model.py:76-80.
     eps, u are the injected random draws (reference draws eps = randn first, then u = rand).
     Returns (mean loss, per-sample loss, dict of intermediates)."""
     logsnr = logsnr_cosine(u)
     z = q_sample(x, logsnr, eps)
-    out = unet_forward(sd, z, logsnr, guide=y)
+    out = unet_forward(sd, z, logsnr, guide=y, drop=drop)
     xc, ec = run_model(out, z, logsnr, mean_type)
     x_mse = ((xc - x) ** 2).flatten(1).mean(1)
     e_mse = ((ec - eps) ** 2).flatten(1).mean(1)

@@ -20,7 +20,7 @@ def test_library_exports_every_declared_symbol(built_lib):
     so = C.CDLL(built_lib.LIB_PATH)
     for name in declared:
         assert hasattr(so, name), name
-    assert built_lib.load().b200_abi_version() == 5
+    assert built_lib.load().b200_abi_version() == 6
 
 
 def test_ctypes_structs_match_header_field_order(built_lib):
