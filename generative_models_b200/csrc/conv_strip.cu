@@ -669,18 +669,17 @@ int conv_strip_applicable(const b200_conv_args* a) {
   if (!flat && Wp > 256) return 0;
   const long long positions = flat ? static_cast<long long>(a->N) * a->H * a->W : static_cast<long long>(a->N) * Hp * Wp;
   const long long num_tiles = (positions + kTileM - 1) / kTileM;
-  // few tiles (small spatial levels at small batch): one 256-position tile per SM leaves the machine under-filled and
-  // the im2col kernel (128-position tiles, 2 CTAs/SM) is faster there — measured crossover ~2 tiles per SM (it was ~4
-  // before the strip rows and filter taps were fetched in multi-row / two-tap TMA boxes: at batch 512 the 14x14 layers
-  // now take 72 us here against 74 us there, the 7x7 layers 25 us on either).
-  // bf16 operands exist only in this kernel.
-  static int min_tiles = -1;  // developer knob B200_STRIP_MIN_TILES
+  // Few tiles (small spatial levels, small batches) used to go to the im2col kernel (128-position tiles, 2 CTAs/SM):
+  // the measured crossover was ~4 tiles per SM in round 1 and ~2 once the strip rows and filter taps were fetched in
+  // multi-row / two-tap TMA boxes.  With the tail wave split evenly over the CTAs it is gone: taking every applicable
+  // layer here is faster at every batch measured (train step 4.35 -> 4.01 ms at batch 64, 5.79 -> 5.61 at 128,
+  // 10.00 -> 9.84 at 256, 19.23 -> 19.16 at 512; sample(16, y) 1.13 -> 0.94 ms per step).  B200_STRIP_MIN_TILES=n restores
+  // a threshold (developer knob; halved for launches with a residual operand).
+  static int min_tiles = -1;
   if (min_tiles < 0) {
     const char* e = getenv("B200_STRIP_MIN_TILES");
-    min_tiles = e ? atoi(e) : 2 * 148;
+    min_tiles = e ? atoi(e) : 0;
   }
-  // with a residual operand the crossover sits lower: the strip epilogue prefetches the residual rows one chunk ahead
-  // (+3 us at 14x14, batch 512: 92 us), the im2col kernel's does not (+33 us: 107 us)
   const int need = a->residual ? min_tiles / 2 : min_tiles;
   if (!a->skip_x && num_tiles < need && !flat && a->op_dtype == 0) return 0;
   return 1;

