@@ -391,7 +391,8 @@ class UNetPlan:
                               emb=_p(self.embout, k * 128), round_out=0, bf=bf, out_dtype=1 if bfs else 0))
         pool.release(a1)
         a2 = self._get_bf(pool, B, HW, 128) if bf else pool.get(B, HW, 128)
-        g2 = self._gn(h1, None, name + ".out_layers.0", a2, HW, 0, st2, bf=bf, x_bf=bfs, drop=True)
+        # (the reference builds up.seq.3's ResBlock without its dropout argument, simple_unet.py:137-139: p = 0 there)
+        g2 = self._gn(h1, None, name + ".out_layers.0", a2, HW, 0, st2, bf=bf, x_bf=bfs, drop=(name != "up.seq.3.0"))
         ops.append(Op("b200_gn_fwd", g2))
         pool.release(h1)
         skip = None

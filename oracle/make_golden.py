@@ -191,6 +191,38 @@ def main():
             torch.manual_seed(79)
             fx[tag]["teacher_test"] = dict(init=init, y=ys, net_cond_w=4.0 * torch.rand(2), zs=zs, xs=xs, es=es)
 
+    # ---- 8. dropout (simple_unet.py:168-172: GroupNorm -> SiLU -> nn.Dropout(p) -> conv in ResBlock.out_layers).  The
+    # reference SimpleUnet with p = 0.3 in train mode; forward hooks on its nn.Dropout modules record which elements were
+    # kept, so the oracle (and the device tests) can be handed the same masks.  Stored bit-packed.
+    import numpy as np
+    from torch import nn
+    from gms.diffusion.simple_unet import SimpleUnet
+    p_drop = 0.3
+    net = SimpleUnet(128, p_drop)
+    net.load_state_dict(O.random_state_dict(1))
+    net.train()
+    g = torch.Generator().manual_seed(2024)
+    xd = torch.randn(2, 1, 28, 28, generator=g)
+    ld = torch.tensor([1.5, -3.0])
+    yd = torch.tensor([7, -1])
+    keep = {}
+
+    def hook(name):
+        def fn(mod, inp, out):
+            keep[name] = (out != 0) | (inp[0] == 0)  # an input that is exactly 0 says nothing: count it as kept
+        return fn
+
+    handles = [mod.register_forward_hook(hook(name[:-len(".out_layers.2")]))
+               for name, mod in net.named_modules() if isinstance(mod, nn.Dropout)]
+    torch.manual_seed(4242)
+    with torch.no_grad():
+        out_d = net(xd, ld, guide=yd)
+    for h in handles:
+        h.remove()
+    assert len(keep) == 12, sorted(keep)
+    fx["dropout"] = dict(p=p_drop, x=xd, logsnr=ld, y=yd, out=out_d,
+                         keep={k: (tuple(v.shape), torch.from_numpy(np.packbits(v.numpy().reshape(-1)))) for k, v in keep.items()})
+
     torch.save(fx, os.path.join(out_dir, "reference_fixtures.pt"))
     print("wrote", os.path.join(out_dir, "reference_fixtures.pt"),
           os.path.getsize(os.path.join(out_dir, "reference_fixtures.pt")) // 1024, "KiB")

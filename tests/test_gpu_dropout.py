@@ -134,6 +134,8 @@ def test_train_step_with_dropout_vs_oracle(built_lib, prec):
     step = int(m.adam_step.item())
     drop = {}
     for name, S in sizes.items():
+        if name == "up.seq.3.0":  # built without the dropout argument in the reference (simple_unet.py:137-139)
+            continue
         seed = (zlib.crc32((name + ".out_layers.0").encode()) ^ m.drop_seed) & M32
         mult, _ = keep_multiplier(seed, step, B, S * S, 128, p)
         drop[name] = mult.view(B, S, S, 128).permute(0, 3, 1, 2)

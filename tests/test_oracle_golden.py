@@ -111,3 +111,29 @@ def test_distilled_student_sampling_vs_reference_fixture(golden):
         net = lambda z, l, uncond: O.unet_forward(sdt, z, l, guide=(-torch.ones_like(t["y"]) if uncond else t["y"]))
         zs, xs, es = O.sample_loop(net, t["init"], f["T"], sampler="ddim", mean_type="eps", cond_w=t["net_cond_w"])
     assert (zs - t["zs"]).abs().max() < 1e-4 and (xs - t["xs"]).abs().max() < 1e-4
+
+
+def unpack_keep(entry):
+    """fixture["dropout"]["keep"][block] -> bool [B, C, H, W] (bit-packed by oracle/make_golden.py)."""
+    import numpy as np
+    shape, packed = entry
+    n = 1
+    for d in shape:
+        n *= d
+    return torch.from_numpy(np.unpackbits(packed.numpy())[:n].astype(bool)).view(*shape)
+
+
+def test_dropout_placement_and_scaling_vs_reference_fixture(golden):
+    """The reference SimpleUnet(128, dropout=0.3) in train mode, its nn.Dropout keep-decisions recorded by forward hooks:
+    the oracle handed the same masks (multiplier keep / (1 - p) after the SiLU of out_layers, simple_unet.py:168-172)
+    reproduces the reference's output."""
+    f = golden["dropout"]
+    sd = O.random_state_dict(1)
+    keep = {k: unpack_keep(v) for k, v in f["keep"].items()}
+    # eleven blocks drop 30 %; up.seq.3's ResBlock is built without the dropout argument (simple_unet.py:137-139): p = 0
+    assert len(keep) == 12 and keep["up.seq.3.0"].all()
+    drop = {k: v.float() / (1.0 - f["p"]) for k, v in keep.items() if k != "up.seq.3.0"}
+    assert all(abs(v.gt(0).float().mean().item() - (1 - f["p"])) < 0.02 for v in drop.values())
+    out = O.unet_forward(sd, f["x"], f["logsnr"], guide=f["y"], drop=drop)
+    assert rel(out, f["out"]) < 1e-5
+    assert rel(O.unet_forward(sd, f["x"], f["logsnr"], guide=f["y"]), f["out"]) > 1e-2  # without the masks it does not
