@@ -79,8 +79,8 @@ typedef struct {
   void* out_bf16;
 } b200_conv_args;
 int b200_conv_igemm(const b200_conv_args* a, void* ws, size_t ws_bytes, void* stream);
-/* which kernel b200_conv_igemm launches for these arguments: 1 = conv_strip_tf32_kernel (strip implicit GEMM, stride-1
- * layers with enough tiles), 0 = conv_igemm_tf32_kernel (TMA-im2col).  Used by bench.py's per-kernel roofline. */
+/* which kernel b200_conv_igemm launches for these arguments: 1 = conv_strip_kernel (strip implicit GEMM: every stride-1
+ * 3x3 / 1x1 layer with W <= 64), 0 = conv_igemm_tf32_kernel (TMA-im2col: the stride-2 layers).  Used by bench.py's per-kernel roofline. */
 int b200_conv_kernel_of(const b200_conv_args* a);
 
 /* weight gradient (nn.Conv2d backward-weight of the same layers):
